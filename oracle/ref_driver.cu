@@ -1,0 +1,299 @@
+// TEST INFRASTRUCTURE -- not part of the product, never linked into it.
+//
+// C-ABI driver around the UNMODIFIED reference implementation
+// (/root/reference/sift_cuda/...), built by oracle/Makefile into
+// oracle/_ref/libref_sift.so. It is the strongest oracle we have for the hot
+// path: the reference's own CUDA kernels compiled for sm_100 by this image's
+// nvcc, run on the same inputs as the B200-native engine.
+//
+// The reference's Detector.cu is textually included so that the (inline, hence
+// not exported) stage methods Detector::createInitialImage ... can be driven
+// one by one and the private SiftData inspected between stages. No reference
+// source is copied into this repository: the #include resolves into
+// /root/reference at build time only.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <filesystem>
+#include <fstream>
+#include <iostream>
+#include <memory>
+#include <sstream>
+#include <string>
+#include <vector>
+#include <cuda_runtime.h>
+#include <cuda_fp16.h>
+#include <thrust/device_vector.h>
+#include <thrust/host_vector.h>
+#include <cub/device/device_scan.cuh>
+#include <zlib.h>
+#include <msgpack.hpp>
+
+#define private public
+#include "sift_cuda/interface/Detector.cu"
+#undef private
+#include "sift_cuda/sift_func/Match.cuh"
+
+namespace {
+struct RefHandle {
+    std::unique_ptr<sift_cuda::Detector> det;
+    Imagef img;
+    int rows = 0, cols = 0;
+};
+
+template <typename T>
+int copy_dev(const thrust::device_vector<T>& v, void* out, size_t max_elems) {
+    size_t n = std::min(max_elems, v.size());
+    if (out && n) {
+        cudaMemcpy(out, thrust::raw_pointer_cast(v.data()), n * sizeof(T), cudaMemcpyDeviceToHost);
+    }
+    return int(v.size());
+}
+}  // namespace
+
+extern "C" {
+
+void* ref_create(int cols, int rows, int num_features) {
+    CudaSiftConfig cfg;
+    cfg.col_width = cols;
+    cfg.row_width = rows;
+    cfg.numFeatures = num_features;
+    cfg.upscale = false;
+    auto* h = new RefHandle;
+    h->rows = rows;
+    h->cols = cols;
+    // The constructor prints one line to stdout (Detector.hh:28); keep it off
+    // the caller's stdout (bench.py prints exactly one JSON line there).
+    std::streambuf* old = std::cout.rdbuf();
+    std::ostringstream sink;
+    std::cout.rdbuf(sink.rdbuf());
+    h->det = std::make_unique<sift_cuda::Detector>(cfg);
+    std::cout.rdbuf(old);
+    if (!h->det->gpuWarmUpAndAllocate()) {
+        delete h;
+        return nullptr;
+    }
+    h->img.m_image_size = Size{float(rows), float(cols)};
+    h->img.m_data = std::make_shared<std::vector<float>>(size_t(rows) * cols);
+    cudaDeviceSynchronize();
+    return h;
+}
+
+void ref_destroy(void* p) { delete static_cast<RefHandle*>(p); }
+
+int ref_num_octaves(void* p) { return static_cast<RefHandle*>(p)->det->m_nOctaves; }
+
+// dims[0..3] = width, height, pitch in floats (Gaussian stack), cap (kpt slots)
+void ref_octave_info(void* p, int o, int* dims) {
+    auto& d = *static_cast<RefHandle*>(p)->det;
+    auto& g = d.m_data.gaussian_block_pyramid.at(o);
+    dims[0] = int(g.getDim().x);
+    dims[1] = int(g.getDim().y);
+    dims[2] = int(g.getPitch() / sizeof(float));
+    dims[3] = int(d.m_data.extremas.at(o).collectedKpts.size());
+}
+
+void ref_set_image(void* p, const float* img) {
+    auto* h = static_cast<RefHandle*>(p);
+    std::memcpy(h->img.m_data->data(), img, size_t(h->rows) * h->cols * sizeof(float));
+}
+
+// The reference's public entry point, unmodified: H2D + all stages.
+int ref_detect(void* p) {
+    auto* h = static_cast<RefHandle*>(p);
+    h->det->detectAndCompute(h->img);
+    cudaDeviceSynchronize();
+    return h->det->total_size;
+}
+
+// Stage-by-stage replay of Detector::detectAndCompute (Detector.cu:133-233)
+// with the same calls in the same order; `stage` selects how far to go:
+// 0 upload+prev copy+initial blur, 1 gaussian, 2 dog, 3 extrema, 4 refine,
+// 5 orientation, 6 descriptor, 7 gather. Each call runs exactly one stage.
+int ref_stage(void* p, int stage) {
+    auto* h = static_cast<RefHandle*>(p);
+    auto& d = *h->det;
+    switch (stage) {
+        case 0:
+            d.m_data.original_image = h->img;
+            cudaMemcpyAsync(thrust::raw_pointer_cast(d.prev_descriptor.data()),
+                            thrust::raw_pointer_cast(d.device_descriptor.data()),
+                            d.prev_descriptor.size() * sizeof(half), cudaMemcpyDeviceToDevice);
+            d.createInitialImage();
+            break;
+        case 1: d.getGaussianPyramid(); break;
+        case 2: d.getDogPyramid(); break;
+        case 3: d.getKeyPoints(); break;
+        case 4: d.adjustKpts(); break;
+        case 5: d.adjustOrientationAndCleanup(); break;
+        case 6: d.extractDescriptor(); break;
+        case 7: d.collectAcrossOctaves(); break;
+        default: return -1;
+    }
+    cudaDeviceSynchronize();
+    return cudaGetLastError() == cudaSuccess ? 0 : -2;
+}
+
+// Device-resident timing: stages 0' (initial blur only, no H2D) .. 7, `iters`
+// times, CUDA events on the legacy default stream around the host-driven loop
+// (the reference blocks the host between stages, so wall clock == its latency).
+float ref_time_device_resident(void* p, int warmup, int iters) {
+    auto* h = static_cast<RefHandle*>(p);
+    auto& d = *h->det;
+    d.m_data.original_image = h->img;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    float total = 0.f;
+    for (int i = 0; i < warmup + iters; i++) {
+        cudaDeviceSynchronize();
+        cudaEventRecord(e0);
+        cudaMemcpyAsync(thrust::raw_pointer_cast(d.prev_descriptor.data()),
+                        thrust::raw_pointer_cast(d.device_descriptor.data()),
+                        d.prev_descriptor.size() * sizeof(half), cudaMemcpyDeviceToDevice);
+        d.createInitialImage();
+        d.getGaussianPyramid();
+        d.getDogPyramid();
+        d.getKeyPoints();
+        d.adjustKpts();
+        d.adjustOrientationAndCleanup();
+        d.extractDescriptor();
+        d.collectAcrossOctaves();
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (i >= warmup) total += ms;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return total / float(iters);
+}
+
+// End-to-end timing through the public API (pageable H2D inside), host clock.
+float ref_time_e2e(void* p, int warmup, int iters, int copy_to_host) {
+    auto* h = static_cast<RefHandle*>(p);
+    auto& d = *h->det;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    float total = 0.f;
+    for (int i = 0; i < warmup + iters; i++) {
+        cudaDeviceSynchronize();
+        cudaEventRecord(e0);
+        d.detectAndCompute(h->img);
+        if (copy_to_host) d.copyToHost(true);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (i >= warmup) total += ms;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return total / float(iters);
+}
+
+int ref_total_size(void* p) { return static_cast<RefHandle*>(p)->det->total_size; }
+
+// Final results (device vectors, first total_size entries valid).
+int ref_results(void* p, float* kpts3, float* feats4, uint16_t* desc, uint16_t* prev_desc) {
+    auto& d = *static_cast<RefHandle*>(p)->det;
+    cudaDeviceSynchronize();
+    copy_dev(d.device_kpts, kpts3, d.device_kpts.size());
+    copy_dev(d.device_features, feats4, d.device_features.size());
+    copy_dev(d.device_descriptor, desc, d.device_descriptor.size());
+    copy_dev(d.prev_descriptor, prev_desc, d.prev_descriptor.size());
+    return d.total_size;
+}
+
+// Dense (unpadded) copy of one layer stack: which = 0 gaussian (6 layers), 1 dog (5 layers).
+int ref_get_stack(void* p, int o, int which, float* out) {
+    auto& d = *static_cast<RefHandle*>(p)->det;
+    auto& b = which == 0 ? d.m_data.gaussian_block_pyramid.at(o) : d.m_data.dog_pyramid.at(o);
+    auto dim = b.getDim();
+    cudaError_t e = cudaMemcpy2D(out, size_t(dim.x) * 4, b.getData(), b.getPitch(), size_t(dim.x) * 4,
+                                 size_t(dim.y) * size_t(dim.z), cudaMemcpyDeviceToHost);
+    return e == cudaSuccess ? 0 : -1;
+}
+
+// Raw pitched copy incl. padding (to see what the reference reads at x == w, quirk Q12).
+int ref_get_stack_pitched(void* p, int o, int which, float* out) {
+    auto& d = *static_cast<RefHandle*>(p)->det;
+    auto& b = which == 0 ? d.m_data.gaussian_block_pyramid.at(o) : d.m_data.dog_pyramid.at(o);
+    auto dim = b.getDim();
+    cudaError_t e = cudaMemcpy(out, b.getData(), b.getPitch() * size_t(dim.y) * size_t(dim.z), cudaMemcpyDeviceToHost);
+    return e == cudaSuccess ? 0 : -1;
+}
+
+// Keypoint buffers of one octave. which: 0 candidateKpts(float3) 1 candidateFeatures(float4)
+// 2 collectedKpts 3 collectedFeatures 4 collectedMask(int) 5 descriptor(half)
+// 6 prefix_sum[0:cap] (int). Returns element count of the buffer.
+int ref_get_kpt_buffer(void* p, int o, int which, void* out, int max_elems) {
+    auto& k = static_cast<RefHandle*>(p)->det->m_data.extremas.at(o);
+    switch (which) {
+        case 0: return copy_dev(k.candidateKpts, out, max_elems);
+        case 1: return copy_dev(k.candidateFeatures, out, max_elems);
+        case 2: return copy_dev(k.collectedKpts, out, max_elems);
+        case 3: return copy_dev(k.collectedFeatures, out, max_elems);
+        case 4: return copy_dev(k.collectedMask, out, max_elems);
+        case 5: return copy_dev(k.descriptor, out, max_elems);
+        case 6: return copy_dev(k.prefix_sum, out, max_elems);
+        default: return -1;
+    }
+}
+
+// counts[0] = prefix_sum[last] (extrema count P right after stage 3),
+// counts[1] = prefix_sum[cap-1] (M after stage 4, T after stage 5).
+void ref_get_counts(void* p, int o, int* counts) {
+    auto& k = static_cast<RefHandle*>(p)->det->m_data.extremas.at(o);
+    cudaMemcpy(&counts[0], thrust::raw_pointer_cast(k.prefix_sum.data()) + k.prefix_sum.size() - 1, sizeof(int),
+               cudaMemcpyDeviceToHost);
+    cudaMemcpy(&counts[1], thrust::raw_pointer_cast(k.prefix_sum.data()) + k.collectedMask.size() - 1, sizeof(int),
+               cudaMemcpyDeviceToHost);
+}
+
+// Gaussian taps as the reference generated them: which = -1 initial blur, 0..5 layer taps.
+int ref_get_taps(void* p, int which, float* out, int max_elems) {
+    auto& d = *static_cast<RefHandle*>(p)->det;
+    const sift_cuda::CudaImage& k = which < 0 ? d.m_data.initial_image_kernel_1d : d.m_data.gaussian_kernels_1d.at(which);
+    int n = int(k.getDim().x);
+    if (out && n <= max_elems) cudaMemcpy(out, k.getData(), n * sizeof(float), cudaMemcpyDeviceToHost);
+    return n;
+}
+
+// sift_cuda::matchBruteForce (Match.cu:8), host buffers in / out.
+int ref_match(const uint16_t* des, int num_des, const uint16_t* src, int num_src, int* out_idx) {
+    thrust::device_vector<half> d(size_t(num_des) * 128), s(size_t(num_src) * 128);
+    cudaMemcpy(thrust::raw_pointer_cast(d.data()), des, size_t(num_des) * 256, cudaMemcpyHostToDevice);
+    cudaMemcpy(thrust::raw_pointer_cast(s.data()), src, size_t(num_src) * 256, cudaMemcpyHostToDevice);
+    std::vector<int> r = sift_cuda::matchBruteForce(d, num_des, s, num_src);
+    std::memcpy(out_idx, r.data(), r.size() * sizeof(int));
+    return int(r.size());
+}
+
+// Same call timed with CUDA events (includes the reference's per-call
+// allocation of the score matrix and its cudaDeviceSynchronize, Match.cu:16-28).
+float ref_time_match(const uint16_t* des, int num_des, const uint16_t* src, int num_src, int warmup, int iters) {
+    thrust::device_vector<half> d(size_t(num_des) * 128), s(size_t(num_src) * 128);
+    cudaMemcpy(thrust::raw_pointer_cast(d.data()), des, size_t(num_des) * 256, cudaMemcpyHostToDevice);
+    cudaMemcpy(thrust::raw_pointer_cast(s.data()), src, size_t(num_src) * 256, cudaMemcpyHostToDevice);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    float total = 0.f;
+    for (int i = 0; i < warmup + iters; i++) {
+        cudaDeviceSynchronize();
+        cudaEventRecord(e0);
+        std::vector<int> r = sift_cuda::matchBruteForce(d, num_des, s, num_src);
+        cudaEventRecord(e1);
+        cudaEventSynchronize(e1);
+        float ms = 0.f;
+        cudaEventElapsedTime(&ms, e0, e1);
+        if (i >= warmup) total += ms;
+    }
+    return total / float(iters);
+}
+
+}  // extern "C"
