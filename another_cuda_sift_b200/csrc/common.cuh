@@ -1,0 +1,96 @@
+// Shared device-side structures and stage launchers of the B200 SIFT engine.
+//
+// Data layout in HBM (one slab per detector, allocated once):
+//   * input image            : pitched float, pitch = round_up(w*4, 512) bytes
+//   * Gaussian stack/octave  : 6 layers, layer-major then row-major, row pitch rounded up to
+//                              512 B, layer stride pitch*h floats -- the layout the reference gets
+//                              from cudaMallocPitch (types/CudaImage.cu:192-207), kept because its
+//                              descriptor kernel reads one element past a row / layer (quirk Q12)
+//   * no DoG stack           : DoG[l] = G[l+1]-G[l] is one exact FADD, recomputed where needed
+//   * extrema bitmask        : 1 bit per pixel per scale (3 scales), + per-row popcounts
+//   * keypoint slots/octave  : cand/candF/coll/collF with the reference's slot semantics
+//                              (types/KeyPoint.cuh:9-29)
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b200sift {
+
+constexpr int kMaxOctaves = 16;
+constexpr int kGaussLayers = 6;   // numOctaveLayers + 3
+constexpr int kScales = 3;        // numOctaveLayers
+constexpr int kBorder = 5;        // SIFT_IMG_BORDER (sift_func/SiftOps.cuh:8)
+constexpr int kOriBins = 36;      // sift_func/SiftOps.cu:261
+constexpr int kMaxTaps = 21;
+
+struct Taps {
+    float v[kMaxTaps];
+    int n;
+};
+
+struct OctParams {
+    float* gauss;        // [6][h][pitch]
+    uint32_t* mask;      // [3][h][words] extrema bits
+    int* rowcount;       // [3*h] extrema per (scale,row); zeroed every frame
+    int* rowoff;         // [3*h] exclusive prefix of rowcount
+    float3* cand;        // [cap]
+    float4* candF;       // [cap]
+    float3* coll;        // [cap]
+    float4* collF;       // [cap]
+    int* flag;           // [cap] refine accept flags
+    int* oricnt;         // [cap] peaks emitted per refined keypoint
+    int* counts;         // [4]: P (raw extrema), M (refined), T (oriented), n = min(P, cap)
+    int w, h, pitch, cap;
+    int words;           // mask words per row = ceil(w/32)
+    int det_task0;       // first warp task of this octave in the detect kernel
+    int det_cols, det_rows;  // column strips (32 px) x row strips (kDetRows rows)
+    int row0;            // first (scale,row) index of this octave in the scatter kernel
+};
+
+struct FrameParams {
+    OctParams oct[kMaxOctaves];
+    int nOct;
+    int numFeatures;
+    int det_tasks;       // total warp tasks of the detect kernel
+    int rows_total;      // total (scale,row) entries over all octaves
+    float3* out_kpts;    // [numFeatures]
+    float4* out_feats;   // [numFeatures]
+    __half* out_desc;    // [numFeatures*128]
+    int* total;          // device: keypoints returned by the last frame
+    float extrema_thr;   // floor(0.5*contrast/nLayers*255) (interface/Detector.cu:362)
+    float contrast_thr, edge_thr, sigma;
+};
+
+constexpr int kDetRows = 16;  // rows per warp task in the detect kernel
+
+// ---- stage launchers (each enqueues on `s`; no host synchronisation inside) ----
+void launch_u8_to_float(const uint8_t* in, size_t in_pitch, float* out, int out_pitch, int w, int h, cudaStream_t s);
+void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s);
+void launch_downsample(const float* in, int in_pitch, int iw, int ih, float* out, int out_pitch, int ow, int oh, cudaStream_t s);
+void launch_detect(const FrameParams& fp, cudaStream_t s);       // bitmask + row counts
+void launch_scan_rows(const FrameParams& fp, cudaStream_t s);    // row offsets, P
+void launch_scatter(const FrameParams& fp, cudaStream_t s);      // ordered candidate list
+void launch_refine(const FrameParams& fp, cudaStream_t s);       // Taylor refinement + tests
+void launch_compact_refined(const FrameParams& fp, cudaStream_t s);
+void launch_orientation(const FrameParams& fp, cudaStream_t s);
+void launch_compact_oriented(const FrameParams& fp, cudaStream_t s);
+void launch_descriptor(const FrameParams& fp, cudaStream_t s);
+
+int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s);
+size_t match_scratch_bytes(int nq, int nt);
+int match_num_launches(int nq, int nt);
+
+// reflect-101 border index (same mapping as image_func/Filter.cuh:52-66).
+__host__ __device__ inline int reflect101(int idx, int length) {
+    if (length <= 1) return 0;
+    idx = idx < 0 ? -idx : idx;
+    if (idx >= length) {
+        int period = 2 * (length - 1);
+        idx = idx % period;
+        if (idx >= length) idx = period - idx;
+    }
+    return idx;
+}
+
+}  // namespace b200sift

@@ -1,0 +1,361 @@
+// Orientation assignment, keypoint expansion / compaction and the 128-D descriptor.
+//
+// Replaces sift_func/SiftOps.cu:237-376 (calOriHistMultiThread), :210-235 (collectKpts, second
+// use), :389-623 (genDescriptorMultiThread and helpers), utils/CudaMemcpyUtils.cu (copyValidNum,
+// collectKptsAndDescriptor) and the host round trip of interface/Detector.cu:536-604: all counts
+// stay on the device and descriptors are written straight into the final output arrays.
+//
+// Per-sample arithmetic follows the reference's expression trees with the FMA contraction its
+// sm_100a SASS shows. The one deliberate difference: the reference accumulates histogram votes
+// with float shared-memory atomics, whose order -- and therefore rounding -- changes from run to
+// run; here votes are accumulated as 2^-32 fixed point in 64-bit shared-memory atomics, which is
+// order independent (deterministic) and lies inside the reference's own run-to-run envelope.
+#include "common.cuh"
+
+namespace b200sift {
+
+namespace {
+
+constexpr float kFix = 4294967296.f;          // 2^32
+constexpr double kUnfix = 1.0 / 4294967296.0;
+
+__device__ __forceinline__ void fix_add(unsigned long long* slot, float v) {
+    atomicAdd(slot, (unsigned long long)__float2ll_rn(__fmul_rn(v, kFix)));
+}
+__device__ __forceinline__ float fix_get(unsigned long long v) { return (float)((double)(long long)v * kUnfix); }
+
+// ---------------------------------------------------------------- orientation
+constexpr int kOriWarps = 8;
+
+__global__ void __launch_bounds__(kOriWarps * 32)
+orientation_kernel(const __grid_constant__ FrameParams fp) {
+    const int oi = blockIdx.y;
+    const OctParams& o = fp.oct[oi];
+    const int M = o.counts[1];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    __shared__ unsigned long long s_hist[kOriWarps][kOriBins];
+    __shared__ float s_raw[kOriWarps][kOriBins];
+    __shared__ float s_smooth[kOriWarps][kOriBins];
+    unsigned long long* hist = s_hist[warp];
+    float* raw = s_raw[warp];
+    float* smooth = s_smooth[warp];
+    const size_t ls = (size_t)o.pitch * o.h;
+    const int h_dim = o.pitch;
+
+    for (int k = blockIdx.x * kOriWarps + warp; k < M; k += gridDim.x * kOriWarps) {
+        const float3 kp = o.coll[k];
+        const float4 ft = o.collF[k];
+        for (int i = lane; i < kOriBins; i += 32) hist[i] = 0ull;
+        __syncwarp();
+        // SiftOps.cu:271-297
+        const float scale = __fdiv_rn(__fmul_rn(1.5f, ft.y), (float)(1 << (oi + 1)));
+        const float radius = roundf(__fmul_rn(3.f, scale));
+        const int base_px = (int)roundf(__fdiv_rn(kp.x, (float)(1 << oi)));
+        const int base_py = (int)roundf(__fdiv_rn(kp.y, (float)(1 << oi)));
+        int side = (int)__fmaf_rn(2.f, radius, 1.f);
+        if (side > 1024) side = 1024;  // only a corrupt stale slot could ask for more
+        const int total_dim = side * side;
+        const float weight_factor = __fdiv_rn(-0.5f, __fmul_rn(scale, scale));
+        int layer = (int)kp.z;
+        layer = min(max(layer, 0), 4);
+        const float* g0 = o.gauss + ls * layer;  // DoG[layer] = G[layer+1] - G[layer]
+        for (int idx = lane; idx < total_dim; idx += 32) {
+            const int py_off = (int)__fsub_rn((float)(idx / side), radius);
+            const int py = base_py + py_off;
+            if (py < 1 || (float)py >= (float)o.h - 1.f) continue;
+            const int px_off = (int)__fsub_rn((float)(idx % side), radius);
+            const int px = base_px + px_off;
+            if (px < 1 || (float)px >= (float)o.w - 1.f) continue;
+            const float* p = g0 + (size_t)py * h_dim + px;
+            const float dx = __fsub_rn(__fsub_rn(__ldg(p + ls + 1), __ldg(p + 1)), __fsub_rn(__ldg(p + ls - 1), __ldg(p - 1)));
+            const float dy = __fsub_rn(__fsub_rn(__ldg(p + ls - h_dim), __ldg(p - h_dim)), __fsub_rn(__ldg(p + ls + h_dim), __ldg(p + h_dim)));
+            const float mag = __fsqrt_rd(__fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+            float ori = __fmul_rn(__fdiv_rn(atan2f(dy, dx), 3.14159265358979323846f), 180.f);
+            if (ori < 0.f) ori = __fadd_rn(ori, 360.f);
+            const float weight = __expf(__fmul_rn(weight_factor, (float)(px_off * px_off + py_off * py_off)));
+            int bin = __float2int_rd(__fmul_rn(__fdiv_rn(ori, 360.f), 36.f)) % kOriBins;
+            if (bin < 0) bin += kOriBins;  // NaN guard; never taken for finite input
+            fix_add(hist + bin, __fmul_rn(weight, mag));
+        }
+        __syncwarp();
+        for (int i = lane; i < kOriBins; i += 32) raw[i] = fix_get(hist[i]);
+        __syncwarp();
+        // [1 4 6 4 1]/16 smoothing with the reference's association (SiftOps.cu:335)
+        for (int i = lane; i < kOriBins; i += 32) {
+            const int l = i > 0 ? i - 1 : kOriBins - 1, r = i < kOriBins - 1 ? i + 1 : 0;
+            const int r2 = r < kOriBins - 1 ? r + 1 : 0, l2 = l > 0 ? l - 1 : kOriBins - 1;
+            const float a = __fmaf_rn(raw[i], 6.f, __fmul_rn(__fadd_rn(raw[l], raw[r]), 4.f));
+            smooth[i] = __fmul_rn(__fadd_rn(__fadd_rn(a, raw[l2]), raw[r2]), 0.0625f);
+        }
+        __syncwarp();
+        float mx = fmaxf(smooth[lane], lane < 4 ? smooth[lane + 32] : 0.f);
+        mx = fmaxf(mx, 0.f);
+#pragma unroll
+        for (int d = 16; d > 0; d >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
+        const float thr = __fmul_rn(mx, 0.8f);
+        auto is_peak = [&](int i) {
+            const int l = i > 0 ? i - 1 : kOriBins - 1, r = i < kOriBins - 1 ? i + 1 : 0;
+            return smooth[i] > smooth[l] && smooth[i] > smooth[r] && smooth[i] >= thr;
+        };
+        const bool p0 = is_peak(lane);
+        const bool p1 = lane < 4 ? is_peak(lane + 32) : false;
+        const unsigned m0 = __ballot_sync(0xffffffffu, p0);
+        const unsigned m1 = __ballot_sync(0xffffffffu, p1);
+        // copy c of keypoint k goes to slot M + 36k + c, dropped once slot >= cap (quirk Q6)
+        const int slot0 = k * kOriBins + M;
+        int emitted = 0;
+        for (int pass = 0; pass < 2; pass++) {
+            const unsigned m = pass == 0 ? m0 : m1;
+            const bool mine = pass == 0 ? p0 : p1;
+            const int bin = lane + 32 * pass;
+            const int c = (pass == 0 ? 0 : __popc(m0)) + __popc(m & ((1u << lane) - 1u));
+            const int slot = slot0 + c;
+            if (mine && slot < o.cap) {
+                o.coll[slot] = kp;
+                float4 f = ft;
+                f.w = __fsub_rn(360.f, __fmul_rn(__fdiv_rn((float)bin, 36.f), 360.f));
+                o.collF[slot] = f;
+            }
+            emitted += __popc(m);
+        }
+        if (lane == 0) {
+            const int room = o.cap - slot0;
+            o.oricnt[k] = max(0, min(emitted, room));
+        }
+        __syncwarp();
+    }
+}
+
+// One CTA per octave: prefix over per-keypoint peak counts -> cand/candF in (k, bin) order; the
+// entry whose prefix equals the total T is not written (quirk Q5 again).
+__global__ void __launch_bounds__(1024)
+compact_oriented_kernel(const __grid_constant__ FrameParams fp) {
+    const OctParams& o = fp.oct[blockIdx.x];
+    const int M = o.counts[1];
+    __shared__ int warp_sums[32];
+    __shared__ int s_total, carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int local = 0;
+    for (int i = threadIdx.x; i < M; i += 1024) local += o.oricnt[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) local += __shfl_xor_sync(0xffffffffu, local, d);
+    if (lane == 0) warp_sums[warp] = local;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tsum = 0;
+        for (int i = 0; i < 32; i++) tsum += warp_sums[i];
+        s_total = tsum;
+        carry = 0;
+        o.counts[2] = tsum;  // T
+    }
+    __syncthreads();
+    const int total = s_total;
+    for (int base = 0; base < M; base += 1024) {
+        const int k = base + threadIdx.x;
+        const int v = k < M ? o.oricnt[k] : 0;
+        int incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int u = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += u;
+        }
+        __syncthreads();
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int ws = warp_sums[lane];
+            int wi = ws;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int u = __shfl_up_sync(0xffffffffu, wi, d);
+                if (lane >= d) wi += u;
+            }
+            warp_sums[lane] = wi - ws;
+        }
+        __syncthreads();
+        const int c0 = carry;
+        const int excl = c0 + warp_sums[warp] + incl - v;
+        for (int c = 0; c < v; c++) {
+            const int p = excl + c + 1;
+            if (p < total) {
+                const int slot = M + k * kOriBins + c;
+                o.cand[p - 1] = o.coll[slot];
+                o.candF[p - 1] = o.collF[slot];
+            }
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = excl + v;
+        __syncthreads();
+    }
+}
+
+// ---------------------------------------------------------------- descriptor
+// fast_atan2f (SiftOps.cu:403-419), contraction as in the reference SASS.
+__device__ __forceinline__ float fast_atan2f(float y, float x) {
+    const float abs_y = __fadd_rn(fabsf(y), 1e-10f);
+    float r, angle;
+    if (x < 0.0f) {
+        r = __fdiv_rn(__fadd_rn(x, abs_y), __fsub_rn(abs_y, x));
+        angle = 2.356194490f;
+    } else {
+        r = __fdiv_rn(__fsub_rn(x, abs_y), __fadd_rn(x, abs_y));
+        angle = 0.785398163f;
+    }
+    angle = __fmaf_rn(__fmaf_rn(__fmul_rn(0.1963f, r), r, -0.9817f), r, angle);
+    return (y < 0.0f) ? -angle : angle;
+}
+
+constexpr int kDescThreads = 128;
+constexpr int kHistSize = 6 * 6 * 10;
+
+// One CTA per returned keypoint (global index g over octaves in ascending order, truncated at
+// numFeatures: utils/CudaMemcpyUtils.cu:38-67). 128 threads stride over the rotated patch.
+__global__ void __launch_bounds__(kDescThreads)
+descriptor_kernel(const __grid_constant__ FrameParams fp) {
+    const int g = blockIdx.x;
+    int oi = 0, j = g, sum = 0;
+    bool found = false;
+    for (int i = 0; i < fp.nOct; i++) {
+        const int T = fp.oct[i].counts[2];
+        if (!found && j < T) { oi = i; found = true; }
+        if (!found) j -= T;
+        sum += T;
+    }
+    if (g == 0 && threadIdx.x == 0) *fp.total = min(sum, fp.numFeatures);
+    if (!found) return;
+    const OctParams& o = fp.oct[oi];
+    const float3 kp = o.cand[j];
+    const float4 ft = o.candF[j];
+    const int tid = threadIdx.x;
+
+    __shared__ unsigned long long s_hist[kHistSize];
+    __shared__ float s_f[kHistSize];
+    __shared__ float s_desc[128];
+    __shared__ float s_norm;
+    for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0ull;
+    __syncthreads();
+
+    // unpackOctave (SiftOps.cu:389-401)
+    const int packed = (int)ft.x;
+    int octv = packed & 255;
+    const int layer = (packed >> 8) & 255;
+    octv = octv < 128 ? octv : (-128 | octv);
+    const float scale = octv >= 0 ? __fdiv_rn(1.f, (float)(1 << octv)) : (float)(1 << -octv);
+    const int hdim = o.pitch;
+    const long stack_len = (long)o.pitch * o.h * kGaussLayers;
+    const long img_off = (long)((float)hdim * (float)o.h * (float)layer);
+    const float x = (float)__float2int_rn(__fmul_rn(kp.x, scale));
+    const float y = (float)__float2int_rn(__fmul_rn(kp.y, scale));
+    float angle = __fsub_rn(360.f, ft.w);
+    if (fabsf(__fsub_rn(angle, 360.f)) < 1e-6f) angle = 0.f;
+    const float scl = __fmul_rn(__fmul_rn(ft.y, scale), 0.5f);
+    constexpr float deg2rad = (float)(3.14159265358979323846 / 180.0);
+    float cos_t, sin_t;
+    __sincosf(__fmul_rn(angle, deg2rad), &sin_t, &cos_t);
+    constexpr float bins_per_degree = 8 / 360.f;
+    const float hist_width = __fmul_rn(3.f, scl);
+    int radius = __float2int_rn(__fmul_rn(__fmul_rn(__fmul_rn(hist_width, 1.4142135623730951f), 5.f), 0.5f));
+    const float diag = sqrtf(__fmaf_rn((float)o.w, (float)o.w, __fmul_rn((float)o.h, (float)o.h)));
+    radius = (int)fmin((double)radius, (double)diag);
+    cos_t = __fdiv_rn(cos_t, hist_width);
+    sin_t = __fdiv_rn(sin_t, hist_width);
+    const int side = 2 * radius + 1;
+    const int total_dim = side * side;
+    const float fw = (float)o.w, fh = (float)o.h;
+    const float* stack = o.gauss;
+
+    for (int idx = tid; idx < total_dim; idx += kDescThreads) {
+        const int idx_i = idx / side - radius, idx_j = idx % side - radius;
+        const float fi = (float)idx_i, fj = (float)idx_j;
+        const float c_rot = __fmaf_rn(fj, cos_t, -__fmul_rn(fi, sin_t));
+        const float r_rot = __fmaf_rn(fi, cos_t, __fmul_rn(fj, sin_t));
+        const float cbin = __fadd_rn(c_rot, 1.5f), rbin = __fadd_rn(r_rot, 1.5f);
+        const int base_py = (int)__fadd_rn(y, fi), base_px = (int)__fadd_rn(x, fj);
+        if (rbin > -1.f && rbin < 4.f && cbin > -1.f && cbin < 4.f && (float)base_px > 0.f && (float)base_px < fw &&
+            (float)base_py > 0.f && (float)base_py < fh) {
+            // quirk Q12: px == w-1 / py == h-1 pass the test above, so these reads may land in the
+            // row padding, the next row or the next layer; clamp only at the end of the stack.
+            const long a = img_off + (long)base_py * hdim + base_px;
+            const long a_dn = a + hdim;
+            const float v_l = __ldg(stack + a - 1), v_r = __ldg(stack + a + 1);
+            const float v_up = __ldg(stack + a - hdim);
+            const float v_dn = a_dn < stack_len ? __ldg(stack + a_dn) : 0.f;
+            const float dx = __fsub_rn(v_r, v_l);
+            const float dy = __fsub_rn(v_up, v_dn);
+            const float rbin_int = truncf(rbin), cbin_int = truncf(cbin);
+            const float rbin_frac = __fsub_rn(rbin, rbin_int), cbin_frac = __fsub_rn(cbin, cbin_int);
+            const float weight = __expf(__fmul_rn(__fmaf_rn(c_rot, c_rot, __fmul_rn(r_rot, r_rot)), -0.125f));
+            const float grad_mag = __fsqrt_rn(__fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
+            float grad_ori = (float)(((double)fast_atan2f(dy, dx) / 3.14159265358979323846) * 180.0);
+            grad_ori = grad_ori < 0.f ? __fadd_rn(grad_ori, 360.f) : grad_ori;
+            const float obin = __fmul_rn(__fsub_rn(grad_ori, angle), bins_per_degree);
+            const float mag = __fmul_rn(grad_mag, weight);
+            float obin_int = truncf(obin);
+            const float obin_frac = __fsub_rn(obin, obin_int);
+            if (obin_int < 0.f) obin_int += 8.f;
+            if (obin_int >= 8.f) obin_int -= 8.f;
+            const int hi = (int)(((rbin_int + 1.f) * 6.f + cbin_int + 1.f) * 10.f + obin_int);
+            const float v_r1 = __fmul_rn(mag, rbin_frac), v_r0 = __fmul_rn(mag, __fsub_rn(1.f, rbin_frac));
+            const float omc = __fsub_rn(1.f, cbin_frac), omo = __fsub_rn(1.f, obin_frac);
+            const float v_rc11 = __fmul_rn(v_r1, cbin_frac), v_rc10 = __fmul_rn(v_r1, omc);
+            const float v_rc01 = __fmul_rn(v_r0, cbin_frac), v_rc00 = __fmul_rn(v_r0, omc);
+            if (hi >= 0 && hi + 71 < kHistSize) {
+                fix_add(s_hist + hi + 70, __fmul_rn(v_rc11, omo));
+                fix_add(s_hist + hi + 71, __fmul_rn(v_rc11, obin_frac));
+                fix_add(s_hist + hi + 60, __fmul_rn(v_rc10, omo));
+                fix_add(s_hist + hi + 61, __fmul_rn(v_rc10, obin_frac));
+                fix_add(s_hist + hi + 10, __fmul_rn(v_rc01, omo));
+                fix_add(s_hist + hi + 11, __fmul_rn(v_rc01, obin_frac));
+                fix_add(s_hist + hi, __fmul_rn(v_rc00, omo));
+                fix_add(s_hist + hi + 1, __fmul_rn(v_rc00, obin_frac));
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = tid; i < kHistSize; i += kDescThreads) s_f[i] = fix_get(s_hist[i]);
+    __syncthreads();
+    // copyToDescriptor (SiftOps.cu:431-446): fold orientation bins 8,9 onto 0,1
+    {
+        const int cell = tid >> 3, k = tid & 7;
+        const int ci = cell >> 2, cj = cell & 3;
+        const int base = ((ci + 1) * 6 + (cj + 1)) * 10;
+        float v = s_f[base + k];
+        if (k < 2) v = __fadd_rn(v, s_f[base + 8 + k]);
+        s_desc[tid] = v;
+    }
+    __syncthreads();
+    if (tid == 0) {
+        // norm / clip_lower / norm, sequential FMA chains as the reference's lane 0 (SiftOps.cu:606-615)
+        float cnt = 0.f;
+        for (int i = 0; i < 128; i++) cnt = __fmaf_rn(s_desc[i], s_desc[i], cnt);
+        const float nrm = sqrtf(cnt);
+        const float thr = (float)((double)nrm * 0.2);
+        cnt = 0.f;
+        for (int i = 0; i < 128; i++) {
+            const float v = fminf(s_desc[i], thr);
+            s_desc[i] = v;
+            cnt = __fmaf_rn(v, v, cnt);
+        }
+        s_norm = fmaxf(sqrtf(cnt), 1e-7f);
+    }
+    __syncthreads();
+    const float v = __saturatef(__fdiv_rn(s_desc[tid], s_norm));
+    fp.out_desc[(size_t)g * 128 + tid] = __float2half(__fmul_rn(v, 512.f));
+    if (tid == 0) {
+        fp.out_kpts[g] = kp;
+        fp.out_feats[g] = ft;
+    }
+}
+
+}  // namespace
+
+void launch_orientation(const FrameParams& fp, cudaStream_t s) {
+    dim3 grid(148, fp.nOct);
+    orientation_kernel<<<grid, kOriWarps * 32, 0, s>>>(fp);
+}
+void launch_compact_oriented(const FrameParams& fp, cudaStream_t s) { compact_oriented_kernel<<<fp.nOct, 1024, 0, s>>>(fp); }
+void launch_descriptor(const FrameParams& fp, cudaStream_t s) {
+    descriptor_kernel<<<fp.numFeatures, kDescThreads, 0, s>>>(fp);
+}
+
+}  // namespace b200sift

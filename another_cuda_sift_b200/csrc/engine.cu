@@ -1,0 +1,529 @@
+// Host side of the B200 SIFT engine: allocation, per-frame CUDA graph, C ABI (include/b200sift.h).
+//
+// Replaces the orchestration of interface/Detector.cu (5 CUDA graphs, 6 host synchronisations and
+// a pinned-memory count round trip per frame) with ONE graph per frame and no host involvement
+// between its first and last kernel: every count stays on the device.
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/b200sift.h"
+#include "common.cuh"
+
+using namespace b200sift;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+
+#define CU(call)                                                                                  \
+    do {                                                                                          \
+        cudaError_t e_ = (call);                                                                  \
+        if (e_ != cudaSuccess)                                                                    \
+            return fail(B200SIFT_ECUDA, "%s:%d %s: %s", __FILE__, __LINE__, cudaGetErrorName(e_), \
+                        cudaGetErrorString(e_));                                                  \
+    } while (0)
+
+// get1DGaussian (utils/GaussianUtils.cc:39-67), float arithmetic on the host, bit-identical taps.
+Taps gaussian_taps(float sigma) {
+    Taps t;
+    std::memset(&t, 0, sizeof(t));
+    const int size = int(std::round(sigma * 6 + 1)) | 1;
+    t.n = size;
+    if (size > kMaxTaps) return t;
+    float mean = size / 2;
+    float cov_double = sigma * sigma * 2;
+    float sum = 0;
+    int i = 0;
+    for (float row = 0; row < size; row++) {
+        float g = expf(-((powf(row - mean, 2)) / cov_double));
+        sum += g;
+        t.v[i++] = g;
+    }
+    for (int k = 0; k < size; k++) t.v[k] = t.v[k] / sum;
+    return t;
+}
+
+bool radius_supported(int n) {
+    const int r = n / 2;
+    return (n & 1) && (r == 4 || r == 5 || r == 6 || r == 8 || r == 10);
+}
+
+inline int pitch_floats(int w) { return ((w * 4 + 511) / 512) * 512 / 4; }
+
+}  // namespace
+
+struct b200sift_detector {
+    b200sift_config cfg;
+    int device = 0;
+    int nOct = 0;
+    Taps init_taps;
+    Taps taps[kGaussLayers];
+    FrameParams fp;
+    float* d_input = nullptr;
+    int in_pitch = 0;
+    uint8_t* d_input_u8 = nullptr;
+    size_t u8_pitch = 0;
+    int* d_rowcount_all = nullptr;
+    size_t rowcount_bytes = 0;
+    __half* d_prev_desc = nullptr;
+    int* h_total = nullptr;  // pinned
+    std::vector<void*> allocs;
+    cudaStream_t stream = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    int launches = 0;
+    bool have_frame = false;
+};
+
+namespace {
+
+template <typename T>
+int dev_alloc(b200sift_detector* d, T** p, size_t count) {
+    void* q = nullptr;
+    const size_t bytes = std::max<size_t>(count * sizeof(T), 16);
+    CU(cudaMalloc(&q, bytes));
+    CU(cudaMemset(q, 0, bytes));
+    d->allocs.push_back(q);
+    *p = static_cast<T*>(q);
+    return 0;
+}
+
+// The frame pipeline, stages numbered as in Detector::detectAndCompute (Detector.cu:133-233):
+// 0 prev-descriptor copy, 1 pyramid, 3 extrema, 4 refinement, 5 orientation, 6/7 descriptor+gather.
+int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* launches) {
+    FrameParams& fp = d->fp;
+    int n = 0;
+    CU(cudaMemcpyAsync(d->d_prev_desc, fp.out_desc, (size_t)fp.numFeatures * 128 * sizeof(__half),
+                       cudaMemcpyDeviceToDevice, s));
+    CU(cudaMemsetAsync(d->d_rowcount_all, 0, d->rowcount_bytes, s));
+    for (int o = 0; o < d->nOct; o++) {
+        OctParams& oc = fp.oct[o];
+        const size_t ls = (size_t)oc.pitch * oc.h;
+        for (int l = 0; l < kGaussLayers; l++) {
+            float* dst = oc.gauss + ls * l;
+            if (o == 0 && l == 0) {
+                launch_blur(d->d_input, d->in_pitch, dst, oc.pitch, oc.w, oc.h, d->init_taps, s);
+            } else if (l == 0) {
+                const OctParams& pv = fp.oct[o - 1];
+                const float* src = pv.gauss + (size_t)pv.pitch * pv.h * kScales;
+                launch_downsample(src, pv.pitch, pv.w, pv.h, dst, oc.pitch, oc.w, oc.h, s);
+            } else {
+                launch_blur(oc.gauss + ls * (l - 1), oc.pitch, dst, oc.pitch, oc.w, oc.h, d->taps[l], s);
+            }
+            n++;
+        }
+    }
+    if (last_stage >= 3) {
+        if (fp.det_tasks > 0) { launch_detect(fp, s); n++; }
+        launch_scan_rows(fp, s); n++;
+        launch_scatter(fp, s); n++;
+    }
+    if (last_stage >= 4) {
+        launch_refine(fp, s); n++;
+        launch_compact_refined(fp, s); n++;
+    }
+    if (last_stage >= 5) {
+        launch_orientation(fp, s); n++;
+        launch_compact_oriented(fp, s); n++;
+    }
+    if (last_stage >= 6) {
+        launch_descriptor(fp, s); n++;
+        CU(cudaMemcpyAsync(d->h_total, fp.total, sizeof(int), cudaMemcpyDeviceToHost, s));
+    }
+    CU(cudaGetLastError());
+    if (launches) *launches = n;
+    return 0;
+}
+
+int build(b200sift_detector* d) {
+    const b200sift_config& c = d->cfg;
+    CU(cudaGetDevice(&d->device));
+    CU(cudaFree(0));
+    // Detector.hh:27
+    d->nOct = (int)(std::round(std::log(double(std::min(c.col_width * 2, c.row_width * 2))) / std::log(2.) - 2) + 1);
+    if (d->nOct < 1 || d->nOct > kMaxOctaves) return fail(B200SIFT_EINVAL, "unsupported image size (%d octaves)", d->nOct);
+    // Detector.cu:54-59 and :63-77
+    float sigma_diff = sqrtf(fmax(c.sigma * c.sigma - 0.5f * 0.5f * 4, 0.01f));
+    d->init_taps = gaussian_taps(sigma_diff);
+    std::vector<float> sigmas(kGaussLayers);
+    sigmas[0] = (float)c.sigma;
+    double k = std::pow(2., 1. / c.numOctaveLayers);
+    for (int i = 1; i < kGaussLayers; i++) {
+        double sig_prev = std::pow(k, (double)(i - 1)) * c.sigma;
+        double sig_total = sig_prev * k;
+        sigmas[i] = (float)std::sqrt(sig_total * sig_total - sig_prev * sig_prev);
+    }
+    for (int i = 0; i < kGaussLayers; i++) d->taps[i] = gaussian_taps(sigmas[i]);
+    if (!radius_supported(d->init_taps.n)) return fail(B200SIFT_EINVAL, "sigma %.3f: unsupported tap count %d", c.sigma, d->init_taps.n);
+    for (int i = 1; i < kGaussLayers; i++)
+        if (!radius_supported(d->taps[i].n)) return fail(B200SIFT_EINVAL, "sigma %.3f: unsupported tap count %d", c.sigma, d->taps[i].n);
+
+    FrameParams& fp = d->fp;
+    std::memset(&fp, 0, sizeof(fp));
+    fp.nOct = d->nOct;
+    fp.numFeatures = c.numFeatures;
+    fp.extrema_thr = (float)std::floor(0.5 * c.contrastThreshould / c.numOctaveLayers * 255 * 1.f);  // Detector.cu:362
+    fp.contrast_thr = (float)c.contrastThreshould;
+    fp.edge_thr = (float)c.edgeThreshould;
+    fp.sigma = (float)c.sigma;
+
+    d->in_pitch = pitch_floats(c.col_width);
+    if (int rc = dev_alloc(d, &d->d_input, (size_t)d->in_pitch * c.row_width)) return rc;
+    d->u8_pitch = ((size_t)c.col_width + 511) / 512 * 512;
+    if (int rc = dev_alloc(d, &d->d_input_u8, d->u8_pitch * c.row_width)) return rc;
+
+    int rows_total = 0;
+    for (int o = 0; o < d->nOct; o++) {
+        OctParams& oc = fp.oct[o];
+        oc.w = (int)roundf(c.col_width / powf(2, o));  // Detector.cu:83
+        oc.h = (int)roundf(c.row_width / powf(2, o));
+        if (oc.w < 1 || oc.h < 1) return fail(B200SIFT_EINVAL, "octave %d is empty", o);
+        oc.pitch = pitch_floats(oc.w);
+        oc.cap = std::min(oc.pitch * oc.h, c.numFeatures * 10);  // KeyPoint.cu:13, Detector.cu:109
+        oc.words = (oc.w + 31) / 32;
+        oc.row0 = rows_total;
+        rows_total += kScales * oc.h;
+    }
+    fp.rows_total = rows_total;
+    if (int rc = dev_alloc(d, &d->d_rowcount_all, (size_t)rows_total)) return rc;
+    d->rowcount_bytes = (size_t)rows_total * sizeof(int);
+    int* d_rowoff_all = nullptr;
+    if (int rc = dev_alloc(d, &d_rowoff_all, (size_t)rows_total)) return rc;
+    int* d_counts = nullptr;
+    if (int rc = dev_alloc(d, &d_counts, (size_t)4 * kMaxOctaves + 4)) return rc;
+    fp.total = d_counts + 4 * kMaxOctaves;
+
+    int task0 = 0;
+    for (int o = 0; o < d->nOct; o++) {
+        OctParams& oc = fp.oct[o];
+        const size_t ls = (size_t)oc.pitch * oc.h;
+        // +pitch floats of zeroed tail so that the reference's read one row past layer 5 of a
+        // stale slot stays inside the allocation
+        if (int rc = dev_alloc(d, &oc.gauss, ls * kGaussLayers + oc.pitch)) return rc;
+        if (int rc = dev_alloc(d, &oc.mask, (size_t)kScales * oc.h * oc.words)) return rc;
+        oc.rowcount = d->d_rowcount_all + oc.row0;
+        oc.rowoff = d_rowoff_all + oc.row0;
+        if (int rc = dev_alloc(d, &oc.cand, (size_t)oc.cap)) return rc;
+        if (int rc = dev_alloc(d, &oc.candF, (size_t)oc.cap)) return rc;
+        if (int rc = dev_alloc(d, &oc.coll, (size_t)oc.cap)) return rc;
+        if (int rc = dev_alloc(d, &oc.collF, (size_t)oc.cap)) return rc;
+        if (int rc = dev_alloc(d, &oc.flag, (size_t)oc.cap)) return rc;
+        if (int rc = dev_alloc(d, &oc.oricnt, (size_t)oc.cap)) return rc;
+        oc.counts = d_counts + 4 * o;
+        const int band = oc.h - 2 * kBorder;
+        oc.det_cols = (oc.w > 2 * kBorder && band > 0) ? oc.words : 0;
+        oc.det_rows = oc.det_cols ? (band + kDetRows - 1) / kDetRows : 0;
+        oc.det_task0 = task0;
+        task0 += oc.det_cols * oc.det_rows;
+    }
+    fp.det_tasks = task0;
+    if (int rc = dev_alloc(d, &fp.out_kpts, (size_t)c.numFeatures)) return rc;
+    if (int rc = dev_alloc(d, &fp.out_feats, (size_t)c.numFeatures)) return rc;
+    if (int rc = dev_alloc(d, &fp.out_desc, (size_t)c.numFeatures * 128)) return rc;
+    if (int rc = dev_alloc(d, &d->d_prev_desc, (size_t)c.numFeatures * 128)) return rc;
+    CU(cudaMallocHost(&d->h_total, sizeof(int)));
+    *d->h_total = 0;
+    CU(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+
+    // One graph for the whole frame.
+    CU(cudaStreamBeginCapture(d->stream, cudaStreamCaptureModeThreadLocal));
+    int rc = enqueue_frame(d, d->stream, 7, &d->launches);
+    cudaError_t e = cudaStreamEndCapture(d->stream, &d->graph);
+    if (rc) return rc;
+    CU(e);
+    CU(cudaGraphInstantiate(&d->exec, d->graph, 0));
+    CU(cudaStreamSynchronize(d->stream));
+    return 0;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------------------------ C ABI
+extern "C" {
+
+void b200sift_default_config(b200sift_config* cfg) {
+    if (!cfg) return;
+    cfg->col_width = 0;
+    cfg->row_width = 0;
+    cfg->numFeatures = 5000;
+    cfg->numOctaveLayers = 3;
+    cfg->contrastThreshould = 0.04;
+    cfg->edgeThreshould = 10;
+    cfg->sigma = 1.6;
+    cfg->upscale = 0;
+}
+
+const char* b200sift_last_error(void) { return g_err.c_str(); }
+const char* b200sift_version(void) { return "b200sift 0.1 (sm_100a)"; }
+
+int b200sift_create(const b200sift_config* cfg, b200sift_detector** out) {
+    if (!cfg || !out) return fail(B200SIFT_EINVAL, "null argument");
+    *out = nullptr;
+    if (cfg->col_width <= 0 || cfg->row_width <= 0)
+        return fail(B200SIFT_EINVAL, "Image width or height not set.");  // Detector.cu:22-25
+    if (cfg->upscale) return fail(B200SIFT_EINVAL, "upscale=true is broken in the reference (CudaSiftConfig.hh:12) and unsupported");
+    if (cfg->numOctaveLayers != 3) return fail(B200SIFT_EINVAL, "numOctaveLayers must be 3");
+    if (cfg->numFeatures <= 0) return fail(B200SIFT_EINVAL, "numFeatures must be positive");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
+        cudaGetLastError();
+        return fail(B200SIFT_ECUDA, "no CUDA device: this engine has no CPU fallback");
+    }
+    b200sift_detector* d = new b200sift_detector;
+    d->cfg = *cfg;
+    int rc = build(d);
+    if (rc) {
+        std::string keep = g_err;
+        b200sift_destroy(d);
+        g_err = keep;
+        return rc;
+    }
+    *out = d;
+    return 0;
+}
+
+int b200sift_destroy(b200sift_detector* d) {
+    if (!d) return 0;
+    if (d->stream) cudaStreamSynchronize(d->stream);
+    if (d->exec) cudaGraphExecDestroy(d->exec);
+    if (d->graph) cudaGraphDestroy(d->graph);
+    for (void* p : d->allocs) cudaFree(p);
+    if (d->h_total) cudaFreeHost(d->h_total);
+    if (d->stream) cudaStreamDestroy(d->stream);
+    delete d;
+    return 0;
+}
+
+int b200sift_num_octaves(const b200sift_detector* d) { return d ? d->nOct : B200SIFT_EINVAL; }
+
+int b200sift_octave_info(const b200sift_detector* d, int o, int* dims) {
+    if (!d || !dims || o < 0 || o >= d->nOct) return fail(B200SIFT_EINVAL, "bad octave");
+    const OctParams& oc = d->fp.oct[o];
+    dims[0] = oc.w; dims[1] = oc.h; dims[2] = oc.pitch; dims[3] = oc.cap;
+    return 0;
+}
+
+static int launch_frame(b200sift_detector* d) {
+    CU(cudaGraphLaunch(d->exec, d->stream));
+    d->have_frame = true;
+    return 0;
+}
+
+int b200sift_detect_host_async(b200sift_detector* d, const float* img, int rows, int cols) {
+    if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
+    if (rows != d->cfg.row_width || cols != d->cfg.col_width)
+        return fail(B200SIFT_EINVAL, "image is %dx%d, detector was configured for %dx%d", cols, rows, d->cfg.col_width, d->cfg.row_width);
+    CU(cudaMemcpy2DAsync(d->d_input, (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
+                         cudaMemcpyHostToDevice, d->stream));
+    return launch_frame(d);
+}
+
+int b200sift_sync(b200sift_detector* d, int* total) {
+    if (!d) return fail(B200SIFT_EINVAL, "null argument");
+    CU(cudaStreamSynchronize(d->stream));
+    if (total) *total = d->have_frame ? *d->h_total : 0;
+    return 0;
+}
+
+int b200sift_detect_host(b200sift_detector* d, const float* img, int rows, int cols, int* total) {
+    int rc = b200sift_detect_host_async(d, img, rows, cols);
+    if (rc) return rc;
+    return b200sift_sync(d, total);
+}
+
+int b200sift_detect_device_async(b200sift_detector* d, const float* d_img, size_t pitch_bytes) {
+    if (!d || !d_img) return fail(B200SIFT_EINVAL, "null argument");
+    const int cols = d->cfg.col_width, rows = d->cfg.row_width;
+    if (pitch_bytes < (size_t)cols * 4) return fail(B200SIFT_EINVAL, "pitch smaller than a row");
+    CU(cudaMemcpy2DAsync(d->d_input, (size_t)d->in_pitch * 4, d_img, pitch_bytes, (size_t)cols * 4, rows,
+                         cudaMemcpyDeviceToDevice, d->stream));
+    return launch_frame(d);
+}
+
+int b200sift_detect_host_u8_async(b200sift_detector* d, const uint8_t* img, int rows, int cols) {
+    if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
+    if (rows != d->cfg.row_width || cols != d->cfg.col_width)
+        return fail(B200SIFT_EINVAL, "image is %dx%d, detector was configured for %dx%d", cols, rows, d->cfg.col_width, d->cfg.row_width);
+    CU(cudaMemcpy2DAsync(d->d_input_u8, d->u8_pitch, img, (size_t)cols, (size_t)cols, rows, cudaMemcpyHostToDevice, d->stream));
+    launch_u8_to_float(d->d_input_u8, d->u8_pitch, d->d_input, d->in_pitch, cols, rows, d->stream);
+    return launch_frame(d);
+}
+
+void* b200sift_stream(b200sift_detector* d) { return d ? (void*)d->stream : nullptr; }
+
+int b200sift_results(b200sift_detector* d, const float** kpts, const float** feats, const uint16_t** desc,
+                     const uint16_t** prev_desc, int* total) {
+    if (!d) return fail(B200SIFT_EINVAL, "null argument");
+    if (kpts) *kpts = reinterpret_cast<const float*>(d->fp.out_kpts);
+    if (feats) *feats = reinterpret_cast<const float*>(d->fp.out_feats);
+    if (desc) *desc = reinterpret_cast<const uint16_t*>(d->fp.out_desc);
+    if (prev_desc) *prev_desc = reinterpret_cast<const uint16_t*>(d->d_prev_desc);
+    if (total) return b200sift_sync(d, total);
+    return 0;
+}
+
+int b200sift_copy_to_host(b200sift_detector* d, float* kpts3, float* feats4, uint16_t* desc, int with_desc) {
+    if (!d) return fail(B200SIFT_EINVAL, "null argument");
+    int total = 0;
+    int rc = b200sift_sync(d, &total);
+    if (rc) return rc;
+    if (kpts3) CU(cudaMemcpyAsync(kpts3, d->fp.out_kpts, (size_t)total * sizeof(float3), cudaMemcpyDeviceToHost, d->stream));
+    if (feats4) CU(cudaMemcpyAsync(feats4, d->fp.out_feats, (size_t)total * sizeof(float4), cudaMemcpyDeviceToHost, d->stream));
+    if (with_desc && desc)
+        CU(cudaMemcpyAsync(desc, d->fp.out_desc, (size_t)total * 128 * sizeof(__half), cudaMemcpyDeviceToHost, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    return 0;
+}
+
+int b200sift_debug_get_stack(b200sift_detector* d, int o, int which, float* out) {
+    if (!d || !out || o < 0 || o >= d->nOct || which != 0) return fail(B200SIFT_EINVAL, "bad argument");
+    const OctParams& oc = d->fp.oct[o];
+    CU(cudaStreamSynchronize(d->stream));
+    CU(cudaMemcpy2D(out, (size_t)oc.w * 4, oc.gauss, (size_t)oc.pitch * 4, (size_t)oc.w * 4, (size_t)oc.h * kGaussLayers,
+                    cudaMemcpyDeviceToHost));
+    return 0;
+}
+
+int b200sift_debug_get_kpt_buffer(b200sift_detector* d, int o, int which, void* out, int max_elems) {
+    if (!d || !out || o < 0 || o >= d->nOct) return fail(B200SIFT_EINVAL, "bad argument");
+    const OctParams& oc = d->fp.oct[o];
+    const int n = std::min(max_elems, oc.cap);
+    CU(cudaStreamSynchronize(d->stream));
+    switch (which) {
+        case 0: CU(cudaMemcpy(out, oc.cand, (size_t)n * sizeof(float3), cudaMemcpyDeviceToHost)); break;
+        case 1: CU(cudaMemcpy(out, oc.candF, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost)); break;
+        case 2: CU(cudaMemcpy(out, oc.coll, (size_t)n * sizeof(float3), cudaMemcpyDeviceToHost)); break;
+        case 3: CU(cudaMemcpy(out, oc.collF, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost)); break;
+        default: return fail(B200SIFT_EINVAL, "bad buffer id");
+    }
+    return oc.cap;
+}
+
+int b200sift_debug_get_counts(b200sift_detector* d, int o, int* counts) {
+    if (!d || !counts || o < 0 || o >= d->nOct) return fail(B200SIFT_EINVAL, "bad argument");
+    CU(cudaStreamSynchronize(d->stream));
+    int c[4];
+    CU(cudaMemcpy(c, d->fp.oct[o].counts, sizeof(c), cudaMemcpyDeviceToHost));
+    counts[0] = c[0]; counts[1] = c[1]; counts[2] = c[2];
+    return 0;
+}
+
+int b200sift_debug_get_taps(b200sift_detector* d, int which, float* out, int max_elems) {
+    if (!d || which < -1 || which >= kGaussLayers) return fail(B200SIFT_EINVAL, "bad argument");
+    const Taps& t = which < 0 ? d->init_taps : d->taps[which];
+    if (out && t.n <= max_elems) std::memcpy(out, t.v, t.n * sizeof(float));
+    return t.n;
+}
+
+int b200sift_debug_run_stages(b200sift_detector* d, const float* img, int rows, int cols, int last_stage) {
+    if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
+    if (rows != d->cfg.row_width || cols != d->cfg.col_width) return fail(B200SIFT_EINVAL, "image size mismatch");
+    CU(cudaMemcpy2DAsync(d->d_input, (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
+                         cudaMemcpyHostToDevice, d->stream));
+    int rc = enqueue_frame(d, d->stream, last_stage, nullptr);
+    if (rc) return rc;
+    if (last_stage >= 6) d->have_frame = true;
+    CU(cudaStreamSynchronize(d->stream));
+    return 0;
+}
+
+int b200sift_launches_per_frame(const b200sift_detector* d) { return d ? d->launches : B200SIFT_EINVAL; }
+
+int b200sift_time_frames(b200sift_detector* d, int warmup, int iters, float* ms_per_frame) {
+    if (!d || !ms_per_frame || iters <= 0) return fail(B200SIFT_EINVAL, "bad argument");
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    for (int i = 0; i < warmup; i++) CU(cudaGraphLaunch(d->exec, d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    CU(cudaEventRecord(e0, d->stream));
+    for (int i = 0; i < iters; i++) CU(cudaGraphLaunch(d->exec, d->stream));
+    CU(cudaEventRecord(e1, d->stream));
+    CU(cudaEventSynchronize(e1));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    d->have_frame = true;
+    *ms_per_frame = ms / (float)iters;
+    return 0;
+}
+
+// ---- matcher
+namespace {
+std::mutex g_scratch_mu;
+void* g_scratch[64] = {nullptr};
+size_t g_scratch_bytes[64] = {0};
+}  // namespace
+
+int b200sift_match_device(const uint16_t* d_query, int nq, const uint16_t* d_train, int nt, int* d_out_idx, void* stream) {
+    if (nq < 0 || nt < 0 || (nq > 0 && (!d_query || !d_out_idx)) || (nt > 0 && !d_train))
+        return fail(B200SIFT_EINVAL, "bad argument");
+    if (nq == 0) return 0;
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(B200SIFT_EINVAL, "device index out of range");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    const size_t need = match_scratch_bytes(nq, nt);
+    void* scratch = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_scratch_mu);
+        if (g_scratch_bytes[dev] < need) {
+            if (g_scratch[dev]) {
+                CU(cudaDeviceSynchronize());
+                CU(cudaFree(g_scratch[dev]));
+                g_scratch[dev] = nullptr;
+                g_scratch_bytes[dev] = 0;
+            }
+            CU(cudaMalloc(&g_scratch[dev], need));
+            g_scratch_bytes[dev] = need;
+        }
+        scratch = g_scratch[dev];
+    }
+    if (match_launch(reinterpret_cast<const __half*>(d_query), nq, reinterpret_cast<const __half*>(d_train), nt, d_out_idx,
+                     scratch, need, s))
+        return fail(B200SIFT_EINVAL, "matcher scratch too small");
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int b200sift_match_host(const uint16_t* query, int nq, const uint16_t* train, int nt, int* out_idx) {
+    if (nq < 0 || nt < 0 || (nq > 0 && (!query || !out_idx)) || (nt > 0 && !train)) return fail(B200SIFT_EINVAL, "bad argument");
+    if (nq == 0) return 0;
+    uint16_t *dq = nullptr, *dt = nullptr;
+    int* dout = nullptr;
+    CU(cudaMalloc(&dq, (size_t)nq * 256));
+    CU(cudaMalloc(&dt, std::max<size_t>((size_t)nt * 256, 16)));
+    CU(cudaMalloc(&dout, (size_t)nq * sizeof(int)));
+    CU(cudaMemcpy(dq, query, (size_t)nq * 256, cudaMemcpyHostToDevice));
+    if (nt) CU(cudaMemcpy(dt, train, (size_t)nt * 256, cudaMemcpyHostToDevice));
+    int rc = b200sift_match_device(dq, nq, dt, nt, dout, nullptr);
+    if (!rc) {
+        cudaError_t e = cudaMemcpy(out_idx, dout, (size_t)nq * sizeof(int), cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) rc = fail(B200SIFT_ECUDA, "%s", cudaGetErrorString(e));
+    }
+    cudaFree(dq);
+    cudaFree(dt);
+    cudaFree(dout);
+    return rc;
+}
+
+int b200sift_match_launches(int nq, int nt) { return match_num_launches(nq, nt); }
+
+}  // extern "C"

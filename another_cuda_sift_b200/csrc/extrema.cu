@@ -1,0 +1,393 @@
+// DoG + 3x3x3 extrema + ordered compaction + Taylor refinement.
+//
+// Replaces image_func/MatOps.cu (minus, findPeaksBlockFirstPass, cub scan over an int-per-pixel
+// mask, findPeaksBlockSecondPass), sift_func/SiftOps.cu:63-235 (adjustExtrema, collectKpts) and
+// the memsetMask launches of interface/Detector.cu:330-343.
+//
+//  detect  : one pass over the 6 Gaussian layers of every octave. DoG is formed in registers
+//            (G[l+1]-G[l] is a single exact FADD, so nothing is lost by not storing it); a warp
+//            slides down a 32-pixel-wide column strip keeping a 3-row window of horizontal
+//            3-max / 3-min per DoG layer, so each Gaussian pixel is loaded once per strip.
+//            Output: 1 bit per pixel per scale (warp ballot) + per-row popcounts.
+//  scan    : exclusive prefix over (scale,row) counts -> raster order (scale, y, x) exactly as
+//            the reference's global inclusive scan gives it.
+//  scatter : warp per non-empty row, popc/prefix-sum append of (x, y, scale+1) at slot prefix-1
+//            while prefix < cap (MatOps.cu:172-179).
+//  refine  : thread per candidate, same expression tree and FMA contraction as the reference
+//            kernel compiled for sm_100a (checked against its SASS), DoG recomputed on the fly.
+//
+// Roofline: HBM-bound. Algorithmic bytes of detect = 24 B per pixel of every octave (6 layers
+// read once) + 3/8 B per pixel of mask.
+#include "common.cuh"
+
+namespace b200sift {
+
+namespace {
+
+constexpr int kDetThreads = 256;
+
+struct Row5 {  // per DoG layer: horizontal 3-max, 3-min of one row; centre value
+    float mx[5], mn[5], c[5];
+};
+
+__device__ __forceinline__ void load_row(const OctParams& o, int y, int xc, int xh, bool halo_lane, int lane, Row5& r) {
+    const size_t ls = (size_t)o.pitch * o.h;
+    const float* base = o.gauss + (size_t)y * o.pitch;
+    float g[6], gh[6];
+#pragma unroll
+    for (int l = 0; l < 6; l++) g[l] = __ldg(base + ls * l + xc);
+#pragma unroll
+    for (int l = 0; l < 6; l++) gh[l] = halo_lane ? __ldg(base + ls * l + xh) : 0.f;
+#pragma unroll
+    for (int l = 0; l < 5; l++) {
+        const float d = __fsub_rn(g[l + 1], g[l]);
+        const float dh = __fsub_rn(gh[l + 1], gh[l]);
+        float left = __shfl_up_sync(0xffffffffu, d, 1);
+        float right = __shfl_down_sync(0xffffffffu, d, 1);
+        if (lane == 0) left = dh;
+        if (lane == 31) right = dh;
+        r.c[l] = d;
+        r.mx[l] = fmaxf(fmaxf(left, d), right);
+        r.mn[l] = fminf(fminf(left, d), right);
+    }
+}
+
+__global__ void __launch_bounds__(kDetThreads)
+detect_kernel(const __grid_constant__ FrameParams fp) {
+    const int lane = threadIdx.x & 31;
+    const int task = blockIdx.x * (kDetThreads / 32) + (threadIdx.x >> 5);
+    if (task >= fp.det_tasks) return;
+    int oi = 0;
+    while (oi + 1 < fp.nOct && task >= fp.oct[oi + 1].det_task0) oi++;
+    const OctParams& o = fp.oct[oi];
+    const int t = task - o.det_task0;
+    const int cs = t % o.det_cols, rs = t / o.det_cols;
+    const int x = cs * 32 + lane;
+    const int xc = min(x, o.w - 1);
+    const int xh = lane == 0 ? max(cs * 32 - 1, 0) : min(cs * 32 + 32, o.w - 1);
+    const bool halo_lane = (lane == 0) || (lane == 31);
+    const int ys = kBorder + rs * kDetRows;
+    const int ye = min(o.h - kBorder, ys + kDetRows);
+    const bool x_ok = x >= kBorder && x < o.w - kBorder;
+    const float thr = fp.extrema_thr;
+
+    Row5 ra, rb, rc;  // rows y-1, y, y+1
+    load_row(o, ys - 1, xc, xh, halo_lane, lane, ra);
+    load_row(o, ys, xc, xh, halo_lane, lane, rb);
+    for (int y = ys; y < ye; y++) {
+        load_row(o, y + 1, xc, xh, halo_lane, lane, rc);
+        float vmx[5], vmn[5];
+#pragma unroll
+        for (int l = 0; l < 5; l++) {
+            vmx[l] = fmaxf(fmaxf(ra.mx[l], rb.mx[l]), rc.mx[l]);
+            vmn[l] = fminf(fminf(ra.mn[l], rb.mn[l]), rc.mn[l]);
+        }
+#pragma unroll
+        for (int s = 0; s < kScales; s++) {
+            const float v = rb.c[s + 1];
+            const float m3 = fmaxf(fmaxf(vmx[s], vmx[s + 1]), vmx[s + 2]);
+            const float n3 = fminf(fminf(vmn[s], vmn[s + 1]), vmn[s + 2]);
+            // MatOps.cu:122-143: |v| > thr, and v >= all 27 (v > 0) or v <= all 27 (v < 0).
+            const bool ext = x_ok && (fabsf(v) > thr) && ((v > 0.f) ? (v >= m3) : ((v < 0.f) && (v <= n3)));
+            const unsigned bits = __ballot_sync(0xffffffffu, ext);
+            if (lane == 0) {
+                const int row = s * o.h + y;
+                o.mask[(size_t)row * o.words + cs] = bits;
+                if (bits) atomicAdd(o.rowcount + row, __popc(bits));
+            }
+        }
+        ra = rb;
+        rb = rc;
+    }
+}
+
+// One CTA per octave: exclusive scan of the (scale,row) counts.
+__global__ void __launch_bounds__(1024)
+scan_rows_kernel(const __grid_constant__ FrameParams fp) {
+    const OctParams& o = fp.oct[blockIdx.x];
+    const int n = kScales * o.h;
+    __shared__ int warp_sums[32];
+    __shared__ int carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int v = i < n ? o.rowcount[i] : 0;
+        int incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int u = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += u;
+        }
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int ws = warp_sums[lane];
+            int wi = ws;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int u = __shfl_up_sync(0xffffffffu, wi, d);
+                if (lane >= d) wi += u;
+            }
+            warp_sums[lane] = wi - ws;  // exclusive
+        }
+        __syncthreads();
+        const int c = carry;
+        if (i < n) o.rowoff[i] = c + warp_sums[warp] + incl - v;
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = c + warp_sums[31] + incl;
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        o.counts[0] = carry;                 // P
+        o.counts[3] = min(carry, o.cap);     // candidates the refinement looks at
+    }
+}
+
+// Warp per (octave, scale, row): append the row's extrema in x order.
+__global__ void __launch_bounds__(256)
+scatter_kernel(const __grid_constant__ FrameParams fp) {
+    const int lane = threadIdx.x & 31;
+    const int gw = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (gw >= fp.rows_total) return;
+    int oi = 0;
+    while (oi + 1 < fp.nOct && gw >= fp.oct[oi + 1].row0) oi++;
+    const OctParams& o = fp.oct[oi];
+    const int row = gw - o.row0;
+    if (o.rowcount[row] == 0) return;
+    const int s = row / o.h, y = row - s * o.h;
+    int base = o.rowoff[row];
+    const uint32_t* m = o.mask + (size_t)row * o.words;
+    for (int w0 = 0; w0 < o.words; w0 += 32) {
+        const int wi = w0 + lane;
+        uint32_t bits = wi < o.words ? m[wi] : 0u;
+        const int cnt = __popc(bits);
+        int incl = cnt;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int u = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += u;
+        }
+        int idx = base + incl - cnt;
+        while (bits) {
+            const int b = __ffs(bits) - 1;
+            bits &= bits - 1;
+            if (idx + 1 < o.cap) o.cand[idx] = make_float3((float)(wi * 32 + b), (float)y, (float)(s + 1));
+            idx++;
+        }
+        base += __shfl_sync(0xffffffffu, incl, 31);
+    }
+}
+
+// ---------------------------------------------------------------- refinement
+struct DogView {
+    const float* g;
+    int pitch;
+    size_t ls;
+    __device__ __forceinline__ float operator()(int l, int r, int c) const {
+        const float* p = g + ls * l + (size_t)r * pitch + c;
+        return __fsub_rn(__ldg(p + ls), __ldg(p));
+    }
+};
+
+// solve_3x3_system (SiftOps.cu:6-61): partial pivoting; every `x -= t*y` is one FFMA, divisions
+// are IEEE (the reference is built without fast-math).
+__device__ __forceinline__ void solve3(const float* A, const float* b, float* x) {
+    float a[3][3], bb[3], t;
+#pragma unroll
+    for (int i = 0; i < 3; i++) {
+        bb[i] = b[i];
+#pragma unroll
+        for (int j = 0; j < 3; j++) a[i][j] = A[i * 3 + j];
+    }
+#pragma unroll
+    for (int k = 0; k < 2; k++) {
+        int mi = k;
+        float mv = fabsf(a[k][k]);
+#pragma unroll
+        for (int i = k + 1; i < 3; i++)
+            if (fabsf(a[i][k]) > mv) { mv = fabsf(a[i][k]); mi = i; }
+        if (mi != k) {
+#pragma unroll
+            for (int i = k + 1; i < 3; i++)
+                if (i == mi) {
+#pragma unroll
+                    for (int j = k; j < 3; j++) { t = a[k][j]; a[k][j] = a[i][j]; a[i][j] = t; }
+                    t = bb[k]; bb[k] = bb[i]; bb[i] = t;
+                }
+        }
+#pragma unroll
+        for (int i = k + 1; i < 3; i++) {
+            t = __fdiv_rn(a[i][k], a[k][k]);
+            bb[i] = __fmaf_rn(-t, bb[k], bb[i]);
+#pragma unroll
+            for (int j = k; j < 3; j++) a[i][j] = __fmaf_rn(-t, a[k][j], a[i][j]);
+        }
+    }
+    x[2] = __fdiv_rn(bb[2], a[2][2]);
+    x[1] = __fdiv_rn(__fmaf_rn(-a[1][2], x[2], bb[1]), a[1][1]);
+    x[0] = __fdiv_rn(__fmaf_rn(-a[0][2], x[2], __fmaf_rn(-a[0][1], x[1], bb[0])), a[0][0]);
+}
+
+__global__ void __launch_bounds__(128)
+refine_kernel(const __grid_constant__ FrameParams fp) {
+    const int oi = blockIdx.y;
+    const OctParams& o = fp.oct[oi];
+    const int idx = blockIdx.x * 128 + threadIdx.x;
+    if (idx >= o.counts[3]) return;
+    const float3 kp = o.cand[idx];
+    int c = (int)kp.x, r = (int)kp.y, l = (int)kp.z;
+    const float sx = (float)o.w, sy = (float)o.h;
+    constexpr float img_scale = 1.f / 255.f;
+    constexpr float deriv_scale = img_scale * 0.5f, second = img_scale, cross = img_scale * 0.25f;
+    const DogView D{o.gauss, o.pitch, (size_t)o.pitch * o.h};
+    float A[9], b[3], x[3] = {0.f, 0.f, 0.f};
+    int it = 0;
+    int accept = 1;
+    // A stale slot (only reachable when an octave overflows its cap, appendix A.1) can hold
+    // anything; the reference would read outside its DoG block there. Reject instead.
+    if (l < 1 || l > 3 || r < 1 || r >= o.h - 1 || c < 1 || c >= o.w - 1) { accept = 0; it = 5; }
+    for (; it < 5; it++) {
+        const float c_c = D(l, r, c);
+        const float c_xp = D(l, r, c + 1), c_xm = D(l, r, c - 1);
+        const float c_yp = D(l, r + 1, c), c_ym = D(l, r - 1, c);
+        const float n_c = D(l + 1, r, c), p_c = D(l - 1, r, c);
+        b[0] = __fmul_rn(deriv_scale, __fsub_rn(c_xp, c_xm));
+        b[1] = __fmul_rn(deriv_scale, __fsub_rn(c_yp, c_ym));
+        b[2] = __fmul_rn(deriv_scale, __fsub_rn(n_c, p_c));
+        const float v2 = __fadd_rn(c_c, c_c);
+        A[0] = __fmul_rn(__fsub_rn(__fadd_rn(c_xp, c_xm), v2), second);
+        A[4] = __fmul_rn(__fsub_rn(__fadd_rn(c_yp, c_ym), v2), second);
+        A[8] = __fmul_rn(__fsub_rn(__fadd_rn(n_c, p_c), v2), second);
+        const float dxy = __fmul_rn(__fadd_rn(__fsub_rn(__fsub_rn(D(l, r + 1, c + 1), D(l, r + 1, c - 1)), D(l, r - 1, c + 1)), D(l, r - 1, c - 1)), cross);
+        const float dxs = __fmul_rn(__fadd_rn(__fsub_rn(__fsub_rn(D(l + 1, r, c + 1), D(l + 1, r, c - 1)), D(l - 1, r, c + 1)), D(l - 1, r, c - 1)), cross);
+        const float dys = __fmul_rn(__fadd_rn(__fsub_rn(__fsub_rn(D(l + 1, r + 1, c), D(l + 1, r - 1, c)), D(l - 1, r + 1, c)), D(l - 1, r - 1, c)), cross);
+        A[1] = A[3] = dxy;
+        A[2] = A[6] = dxs;
+        A[5] = A[7] = dys;
+        solve3(A, b, x);
+        if (fabsf(x[0]) < 0.5f && fabsf(x[1]) < 0.5f && fabsf(x[2]) < 0.5f) break;
+        if (fabsf(x[0]) > sx || fabsf(x[1]) > sy || fabsf(x[2]) > 100.f) { accept = 0; break; }
+        l = (int)__fsub_rn((float)l, roundf(x[2]));
+        r = (int)__fsub_rn((float)r, roundf(x[1]));
+        c = (int)__fsub_rn((float)c, roundf(x[0]));
+        if (l < 1 || l > 3) { accept = 0; break; }
+        if ((float)r < 5.f || (float)r >= sy - 5.f || (float)c < 5.f || (float)c >= sx - 5.f) { accept = 0; break; }
+    }
+    if (it >= 5) accept = 0;
+    if (accept) {
+        const float c_c = D(l, r, c);
+        const float c_xp = D(l, r, c + 1), c_xm = D(l, r, c - 1);
+        const float c_yp = D(l, r + 1, c), c_ym = D(l, r - 1, c);
+        const float d0 = __fmul_rn(deriv_scale, __fsub_rn(c_xp, c_xm));
+        const float d1 = __fmul_rn(deriv_scale, __fsub_rn(c_yp, c_ym));
+        const float d2 = __fmul_rn(deriv_scale, __fsub_rn(D(l + 1, r, c), D(l - 1, r, c)));
+        // reference SASS: t = fma(d2,x2, fma(d0,x0, d1*x1)); contrast = fma(v, 1/255, t*-0.5)
+        const float t = __fmaf_rn(d2, x[2], __fmaf_rn(d0, x[0], __fmul_rn(d1, x[1])));
+        const float contrast = __fmaf_rn(c_c, img_scale, __fmul_rn(t, -0.5f));
+        if (__fmul_rn(fabsf(contrast), (float)kScales) < fp.contrast_thr) accept = 0;
+        if (accept) {
+            const float v2 = __fadd_rn(c_c, c_c);
+            const float dxx = __fmul_rn(__fsub_rn(__fadd_rn(c_xp, c_xm), v2), second);
+            const float dyy = __fmul_rn(__fsub_rn(__fadd_rn(c_yp, c_ym), v2), second);
+            const float dxy = __fmul_rn(__fadd_rn(__fsub_rn(__fsub_rn(D(l, r + 1, c + 1), D(l, r + 1, c - 1)), D(l, r - 1, c + 1)), D(l, r - 1, c - 1)), cross);
+            const float tr = __fadd_rn(dxx, dyy);
+            const float det = __fmaf_rn(dxx, dyy, -__fmul_rn(dxy, dxy));
+            const float e = fp.edge_thr;
+            const float e1 = __fadd_rn(e, 1.f);
+            if (det <= 0.f || __fmul_rn(__fmul_rn(tr, tr), e) >= __fmul_rn(__fmul_rn(e1, e1), det)) accept = 0;
+        }
+        if (accept) {
+            // SiftOps.cu:201-207 (quirk Q10: integer position, sub-pixel offset not added)
+            o.cand[idx] = make_float3((float)(c * (1 << oi)), (float)(r * (1 << oi)), (float)l);
+            float4 f = o.candF[idx];
+            f.x = (float)(oi + (l << 8) + ((int)__fmul_rn(roundf(__fadd_rn(x[2], 0.5f)), 255.f) << 16));
+            const float pw = powf(2.f, __fdiv_rn(__fsub_rn((float)l, x[2]), (float)kScales));
+            const float sp = __fmul_rn(__fmul_rn(fp.sigma, pw), (float)(1 << oi));
+            f.y = __fadd_rn(sp, sp);
+            f.z = fabsf(contrast);
+            o.candF[idx] = f;
+        }
+    }
+    o.flag[idx] = accept;
+}
+
+// One CTA per octave: stable compaction of accepted candidates into coll/collF. The element
+// whose prefix equals the total is not written (quirk Q5, SiftOps.cu:228).
+__global__ void __launch_bounds__(1024)
+compact_refined_kernel(const __grid_constant__ FrameParams fp) {
+    const OctParams& o = fp.oct[blockIdx.x];
+    const int n = o.counts[3];
+    __shared__ int warp_sums[32];
+    __shared__ int s_total, carry;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    int local = 0;
+    for (int i = threadIdx.x; i < n; i += 1024) local += o.flag[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) local += __shfl_xor_sync(0xffffffffu, local, d);
+    if (lane == 0) warp_sums[warp] = local;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        int tsum = 0;
+        for (int i = 0; i < 32; i++) tsum += warp_sums[i];
+        s_total = tsum;
+        carry = 0;
+        o.counts[1] = tsum;  // M
+    }
+    __syncthreads();
+    const int total = s_total;
+    for (int base = 0; base < n; base += 1024) {
+        const int i = base + threadIdx.x;
+        const int v = i < n ? o.flag[i] : 0;
+        int incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            int u = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += u;
+        }
+        __syncthreads();
+        if (lane == 31) warp_sums[warp] = incl;
+        __syncthreads();
+        if (warp == 0) {
+            int ws = warp_sums[lane];
+            int wi = ws;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                int u = __shfl_up_sync(0xffffffffu, wi, d);
+                if (lane >= d) wi += u;
+            }
+            warp_sums[lane] = wi - ws;
+        }
+        __syncthreads();
+        const int c = carry;
+        const int p = c + warp_sums[warp] + incl;  // inclusive prefix
+        if (v && p < total) {
+            o.coll[p - 1] = o.cand[i];
+            o.collF[p - 1] = o.candF[i];
+        }
+        __syncthreads();
+        if (threadIdx.x == 1023) carry = p;
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+void launch_detect(const FrameParams& fp, cudaStream_t s) {
+    const int warps = kDetThreads / 32;
+    if (fp.det_tasks > 0) detect_kernel<<<(fp.det_tasks + warps - 1) / warps, kDetThreads, 0, s>>>(fp);
+}
+void launch_scan_rows(const FrameParams& fp, cudaStream_t s) { scan_rows_kernel<<<fp.nOct, 1024, 0, s>>>(fp); }
+void launch_scatter(const FrameParams& fp, cudaStream_t s) {
+    scatter_kernel<<<(fp.rows_total + 7) / 8, 256, 0, s>>>(fp);
+}
+void launch_refine(const FrameParams& fp, cudaStream_t s) {
+    int maxcap = 1;
+    for (int i = 0; i < fp.nOct; i++) maxcap = fp.oct[i].cap > maxcap ? fp.oct[i].cap : maxcap;
+    dim3 grid((maxcap + 127) / 128, fp.nOct);
+    refine_kernel<<<grid, 128, 0, s>>>(fp);
+}
+void launch_compact_refined(const FrameParams& fp, cudaStream_t s) { compact_refined_kernel<<<fp.nOct, 1024, 0, s>>>(fp); }
+
+}  // namespace b200sift

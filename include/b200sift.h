@@ -1,0 +1,130 @@
+/*
+ * b200sift -- C ABI of the B200-native SIFT engine (sm_100a).
+ *
+ * This is the drop-in boundary for the hot path of Cryptum169/another-cuda-sift. Every entry
+ * point names the reference interface it replaces (paths relative to the reference repo).
+ * Plain pointers and sizes only: no C++ / thrust / torch types cross this line. The C++ mirror
+ * of the reference API (sift_cuda::Detector, sift_cuda::matchBruteForce) in
+ * include/sift_cuda/ is a header-only wrapper over these functions.
+ *
+ * Conventions: every function returns 0 on success or a negative B200SIFT_E* code;
+ * b200sift_last_error() gives the message of the last failure on the calling thread.
+ * A handle belongs to the CUDA device that was current when it was created and is not
+ * thread-safe (same as the reference, Detector.hh:24). There is no CPU fallback: without a
+ * CUDA device every call fails with B200SIFT_ECUDA.
+ */
+#ifndef B200SIFT_H
+#define B200SIFT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define B200SIFT_API __attribute__((visibility("default")))
+#else
+#define B200SIFT_API
+#endif
+
+#define B200SIFT_OK 0
+#define B200SIFT_EINVAL (-1) /* bad argument / unsupported configuration */
+#define B200SIFT_ECUDA (-2)  /* CUDA runtime error, see b200sift_last_error() */
+#define B200SIFT_ESTATE (-3) /* call order violated (e.g. results before any frame) */
+
+/* Mirrors `struct CudaSiftConfig` (sift_cuda/types/CudaSiftConfig.hh:3-14), same field order,
+ * names (including the reference's spellings) and defaults. `upscale` must be 0: the reference
+ * documents it as broken (CudaSiftConfig.hh:12) and this engine rejects it. */
+typedef struct b200sift_config {
+    int col_width;
+    int row_width;
+    int numFeatures;           /* 5000 */
+    int numOctaveLayers;       /* 3 (only value supported, as in the reference's kernels) */
+    double contrastThreshould; /* 0.04 */
+    double edgeThreshould;     /* 10 */
+    double sigma;              /* 1.6 */
+    int upscale;               /* 0 */
+} b200sift_config;
+
+typedef struct b200sift_detector b200sift_detector; /* opaque handle */
+
+B200SIFT_API void b200sift_default_config(b200sift_config* cfg);
+B200SIFT_API const char* b200sift_last_error(void);
+B200SIFT_API const char* b200sift_version(void);
+
+/* Detector::Detector + Detector::gpuWarmUpAndAllocate (interface/Detector.hh:26-31,
+ * interface/Detector.cu:17-131): allocates every device / pinned buffer once and captures the
+ * per-frame CUDA graph. Fails with EINVAL when col_width or row_width is 0 (Detector.cu:22-25). */
+B200SIFT_API int b200sift_create(const b200sift_config* cfg, b200sift_detector** out);
+B200SIFT_API int b200sift_destroy(b200sift_detector* det);
+
+/* Geometry the reference derives in Detector.hh:27 and Detector.cu:83,109. */
+B200SIFT_API int b200sift_num_octaves(const b200sift_detector* det);
+/* dims[0..3] = width, height, row pitch in floats, keypoint slot capacity of octave `o`. */
+B200SIFT_API int b200sift_octave_info(const b200sift_detector* det, int o, int* dims);
+
+/* Detector::detectAndCompute(const Imagef&) (interface/Detector.cu:133-233), host image:
+ * row-major float32, rows x cols, values 0..255 (HostImage.hh:36). The H2D copy is enqueued on
+ * the detector's stream from `img` (pinned memory makes it asynchronous) followed by the frame
+ * graph. `_host` blocks until the frame is done and returns the keypoint count in *total
+ * (Detector::total_size); `_host_async` only enqueues (img must stay valid until
+ * b200sift_sync). */
+B200SIFT_API int b200sift_detect_host(b200sift_detector* det, const float* img, int rows, int cols, int* total);
+B200SIFT_API int b200sift_detect_host_async(b200sift_detector* det, const float* img, int rows, int cols);
+/* Same frame, input already resident in HBM (`pitch_bytes` between rows); copied device to
+ * device into the detector's input image on the detector's stream. */
+B200SIFT_API int b200sift_detect_device_async(b200sift_detector* det, const float* d_img, size_t pitch_bytes);
+/* 8-bit input: converted to float on the device, 4x less PCIe traffic. */
+B200SIFT_API int b200sift_detect_host_u8_async(b200sift_detector* det, const uint8_t* img, int rows, int cols);
+/* Waits for the frames enqueued so far; *total = keypoints of the last frame. */
+B200SIFT_API int b200sift_sync(b200sift_detector* det, int* total);
+/* The detector's CUDA stream (cudaStream_t) so callers can order their own work after a frame. */
+B200SIFT_API void* b200sift_stream(b200sift_detector* det);
+
+/* Public result members of Detector (interface/Detector.hh:54-62), borrowed device pointers
+ * owned by the handle and valid until the next detect call: kpts = float3[numFeatures]
+ * (x, y, layer), feats = float4[numFeatures] (packed octave, size, |contrast|, angle deg),
+ * desc / prev_desc = half[numFeatures*128]. Any out pointer may be NULL. */
+B200SIFT_API int b200sift_results(b200sift_detector* det, const float** kpts, const float** feats,
+                     const uint16_t** desc, const uint16_t** prev_desc, int* total);
+/* Detector::copyToHost(bool descriptor) (interface/Detector.cu:606-634): first `total` entries
+ * into caller buffers (any may be NULL); blocks until done. */
+B200SIFT_API int b200sift_copy_to_host(b200sift_detector* det, float* kpts3, float* feats4, uint16_t* desc, int with_desc);
+
+/* Test / profiling access to intermediate state (the reference exposes the same through
+ * Detector::setDataGen dumps, Detector.cu:145-229). which: 0 Gaussian stack (6 layers).
+ * Dense copy (no pitch) into host memory: layers*h*w floats. */
+B200SIFT_API int b200sift_debug_get_stack(b200sift_detector* det, int o, int which, float* out);
+/* which: 0 cand float3, 1 candF float4, 2 coll float3, 3 collF float4 (cap entries each). */
+B200SIFT_API int b200sift_debug_get_kpt_buffer(b200sift_detector* det, int o, int which, void* out, int max_elems);
+/* counts[0..2] = P raw extrema, M refined, T oriented (after the last frame). */
+B200SIFT_API int b200sift_debug_get_counts(b200sift_detector* det, int o, int* counts);
+/* Host-generated Gaussian taps: which = -1 initial blur, 0..5 layer taps. Returns tap count. */
+B200SIFT_API int b200sift_debug_get_taps(b200sift_detector* det, int which, float* out, int max_elems);
+/* Runs the frame pipeline only up to and including `last_stage` (1 pyramid, 3 extrema,
+ * 4 refine, 5 orientation, 7 all) eagerly, for stage-level parity tests. Blocks. */
+B200SIFT_API int b200sift_debug_run_stages(b200sift_detector* det, const float* img, int rows, int cols, int last_stage);
+/* Number of kernel launches (graph kernel nodes) one frame issues. */
+B200SIFT_API int b200sift_launches_per_frame(const b200sift_detector* det);
+/* Average device time (ms) of one frame with the input resident in HBM: `iters` graph launches
+ * bracketed by CUDA events on the detector's stream after `warmup` launches. */
+B200SIFT_API int b200sift_time_frames(b200sift_detector* det, int warmup, int iters, float* ms_per_frame);
+
+/* sift_cuda::matchBruteForce (sift_func/Match.cuh:9-14, Match.cu:8-33): for each of the nq query
+ * descriptors (half[nq*128]) the index of its nearest train descriptor (half[nt*128]) under the
+ * reference's half-precision L2 recipe, or -1 if the 0.8 ratio test fails. Device pointers;
+ * out_idx = int[nq] on the device. `stream` is a cudaStream_t (NULL = legacy default stream).
+ * Asynchronous; scratch memory is cached per device and grown on demand. */
+B200SIFT_API int b200sift_match_device(const uint16_t* d_query, int nq, const uint16_t* d_train, int nt,
+                          int* d_out_idx, void* stream);
+/* Host-buffer convenience (copies in, matches, copies out, blocks). */
+B200SIFT_API int b200sift_match_host(const uint16_t* query, int nq, const uint16_t* train, int nt, int* out_idx);
+/* Kernel launches issued by one b200sift_match_device call for this problem size. */
+B200SIFT_API int b200sift_match_launches(int nq, int nt);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SIFT_H */
