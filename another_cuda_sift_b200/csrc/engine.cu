@@ -93,6 +93,27 @@ struct b200sift_detector {
 
 namespace {
 
+// Optional per-launch event marks for b200sift_profile_frame: the time between two consecutive marks is
+// charged to the kernel class of the later one.
+struct Profiler {
+    std::vector<cudaEvent_t> ev;
+    std::vector<int> cls;
+    size_t used = 0;
+    cudaStream_t s = nullptr;
+    void mark(int c) {
+        if (used == ev.size()) {
+            cudaEvent_t e;
+            cudaEventCreate(&e);
+            ev.push_back(e);
+            cls.push_back(c);
+        }
+        cls[used] = c;
+        cudaEventRecord(ev[used++], s);
+    }
+    ~Profiler() { for (auto e : ev) cudaEventDestroy(e); }
+};
+#define MARK(c) do { if (prof) prof->mark(c); } while (0)
+
 template <typename T>
 int dev_alloc(b200sift_detector* d, T** p, size_t count) {
     void* q = nullptr;
@@ -106,12 +127,14 @@ int dev_alloc(b200sift_detector* d, T** p, size_t count) {
 
 // The frame pipeline, stages numbered as in Detector::detectAndCompute (Detector.cu:133-233):
 // 0 prev-descriptor copy, 1 pyramid, 3 extrema, 4 refinement, 5 orientation, 6/7 descriptor+gather.
-int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* launches) {
+int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* launches, Profiler* prof = nullptr) {
     FrameParams& fp = d->fp;
     int n = 0;
+    MARK(B200SIFT_K_COPY);
     CU(cudaMemcpyAsync(d->d_prev_desc, fp.out_desc, (size_t)fp.numFeatures * 128 * sizeof(__half),
                        cudaMemcpyDeviceToDevice, s));
     CU(cudaMemsetAsync(d->d_rowcount_all, 0, d->rowcount_bytes, s));
+    MARK(B200SIFT_K_COPY);
     for (int o = 0; o < d->nOct; o++) {
         OctParams& oc = fp.oct[o];
         const size_t ls = (size_t)oc.pitch * oc.h;
@@ -119,32 +142,42 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
             float* dst = oc.gauss + ls * l;
             if (o == 0 && l == 0) {
                 launch_blur(d->d_input, d->in_pitch, dst, oc.pitch, oc.w, oc.h, d->init_taps, s);
+                MARK(B200SIFT_K_BLUR);
             } else if (l == 0) {
                 const OctParams& pv = fp.oct[o - 1];
                 const float* src = pv.gauss + (size_t)pv.pitch * pv.h * kScales;
                 launch_downsample(src, pv.pitch, pv.w, pv.h, dst, oc.pitch, oc.w, oc.h, s);
+                MARK(B200SIFT_K_DOWNSAMPLE);
             } else {
                 launch_blur(oc.gauss + ls * (l - 1), oc.pitch, dst, oc.pitch, oc.w, oc.h, d->taps[l], s);
+                MARK(o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL);
             }
             n++;
         }
     }
     if (last_stage >= 3) {
-        if (fp.det_tasks > 0) { launch_detect(fp, s); n++; }
+        if (fp.det_tasks > 0) { launch_detect(fp, s); n++; MARK(B200SIFT_K_DETECT); }
         launch_scan_rows(fp, s); n++;
         launch_scatter(fp, s); n++;
+        MARK(B200SIFT_K_COMPACT);
     }
     if (last_stage >= 4) {
         launch_refine(fp, s); n++;
+        MARK(B200SIFT_K_REFINE);
         launch_compact_refined(fp, s); n++;
+        MARK(B200SIFT_K_COMPACT);
     }
     if (last_stage >= 5) {
         launch_orientation(fp, s); n++;
+        MARK(B200SIFT_K_ORIENT);
         launch_compact_oriented(fp, s); n++;
+        MARK(B200SIFT_K_COMPACT);
     }
     if (last_stage >= 6) {
         launch_descriptor(fp, s); n++;
+        MARK(B200SIFT_K_DESCRIBE);
         CU(cudaMemcpyAsync(d->h_total, fp.total, sizeof(int), cudaMemcpyDeviceToHost, s));
+        MARK(B200SIFT_K_COPY);
     }
     CU(cudaGetLastError());
     if (launches) *launches = n;
@@ -462,6 +495,33 @@ int b200sift_time_frames(b200sift_detector* d, int warmup, int iters, float* ms_
     cudaEventDestroy(e1);
     d->have_frame = true;
     *ms_per_frame = ms / (float)iters;
+    return 0;
+}
+
+int b200sift_profile_frame(b200sift_detector* d, int warmup, int iters, float* ms_per_class, int* launches_per_class) {
+    if (!d || !ms_per_class || iters <= 0) return fail(B200SIFT_EINVAL, "bad argument");
+    Profiler prof;
+    prof.s = d->stream;
+    std::vector<double> acc(B200SIFT_K_COUNT, 0.0);
+    std::vector<int> cnt(B200SIFT_K_COUNT, 0);
+    for (int it = 0; it < warmup + iters; it++) {
+        prof.used = 0;
+        int rc = enqueue_frame(d, d->stream, 7, nullptr, &prof);
+        if (rc) return rc;
+        CU(cudaStreamSynchronize(d->stream));
+        if (it < warmup) continue;
+        for (size_t i = 1; i < prof.used; i++) {
+            float ms = 0.f;
+            CU(cudaEventElapsedTime(&ms, prof.ev[i - 1], prof.ev[i]));
+            acc[prof.cls[i]] += ms;
+            if (it == warmup) cnt[prof.cls[i]]++;
+        }
+    }
+    d->have_frame = true;
+    for (int c = 0; c < B200SIFT_K_COUNT; c++) {
+        ms_per_class[c] = (float)(acc[c] / iters);
+        if (launches_per_class) launches_per_class[c] = cnt[c];
+    }
     return 0;
 }
 

@@ -175,6 +175,15 @@ class Detector:
         check(self.lib.b200sift_time_frames(self._handle(), warmup, iters, C.byref(ms)))
         return float(ms.value)
 
+    KERNEL_CLASSES = ("copy", "blur_oct0", "blur_small", "downsample", "detect", "compact", "refine", "orient", "describe")
+
+    def profile_frame(self, warmup: int, iters: int) -> dict:
+        """ms per kernel class of one frame (CUDA events after every launch, eager frame)."""
+        n = len(self.KERNEL_CLASSES)
+        ms, cnt = (C.c_float * n)(), (C.c_int * n)()
+        check(self.lib.b200sift_profile_frame(self._handle(), warmup, iters, ms, cnt))
+        return {k: dict(ms=float(ms[i]), launches=int(cnt[i])) for i, k in enumerate(self.KERNEL_CLASSES)}
+
     def debug_run_stages(self, image: np.ndarray, last_stage: int) -> None:
         image = np.ascontiguousarray(image, dtype=np.float32)
         check(self.lib.b200sift_debug_run_stages(self._handle(), image.ctypes.data, image.shape[0], image.shape[1], last_stage))

@@ -112,6 +112,23 @@ B200SIFT_API int b200sift_launches_per_frame(const b200sift_detector* det);
  * bracketed by CUDA events on the detector's stream after `warmup` launches. */
 B200SIFT_API int b200sift_time_frames(b200sift_detector* det, int warmup, int iters, float* ms_per_frame);
 
+/* Per-kernel-class device time of one frame (ms, averaged over `iters` eager frames with a CUDA event
+ * after every launch on the detector's stream): ms_per_class[B200SIFT_K_COUNT]; launches_per_class (may
+ * be NULL) = launches (event intervals) charged to each class per frame. bench.py's roofline figures
+ * come from here. */
+#define B200SIFT_K_COPY 0       /* prev-descriptor copy, count memset, count read-back */
+#define B200SIFT_K_BLUR 1       /* fused V+H Gaussian blur, octave 0 (the full-resolution layers) */
+#define B200SIFT_K_BLUR_SMALL 2 /* the same kernel on octaves >= 1 */
+#define B200SIFT_K_DOWNSAMPLE 3
+#define B200SIFT_K_DETECT 4     /* DoG + 3x3x3 extrema bitmask */
+#define B200SIFT_K_COMPACT 5    /* row scan / scatter / refined + oriented compaction */
+#define B200SIFT_K_REFINE 6
+#define B200SIFT_K_ORIENT 7
+#define B200SIFT_K_DESCRIBE 8
+#define B200SIFT_K_COUNT 9
+B200SIFT_API int b200sift_profile_frame(b200sift_detector* det, int warmup, int iters, float* ms_per_class,
+                           int* launches_per_class);
+
 /* sift_cuda::matchBruteForce (sift_func/Match.cuh:9-14, Match.cu:8-33): for each of the nq query
  * descriptors (half[nq*128]) the index of its nearest train descriptor (half[nt*128]) under the
  * reference's half-precision L2 recipe, or -1 if the 0.8 ratio test fails. Device pointers;

@@ -39,7 +39,9 @@ namespace {
 struct RefHandle {
     std::unique_ptr<sift_cuda::Detector> det;
     Imagef img;
+    std::vector<Imagef> frames;  // pre-built host images for the bench loop (the caller's Imagef objects)
     int rows = 0, cols = 0;
+    int prev_size = 0;
 };
 
 template <typename T>
@@ -193,6 +195,64 @@ float ref_time_e2e(void* p, int warmup, int iters, int copy_to_host) {
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     return total / float(iters);
+}
+
+// --- bench helpers: the loop of tool/extract_and_match_example.cc:68-101 through the public API only.
+int ref_add_frame(void* p, const float* img) {
+    auto* h = static_cast<RefHandle*>(p);
+    Imagef f;
+    f.m_image_size = Size{float(h->rows), float(h->cols)};
+    f.m_data = std::make_shared<std::vector<float>>(img, img + size_t(h->rows) * h->cols);
+    h->frames.push_back(f);
+    return int(h->frames.size()) - 1;
+}
+// detectAndCompute(host image) [+ copyToHost(descriptor)] [+ matchBruteForce(prev, cur)]; returns total_size.
+// n_matched (may be NULL) receives the number of accepted matches (forces use of the returned vector).
+int ref_process_frame(void* p, int idx, int copy_desc, int do_match, int* n_matched) {
+    auto* h = static_cast<RefHandle*>(p);
+    auto& d = *h->det;
+    d.detectAndCompute(h->frames.at(idx));
+    d.copyToHost(copy_desc != 0);
+    cudaDeviceSynchronize();
+    const int cur = d.total_size;
+    int acc = 0;
+    if (do_match && h->prev_size > 0 && cur > 0) {
+        std::vector<int> m = sift_cuda::matchBruteForce(d.prev_descriptor, h->prev_size, d.device_descriptor, cur);
+        for (int v : m) acc += v >= 0;
+    }
+    if (n_matched) *n_matched = acc;
+    h->prev_size = cur;
+    return cur;
+}
+// Device-resident variant: the frame is already in original_image; stages as in ref_time_device_resident.
+int ref_process_resident(void* p, int do_match, int* n_matched) {
+    auto* h = static_cast<RefHandle*>(p);
+    auto& d = *h->det;
+    cudaMemcpyAsync(thrust::raw_pointer_cast(d.prev_descriptor.data()), thrust::raw_pointer_cast(d.device_descriptor.data()),
+                    d.prev_descriptor.size() * sizeof(half), cudaMemcpyDeviceToDevice);
+    d.createInitialImage();
+    d.getGaussianPyramid();
+    d.getDogPyramid();
+    d.getKeyPoints();
+    d.adjustKpts();
+    d.adjustOrientationAndCleanup();
+    d.extractDescriptor();
+    d.collectAcrossOctaves();
+    cudaDeviceSynchronize();
+    const int cur = d.total_size;
+    int acc = 0;
+    if (do_match && h->prev_size > 0 && cur > 0) {
+        std::vector<int> m = sift_cuda::matchBruteForce(d.prev_descriptor, h->prev_size, d.device_descriptor, cur);
+        for (int v : m) acc += v >= 0;
+    }
+    if (n_matched) *n_matched = acc;
+    h->prev_size = cur;
+    return cur;
+}
+void ref_upload_frame(void* p, int idx) {
+    auto* h = static_cast<RefHandle*>(p);
+    h->det->m_data.original_image = h->frames.at(idx);
+    cudaDeviceSynchronize();
 }
 
 int ref_total_size(void* p) { return static_cast<RefHandle*>(p)->det->total_size; }

@@ -1,0 +1,201 @@
+"""Parity tests proper: the CUDA engine, called through the C ABI (ctypes), against
+(1) golden vectors captured from the unmodified reference on a B200,
+(2) the CPU oracle on the same seeded inputs,
+(3) the live reference build (oracle/_ref/libref_sift.so) when it travelled to the box."""
+import numpy as np
+import pytest
+
+from conftest import golden
+from util import check_results
+
+pytestmark = pytest.mark.gpu
+
+# Bars (BASELINE.json north_star): extrema and refined positions bit-exact; >= 99.5% keypoint-set agreement;
+# size 1e-3 relative; descriptors 1e-3 L2 -- asserted for DESC_FRAC of the keypoints because the reference
+# itself is not run-to-run reproducible there (float shared-memory atomics; envelope_752x480.npz).
+DESC_TOL, DESC_FRAC = 1e-3, 0.98
+
+
+def _det(cols, rows, nf=5000):
+    from another_cuda_sift_b200 import CudaSiftConfig, Detector
+
+    d = Detector(CudaSiftConfig(col_width=cols, row_width=rows, numFeatures=nf))
+    assert d.gpuWarmUpAndAllocate()
+    return d
+
+
+def _res(det):
+    det.copyToHost(True)
+    return dict(n=det.total_size, kpts=det.final_kpts, feats=det.final_features, desc=det.descriptors)
+
+
+def _img(g, fr):
+    return g[f"f{fr}_img_u8"].astype(np.float32)
+
+
+def test_taps_bit_exact_vs_golden():
+    g = golden("taps.npz")
+    det = _det(64, 64)
+    for i in range(-1, 6):
+        assert np.array_equal(det.debug_taps(i).view(np.uint32), g[f"taps{i}"].view(np.uint32)), i
+
+
+@pytest.mark.parametrize("name", ["frames_160x120.npz", "frames_203x151.npz", "frames_752x480.npz",
+                                  "frames_caps_752x480.npz", "frames_1920x1200.npz"])
+def test_frames_vs_golden(name):
+    g = golden(name)
+    cols, rows = int(g["cols"]), int(g["rows"])
+    det = _det(cols, rows, int(g["num_features"]))
+    assert det.n_octaves == int(g["n_octaves"])
+    assert np.array_equal(np.array([[x["w"], x["h"], x["pitch"], x["cap"]] for x in det.octaves]), g["octaves"])
+    for fr in range(int(g["nframes"])):
+        img = _img(g, fr)
+        det.debug_run_stages(img, 1)
+        for oi in range(det.n_octaves):
+            gs = det.debug_gauss(oi)
+            if f"f{fr}_gauss{oi}" in g:
+                assert np.array_equal(gs.view(np.uint32), g[f"f{fr}_gauss{oi}"].view(np.uint32)), (fr, oi)
+            assert np.array_equal(gs.astype(np.float64).sum(axis=(1, 2)), g[f"f{fr}_gauss_sum"][oi])
+            assert np.array_equal(np.bitwise_xor.reduce(gs.view(np.uint32).reshape(6, -1), axis=1), g[f"f{fr}_gauss_xor"][oi])
+        det.detectAndCompute(img)  # the graph path, full frame (keeps the Q5 slot history like the reference)
+        counts = g[f"f{fr}_counts"]
+        for oi in range(det.n_octaves):
+            c = det.debug_counts(oi)
+            assert (c["P"], c["M"]) == (counts[0][oi], counts[1][oi]), (fr, oi, c)
+        want = dict(n=int(g[f"f{fr}_total"]), kpts=g[f"f{fr}_kpts"], feats=g[f"f{fr}_feats"], desc=g[f"f{fr}_desc"])
+        info = check_results(_res(det), want, desc_tol=DESC_TOL, desc_frac=DESC_FRAC)
+        print(name, fr, info)
+
+
+def test_extrema_and_refinement_bit_exact_vs_golden():
+    g = golden("frames_752x480.npz")
+    det = _det(752, 480)
+    img = _img(g, 0)
+    det.debug_run_stages(img, 3)
+    for oi in range(det.n_octaves):
+        ext = g[f"f0_extrema{oi}"]
+        assert np.array_equal(det.debug_kpt_buffer(oi, "cand")[:len(ext)].astype(np.int16), ext), oi
+    det.debug_run_stages(img, 4)
+    for oi in range(det.n_octaves):
+        want, wantF = g[f"f0_refined{oi}"], g[f"f0_refinedF{oi}"]
+        n = len(want)
+        assert np.array_equal(det.debug_kpt_buffer(oi, "coll")[:n], want)
+        gotF = det.debug_kpt_buffer(oi, "collF")[:n, :3]
+        assert np.array_equal(gotF.view(np.uint32), wantF.view(np.uint32)), oi  # incl. powf: same libdevice
+    det.debug_run_stages(img, 5)
+    for oi in range(det.n_octaves):
+        want, wantF = g[f"f0_oriented{oi}"], g[f"f0_orientedF{oi}"]
+        got, gotF = det.debug_kpt_buffer(oi, "cand"), det.debug_kpt_buffer(oi, "candF")
+        n = len(want)
+        if det.debug_counts(oi)["T"] == int(g["f0_counts"][2][oi]):
+            same = np.all(got[:n] == want, axis=1) & np.all(gotF[:n] == wantF, axis=1)
+            assert same.mean() >= 0.99 if n else True
+
+
+@pytest.mark.parametrize("cols,rows", [(160, 120), (203, 151), (752, 480)])
+def test_stages_vs_cpu_oracle(cols, rows):
+    from another_cuda_sift_b200.synth import next_frame, synth_frame
+    from oracle.pyoracle import CpuOracle
+
+    det, cpu = _det(cols, rows), CpuOracle(cols, rows, 5000)
+    img = synth_frame(rows, cols, 7)
+    for fr in range(2):
+        if fr:
+            img = next_frame(img, 7 + fr)
+        cpu.detect(img)
+        det.debug_run_stages(img, 4)
+        for oi in range(det.n_octaves):
+            assert np.array_equal(det.debug_gauss(oi).view(np.uint32), cpu.stack(oi, "gauss").view(np.uint32)), (fr, oi)
+            c = cpu.counts(oi)
+            d = det.debug_counts(oi)
+            assert (d["P"], d["M"]) == (c["P"], c["M"])
+        det.detectAndCompute(img)
+        info = check_results(_res(det), cpu.results(), min_agree=0.97, desc_tol=3e-2, desc_frac=0.95, size_rtol=1e-5)
+        print(cols, rows, fr, info)
+
+
+def test_live_reference_when_available():
+    from oracle.pyoracle import RefOracle, ref_available
+
+    if not ref_available():
+        pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
+    from another_cuda_sift_b200.synth import next_frame, synth_frame
+
+    cols, rows = 640, 360
+    det, ref = _det(cols, rows), RefOracle(cols, rows, 5000)
+    img = synth_frame(rows, cols, 11)
+    for fr in range(3):
+        if fr:
+            img = next_frame(img, 11 + fr)
+        ref.detect(img)
+        det.debug_run_stages(img, 1)
+        for oi in range(det.n_octaves):
+            assert np.array_equal(det.debug_gauss(oi).view(np.uint32), ref.stack(oi, "gauss").view(np.uint32)), (fr, oi)
+        det.detectAndCompute(img)
+        info = check_results(_res(det), ref.results(), desc_tol=DESC_TOL, desc_frac=DESC_FRAC)
+        print("live", fr, info)
+
+
+def test_input_paths_agree_and_engine_is_deterministic():
+    """float host == uint8 host == device-resident input; two runs are bit-identical (votes are
+    accumulated in fixed point, unlike the reference's float atomics)."""
+    import torch
+
+    from another_cuda_sift_b200.synth import synth_frame
+
+    cols, rows = 1920, 1200
+    img = synth_frame(rows, cols, 0)
+    det = _det(cols, rows)
+    outs = []
+    for variant in (img, img.astype(np.uint8), torch.from_numpy(img).cuda(), img):
+        det.detectAndCompute(variant)
+        r = _res(det)
+        outs.append((r["n"], r["kpts"][:r["n"]].copy(), r["feats"][:r["n"]].copy(), r["desc"][:r["n"]].copy()))
+    for o in outs[1:]:
+        assert o[0] == outs[0][0] and o[0] > 1000
+        for a, b in zip(o[1:], outs[0][1:]):
+            assert np.array_equal(a.view(np.uint8), b.view(np.uint8))
+
+
+def test_prev_descriptor_is_previous_frame():
+    # Detector.cu:136-141
+    import torch
+
+    from another_cuda_sift_b200.synth import next_frame, synth_frame
+
+    det = _det(320, 240)
+    a = synth_frame(240, 320, 3)
+    det.detectAndCompute(a)
+    det.copyToHost(True)
+    first = det.descriptors.copy()
+    det.detectAndCompute(next_frame(a, 4))
+    prev = torch.as_tensor(det.prev_descriptor, device="cuda").cpu().numpy()
+    assert np.array_equal(prev.view(np.uint16), first.view(np.uint16))
+
+
+def test_wrong_size_and_bad_config_are_errors():
+    from another_cuda_sift_b200 import B200SiftError, CudaSiftConfig, Detector
+
+    det = _det(64, 48)
+    with pytest.raises(B200SiftError):
+        det.detectAndCompute(np.zeros((48, 65), np.float32))
+    with pytest.raises(B200SiftError):
+        Detector(CudaSiftConfig(col_width=64, row_width=48, upscale=True)).gpuWarmUpAndAllocate()
+    flat = np.full((48, 64), 17.0, np.float32)  # featureless frame: zero keypoints, not an error
+    det.detectAndCompute(flat)
+    assert det.total_size == 0
+
+
+@pytest.mark.parametrize("cols,rows", [(33, 21), (16, 16), (9, 400)])
+def test_tiny_and_ragged_sizes_vs_cpu_oracle(cols, rows):
+    from oracle.pyoracle import CpuOracle
+
+    rng = np.random.default_rng(5)
+    img = np.floor(rng.random((rows, cols)) * 256).astype(np.float32)
+    det, cpu = _det(cols, rows), CpuOracle(cols, rows, 5000)
+    cpu.detect(img)
+    det.debug_run_stages(img, 4)
+    for oi in range(det.n_octaves):
+        assert np.array_equal(det.debug_gauss(oi).view(np.uint32), cpu.stack(oi, "gauss").view(np.uint32)), oi
+        c, d = cpu.counts(oi), det.debug_counts(oi)
+        assert (d["P"], d["M"]) == (c["P"], c["M"])
