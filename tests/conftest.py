@@ -40,3 +40,29 @@ def golden(name):
     if not os.path.exists(path):
         pytest.skip(f"golden fixture {name} not generated yet (tests/golden/make_golden.py on a B200)")
     return np.load(path)
+
+
+def golden_frames(g):
+    """The input frames of a golden capture: stored uint8 copies for small frames, regenerated from the
+    seed (and checked against the stored SHA-1) for big ones."""
+    import hashlib
+
+    import numpy as np
+
+    from another_cuda_sift_b200.synth import next_frame, synth_frame
+
+    rows, cols, n = int(g["rows"]), int(g["cols"]), int(g["nframes"])
+    regen = [synth_frame(rows, cols, 0, density=float(g["density"]))]
+    for fr in range(1, n):
+        regen.append(next_frame(regen[-1], fr))
+    out = []
+    for fr in range(n):
+        if f"f{fr}_img_u8" in g:
+            stored = g[f"f{fr}_img_u8"].astype(np.float32)
+            assert np.array_equal(stored, regen[fr]), "synthetic generator drifted from the golden capture"
+            out.append(stored)
+        else:
+            assert hashlib.sha1(regen[fr].tobytes()).hexdigest() == str(g[f"f{fr}_img_sha1"]), \
+                "synthetic generator drifted from the golden capture"
+            out.append(regen[fr])
+    return out

@@ -5,7 +5,7 @@
 import numpy as np
 import pytest
 
-from conftest import golden
+from conftest import golden, golden_frames
 from util import check_results
 
 pytestmark = pytest.mark.gpu
@@ -13,7 +13,7 @@ pytestmark = pytest.mark.gpu
 # Bars (BASELINE.json north_star): extrema and refined positions bit-exact; >= 99.5% keypoint-set agreement;
 # size 1e-3 relative; descriptors 1e-3 L2 -- asserted for DESC_FRAC of the keypoints because the reference
 # itself is not run-to-run reproducible there (float shared-memory atomics; envelope_752x480.npz).
-DESC_TOL, DESC_FRAC = 1e-3, 0.98
+DESC_TOL, DESC_FRAC = 1e-3, 0.995
 
 
 def _det(cols, rows, nf=5000):
@@ -29,10 +29,6 @@ def _res(det):
     return dict(n=det.total_size, kpts=det.final_kpts, feats=det.final_features, desc=det.descriptors)
 
 
-def _img(g, fr):
-    return g[f"f{fr}_img_u8"].astype(np.float32)
-
-
 def test_taps_bit_exact_vs_golden():
     g = golden("taps.npz")
     det = _det(64, 64)
@@ -45,11 +41,12 @@ def test_taps_bit_exact_vs_golden():
 def test_frames_vs_golden(name):
     g = golden(name)
     cols, rows = int(g["cols"]), int(g["rows"])
+    frames = golden_frames(g)
     det = _det(cols, rows, int(g["num_features"]))
     assert det.n_octaves == int(g["n_octaves"])
     assert np.array_equal(np.array([[x["w"], x["h"], x["pitch"], x["cap"]] for x in det.octaves]), g["octaves"])
     for fr in range(int(g["nframes"])):
-        img = _img(g, fr)
+        img = frames[fr]
         det.debug_run_stages(img, 1)
         for oi in range(det.n_octaves):
             gs = det.debug_gauss(oi)
@@ -63,14 +60,14 @@ def test_frames_vs_golden(name):
             c = det.debug_counts(oi)
             assert (c["P"], c["M"]) == (counts[0][oi], counts[1][oi]), (fr, oi, c)
         want = dict(n=int(g[f"f{fr}_total"]), kpts=g[f"f{fr}_kpts"], feats=g[f"f{fr}_feats"], desc=g[f"f{fr}_desc"])
-        info = check_results(_res(det), want, desc_tol=DESC_TOL, desc_frac=DESC_FRAC)
+        info = check_results(_res(det), want, desc_tol=DESC_TOL, desc_frac=DESC_FRAC, octaves=g["octaves"])
         print(name, fr, info)
 
 
 def test_extrema_and_refinement_bit_exact_vs_golden():
     g = golden("frames_752x480.npz")
     det = _det(752, 480)
-    img = _img(g, 0)
+    img = golden_frames(g)[0]
     det.debug_run_stages(img, 3)
     for oi in range(det.n_octaves):
         ext = g[f"f0_extrema{oi}"]

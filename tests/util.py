@@ -35,7 +35,21 @@ def desc_l2(d1, d2):
     return np.linalg.norm((d1.astype(np.float32) - d2.astype(np.float32)) / 512.0, axis=1)
 
 
-def check_results(got, want, *, min_agree=0.995, desc_tol=1e-3, desc_frac=0.99, size_rtol=1e-3):
+def touches_padding(kpts, feats, octaves):
+    """True for keypoints whose descriptor patch reaches the last column of an octave whose rows are padded
+    (pitch > width). There the reference reads one float past the row (quirk Q12, SiftOps.cu:553-557), i.e.
+    UNINITIALISED cudaMallocPitch padding: its result is undefined (it depends on what the allocation held
+    before), so those descriptors cannot be pinned. The engine and the CPU oracle read zeros there."""
+    octv = feats[:, 0].astype(np.int64) & 255
+    scale = 1.0 / (2.0 ** octv)
+    x = np.rint(kpts[:, 0] * scale)
+    radius = np.rint(3.0 * (feats[:, 1] * scale * 0.5) * 1.4142135623730951 * 2.5)
+    w = np.array([octaves[o][0] for o in octv])
+    pitch = np.array([octaves[o][2] for o in octv])
+    return (pitch > w) & (x + radius >= w - 1)
+
+
+def check_results(got, want, *, min_agree=0.995, desc_tol=1e-3, desc_frac=0.99, size_rtol=1e-3, octaves=None):
     """got / want: dict(n, kpts, feats, desc). Returns a dict of measured figures, asserts the bars:
     >= 99.5% keypoint-set agreement; on the paired keypoints x/y/layer/octave/angle are identical
     by construction of the key, size within 1e-3 relative, |contrast| within 1e-5, and descriptors
@@ -52,6 +66,11 @@ def check_results(got, want, *, min_agree=0.995, desc_tol=1e-3, desc_frac=0.99, 
         size_err = np.abs(f1[i1, 1] - f2[i2, 1]) / np.maximum(np.abs(f2[i2, 1]), 1e-12)
         con_err = np.abs(f1[i1, 2] - f2[i2, 2])
         l2 = desc_l2(d1[i1], d2[i2])
+        if octaves is not None:  # descriptors that depend on uninitialised padding in the reference
+            undefined = touches_padding(k2[i2], f2[i2], octaves)
+            out.update(undefined_frac=float(undefined.mean()))
+            assert undefined.mean() <= 0.5, out
+            l2 = l2[~undefined]
         out.update(size_rel_max=float(size_err.max()), contrast_abs_max=float(con_err.max()),
                    desc_l2_max=float(l2.max()), desc_l2_p99=float(np.quantile(l2, 0.99)),
                    desc_within=float((l2 <= desc_tol).mean()))
