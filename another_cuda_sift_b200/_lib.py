@@ -63,6 +63,8 @@ SIGNATURES = {
     "b200sift_match_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "b200sift_match_host": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "b200sift_match_launches": (C.c_int, [C.c_int, C.c_int]),
+    "b200sift_match_set_path": (C.c_int, [C.c_int]),
+    "b200sift_debug_match_dist": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
 }
 
 _lib = None

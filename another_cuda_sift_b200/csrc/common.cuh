@@ -77,7 +77,11 @@ void launch_orientation(const FrameParams& fp, cudaStream_t s);
 void launch_compact_oriented(const FrameParams& fp, cudaStream_t s);
 void launch_descriptor(const FrameParams& fp, cudaStream_t s);
 
-int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s);
+int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s,
+                 float* dbg = nullptr);
+int match_launch_simt(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s);
+void match_set_path(int path);
+int match_get_path();
 size_t match_scratch_bytes(int nq, int nt);
 int match_num_launches(int nq, int nt);
 

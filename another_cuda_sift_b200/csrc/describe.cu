@@ -19,8 +19,18 @@ namespace {
 constexpr float kFix = 4294967296.f;          // 2^32
 constexpr double kUnfix = 1.0 / 4294967296.0;
 
+// 64-bit fixed-point accumulate built from NATIVE 32-bit shared-memory atomics (ATOMS.ADD): add the low
+// word, derive the carry from the returned old value, add high word + carry. The final 64-bit value is
+// the exact sum mod 2^64 whatever the order, i.e. deterministic; a 64-bit or float shared atomicAdd would
+// compile to a compare-and-swap loop that serialises the many lanes voting into the same bin.
 __device__ __forceinline__ void fix_add(unsigned long long* slot, float v) {
-    atomicAdd(slot, (unsigned long long)__float2ll_rn(__fmul_rn(v, kFix)));
+    const long long q = __float2ll_rn(__fmul_rn(v, kFix));
+    const unsigned lo = (unsigned)q;
+    int hi = (int)(q >> 32);
+    unsigned* p = reinterpret_cast<unsigned*>(slot);
+    const unsigned old = atomicAdd(p, lo);
+    hi += (old + lo < old) ? 1 : 0;
+    if (hi) atomicAdd(p + 1, (unsigned)hi);
 }
 __device__ __forceinline__ float fix_get(unsigned long long v) { return (float)((double)(long long)v * kUnfix); }
 

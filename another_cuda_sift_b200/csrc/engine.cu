@@ -586,4 +586,24 @@ int b200sift_match_host(const uint16_t* query, int nq, const uint16_t* train, in
 
 int b200sift_match_launches(int nq, int nt) { return match_num_launches(nq, nt); }
 
+int b200sift_match_set_path(int path) {
+    if (path != 0 && path != 1) return fail(B200SIFT_EINVAL, "path must be 0 (tensor core) or 1 (CUDA core)");
+    match_set_path(path);
+    return 0;
+}
+
+int b200sift_debug_match_dist(const uint16_t* d_query, int nq, const uint16_t* d_train, int nt, float* d_dist, int* d_out_idx) {
+    if (nq <= 0 || nt <= 0 || !d_query || !d_train || !d_dist || !d_out_idx) return fail(B200SIFT_EINVAL, "bad argument");
+    void* scratch = nullptr;
+    const size_t need = match_scratch_bytes(nq, nt);
+    CU(cudaMalloc(&scratch, need));
+    int rc = match_launch(reinterpret_cast<const __half*>(d_query), nq, reinterpret_cast<const __half*>(d_train), nt, d_out_idx,
+                          scratch, need, nullptr, d_dist);
+    cudaError_t e = cudaDeviceSynchronize();
+    cudaFree(scratch);
+    if (rc) return fail(B200SIFT_EINVAL, "matcher scratch too small");
+    CU(e);
+    return 0;
+}
+
 }  // extern "C"

@@ -1,4 +1,5 @@
-// Brute-force ratio-test matcher, bit-exact with sift_func/Match.cu:35-177.
+// Brute-force ratio-test matcher on CUDA cores, bit-exact with sift_func/Match.cu:35-177. This is the
+// on-device cross-check of the tensor-core path in match_tc.cu (b200sift_match_set_path(1)).
 //
 // The reference computes, for query q and train t,
 //     score = fp32 tree-sum over 32 lanes of ((e[2i] + e[2i+1]) + (e[2i+64] + e[2i+65])),
@@ -127,16 +128,9 @@ match_merge_kernel(const ChunkRec* __restrict__ rec, int nq, int* __restrict__ o
 
 }  // namespace
 
-size_t match_scratch_bytes(int nq, int nt) {
-    (void)nt;
-    return (size_t)nq * 32 * sizeof(ChunkRec);
-}
-
-int match_num_launches(int nq, int nt) { return (nq > 0 && nt >= 0) ? 2 : 0; }
-
-int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s) {
+int match_launch_simt(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s) {
     if (nq <= 0) return 0;
-    if (scratch_bytes < match_scratch_bytes(nq, nt)) return -1;
+    if (scratch_bytes < (size_t)nq * 32 * sizeof(ChunkRec)) return -1;
     ChunkRec* rec = static_cast<ChunkRec*>(scratch);
     // ceil(float(nt)/32) as in Match.cu:131 (float arithmetic)
     const int per = (int)ceilf((float)nt / 32.f);

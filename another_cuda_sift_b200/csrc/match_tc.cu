@@ -1,0 +1,413 @@
+// Tensor-core brute-force matcher for sm_100a: tcgen05.mma + TMEM candidate filter, exact re-rank.
+//
+// The reference (sift_func/Match.cu:35-177) scores every (query, train) pair with rounded-half arithmetic
+//     score = sum_j half( d_j*d_j ),  d_j = half( half(a_j - b_j) * 0.25 )            (~ |a-b|^2 / 16)
+// keeps, per query, the top-2 of each of 32 contiguous column chunks (strict '<', lowest index wins) and
+// merges the 32 results with a shuffle tree (quirk Q15). Only the top-2 of every (query, chunk) can
+// influence the output, so:
+//
+//  1. match_filter_kernel: D = |a|^2 + |b|^2 - 2 a.b^T on the 5th-gen tensor cores (tcgen05.mma
+//     kind::f16, 128 x 128 x 16 per instruction, fp32 accumulators in TMEM). Inputs are exact halves, so
+//     D is the true squared distance up to fp32 accumulation error. Every half rounding of the reference
+//     recipe is a relative error <= 2^-11 on a non-negative term, hence |16*score - D| <= 1.5e-3 * D
+//     (+ tiny absolute slack). Pass 1 finds the 2nd smallest D of the chunk, pass 2 emits every column
+//     with D <= D2nd * 1.004 + eps: a superset of the exact top-2 including ties. Typically 2-3 columns
+//     per (query, chunk) survive.
+//  2. match_rerank_kernel: warp per query re-scores the survivors with the reference's exact arithmetic
+//     (lane i owns half2 i and i+32, same fp32 tree), in ascending column order with the same strict-'<'
+//     updates, then replays the reference's 32-lane merge and the double-precision ratio test.
+//     A (query, chunk) whose survivor list overflows is re-scored column by column (rare, still exact).
+//
+// Roofline: tensor-bound in the limit (2*nq*nt*128 flop); at 2k x 2k it is launch/latency-bound.
+#include "common.cuh"
+
+namespace b200sift {
+
+namespace {
+
+constexpr int kTileM = 128;   // queries per CTA  (= TMEM lanes)
+constexpr int kCand = 7;      // survivors kept per (query, chunk); record = {count, c0..c6}
+constexpr int kFilterThreads = 128;
+constexpr uint32_t kTileBytes = kTileM * 256;  // 128 rows x 128 halves
+constexpr uint32_t kKcStride = kTileM * 16;    // bytes between consecutive 8-column K chunks
+
+struct __align__(16) CandRec {
+    int n;            // 0..kCand, or kCand+1 = overflow (re-score the whole chunk)
+    int c[kCand];
+};
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+// K-major, no-swizzle UMMA shared-memory descriptor. Tile layout in smem: [k_chunk(16)][row(128)][8 halves]:
+// a core matrix is 8 rows x 16 B = 128 contiguous bytes; next 8-row group +128 B (SBO); next 8-column
+// K chunk +128*16 B (LBO).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+    d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+    d |= (uint64_t)1 << 46;  // descriptor version (Blackwell)
+    return d;                // base_offset 0, lbo_mode 0, layout_type 0 = SWIZZLE_NONE
+}
+
+// kind::f16 instruction descriptor: D=f32, A=B=f16, both K-major, M=128, N=n.
+__host__ __device__ constexpr uint32_t make_idesc(int n) {
+    return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
+}
+
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+    uint32_t done = 0;
+    for (uint32_t spins = 0; !done; spins++) {
+        if (spins > (1u << 28)) __trap();  // a lost commit must fail loudly, never hang the GPU
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(done) : "r"(bar), "r"(parity) : "memory");
+    }
+}
+
+// TR rows x 256 B from global (row-major) into the UMMA layout [k_chunk][row(TR)][16 B]. Rows in
+// [rows, round_up(rows, 32)) are zero-filled (their distances become +inf through s_nb and are scanned);
+// rows beyond that are left as they are: their products land in TMEM columns nobody reads.
+template <int TR>
+__device__ __forceinline__ void load_tile(const __half* __restrict__ g, int rows, uint8_t* s, int warp, int lane) {
+    const int r8 = lane & 7, k4 = lane >> 3;
+    const int rows32 = (rows + 31) & ~31;
+    constexpr int kBatch = 16;  // 16-byte loads in flight per thread
+#pragma unroll 1
+    for (int u0 = warp; u0 < TR / 2; u0 += kBatch * (kFilterThreads / 32)) {
+        uint4 v[kBatch];
+#pragma unroll
+        for (int i = 0; i < kBatch; i++) {
+            const int u = u0 + i * (kFilterThreads / 32);
+            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
+            v[i] = make_uint4(0u, 0u, 0u, 0u);
+            if (row < rows) v[i] = __ldg(reinterpret_cast<const uint4*>(g + (size_t)row * 128) + kc);
+        }
+#pragma unroll
+        for (int i = 0; i < kBatch; i++) {
+            const int u = u0 + i * (kFilterThreads / 32);
+            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
+            if (row < rows32) *reinterpret_cast<uint4*>(s + kc * (TR * 16) + row * 16) = v[i];
+        }
+    }
+}
+
+template <int TR>
+__device__ __forceinline__ float row_norm2(const uint8_t* s, int row) {
+    float acc = 0.f;
+#pragma unroll
+    for (int kc = 0; kc < 16; kc++) {
+        const uint4 v = *reinterpret_cast<const uint4*>(s + kc * (TR * 16) + row * 16);
+        const __half2* h = reinterpret_cast<const __half2*>(&v);
+#pragma unroll
+        for (int i = 0; i < 4; i++) {
+            const float2 f = __half22float2(h[i]);
+            acc = __fmaf_rn(f.x, f.x, acc);
+            acc = __fmaf_rn(f.y, f.y, acc);
+        }
+    }
+    return acc;
+}
+
+// TN = train rows per MMA tile (= TMEM columns). When the whole chunk fits one tile (per <= TN) the
+// distances stay resident in TMEM and pass 2 only re-reads them (no reload, no second MMA).
+template <int TN, bool DBG>
+__global__ void __launch_bounds__(kFilterThreads)
+match_filter_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per,
+                    CandRec* __restrict__ rec, float* __restrict__ dbg) {
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sQ = smem;
+    uint8_t* sB = smem + kTileBytes;
+    float* s_nb = reinterpret_cast<float*>(smem + kTileBytes + TN * 256);
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_nb + TN);
+    constexpr uint32_t kIdesc = make_idesc(TN);
+    constexpr uint32_t kKcStrideB = TN * 16;
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 1);
+    int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int q0 = blockIdx.x * kTileM;
+    const int chunk = blockIdx.y;
+    const int t_begin = chunk * per;
+    const int t_end = min(nt, t_begin + per);
+    const int q = q0 + tid;
+    if (t_begin >= t_end) {  // empty chunk (uniform for the CTA): nothing to score
+        if (q < nq) rec[(size_t)q * 32 + chunk].n = 0;
+        return;
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(TN));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (tid == 0) {
+        *s_nbmax = 0;
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    load_tile<kTileM>(des + (size_t)q0 * 128, min(kTileM, nq - q0), sQ, warp, lane);
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem = *s_tmem;
+    const float na = (q < nq) ? row_norm2<kTileM>(sQ, tid) : 0.f;
+    const bool resident = per <= TN;
+
+    const uint32_t bar = smem_u32(s_bar);
+    const uint32_t aQ = smem_u32(sQ), aB = smem_u32(sB);
+    uint32_t phase = 0;
+    float a1 = INFINITY, a2 = INFINITY, thr = 0.f;
+    int cn = 0, c0 = -1, c1 = -1, c2 = -1, c3 = -1, c4 = -1, c5 = -1, c6 = -1;
+
+    for (int pass = 0; pass < 2; pass++) {
+        for (int t0 = t_begin; t0 < t_end; t0 += TN) {
+            const int rows = min(TN, t_end - t0);
+            if (!(resident && pass == 1)) {
+            load_tile<TN>(src + (size_t)t0 * 128, rows, sB, warp, lane);
+            __syncthreads();
+            for (int r = tid; r < ((rows + 31) & ~31); r += kFilterThreads) {
+                const float nb = r < rows ? row_norm2<TN>(sB, r) : INFINITY;  // padded columns can never win
+                s_nb[r] = nb;
+                if (r < rows) atomicMax(s_nbmax, __float_as_int(nb));         // norms are >= 0: int order == float order
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // st.shared -> visible to the tensor core
+            __syncthreads();
+            if (tid == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;");
+#pragma unroll
+                for (int k = 0; k < 8; k++) {  // K = 128 = 8 x 16; one instruction consumes 2 K chunks
+                    const uint64_t da = umma_desc(aQ + k * 2 * kKcStride, kKcStride, 128);
+                    const uint64_t db = umma_desc(aB + k * 2 * kKcStrideB, kKcStrideB, 128);
+                    const uint32_t acc = k > 0 ? 1u : 0u;
+                    asm volatile(
+                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                        ::"r"(tmem), "l"(da), "l"(db), "r"(kIdesc), "r"(acc) : "memory");
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+            }
+            mbar_wait(bar, phase);
+            phase ^= 1;
+            asm volatile("tcgen05.fence::after_thread_sync;");
+            }
+            const uint32_t taddr = tmem + ((uint32_t)(warp * 32) << 16);
+            for (int cb = 0; cb < TN / 32; cb++) {
+                if (cb * 32 >= rows) break;  // warp-uniform
+                uint32_t v[32];
+                asm volatile(
+                    "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                    "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                    "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                    : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                      "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                      "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                      "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                    : "r"(taddr + cb * 32));
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                if (pass == 0) {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        const float d = __fadd_rn(na, __fmaf_rn(-2.f, __uint_as_float(v[j]), s_nb[cb * 32 + j]));
+                        a2 = fminf(a2, fmaxf(a1, d));  // branch-free running top-2
+                        a1 = fminf(a1, d);
+                        if (DBG) { if (q < nq && cb * 32 + j < rows) dbg[(size_t)q * nt + t0 + cb * 32 + j] = d; }
+                    }
+                } else {
+#pragma unroll
+                    for (int j = 0; j < 32; j++) {
+                        const float d = __fadd_rn(na, __fmaf_rn(-2.f, __uint_as_float(v[j]), s_nb[cb * 32 + j]));
+                        if (__any_sync(0xffffffffu, d <= thr)) {  // warp-uniform: survivors are rare
+                            if (d <= thr) {
+                                const int col = t0 + cb * 32 + j;
+                                switch (cn) {
+                                    case 0: c0 = col; break;
+                                    case 1: c1 = col; break;
+                                    case 2: c2 = col; break;
+                                    case 3: c3 = col; break;
+                                    case 4: c4 = col; break;
+                                    case 5: c5 = col; break;
+                                    case 6: c6 = col; break;
+                                    default: break;
+                                }
+                                cn = min(cn + 1, kCand + 1);
+                            }
+                        }
+                    }
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;");
+            __syncthreads();  // sB, s_nb and the TMEM tile are free for the next tile
+        }
+        // survivors: D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings), + fp32 accumulation slack
+        thr = __fmaf_rn(fmaxf(a2, 0.f), 1.004f, __fmaf_rn(4e-5f, __fadd_rn(na, __int_as_float(*s_nbmax)), 1e-3f));
+    }
+    if (q < nq) {
+        int4* dst = reinterpret_cast<int4*>(rec + (size_t)q * 32 + chunk);
+        dst[0] = make_int4(cn, c0, c1, c2);
+        dst[1] = make_int4(c3, c4, c5, c6);
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TN));
+    }
+}
+
+// The reference's per-pair score (Match.cu:93-111), warp-cooperative: lane i owns half2 i and i+32 of both
+// rows. The xor butterfly adds the same operand pairs in the same order as the reference's shfl_down tree
+// does for lane 0, and fp32 addition is commutative, so EVERY lane ends up with lane 0's exact value.
+__device__ __forceinline__ float exact_score(__half2 a0, __half2 a1, __half2 b0, __half2 b1) {
+    const __half2 inv = __floats2half2_rn(0.25f, 0.25f);
+    __half2 d0 = __hmul2(__hsub2(a0, b0), inv);
+    __half2 d1 = __hmul2(__hsub2(a1, b1), inv);
+    d0 = __hmul2(d0, d0);
+    d1 = __hmul2(d1, d1);
+    const float2 f0 = __half22float2(d0), f1 = __half22float2(d1);
+    float s = __fadd_rn(__fadd_rn(f0.x, f0.y), __fadd_rn(f1.x, f1.y));
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) s = __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, off));
+    return s;
+}
+
+constexpr int kRerankWarps = 4;
+constexpr int kListCap = 32 * kCand;
+
+__global__ void __launch_bounds__(kRerankWarps * 32)
+match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per,
+                    const CandRec* __restrict__ rec, int* __restrict__ out_idx) {
+    __shared__ int s_col[kRerankWarps][kListCap];
+    __shared__ unsigned char s_chunk[kRerankWarps][kListCap];
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int q = blockIdx.x * kRerankWarps + warp;
+    if (q >= nq) return;
+    const __half2* arow = reinterpret_cast<const __half2*>(des + (size_t)q * 128);
+    const __half2 a0 = arow[lane], a1 = arow[lane + 32];
+    // lane c <- survivors of chunk c
+    const int4* rp = reinterpret_cast<const int4*>(rec + (size_t)q * 32 + lane);
+    const int4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
+    const int cnt = r0.x;
+    const bool overflow = cnt > kCand;
+    const int mine = overflow ? 0 : cnt;
+    int incl = mine;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += u;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    {
+        const int base = incl - mine;
+        const int c[kCand] = {r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
+#pragma unroll
+        for (int i = 0; i < kCand; i++)
+            if (i < mine) { s_col[warp][base + i] = c[i]; s_chunk[warp][base + i] = (unsigned char)lane; }
+    }
+    __syncwarp();
+    float mn = 1e6f, mn2 = 1e6f;   // Match.cu:125-129 sentinels (quirk Q16)
+    int id = -1, id2 = -1;
+    // survivors, ascending column order inside every chunk; one pair in flight ahead of the one scored
+    __half2 b0 = a0, b1 = a1;
+    if (total > 0) {
+        const __half2* brow = reinterpret_cast<const __half2*>(src + (size_t)s_col[warp][0] * 128);
+        b0 = __ldg(brow + lane); b1 = __ldg(brow + lane + 32);
+    }
+    for (int p = 0; p < total; p++) {
+        const int col = s_col[warp][p];
+        const int ch = s_chunk[warp][p];
+        __half2 n0 = b0, n1 = b1;
+        if (p + 1 < total) {
+            const __half2* brow = reinterpret_cast<const __half2*>(src + (size_t)s_col[warp][p + 1] * 128);
+            n0 = __ldg(brow + lane); n1 = __ldg(brow + lane + 32);
+        }
+        const float val = exact_score(a0, a1, b0, b1);
+        if (lane == ch) {
+            if (val < mn) { mn2 = mn; id2 = id; mn = val; id = col; }
+            else if (val < mn2) { mn2 = val; id2 = col; }
+        }
+        b0 = n0; b1 = n1;
+    }
+    // overflowed chunks: every column of the chunk, exactly as the reference scans them
+    unsigned ovf = __ballot_sync(0xffffffffu, overflow);
+    while (ovf) {
+        const int ch = __ffs(ovf) - 1;
+        ovf &= ovf - 1;
+        const int t_end = min(nt, (ch + 1) * per);
+        for (int t = ch * per; t < t_end; t++) {
+            const __half2* brow = reinterpret_cast<const __half2*>(src + (size_t)t * 128);
+            const float val = exact_score(a0, a1, __ldg(brow + lane), __ldg(brow + lane + 32));
+            if (lane == ch) {
+                if (val < mn) { mn2 = mn; id2 = id; mn = val; id = t; }
+                else if (val < mn2) { mn2 = val; id2 = t; }
+            }
+        }
+    }
+    // 32-lane merge, same shuffle sequence as Match.cu:152-169 (second update uses the partner's min2
+    // after the partner's own first update: quirk Q15 reproduced by construction)
+    float min_dist = mn, min_dist_2 = mn2;
+    int min_idx = id, min_idx_2 = id2;
+#pragma unroll
+    for (int offset = 16; offset > 0; offset /= 2) {
+        float nearby_min = __shfl_down_sync(0xffffffffu, min_dist, offset);
+        float nearby_min_idx = (float)__shfl_down_sync(0xffffffffu, min_idx, offset);
+        if (nearby_min < min_dist) {
+            min_dist_2 = min_dist;
+            min_idx_2 = min_idx;
+            min_dist = nearby_min;
+            min_idx = (int)nearby_min_idx;
+        }
+        nearby_min = __shfl_down_sync(0xffffffffu, min_dist_2, offset);
+        nearby_min_idx = (float)__shfl_down_sync(0xffffffffu, min_idx_2, offset);
+        if (nearby_min < min_dist_2) {
+            min_dist_2 = nearby_min;
+            min_idx_2 = (int)nearby_min_idx;
+        }
+    }
+    if (lane == 0) out_idx[q] = ((double)min_dist < 0.8 * (double)min_dist_2) ? min_idx : -1;
+}
+
+}  // namespace
+
+namespace {
+int g_match_path = 0;  // 0 = tensor-core filter + exact re-rank, 1 = all-CUDA-core exact kernel (match.cu)
+constexpr size_t filter_smem(int tn) { return kTileBytes + (size_t)tn * 256 + tn * sizeof(float) + 64; }
+
+template <int TN, bool DBG>
+void launch_filter(dim3 grid, const __half* q, int nq, const __half* t, int nt, int per, CandRec* rec, float* dbg, cudaStream_t s) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(match_filter_kernel<TN, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)filter_smem(TN));
+        attr_set = true;
+    }
+    match_filter_kernel<TN, DBG><<<grid, kFilterThreads, filter_smem(TN), s>>>(q, nq, t, nt, per, rec, dbg);
+}
+}  // namespace
+
+void match_set_path(int path) { g_match_path = path; }
+int match_get_path() { return g_match_path; }
+
+size_t match_scratch_bytes(int nq, int nt) {
+    (void)nt;
+    return (size_t)nq * 32 * sizeof(CandRec);  // >= the 16-byte records of the CUDA-core path
+}
+
+int match_num_launches(int nq, int nt) { return (nq > 0 && nt >= 0) ? 2 : 0; }
+
+int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes,
+                 cudaStream_t s, float* dbg) {
+    if (nq <= 0) return 0;
+    if (scratch_bytes < match_scratch_bytes(nq, nt)) return -1;
+    if (g_match_path == 1 && !dbg) return match_launch_simt(q, nq, t, nt, out, scratch, scratch_bytes, s);
+    CandRec* rec = static_cast<CandRec*>(scratch);
+    const int per = (int)ceilf((float)nt / 32.f);  // Match.cu:131 (float arithmetic)
+    dim3 grid((nq + kTileM - 1) / kTileM, 32);
+    if (dbg) {
+        if (per <= 128) launch_filter<128, true>(grid, q, nq, t, nt, per, rec, dbg, s);
+        else launch_filter<256, true>(grid, q, nq, t, nt, per, rec, dbg, s);
+    } else {
+        if (per <= 128) launch_filter<128, false>(grid, q, nq, t, nt, per, rec, dbg, s);
+        else launch_filter<256, false>(grid, q, nq, t, nt, per, rec, dbg, s);
+    }
+    match_rerank_kernel<<<(nq + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, nq, t, nt, per, rec, out);
+    return 0;
+}
+
+}  // namespace b200sift

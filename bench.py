@@ -233,7 +233,7 @@ def run_b200(args, world, rank, local):
     clocks = sampler.stop()
     kpts_per_frame = state["kpts"] / (args.steps * F)
     launches = state["launches"]
-    ms_e2e, _ = timed(step_e2e, args.steps, args.warmup)
+    ms_e2e, _ = (ms_total, 0) if args.quick else timed(step_e2e, args.steps, args.warmup)
     d2h_per_step = state["d2h"] / args.steps
 
     total_frames = sum_over_ranks(F * args.steps, world)
@@ -244,8 +244,8 @@ def run_b200(args, world, rank, local):
     extra = {}
     if rank == 0:
         det.detectAndCompute(d_frames[0])
-        graph_ms = det.time_frames(5, 100)
-        prof = det.profile_frame(3, 20)
+        graph_ms = det.time_frames(5, 5 if args.quick else 100)
+        prof = det.profile_frame(1 if args.quick else 3, 1 if args.quick else 20)
         extra = dict(graph_ms=graph_ms, prof=prof, kpts=det.total_size)
     return dict(value=value, ms_per_step=ms_total / args.steps, wall_ms=wall, e2e_value=e2e_value,
                 e2e_ms_per_step=ms_e2e / args.steps, clocks=clocks, kpts_per_frame=kpts_per_frame,
@@ -368,6 +368,7 @@ def main():
     ap.add_argument("--frames", type=int, default=16, help="frames per step per GPU")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--quick", action="store_true", help="profiler runs: skip e2e leg, per-class profile and CPU baselines")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
 
@@ -434,7 +435,7 @@ def main():
                            "frac": frame_bytes / (ex["graph_ms"] * 1e-3) / 1e9 / hbm_peak},
         "kernel_ms_per_frame": {k: round(v["ms"], 5) for k, v in prof.items()},
     }
-    if world == 1 and not args.no_cpu_baseline:
+    if world == 1 and not args.no_cpu_baseline and not args.quick:
         line["cpu_baseline"] = cpu_port_baseline(r["frames"])
         line["opencv_cpu"] = opencv_baseline(r["frames"])
     print(json.dumps(line), flush=True)

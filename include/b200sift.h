@@ -141,6 +141,15 @@ B200SIFT_API int b200sift_match_host(const uint16_t* query, int nq, const uint16
 /* Kernel launches issued by one b200sift_match_device call for this problem size. */
 B200SIFT_API int b200sift_match_launches(int nq, int nt);
 
+/* Matcher implementation: 0 (default) = tcgen05 tensor-core filter + exact re-rank (csrc/match_tc.cu),
+ * 1 = all-CUDA-core exact kernel (csrc/match.cu), kept as the on-device cross-check. Both are bit-exact
+ * with the reference; process-wide setting. */
+B200SIFT_API int b200sift_match_set_path(int path);
+/* Test access to the tensor-core stage: d_dist[nq*nt] (device) receives the fp32 squared distances
+ * |a|^2 + |b|^2 - 2ab^T the filter ranks by; d_out_idx[nq] the final result. Blocks. */
+B200SIFT_API int b200sift_debug_match_dist(const uint16_t* d_query, int nq, const uint16_t* d_train, int nt,
+                              float* d_dist, int* d_out_idx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -9,7 +9,7 @@ from conftest import golden
 pytestmark = pytest.mark.gpu
 
 
-def test_2000x2000_vs_golden():
+def test_2000x2000_vs_golden(path):
     from another_cuda_sift_b200 import matchBruteForce
     from another_cuda_sift_b200.synth import synth_descriptors
 
@@ -23,8 +23,22 @@ def test_2000x2000_vs_golden():
     assert np.array_equal(matchBruteForce(q[:300], 300, q[:300], 300), g["self300"])
 
 
-@pytest.mark.parametrize("nq,nt", [(1, 1), (3, 2), (31, 32), (33, 31), (100, 257), (513, 700), (1, 4000), (700, 5)])
-def test_vs_cpu_oracle(nq, nt):
+@pytest.fixture(params=[0, 1], ids=["tensor-core", "cuda-core"])
+def path(request):
+    """Both matcher implementations (csrc/match_tc.cu: tcgen05 filter + exact re-rank; csrc/match.cu: exact
+    CUDA-core kernel) must reproduce the reference bit for bit."""
+    from another_cuda_sift_b200 import _lib
+
+    lib = _lib.load()
+    lib.b200sift_match_set_path(request.param)
+    yield request.param
+    lib.b200sift_match_set_path(0)
+
+
+# (200, 5000): one 256-wide TMEM-resident tile per chunk; (150, 9000): streamed tiles, two passes
+@pytest.mark.parametrize("nq,nt", [(1, 1), (3, 2), (31, 32), (33, 31), (100, 257), (513, 700), (1, 4000), (700, 5),
+                                   (200, 5000), (150, 9000)])
+def test_vs_cpu_oracle(nq, nt, path):
     from another_cuda_sift_b200 import matchBruteForce
     from another_cuda_sift_b200.synth import synth_descriptors
     from oracle.pyoracle import CpuOracle
@@ -34,7 +48,27 @@ def test_vs_cpu_oracle(nq, nt):
     assert np.array_equal(matchBruteForce(q, nq, t, nt), CpuOracle(64, 64, 100).match(q, t))
 
 
-def test_adversarial_ties_and_duplicates_vs_cpu_oracle():
+def test_paths_agree_on_detector_descriptors(path):
+    """Real descriptors (consecutive frames, as tool/extract_and_match_example.cc:82 uses the matcher)."""
+    from another_cuda_sift_b200 import CudaSiftConfig, Detector, matchBruteForce
+    from another_cuda_sift_b200.synth import next_frame, synth_frame
+    from oracle.pyoracle import CpuOracle
+
+    det = Detector(CudaSiftConfig(col_width=752, row_width=480))
+    det.gpuWarmUpAndAllocate()
+    a = synth_frame(480, 752, 21)
+    det.detectAndCompute(a)
+    det.copyToHost(True)
+    n0, d0 = det.total_size, det.descriptors[:det.total_size].copy()
+    det.detectAndCompute(next_frame(a, 22))
+    det.copyToHost(True)
+    n1, d1 = det.total_size, det.descriptors[:det.total_size].copy()
+    got = matchBruteForce(d0, n0, d1, n1)
+    assert np.array_equal(got, CpuOracle(64, 64, 100).match(d0, d1))
+    assert (got >= 0).mean() > 0.2
+
+
+def test_adversarial_ties_and_duplicates_vs_cpu_oracle(path):
     """Duplicate train rows (exact ties: lowest index must win, strict '<'), near ties at the ratio
     threshold, all-zero rows, saturated values."""
     from another_cuda_sift_b200 import matchBruteForce
