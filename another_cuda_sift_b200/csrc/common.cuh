@@ -23,6 +23,7 @@ constexpr int kScales = 3;        // numOctaveLayers
 constexpr int kBorder = 5;        // SIFT_IMG_BORDER (sift_func/SiftOps.cuh:8)
 constexpr int kOriBins = 36;      // sift_func/SiftOps.cu:261
 constexpr int kMaxTaps = 21;
+constexpr int kTailPixels = 4096;  // octaves up to this many pixels are handled by the single-CTA tail kernel
 
 struct Taps {
     float v[kMaxTaps];
@@ -68,6 +69,7 @@ constexpr int kDetRows = 16;  // rows per warp task in the detect kernel
 void launch_u8_to_float(const uint8_t* in, size_t in_pitch, float* out, int out_pitch, int w, int h, cudaStream_t s);
 void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s);
 void launch_downsample(const float* in, int in_pitch, int iw, int ih, float* out, int out_pitch, int ow, int oh, cudaStream_t s);
+void launch_pyramid_tail(const FrameParams& fp, const Taps* taps, int first_octave, cudaStream_t s);
 void launch_detect(const FrameParams& fp, cudaStream_t s);       // bitmask + row counts
 void launch_scan_rows(const FrameParams& fp, cudaStream_t s);    // row offsets, P
 void launch_scatter(const FrameParams& fp, cudaStream_t s);      // ordered candidate list

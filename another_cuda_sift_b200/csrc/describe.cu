@@ -8,8 +8,10 @@
 // Per-sample arithmetic follows the reference's expression trees with the FMA contraction its
 // sm_100a SASS shows. The one deliberate difference: the reference accumulates histogram votes
 // with float shared-memory atomics, whose order -- and therefore rounding -- changes from run to
-// run; here votes are accumulated as 2^-32 fixed point in 64-bit shared-memory atomics, which is
-// order independent (deterministic) and lies inside the reference's own run-to-run envelope.
+// run; here votes are accumulated in fixed point with native integer shared-memory atomics, which is
+// order independent (deterministic) and lies inside the reference's own run-to-run envelope:
+// orientation bins as 2^-32 in 64 bits (peak selection is a discrete decision, keep it as exact as
+// possible), descriptor bins as 2^-15 in 32 bits (8 votes per sample: one ATOMS.ADD each).
 #include "common.cuh"
 
 namespace b200sift {
@@ -33,6 +35,14 @@ __device__ __forceinline__ void fix_add(unsigned long long* slot, float v) {
     if (hi) atomicAdd(p + 1, (unsigned)hi);
 }
 __device__ __forceinline__ float fix_get(unsigned long long v) { return (float)((double)(long long)v * kUnfix); }
+
+// Descriptor bins: int32, unit 2^-15. Two's-complement wrap-around makes partial sums harmless; a final bin
+// must lie within +-65536, far above what 0..255-valued pixels blurred with sigma >= 1.6 can produce
+// (|gradient| < 170, weight <= 1, a few hundred samples per bin). Quantisation: <= 1.5e-5 per vote, i.e.
+// ~1e-6 relative on a bin -- below the fp32 rounding noise of the reference's own float accumulation.
+constexpr float kFix32 = 32768.f;
+constexpr float kUnfix32 = 1.f / 32768.f;
+__device__ __forceinline__ void fix_add32(int* slot, float v_scaled) { atomicAdd(slot, __float2int_rn(v_scaled)); }
 
 // ---------------------------------------------------------------- orientation
 constexpr int kOriWarps = 8;
@@ -238,11 +248,11 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     const float4 ft = o.candF[j];
     const int tid = threadIdx.x;
 
-    __shared__ unsigned long long s_hist[kHistSize];
+    __shared__ int s_hist[kHistSize];
     __shared__ float s_f[kHistSize];
     __shared__ float s_desc[128];
     __shared__ float s_norm;
-    for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0ull;
+    for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0;
     __syncthreads();
 
     // unpackOctave (SiftOps.cu:389-401)
@@ -274,8 +284,14 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     const float fw = (float)o.w, fh = (float)o.h;
     const float* stack = o.gauss;
 
+    // idx = tid + k*128 walks the patch row-major; (row, col) advance incrementally instead of idx / side, idx % side
+    const int step_r = kDescThreads / side, step_c = kDescThreads % side;
+    int prow = tid / side, pcol = tid % side;
     for (int idx = tid; idx < total_dim; idx += kDescThreads) {
-        const int idx_i = idx / side - radius, idx_j = idx % side - radius;
+        const int idx_i = prow - radius, idx_j = pcol - radius;
+        prow += step_r;
+        pcol += step_c;
+        if (pcol >= side) { pcol -= side; prow++; }
         const float fi = (float)idx_i, fj = (float)idx_j;
         const float c_rot = __fmaf_rn(fj, cos_t, -__fmul_rn(fi, sin_t));
         const float r_rot = __fmaf_rn(fi, cos_t, __fmul_rn(fj, sin_t));
@@ -299,7 +315,7 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
             float grad_ori = (float)(((double)fast_atan2f(dy, dx) / 3.14159265358979323846) * 180.0);
             grad_ori = grad_ori < 0.f ? __fadd_rn(grad_ori, 360.f) : grad_ori;
             const float obin = __fmul_rn(__fsub_rn(grad_ori, angle), bins_per_degree);
-            const float mag = __fmul_rn(grad_mag, weight);
+            const float mag = __fmul_rn(__fmul_rn(grad_mag, weight), kFix32);  // x 2^15: exact, commutes with the roundings below
             float obin_int = truncf(obin);
             const float obin_frac = __fsub_rn(obin, obin_int);
             if (obin_int < 0.f) obin_int += 8.f;
@@ -310,19 +326,19 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
             const float v_rc11 = __fmul_rn(v_r1, cbin_frac), v_rc10 = __fmul_rn(v_r1, omc);
             const float v_rc01 = __fmul_rn(v_r0, cbin_frac), v_rc00 = __fmul_rn(v_r0, omc);
             if (hi >= 0 && hi + 71 < kHistSize) {
-                fix_add(s_hist + hi + 70, __fmul_rn(v_rc11, omo));
-                fix_add(s_hist + hi + 71, __fmul_rn(v_rc11, obin_frac));
-                fix_add(s_hist + hi + 60, __fmul_rn(v_rc10, omo));
-                fix_add(s_hist + hi + 61, __fmul_rn(v_rc10, obin_frac));
-                fix_add(s_hist + hi + 10, __fmul_rn(v_rc01, omo));
-                fix_add(s_hist + hi + 11, __fmul_rn(v_rc01, obin_frac));
-                fix_add(s_hist + hi, __fmul_rn(v_rc00, omo));
-                fix_add(s_hist + hi + 1, __fmul_rn(v_rc00, obin_frac));
+                fix_add32(s_hist + hi + 70, __fmul_rn(v_rc11, omo));
+                fix_add32(s_hist + hi + 71, __fmul_rn(v_rc11, obin_frac));
+                fix_add32(s_hist + hi + 60, __fmul_rn(v_rc10, omo));
+                fix_add32(s_hist + hi + 61, __fmul_rn(v_rc10, obin_frac));
+                fix_add32(s_hist + hi + 10, __fmul_rn(v_rc01, omo));
+                fix_add32(s_hist + hi + 11, __fmul_rn(v_rc01, obin_frac));
+                fix_add32(s_hist + hi, __fmul_rn(v_rc00, omo));
+                fix_add32(s_hist + hi + 1, __fmul_rn(v_rc00, obin_frac));
             }
         }
     }
     __syncthreads();
-    for (int i = tid; i < kHistSize; i += kDescThreads) s_f[i] = fix_get(s_hist[i]);
+    for (int i = tid; i < kHistSize; i += kDescThreads) s_f[i] = __fmul_rn((float)s_hist[i], kUnfix32);
     __syncthreads();
     // copyToDescriptor (SiftOps.cu:431-446): fold orientation bins 8,9 onto 0,1
     {

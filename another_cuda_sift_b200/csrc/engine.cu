@@ -68,6 +68,8 @@ inline int pitch_floats(int w) { return ((w * 4 + 511) / 512) * 512 / 4; }
 
 }  // namespace
 
+constexpr int kSideStreams = 2;
+
 struct b200sift_detector {
     b200sift_config cfg;
     int device = 0;
@@ -85,6 +87,9 @@ struct b200sift_detector {
     int* h_total = nullptr;  // pinned
     std::vector<void*> allocs;
     cudaStream_t stream = nullptr;
+    cudaStream_t side[kSideStreams] = {nullptr, nullptr};
+    cudaEvent_t ev_fork[kMaxOctaves] = {nullptr}, ev_join[kMaxOctaves] = {nullptr};
+    int tail_first = 0;  // first octave handled by the single-CTA tail kernel
     cudaGraph_t graph = nullptr;
     cudaGraphExec_t exec = nullptr;
     int launches = 0;
@@ -135,26 +140,54 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
                        cudaMemcpyDeviceToDevice, s));
     CU(cudaMemsetAsync(d->d_rowcount_all, 0, d->rowcount_bytes, s));
     MARK(B200SIFT_K_COPY);
+    // Gaussian pyramid. Octave o+1 only needs layer 3 of octave o, so layers 4 and 5 of every big octave
+    // go to a side stream (a parallel branch of the frame graph) while the main chain moves on to the next
+    // octave; octaves of <= kTailPixels pixels are walked by one CTA (launch_pyramid_tail).
+    const bool fork = (prof == nullptr) && d->side[0] != nullptr;
+    int n_side = 0;
     for (int o = 0; o < d->nOct; o++) {
         OctParams& oc = fp.oct[o];
         const size_t ls = (size_t)oc.pitch * oc.h;
-        for (int l = 0; l < kGaussLayers; l++) {
-            float* dst = oc.gauss + ls * l;
-            if (o == 0 && l == 0) {
-                launch_blur(d->d_input, d->in_pitch, dst, oc.pitch, oc.w, oc.h, d->init_taps, s);
-                MARK(B200SIFT_K_BLUR);
-            } else if (l == 0) {
-                const OctParams& pv = fp.oct[o - 1];
-                const float* src = pv.gauss + (size_t)pv.pitch * pv.h * kScales;
-                launch_downsample(src, pv.pitch, pv.w, pv.h, dst, oc.pitch, oc.w, oc.h, s);
-                MARK(B200SIFT_K_DOWNSAMPLE);
-            } else {
-                launch_blur(oc.gauss + ls * (l - 1), oc.pitch, dst, oc.pitch, oc.w, oc.h, d->taps[l], s);
-                MARK(o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL);
-            }
+        const bool tail = o >= d->tail_first;
+        if (o == 0) {
+            launch_blur(d->d_input, d->in_pitch, oc.gauss, oc.pitch, oc.w, oc.h, d->init_taps, s);
+            MARK(B200SIFT_K_BLUR);
+            n++;
+        } else if (!tail || o == d->tail_first) {
+            const OctParams& pv = fp.oct[o - 1];
+            const float* src = pv.gauss + (size_t)pv.pitch * pv.h * kScales;
+            launch_downsample(src, pv.pitch, pv.w, pv.h, oc.gauss, oc.pitch, oc.w, oc.h, s);
+            MARK(B200SIFT_K_DOWNSAMPLE);
             n++;
         }
+        if (tail) {
+            if (o == d->tail_first) {
+                launch_pyramid_tail(fp, d->taps, o, s);
+                MARK(B200SIFT_K_BLUR_SMALL);
+                n++;
+            }
+            continue;
+        }
+        cudaStream_t ls_stream = s;
+        for (int l = 1; l < kGaussLayers; l++) {
+            if (l == 4 && fork && o + 1 < d->nOct) {  // layers 4,5 off the critical path
+                cudaStream_t side = d->side[n_side % kSideStreams];
+                CU(cudaEventRecord(d->ev_fork[o], s));
+                CU(cudaStreamWaitEvent(side, d->ev_fork[o], 0));
+                ls_stream = side;
+            }
+            launch_blur(oc.gauss + ls * (l - 1), oc.pitch, oc.gauss + ls * l, oc.pitch, oc.w, oc.h, d->taps[l], ls_stream);
+            MARK(o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL);
+            n++;
+        }
+        if (ls_stream != s) {
+            CU(cudaEventRecord(d->ev_join[o], ls_stream));
+            n_side++;
+        }
     }
+    if (fork)
+        for (int o = 0; o < d->nOct; o++)
+            if (o < d->tail_first && o + 1 < d->nOct) CU(cudaStreamWaitEvent(s, d->ev_join[o], 0));
     if (last_stage >= 3) {
         if (fp.det_tasks > 0) { launch_detect(fp, s); n++; MARK(B200SIFT_K_DETECT); }
         launch_scan_rows(fp, s); n++;
@@ -273,6 +306,13 @@ int build(b200sift_detector* d) {
     CU(cudaMallocHost(&d->h_total, sizeof(int)));
     *d->h_total = 0;
     CU(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
+    for (int i = 0; i < kSideStreams; i++) CU(cudaStreamCreateWithFlags(&d->side[i], cudaStreamNonBlocking));
+    for (int o = 0; o < d->nOct; o++) {
+        CU(cudaEventCreateWithFlags(&d->ev_fork[o], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&d->ev_join[o], cudaEventDisableTiming));
+    }
+    d->tail_first = d->nOct;
+    for (int o = d->nOct - 1; o >= 0 && fp.oct[o].w * fp.oct[o].h <= kTailPixels; o--) d->tail_first = o;
 
     // One graph for the whole frame.
     CU(cudaStreamBeginCapture(d->stream, cudaStreamCaptureModeThreadLocal));
@@ -339,6 +379,12 @@ int b200sift_destroy(b200sift_detector* d) {
     for (void* p : d->allocs) cudaFree(p);
     if (d->h_total) cudaFreeHost(d->h_total);
     if (d->stream) cudaStreamDestroy(d->stream);
+    for (int i = 0; i < kSideStreams; i++)
+        if (d->side[i]) cudaStreamDestroy(d->side[i]);
+    for (int o = 0; o < kMaxOctaves; o++) {
+        if (d->ev_fork[o]) cudaEventDestroy(d->ev_fork[o]);
+        if (d->ev_join[o]) cudaEventDestroy(d->ev_join[o]);
+    }
     delete d;
     return 0;
 }

@@ -115,12 +115,7 @@ void launch_blur_r(const float* in, int in_pitch, float* out, int out_pitch, int
 // Bilinear resample with the reference's exact expression tree (image_func/Resize.cu:26-63);
 // the tail is the contraction ptxas chose for the reference on sm_100a:
 //   out = fma(fma(v11, 1-xf, v21*xf), 1-yf, fma(v12, 1-xf, v22*xf) * yf)
-__global__ void __launch_bounds__(256)
-downsample_kernel(const float* __restrict__ in, int in_pitch, int iw, int ih,
-                  float* __restrict__ out, int out_pitch, int ow, int oh) {
-    const int x = blockIdx.x * 32 + (threadIdx.x & 31);
-    const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
-    if (x >= ow || y >= oh) return;
+__device__ __forceinline__ float bilinear_sample(const float* __restrict__ in, int in_pitch, int iw, int ih, int ow, int oh, int x, int y) {
     const float fiw = (float)iw, fih = (float)ih, fow = (float)ow, foh = (float)oh;
     const float coord_x = __fsub_rn(__fdiv_rn(__fmul_rn(__fadd_rn((float)x, 0.5f), fiw), fow), 0.5f);
     const float coord_y = __fsub_rn(__fdiv_rn(__fmul_rn(__fadd_rn((float)y, 0.5f), fih), foh), 0.5f);
@@ -134,11 +129,78 @@ downsample_kernel(const float* __restrict__ in, int in_pitch, int iw, int ih,
     int y2 = yf == 0.f ? y1 + 1 : __float2int_ru(coord_y);
     y2 = min(max_y, max(0, y2));
     const float x2e = __fsub_rn(1.f, xf), y2e = __fsub_rn(1.f, yf);
-    const float v11 = __ldg(in + (size_t)y1 * in_pitch + x1), v21 = __ldg(in + (size_t)y1 * in_pitch + x2);
-    const float v12 = __ldg(in + (size_t)y2 * in_pitch + x1), v22 = __ldg(in + (size_t)y2 * in_pitch + x2);
+    const float v11 = in[(size_t)y1 * in_pitch + x1], v21 = in[(size_t)y1 * in_pitch + x2];
+    const float v12 = in[(size_t)y2 * in_pitch + x1], v22 = in[(size_t)y2 * in_pitch + x2];
     const float a = __fmaf_rn(v11, x2e, __fmul_rn(v21, xf));
     const float r12 = __fmul_rn(__fmaf_rn(v12, x2e, __fmul_rn(v22, xf)), yf);
-    out[(size_t)y * out_pitch + x] = __fmaf_rn(a, y2e, r12);
+    return __fmaf_rn(a, y2e, r12);
+}
+
+__global__ void __launch_bounds__(256)
+downsample_kernel(const float* __restrict__ in, int in_pitch, int iw, int ih,
+                  float* __restrict__ out, int out_pitch, int ow, int oh) {
+    const int x = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int y = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (x >= ow || y >= oh) return;
+    out[(size_t)y * out_pitch + x] = bilinear_sample(in, in_pitch, iw, ih, ow, oh, x, y);
+}
+
+// ---------------------------------------------------------------- pyramid tail
+// Octaves of at most kTailPixels pixels are pure launch latency as separate kernels (5 blurs + 1 resample
+// each, a few microseconds of dependent launches per layer). ONE CTA walks all of them instead: the
+// current layer and the row-filtered intermediate live in shared memory, every layer is also written to
+// its place in the Gaussian stack. Arithmetic is the same in-order fmaf chain as blur_vh_kernel.
+struct TailParams {
+    Taps taps[kGaussLayers];
+    float* gauss[kMaxOctaves];
+    int w[kMaxOctaves], h[kMaxOctaves], pitch[kMaxOctaves];
+    int first, nOct;
+};
+
+constexpr int kTailThreads = 1024;
+
+__global__ void __launch_bounds__(kTailThreads)
+pyramid_tail_kernel(const __grid_constant__ TailParams tp) {
+    __shared__ float s_cur[kTailPixels];
+    __shared__ float s_tmp[kTailPixels];
+    const int tid = threadIdx.x;
+    for (int o = tp.first; o < tp.nOct; o++) {
+        const int w = tp.w[o], h = tp.h[o], pitch = tp.pitch[o], n = w * h;
+        float* g = tp.gauss[o];
+        const size_t ls = (size_t)pitch * h;
+        if (o == tp.first) {  // base layer was produced by the launch before this kernel
+            for (int i = tid; i < n; i += kTailThreads) s_cur[i] = g[(size_t)(i / w) * pitch + i % w];
+        } else {              // bilinear resample of the previous octave's layer 3 (written by this CTA)
+            const float* src = tp.gauss[o - 1] + (size_t)tp.pitch[o - 1] * tp.h[o - 1] * kScales;
+            for (int i = tid; i < n; i += kTailThreads) {
+                const int y = i / w, x = i - y * w;
+                const float v = bilinear_sample(src, tp.pitch[o - 1], tp.w[o - 1], tp.h[o - 1], w, h, x, y);
+                s_cur[i] = v;
+                g[(size_t)y * pitch + x] = v;
+            }
+        }
+        __syncthreads();
+        for (int l = 1; l < kGaussLayers; l++) {
+            const Taps& t = tp.taps[l];
+            const int r = t.n / 2;
+            for (int i = tid; i < n; i += kTailThreads) {
+                const int y = i / w, x = i - y * w;
+                float acc = 0.f;
+                for (int k = 0; k < t.n; k++) acc = __fmaf_rn(s_cur[reflect101(y + k - r, h) * w + x], t.v[k], acc);
+                s_tmp[i] = acc;
+            }
+            __syncthreads();
+            float* dst = g + ls * l;
+            for (int i = tid; i < n; i += kTailThreads) {
+                const int y = i / w, x = i - y * w;
+                float acc = 0.f;
+                for (int k = 0; k < t.n; k++) acc = __fmaf_rn(s_tmp[y * w + reflect101(x + k - r, w)], t.v[k], acc);
+                s_cur[i] = acc;
+                dst[(size_t)y * pitch + x] = acc;
+            }
+            __syncthreads();  // also orders this CTA's global writes of layer 3 before the next octave reads them
+        }
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -172,6 +234,18 @@ void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w
 void launch_downsample(const float* in, int in_pitch, int iw, int ih, float* out, int out_pitch, int ow, int oh, cudaStream_t s) {
     dim3 grid((ow + 31) / 32, (oh + 7) / 8);
     downsample_kernel<<<grid, 256, 0, s>>>(in, in_pitch, iw, ih, out, out_pitch, ow, oh);
+}
+
+void launch_pyramid_tail(const FrameParams& fp, const Taps* taps, int first, cudaStream_t s) {
+    TailParams tp;
+    for (int l = 0; l < kGaussLayers; l++) tp.taps[l] = taps[l];
+    for (int o = 0; o < fp.nOct; o++) {
+        tp.gauss[o] = fp.oct[o].gauss;
+        tp.w[o] = fp.oct[o].w; tp.h[o] = fp.oct[o].h; tp.pitch[o] = fp.oct[o].pitch;
+    }
+    tp.first = first;
+    tp.nOct = fp.nOct;
+    pyramid_tail_kernel<<<1, kTailThreads, 0, s>>>(tp);
 }
 
 void launch_u8_to_float(const uint8_t* in, size_t in_pitch, float* out, int out_pitch, int w, int h, cudaStream_t s) {
