@@ -23,7 +23,9 @@ constexpr int kScales = 3;        // numOctaveLayers
 constexpr int kBorder = 5;        // SIFT_IMG_BORDER (sift_func/SiftOps.cuh:8)
 constexpr int kOriBins = 36;      // sift_func/SiftOps.cu:261
 constexpr int kMaxTaps = 21;
-constexpr int kTailPixels = 4096;  // octaves up to this many pixels are handled by the single-CTA tail kernel
+constexpr int kTailPixels = 4096;  // octaves up to this many pixels (and kTailMaxDim per side) go to the single-CTA tail kernel
+constexpr int kTailMaxDim = 1024;
+inline bool tail_octave(int w, int h) { return w * h <= kTailPixels && w <= kTailMaxDim && h <= kTailMaxDim; }
 
 struct Taps {
     float v[kMaxTaps];

@@ -45,28 +45,36 @@ constexpr float kUnfix32 = 1.f / 32768.f;
 __device__ __forceinline__ void fix_add32(int* slot, float v_scaled) { atomicAdd(slot, __float2int_rn(v_scaled)); }
 
 // ---------------------------------------------------------------- orientation
-constexpr int kOriWarps = 8;
+// One 64-thread CTA per refined keypoint (flattened over the octaves, grid-stride). The patch loop is
+// latency-bound (8 scattered loads + atan2f per sample), so every thread keeps two samples in flight.
+constexpr int kOriThreads = 64;
 
-__global__ void __launch_bounds__(kOriWarps * 32)
+struct OriSample {
+    float val;   // weight * magnitude
+    int bin;
+};
+
+__global__ void __launch_bounds__(kOriThreads)
 orientation_kernel(const __grid_constant__ FrameParams fp) {
-    const int oi = blockIdx.y;
-    const OctParams& o = fp.oct[oi];
-    const int M = o.counts[1];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    __shared__ unsigned long long s_hist[kOriWarps][kOriBins];
-    __shared__ float s_raw[kOriWarps][kOriBins];
-    __shared__ float s_smooth[kOriWarps][kOriBins];
-    unsigned long long* hist = s_hist[warp];
-    float* raw = s_raw[warp];
-    float* smooth = s_smooth[warp];
-    const size_t ls = (size_t)o.pitch * o.h;
-    const int h_dim = o.pitch;
+    __shared__ unsigned long long s_hist[kOriBins];
+    __shared__ float s_raw[kOriBins];
+    __shared__ float s_smooth[kOriBins];
+    __shared__ int s_peak[kOriBins];
+    const int tid = threadIdx.x;
+    int total = 0;
+    for (int i = 0; i < fp.nOct; i++) total += fp.oct[i].counts[1];
 
-    for (int k = blockIdx.x * kOriWarps + warp; k < M; k += gridDim.x * kOriWarps) {
+    for (int g = blockIdx.x; g < total; g += gridDim.x) {
+        int oi = 0, k = g;
+        while (k >= fp.oct[oi].counts[1]) { k -= fp.oct[oi].counts[1]; oi++; }
+        const OctParams& o = fp.oct[oi];
+        const int M = o.counts[1];
+        const size_t ls = (size_t)o.pitch * o.h;
+        const int h_dim = o.pitch;
         const float3 kp = o.coll[k];
         const float4 ft = o.collF[k];
-        for (int i = lane; i < kOriBins; i += 32) hist[i] = 0ull;
-        __syncwarp();
+        if (tid < kOriBins) s_hist[tid] = 0ull;
+        __syncthreads();
         // SiftOps.cu:271-297
         const float scale = __fdiv_rn(__fmul_rn(1.5f, ft.y), (float)(1 << (oi + 1)));
         const float radius = roundf(__fmul_rn(3.f, scale));
@@ -79,70 +87,87 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
         int layer = (int)kp.z;
         layer = min(max(layer, 0), 4);
         const float* g0 = o.gauss + ls * layer;  // DoG[layer] = G[layer+1] - G[layer]
-        for (int idx = lane; idx < total_dim; idx += 32) {
-            const int py_off = (int)__fsub_rn((float)(idx / side), radius);
+        const float fh1 = (float)o.h - 1.f, fw1 = (float)o.w - 1.f;
+
+        auto geometry = [&](int idx, int& px_off, int& py_off, const float*& p) -> bool {
+            if (idx >= total_dim) return false;
+            py_off = (int)__fsub_rn((float)(idx / side), radius);
             const int py = base_py + py_off;
-            if (py < 1 || (float)py >= (float)o.h - 1.f) continue;
-            const int px_off = (int)__fsub_rn((float)(idx % side), radius);
+            px_off = (int)__fsub_rn((float)(idx % side), radius);
             const int px = base_px + px_off;
-            if (px < 1 || (float)px >= (float)o.w - 1.f) continue;
-            const float* p = g0 + (size_t)py * h_dim + px;
-            const float dx = __fsub_rn(__fsub_rn(__ldg(p + ls + 1), __ldg(p + 1)), __fsub_rn(__ldg(p + ls - 1), __ldg(p - 1)));
-            const float dy = __fsub_rn(__fsub_rn(__ldg(p + ls - h_dim), __ldg(p - h_dim)), __fsub_rn(__ldg(p + ls + h_dim), __ldg(p + h_dim)));
+            if (py < 1 || (float)py >= fh1 || px < 1 || (float)px >= fw1) return false;
+            p = g0 + (size_t)py * h_dim + px;
+            return true;
+        };
+        auto vote = [&](const float v[8], int px_off, int py_off) -> OriSample {
+            const float dx = __fsub_rn(__fsub_rn(v[0], v[1]), __fsub_rn(v[2], v[3]));
+            const float dy = __fsub_rn(__fsub_rn(v[4], v[5]), __fsub_rn(v[6], v[7]));
             const float mag = __fsqrt_rd(__fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
             float ori = __fmul_rn(__fdiv_rn(atan2f(dy, dx), 3.14159265358979323846f), 180.f);
             if (ori < 0.f) ori = __fadd_rn(ori, 360.f);
             const float weight = __expf(__fmul_rn(weight_factor, (float)(px_off * px_off + py_off * py_off)));
             int bin = __float2int_rd(__fmul_rn(__fdiv_rn(ori, 360.f), 36.f)) % kOriBins;
             if (bin < 0) bin += kOriBins;  // NaN guard; never taken for finite input
-            fix_add(hist + bin, __fmul_rn(weight, mag));
+            OriSample r;
+            r.val = __fmul_rn(weight, mag);
+            r.bin = bin;
+            return r;
+        };
+        auto load8 = [&](const float* p, float v[8]) {
+            v[0] = __ldg(p + ls + 1); v[1] = __ldg(p + 1); v[2] = __ldg(p + ls - 1); v[3] = __ldg(p - 1);
+            v[4] = __ldg(p + ls - h_dim); v[5] = __ldg(p - h_dim); v[6] = __ldg(p + ls + h_dim); v[7] = __ldg(p + h_dim);
+        };
+
+        for (int idx = tid; idx < total_dim; idx += 2 * kOriThreads) {
+            int ax, ay, bx, by;
+            const float *pa = g0, *pb = g0;
+            const bool va = geometry(idx, ax, ay, pa);
+            const bool vb = geometry(idx + kOriThreads, bx, by, pb);
+            float a8[8], b8[8];
+            if (va) load8(pa, a8);
+            if (vb) load8(pb, b8);
+            if (va) { const OriSample r = vote(a8, ax, ay); fix_add(s_hist + r.bin, r.val); }
+            if (vb) { const OriSample r = vote(b8, bx, by); fix_add(s_hist + r.bin, r.val); }
         }
-        __syncwarp();
-        for (int i = lane; i < kOriBins; i += 32) raw[i] = fix_get(hist[i]);
-        __syncwarp();
+        __syncthreads();
+        if (tid < kOriBins) s_raw[tid] = fix_get(s_hist[tid]);
+        __syncthreads();
         // [1 4 6 4 1]/16 smoothing with the reference's association (SiftOps.cu:335)
-        for (int i = lane; i < kOriBins; i += 32) {
+        if (tid < kOriBins) {
+            const int i = tid;
             const int l = i > 0 ? i - 1 : kOriBins - 1, r = i < kOriBins - 1 ? i + 1 : 0;
             const int r2 = r < kOriBins - 1 ? r + 1 : 0, l2 = l > 0 ? l - 1 : kOriBins - 1;
-            const float a = __fmaf_rn(raw[i], 6.f, __fmul_rn(__fadd_rn(raw[l], raw[r]), 4.f));
-            smooth[i] = __fmul_rn(__fadd_rn(__fadd_rn(a, raw[l2]), raw[r2]), 0.0625f);
+            const float a = __fmaf_rn(s_raw[i], 6.f, __fmul_rn(__fadd_rn(s_raw[l], s_raw[r]), 4.f));
+            s_smooth[i] = __fmul_rn(__fadd_rn(__fadd_rn(a, s_raw[l2]), s_raw[r2]), 0.0625f);
         }
-        __syncwarp();
-        float mx = fmaxf(smooth[lane], lane < 4 ? smooth[lane + 32] : 0.f);
-        mx = fmaxf(mx, 0.f);
-#pragma unroll
-        for (int d = 16; d > 0; d >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, d));
-        const float thr = __fmul_rn(mx, 0.8f);
-        auto is_peak = [&](int i) {
+        __syncthreads();
+        if (tid < kOriBins) {
+            float mx = 0.f;
+            for (int i = 0; i < kOriBins; i++) mx = fmaxf(mx, s_smooth[i]);
+            const float thr = __fmul_rn(mx, 0.8f);
+            const int i = tid;
             const int l = i > 0 ? i - 1 : kOriBins - 1, r = i < kOriBins - 1 ? i + 1 : 0;
-            return smooth[i] > smooth[l] && smooth[i] > smooth[r] && smooth[i] >= thr;
-        };
-        const bool p0 = is_peak(lane);
-        const bool p1 = lane < 4 ? is_peak(lane + 32) : false;
-        const unsigned m0 = __ballot_sync(0xffffffffu, p0);
-        const unsigned m1 = __ballot_sync(0xffffffffu, p1);
+            s_peak[i] = (s_smooth[i] > s_smooth[l] && s_smooth[i] > s_smooth[r] && s_smooth[i] >= thr) ? 1 : 0;
+        }
+        __syncthreads();
         // copy c of keypoint k goes to slot M + 36k + c, dropped once slot >= cap (quirk Q6)
-        const int slot0 = k * kOriBins + M;
-        int emitted = 0;
-        for (int pass = 0; pass < 2; pass++) {
-            const unsigned m = pass == 0 ? m0 : m1;
-            const bool mine = pass == 0 ? p0 : p1;
-            const int bin = lane + 32 * pass;
-            const int c = (pass == 0 ? 0 : __popc(m0)) + __popc(m & ((1u << lane) - 1u));
+        if (tid < kOriBins) {
+            const int slot0 = k * kOriBins + M;
+            int c = 0;
+            for (int i = 0; i < tid; i++) c += s_peak[i];
             const int slot = slot0 + c;
-            if (mine && slot < o.cap) {
+            if (s_peak[tid] && slot < o.cap) {
                 o.coll[slot] = kp;
                 float4 f = ft;
-                f.w = __fsub_rn(360.f, __fmul_rn(__fdiv_rn((float)bin, 36.f), 360.f));
+                f.w = __fsub_rn(360.f, __fmul_rn(__fdiv_rn((float)tid, 36.f), 360.f));
                 o.collF[slot] = f;
             }
-            emitted += __popc(m);
+            if (tid == kOriBins - 1) {
+                const int emitted = c + s_peak[tid];
+                o.oricnt[k] = max(0, min(emitted, o.cap - slot0));
+            }
         }
-        if (lane == 0) {
-            const int room = o.cap - slot0;
-            o.oricnt[k] = max(0, min(emitted, room));
-        }
-        __syncwarp();
+        __syncthreads();
     }
 }
 
@@ -376,8 +401,7 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
 }  // namespace
 
 void launch_orientation(const FrameParams& fp, cudaStream_t s) {
-    dim3 grid(148, fp.nOct);
-    orientation_kernel<<<grid, kOriWarps * 32, 0, s>>>(fp);
+    orientation_kernel<<<148 * 16, kOriThreads, 0, s>>>(fp);
 }
 void launch_compact_oriented(const FrameParams& fp, cudaStream_t s) { compact_oriented_kernel<<<fp.nOct, 1024, 0, s>>>(fp); }
 void launch_descriptor(const FrameParams& fp, cudaStream_t s) {

@@ -312,7 +312,7 @@ int build(b200sift_detector* d) {
         CU(cudaEventCreateWithFlags(&d->ev_join[o], cudaEventDisableTiming));
     }
     d->tail_first = d->nOct;
-    for (int o = d->nOct - 1; o >= 0 && fp.oct[o].w * fp.oct[o].h <= kTailPixels; o--) d->tail_first = o;
+    for (int o = d->nOct - 1; o >= 0 && tail_octave(fp.oct[o].w, fp.oct[o].h); o--) d->tail_first = o;
 
     // One graph for the whole frame.
     CU(cudaStreamBeginCapture(d->stream, cudaStreamCaptureModeThreadLocal));

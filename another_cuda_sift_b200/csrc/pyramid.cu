@@ -16,7 +16,7 @@ namespace {
 
 constexpr int kTW = 128;      // output columns per CTA (one warp row = 32 lanes x 4 outputs)
 constexpr int kRB = 16;       // output rows per vertical register block
-constexpr int kBlurThreads = 256;
+constexpr int kBlurThreads = 320;  // 10 warps: one vertical-pass sweep covers the 128 + 2R columns of two row blocks
 
 // One CTA: TH = nb*kRB output rows x kTW output columns.
 //  pass 1 (vertical):   each thread owns one column of one row block, keeps kRB+2R input pixels
@@ -158,16 +158,59 @@ struct TailParams {
 };
 
 constexpr int kTailThreads = 1024;
+constexpr int kTailR = 10;  // largest blur radius (21 taps)
+
+// One blur layer of the tail: vertical pass s_cur -> s_tmp, horizontal pass s_tmp -> s_cur (+ global).
+template <int R>
+__device__ __forceinline__ void tail_layer(const Taps& t, float* s_cur, float* s_tmp, const int* s_rtab, const int* s_ctab,
+                                           float* __restrict__ dst, int w, int pitch, int n, int tid) {
+    constexpr int NT = 2 * R + 1;
+    float tap[NT];
+#pragma unroll
+    for (int k = 0; k < NT; k++) tap[k] = t.v[k];
+    for (int i = tid; i < n; i += kTailThreads) {
+        const int y = i / w, x = i - y * w;
+        const int* rt = s_rtab + (y - R + kTailR);
+        float v[NT];
+#pragma unroll
+        for (int k = 0; k < NT; k++) v[k] = s_cur[rt[k] + x];
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < NT; k++) acc = __fmaf_rn(v[k], tap[k], acc);
+        s_tmp[i] = acc;
+    }
+    __syncthreads();
+    for (int i = tid; i < n; i += kTailThreads) {
+        const int y = i / w, x = i - y * w;
+        const int* ct = s_ctab + (x - R + kTailR);
+        const float* row = s_tmp + y * w;
+        float v[NT];
+#pragma unroll
+        for (int k = 0; k < NT; k++) v[k] = row[ct[k]];
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < NT; k++) acc = __fmaf_rn(v[k], tap[k], acc);
+        s_cur[i] = acc;
+        dst[(size_t)y * pitch + x] = acc;
+    }
+    __syncthreads();  // also orders this CTA's global writes of layer 3 before the next octave reads them
+}
 
 __global__ void __launch_bounds__(kTailThreads)
 pyramid_tail_kernel(const __grid_constant__ TailParams tp) {
     __shared__ float s_cur[kTailPixels];
     __shared__ float s_tmp[kTailPixels];
+    // reflect-101 lookup tables for offsets -kTailR .. dim+kTailR (row table pre-multiplied by the width):
+    // the per-tap index is one shared-memory read instead of a modulo
+    __shared__ int s_rtab[kTailMaxDim + 2 * kTailR];
+    __shared__ int s_ctab[kTailMaxDim + 2 * kTailR];
     const int tid = threadIdx.x;
     for (int o = tp.first; o < tp.nOct; o++) {
         const int w = tp.w[o], h = tp.h[o], pitch = tp.pitch[o], n = w * h;
         float* g = tp.gauss[o];
         const size_t ls = (size_t)pitch * h;
+        for (int j = tid; j < h + 2 * kTailR; j += kTailThreads) s_rtab[j] = reflect101(j - kTailR, h) * w;
+        for (int j = tid; j < w + 2 * kTailR; j += kTailThreads) s_ctab[j] = reflect101(j - kTailR, w);
         if (o == tp.first) {  // base layer was produced by the launch before this kernel
             for (int i = tid; i < n; i += kTailThreads) s_cur[i] = g[(size_t)(i / w) * pitch + i % w];
         } else {              // bilinear resample of the previous octave's layer 3 (written by this CTA)
@@ -181,24 +224,14 @@ pyramid_tail_kernel(const __grid_constant__ TailParams tp) {
         }
         __syncthreads();
         for (int l = 1; l < kGaussLayers; l++) {
-            const Taps& t = tp.taps[l];
-            const int r = t.n / 2;
-            for (int i = tid; i < n; i += kTailThreads) {
-                const int y = i / w, x = i - y * w;
-                float acc = 0.f;
-                for (int k = 0; k < t.n; k++) acc = __fmaf_rn(s_cur[reflect101(y + k - r, h) * w + x], t.v[k], acc);
-                s_tmp[i] = acc;
-            }
-            __syncthreads();
             float* dst = g + ls * l;
-            for (int i = tid; i < n; i += kTailThreads) {
-                const int y = i / w, x = i - y * w;
-                float acc = 0.f;
-                for (int k = 0; k < t.n; k++) acc = __fmaf_rn(s_tmp[y * w + reflect101(x + k - r, w)], t.v[k], acc);
-                s_cur[i] = acc;
-                dst[(size_t)y * pitch + x] = acc;
+            switch (tp.taps[l].n / 2) {  // compile-time radius: both passes fully unrolled
+                case 4: tail_layer<4>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
+                case 5: tail_layer<5>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
+                case 6: tail_layer<6>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
+                case 8: tail_layer<8>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
+                default: tail_layer<10>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
             }
-            __syncthreads();  // also orders this CTA's global writes of layer 3 before the next octave reads them
         }
     }
 }
