@@ -126,6 +126,7 @@ match_filter_kernel(const __half* __restrict__ des, int nq, const __half* __rest
     constexpr uint32_t kKcStrideB = TN * 16;
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 1);
     int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);
+    int* s_cand = reinterpret_cast<int*>(s_tmem + 4);  // [kCand][128]: survivor columns of thread tid
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const int q0 = blockIdx.x * kTileM;
@@ -158,7 +159,7 @@ match_filter_kernel(const __half* __restrict__ des, int nq, const __half* __rest
     const uint32_t aQ = smem_u32(sQ), aB = smem_u32(sB);
     uint32_t phase = 0;
     float a1 = INFINITY, a2 = INFINITY, thr = 0.f;
-    int cn = 0, c0 = -1, c1 = -1, c2 = -1, c3 = -1, c4 = -1, c5 = -1, c6 = -1;
+    int cn = 0;
 
     for (int pass = 0; pass < 2; pass++) {
         for (int t0 = t_begin; t0 < t_end; t0 += TN) {
@@ -217,21 +218,9 @@ match_filter_kernel(const __half* __restrict__ des, int nq, const __half* __rest
 #pragma unroll
                     for (int j = 0; j < 32; j++) {
                         const float d = __fadd_rn(na, __fmaf_rn(-2.f, __uint_as_float(v[j]), s_nb[cb * 32 + j]));
-                        if (__any_sync(0xffffffffu, d <= thr)) {  // warp-uniform: survivors are rare
-                            if (d <= thr) {
-                                const int col = t0 + cb * 32 + j;
-                                switch (cn) {
-                                    case 0: c0 = col; break;
-                                    case 1: c1 = col; break;
-                                    case 2: c2 = col; break;
-                                    case 3: c3 = col; break;
-                                    case 4: c4 = col; break;
-                                    case 5: c5 = col; break;
-                                    case 6: c6 = col; break;
-                                    default: break;
-                                }
-                                cn = min(cn + 1, kCand + 1);
-                            }
+                        if (d <= thr) {  // survivors are rare: one predicated shared-memory store each
+                            if (cn < kCand) s_cand[cn * kFilterThreads + tid] = t0 + cb * 32 + j;
+                            cn++;
                         }
                     }
                 }
@@ -244,8 +233,11 @@ match_filter_kernel(const __half* __restrict__ des, int nq, const __half* __rest
     }
     if (q < nq) {
         int4* dst = reinterpret_cast<int4*>(rec + (size_t)q * 32 + chunk);
-        dst[0] = make_int4(cn, c0, c1, c2);
-        dst[1] = make_int4(c3, c4, c5, c6);
+        int c[kCand];
+#pragma unroll
+        for (int i = 0; i < kCand; i++) c[i] = i < cn ? s_cand[i * kFilterThreads + tid] : -1;
+        dst[0] = make_int4(min(cn, kCand + 1), c[0], c[1], c[2]);
+        dst[1] = make_int4(c[3], c[4], c[5], c[6]);
     }
     if (warp == 0) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(TN));
@@ -368,7 +360,7 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
 
 namespace {
 int g_match_path = 0;  // 0 = tensor-core filter + exact re-rank, 1 = all-CUDA-core exact kernel (match.cu)
-constexpr size_t filter_smem(int tn) { return kTileBytes + (size_t)tn * 256 + tn * sizeof(float) + 64; }
+constexpr size_t filter_smem(int tn) { return kTileBytes + (size_t)tn * 256 + tn * sizeof(float) + 64 + kCand * kFilterThreads * sizeof(int); }
 
 template <int TN, bool DBG>
 void launch_filter(dim3 grid, const __half* q, int nq, const __half* t, int nt, int per, CandRec* rec, float* dbg, cudaStream_t s) {
