@@ -4,6 +4,6 @@ Public surface mirrors the reference: CudaSiftConfig, Detector (gpuWarmUpAndAllo
 detectAndCompute / copyToHost) and matchBruteForce; the C ABI lives in include/b200sift.h.
 """
 from ._lib import B200SiftError, build_library, load  # noqa: F401
-from .detector import CudaSiftConfig, Detector, DeviceArray, matchBruteForce  # noqa: F401
+from .detector import CudaSiftConfig, Detector, DeviceArray, HostResults, matchBruteForce  # noqa: F401
 
-__all__ = ["CudaSiftConfig", "Detector", "DeviceArray", "matchBruteForce", "B200SiftError", "build_library", "load"]
+__all__ = ["CudaSiftConfig", "Detector", "DeviceArray", "HostResults", "matchBruteForce", "B200SiftError", "build_library", "load"]

@@ -60,7 +60,7 @@ struct FrameParams {
     float3* out_kpts;    // [numFeatures]
     float4* out_feats;   // [numFeatures]
     __half* out_desc;    // [numFeatures*128]
-    int* total;          // device: keypoints returned by the last frame
+    int* total;          // device: total[0] = keypoints returned by the last frame, total[1] = by the frame before
     float extrema_thr;   // floor(0.5*contrast/nLayers*255) (interface/Detector.cu:362)
     float contrast_thr, edge_thr, sigma;
 };
@@ -83,6 +83,8 @@ void launch_descriptor(const FrameParams& fp, cudaStream_t s);
 
 int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s,
                  float* dbg = nullptr);
+int match_launch_counts(const __half* q, const __half* t, int max_n, const int* counts, int* out, void* scratch,
+                        size_t scratch_bytes, cudaStream_t s);
 int match_launch_simt(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s);
 void match_set_path(int path);
 int match_get_path();

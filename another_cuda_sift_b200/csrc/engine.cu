@@ -77,21 +77,28 @@ struct b200sift_detector {
     Taps init_taps;
     Taps taps[kGaussLayers];
     FrameParams fp;
-    float* d_input = nullptr;
+    // Two input buffers + two captured frame graphs: the H2D copy of frame i+1 runs on the copy stream while
+    // the graph of frame i runs on the main stream.
+    float* d_input[2] = {nullptr, nullptr};
     int in_pitch = 0;
-    uint8_t* d_input_u8 = nullptr;
+    uint8_t* d_input_u8[2] = {nullptr, nullptr};
     size_t u8_pitch = 0;
+    cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
+    unsigned long long frame_no = 0;
     int* d_rowcount_all = nullptr;
     size_t rowcount_bytes = 0;
     __half* d_prev_desc = nullptr;
     int* h_total = nullptr;  // pinned
+    void* match_scratch = nullptr;  // survivor records of the consecutive-frame matcher
+    size_t match_scratch_bytes_ = 0;
     std::vector<void*> allocs;
     cudaStream_t stream = nullptr;
     cudaStream_t side[kSideStreams] = {nullptr, nullptr};
     cudaEvent_t ev_fork[kMaxOctaves] = {nullptr}, ev_join[kMaxOctaves] = {nullptr};
     int tail_first = 0;  // first octave handled by the single-CTA tail kernel
-    cudaGraph_t graph = nullptr;
-    cudaGraphExec_t exec = nullptr;
+    cudaGraph_t graph[2] = {nullptr, nullptr};
+    cudaGraphExec_t exec[2] = {nullptr, nullptr};
     int launches = 0;
     bool have_frame = false;
 };
@@ -132,10 +139,11 @@ int dev_alloc(b200sift_detector* d, T** p, size_t count) {
 
 // The frame pipeline, stages numbered as in Detector::detectAndCompute (Detector.cu:133-233):
 // 0 prev-descriptor copy, 1 pyramid, 3 extrema, 4 refinement, 5 orientation, 6/7 descriptor+gather.
-int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* launches, Profiler* prof = nullptr) {
+int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* launches, Profiler* prof = nullptr, int buf = 0) {
     FrameParams& fp = d->fp;
     int n = 0;
     MARK(B200SIFT_K_COPY);
+    CU(cudaMemcpyAsync(fp.total + 1, fp.total, sizeof(int), cudaMemcpyDeviceToDevice, s));  // previous frame's count
     CU(cudaMemcpyAsync(d->d_prev_desc, fp.out_desc, (size_t)fp.numFeatures * 128 * sizeof(__half),
                        cudaMemcpyDeviceToDevice, s));
     CU(cudaMemsetAsync(d->d_rowcount_all, 0, d->rowcount_bytes, s));
@@ -150,7 +158,7 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
         const size_t ls = (size_t)oc.pitch * oc.h;
         const bool tail = o >= d->tail_first;
         if (o == 0) {
-            launch_blur(d->d_input, d->in_pitch, oc.gauss, oc.pitch, oc.w, oc.h, d->init_taps, s);
+            launch_blur(d->d_input[buf], d->in_pitch, oc.gauss, oc.pitch, oc.w, oc.h, d->init_taps, s);
             MARK(B200SIFT_K_BLUR);
             n++;
         } else if (!tail || o == d->tail_first) {
@@ -250,9 +258,11 @@ int build(b200sift_detector* d) {
     fp.sigma = (float)c.sigma;
 
     d->in_pitch = pitch_floats(c.col_width);
-    if (int rc = dev_alloc(d, &d->d_input, (size_t)d->in_pitch * c.row_width)) return rc;
     d->u8_pitch = ((size_t)c.col_width + 511) / 512 * 512;
-    if (int rc = dev_alloc(d, &d->d_input_u8, d->u8_pitch * c.row_width)) return rc;
+    for (int b = 0; b < 2; b++) {
+        if (int rc = dev_alloc(d, &d->d_input[b], (size_t)d->in_pitch * c.row_width)) return rc;
+        if (int rc = dev_alloc(d, &d->d_input_u8[b], d->u8_pitch * c.row_width)) return rc;
+    }
 
     int rows_total = 0;
     for (int o = 0; o < d->nOct; o++) {
@@ -303,6 +313,12 @@ int build(b200sift_detector* d) {
     if (int rc = dev_alloc(d, &fp.out_feats, (size_t)c.numFeatures)) return rc;
     if (int rc = dev_alloc(d, &fp.out_desc, (size_t)c.numFeatures * 128)) return rc;
     if (int rc = dev_alloc(d, &d->d_prev_desc, (size_t)c.numFeatures * 128)) return rc;
+    d->match_scratch_bytes_ = match_scratch_bytes(c.numFeatures, c.numFeatures);
+    {
+        uint8_t* p = nullptr;
+        if (int rc = dev_alloc(d, &p, d->match_scratch_bytes_)) return rc;
+        d->match_scratch = p;
+    }
     CU(cudaMallocHost(&d->h_total, sizeof(int)));
     *d->h_total = 0;
     CU(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
@@ -314,13 +330,20 @@ int build(b200sift_detector* d) {
     d->tail_first = d->nOct;
     for (int o = d->nOct - 1; o >= 0 && tail_octave(fp.oct[o].w, fp.oct[o].h); o--) d->tail_first = o;
 
-    // One graph for the whole frame.
-    CU(cudaStreamBeginCapture(d->stream, cudaStreamCaptureModeThreadLocal));
-    int rc = enqueue_frame(d, d->stream, 7, &d->launches);
-    cudaError_t e = cudaStreamEndCapture(d->stream, &d->graph);
-    if (rc) return rc;
-    CU(e);
-    CU(cudaGraphInstantiate(&d->exec, d->graph, 0));
+    CU(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
+    for (int b = 0; b < 2; b++) {
+        CU(cudaEventCreateWithFlags(&d->ev_copied[b], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&d->ev_consumed[b], cudaEventDisableTiming));
+    }
+    // One graph for the whole frame (one instance per input buffer).
+    for (int b = 0; b < 2; b++) {
+        CU(cudaStreamBeginCapture(d->stream, cudaStreamCaptureModeThreadLocal));
+        int rc = enqueue_frame(d, d->stream, 7, &d->launches, nullptr, b);
+        cudaError_t e = cudaStreamEndCapture(d->stream, &d->graph[b]);
+        if (rc) return rc;
+        CU(e);
+        CU(cudaGraphInstantiate(&d->exec[b], d->graph[b], 0));
+    }
     CU(cudaStreamSynchronize(d->stream));
     return 0;
 }
@@ -374,8 +397,13 @@ int b200sift_create(const b200sift_config* cfg, b200sift_detector** out) {
 int b200sift_destroy(b200sift_detector* d) {
     if (!d) return 0;
     if (d->stream) cudaStreamSynchronize(d->stream);
-    if (d->exec) cudaGraphExecDestroy(d->exec);
-    if (d->graph) cudaGraphDestroy(d->graph);
+    for (int b = 0; b < 2; b++) {
+        if (d->exec[b]) cudaGraphExecDestroy(d->exec[b]);
+        if (d->graph[b]) cudaGraphDestroy(d->graph[b]);
+        if (d->ev_copied[b]) cudaEventDestroy(d->ev_copied[b]);
+        if (d->ev_consumed[b]) cudaEventDestroy(d->ev_consumed[b]);
+    }
+    if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
     for (void* p : d->allocs) cudaFree(p);
     if (d->h_total) cudaFreeHost(d->h_total);
     if (d->stream) cudaStreamDestroy(d->stream);
@@ -398,8 +426,21 @@ int b200sift_octave_info(const b200sift_detector* d, int o, int* dims) {
     return 0;
 }
 
-static int launch_frame(b200sift_detector* d) {
-    CU(cudaGraphLaunch(d->exec, d->stream));
+// Frame i uses input buffer i & 1. Host frames are copied on the copy stream, which only waits until the
+// frame that last read this buffer (i - 2) has consumed it, so the copy overlaps the graph of frame i - 1.
+static int begin_frame(b200sift_detector* d, int* buf, bool on_copy_stream) {
+    *buf = (int)(d->frame_no & 1);
+    if (on_copy_stream) CU(cudaStreamWaitEvent(d->copy_stream, d->ev_consumed[*buf], 0));
+    return 0;
+}
+static int launch_frame(b200sift_detector* d, int buf, bool from_copy_stream) {
+    if (from_copy_stream) {
+        CU(cudaEventRecord(d->ev_copied[buf], d->copy_stream));
+        CU(cudaStreamWaitEvent(d->stream, d->ev_copied[buf], 0));
+    }
+    CU(cudaGraphLaunch(d->exec[buf], d->stream));
+    CU(cudaEventRecord(d->ev_consumed[buf], d->stream));
+    d->frame_no++;
     d->have_frame = true;
     return 0;
 }
@@ -408,9 +449,11 @@ int b200sift_detect_host_async(b200sift_detector* d, const float* img, int rows,
     if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
     if (rows != d->cfg.row_width || cols != d->cfg.col_width)
         return fail(B200SIFT_EINVAL, "image is %dx%d, detector was configured for %dx%d", cols, rows, d->cfg.col_width, d->cfg.row_width);
-    CU(cudaMemcpy2DAsync(d->d_input, (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
-                         cudaMemcpyHostToDevice, d->stream));
-    return launch_frame(d);
+    int buf = 0;
+    if (int rc = begin_frame(d, &buf, true)) return rc;
+    CU(cudaMemcpy2DAsync(d->d_input[buf], (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
+                         cudaMemcpyHostToDevice, d->copy_stream));
+    return launch_frame(d, buf, true);
 }
 
 int b200sift_sync(b200sift_detector* d, int* total) {
@@ -430,18 +473,41 @@ int b200sift_detect_device_async(b200sift_detector* d, const float* d_img, size_
     if (!d || !d_img) return fail(B200SIFT_EINVAL, "null argument");
     const int cols = d->cfg.col_width, rows = d->cfg.row_width;
     if (pitch_bytes < (size_t)cols * 4) return fail(B200SIFT_EINVAL, "pitch smaller than a row");
-    CU(cudaMemcpy2DAsync(d->d_input, (size_t)d->in_pitch * 4, d_img, pitch_bytes, (size_t)cols * 4, rows,
+    int buf = 0;
+    if (int rc = begin_frame(d, &buf, false)) return rc;
+    CU(cudaMemcpy2DAsync(d->d_input[buf], (size_t)d->in_pitch * 4, d_img, pitch_bytes, (size_t)cols * 4, rows,
                          cudaMemcpyDeviceToDevice, d->stream));
-    return launch_frame(d);
+    return launch_frame(d, buf, false);
 }
 
 int b200sift_detect_host_u8_async(b200sift_detector* d, const uint8_t* img, int rows, int cols) {
     if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
     if (rows != d->cfg.row_width || cols != d->cfg.col_width)
         return fail(B200SIFT_EINVAL, "image is %dx%d, detector was configured for %dx%d", cols, rows, d->cfg.col_width, d->cfg.row_width);
-    CU(cudaMemcpy2DAsync(d->d_input_u8, d->u8_pitch, img, (size_t)cols, (size_t)cols, rows, cudaMemcpyHostToDevice, d->stream));
-    launch_u8_to_float(d->d_input_u8, d->u8_pitch, d->d_input, d->in_pitch, cols, rows, d->stream);
-    return launch_frame(d);
+    int buf = 0;
+    if (int rc = begin_frame(d, &buf, true)) return rc;
+    CU(cudaMemcpy2DAsync(d->d_input_u8[buf], d->u8_pitch, img, (size_t)cols, (size_t)cols, rows, cudaMemcpyHostToDevice, d->copy_stream));
+    launch_u8_to_float(d->d_input_u8[buf], d->u8_pitch, d->d_input[buf], d->in_pitch, cols, rows, d->copy_stream);
+    return launch_frame(d, buf, true);
+}
+
+int b200sift_match_consecutive_async(b200sift_detector* d, int* d_out_idx) {
+    if (!d || !d_out_idx) return fail(B200SIFT_EINVAL, "null argument");
+    if (match_launch_counts(d->d_prev_desc, d->fp.out_desc, d->cfg.numFeatures, d->fp.total, d_out_idx, d->match_scratch,
+                            d->match_scratch_bytes_, d->stream))
+        return fail(B200SIFT_EINVAL, "matcher scratch too small");
+    CU(cudaGetLastError());
+    return 0;
+}
+
+int b200sift_copy_results_async(b200sift_detector* d, float* kpts3, float* feats4, uint16_t* desc, int* counts2) {
+    if (!d) return fail(B200SIFT_EINVAL, "null argument");
+    const size_t n = (size_t)d->cfg.numFeatures;
+    if (kpts3) CU(cudaMemcpyAsync(kpts3, d->fp.out_kpts, n * sizeof(float3), cudaMemcpyDeviceToHost, d->stream));
+    if (feats4) CU(cudaMemcpyAsync(feats4, d->fp.out_feats, n * sizeof(float4), cudaMemcpyDeviceToHost, d->stream));
+    if (desc) CU(cudaMemcpyAsync(desc, d->fp.out_desc, n * 128 * sizeof(__half), cudaMemcpyDeviceToHost, d->stream));
+    if (counts2) CU(cudaMemcpyAsync(counts2, d->fp.total, 2 * sizeof(int), cudaMemcpyDeviceToHost, d->stream));
+    return 0;
 }
 
 void* b200sift_stream(b200sift_detector* d) { return d ? (void*)d->stream : nullptr; }
@@ -513,9 +579,11 @@ int b200sift_debug_get_taps(b200sift_detector* d, int which, float* out, int max
 int b200sift_debug_run_stages(b200sift_detector* d, const float* img, int rows, int cols, int last_stage) {
     if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
     if (rows != d->cfg.row_width || cols != d->cfg.col_width) return fail(B200SIFT_EINVAL, "image size mismatch");
-    CU(cudaMemcpy2DAsync(d->d_input, (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
+    CU(cudaStreamSynchronize(d->stream));
+    const int buf = (int)(d->frame_no & 1);
+    CU(cudaMemcpy2DAsync(d->d_input[buf], (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
                          cudaMemcpyHostToDevice, d->stream));
-    int rc = enqueue_frame(d, d->stream, last_stage, nullptr);
+    int rc = enqueue_frame(d, d->stream, last_stage, nullptr, nullptr, buf);
     if (rc) return rc;
     if (last_stage >= 6) d->have_frame = true;
     CU(cudaStreamSynchronize(d->stream));
@@ -529,10 +597,11 @@ int b200sift_time_frames(b200sift_detector* d, int warmup, int iters, float* ms_
     cudaEvent_t e0, e1;
     CU(cudaEventCreate(&e0));
     CU(cudaEventCreate(&e1));
-    for (int i = 0; i < warmup; i++) CU(cudaGraphLaunch(d->exec, d->stream));
+    const int tb = (int)((d->frame_no + 1) & 1);  // buffer of the last frame
+    for (int i = 0; i < warmup; i++) CU(cudaGraphLaunch(d->exec[tb], d->stream));
     CU(cudaStreamSynchronize(d->stream));
     CU(cudaEventRecord(e0, d->stream));
-    for (int i = 0; i < iters; i++) CU(cudaGraphLaunch(d->exec, d->stream));
+    for (int i = 0; i < iters; i++) CU(cudaGraphLaunch(d->exec[tb], d->stream));
     CU(cudaEventRecord(e1, d->stream));
     CU(cudaEventSynchronize(e1));
     float ms = 0.f;
@@ -552,7 +621,7 @@ int b200sift_profile_frame(b200sift_detector* d, int warmup, int iters, float* m
     std::vector<int> cnt(B200SIFT_K_COUNT, 0);
     for (int it = 0; it < warmup + iters; it++) {
         prof.used = 0;
-        int rc = enqueue_frame(d, d->stream, 7, nullptr, &prof);
+        int rc = enqueue_frame(d, d->stream, 7, nullptr, &prof, (int)((d->frame_no + 1) & 1));
         if (rc) return rc;
         CU(cudaStreamSynchronize(d->stream));
         if (it < warmup) continue;

@@ -116,7 +116,12 @@ __device__ __forceinline__ float row_norm2(const uint8_t* s, int row) {
 template <int TN, bool DBG>
 __global__ void __launch_bounds__(kFilterThreads)
 match_filter_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per,
-                    CandRec* __restrict__ rec, float* __restrict__ dbg) {
+                    CandRec* __restrict__ rec, float* __restrict__ dbg, const int* __restrict__ counts) {
+    if (counts) {  // sizes known only on the device (consecutive-frame matching without a host round trip)
+        nt = counts[0];
+        nq = counts[1];
+        per = (int)ceilf((float)nt / 32.f);
+    }
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sQ = smem;
     uint8_t* sB = smem + kTileBytes;
@@ -134,6 +139,7 @@ match_filter_kernel(const __half* __restrict__ des, int nq, const __half* __rest
     const int t_begin = chunk * per;
     const int t_end = min(nt, t_begin + per);
     const int q = q0 + tid;
+    if (q0 >= nq) return;    // grid was sized for the largest possible query set
     if (t_begin >= t_end) {  // empty chunk (uniform for the CTA): nothing to score
         if (q < nq) rec[(size_t)q * 32 + chunk].n = 0;
         return;
@@ -265,7 +271,12 @@ constexpr int kListCap = 32 * kCand;
 
 __global__ void __launch_bounds__(kRerankWarps * 32)
 match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per,
-                    const CandRec* __restrict__ rec, int* __restrict__ out_idx) {
+                    const CandRec* __restrict__ rec, int* __restrict__ out_idx, const int* __restrict__ counts) {
+    if (counts) {
+        nt = counts[0];
+        nq = counts[1];
+        per = (int)ceilf((float)nt / 32.f);
+    }
     __shared__ int s_col[kRerankWarps][kListCap];
     __shared__ unsigned char s_chunk[kRerankWarps][kListCap];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -363,13 +374,14 @@ int g_match_path = 0;  // 0 = tensor-core filter + exact re-rank, 1 = all-CUDA-c
 constexpr size_t filter_smem(int tn) { return kTileBytes + (size_t)tn * 256 + tn * sizeof(float) + 64 + kCand * kFilterThreads * sizeof(int); }
 
 template <int TN, bool DBG>
-void launch_filter(dim3 grid, const __half* q, int nq, const __half* t, int nt, int per, CandRec* rec, float* dbg, cudaStream_t s) {
+void launch_filter(dim3 grid, const __half* q, int nq, const __half* t, int nt, int per, CandRec* rec, float* dbg, cudaStream_t s,
+                   const int* counts = nullptr) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(match_filter_kernel<TN, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)filter_smem(TN));
         attr_set = true;
     }
-    match_filter_kernel<TN, DBG><<<grid, kFilterThreads, filter_smem(TN), s>>>(q, nq, t, nt, per, rec, dbg);
+    match_filter_kernel<TN, DBG><<<grid, kFilterThreads, filter_smem(TN), s>>>(q, nq, t, nt, per, rec, dbg, counts);
 }
 }  // namespace
 
@@ -398,7 +410,22 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
         if (per <= 128) launch_filter<128, false>(grid, q, nq, t, nt, per, rec, dbg, s);
         else launch_filter<256, false>(grid, q, nq, t, nt, per, rec, dbg, s);
     }
-    match_rerank_kernel<<<(nq + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, nq, t, nt, per, rec, out);
+    match_rerank_kernel<<<(nq + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, nq, t, nt, per, rec, out, nullptr);
+    return 0;
+}
+
+// Same matcher with the set sizes read on the device: counts[0] = train rows, counts[1] = query rows, both
+// <= max_n. Grids are sized for max_n; surplus CTAs exit at once.
+int match_launch_counts(const __half* q, const __half* t, int max_n, const int* counts, int* out, void* scratch,
+                        size_t scratch_bytes, cudaStream_t s) {
+    if (max_n <= 0) return 0;
+    if (scratch_bytes < match_scratch_bytes(max_n, max_n)) return -1;
+    CandRec* rec = static_cast<CandRec*>(scratch);
+    const int per_max = (max_n + 31) / 32;
+    dim3 grid((max_n + kTileM - 1) / kTileM, 32);
+    if (per_max <= 128) launch_filter<128, false>(grid, q, max_n, t, max_n, per_max, rec, nullptr, s, counts);
+    else launch_filter<256, false>(grid, q, max_n, t, max_n, per_max, rec, nullptr, s, counts);
+    match_rerank_kernel<<<(max_n + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, max_n, t, max_n, per_max, rec, out, counts);
     return 0;
 }
 

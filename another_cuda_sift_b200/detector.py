@@ -162,6 +162,41 @@ class Detector:
                                              self.final_features.ctypes.data, self.descriptors.ctypes.data,
                                              int(descriptor)))
 
+    # -- pipelined (batched-frame) use: nothing below blocks the host
+    def matchConsecutiveAsync(self, out=None):
+        """matchBruteForce(prev_descriptor, previous total, device_descriptor, this total) as
+        tool/extract_and_match_example.cc:82 calls it, enqueued behind the current frame with both sizes
+        read on the device. Returns a torch int32 CUDA tensor [numFeatures]; entries beyond the previous
+        frame's total are left untouched."""
+        import torch
+
+        if out is None:
+            out = torch.full((self.config.numFeatures,), -1, dtype=torch.int32, device="cuda")
+        check(self.lib.b200sift_match_consecutive_async(self._handle(), out.data_ptr()))
+        return out
+
+    def copyResultsAsync(self, host: "HostResults") -> None:
+        """All numFeatures result slots + {total, previous total} to pinned host buffers, behind the frame."""
+        check(self.lib.b200sift_copy_results_async(self._handle(), host.kpts.data_ptr(), host.feats.data_ptr(),
+                                                   host.desc.data_ptr(), host.counts.data_ptr()))
+
+    def detectAndComputeBatch(self, frames, results, match_out=None):
+        """Frames of a batch, pipelined: the host->device copy of frame i+1 overlaps the graph of frame i;
+        results[i] (HostResults) receives frame i; match_out[i] (pinned int32 torch tensors), when given,
+        receives the matches of frame i-1 -> frame i. One synchronisation at the end."""
+        import torch
+
+        ext = torch.cuda.ExternalStream(self.stream)
+        idx = [torch.empty(self.config.numFeatures, dtype=torch.int32, device="cuda") for _ in range(2)] if match_out is not None else None
+        for i, f in enumerate(frames):
+            self.detectAndComputeAsync(f)
+            if match_out is not None:
+                self.matchConsecutiveAsync(idx[i & 1])
+                with torch.cuda.stream(ext):
+                    match_out[i].copy_(idx[i & 1], non_blocking=True)
+            self.copyResultsAsync(results[i])
+        self.synchronize()
+
     @property
     def stream(self) -> int:
         return int(self.lib.b200sift_stream(self._handle()) or 0)
@@ -210,6 +245,26 @@ class Detector:
         out = np.zeros(64, np.float32)
         n = check(self.lib.b200sift_debug_get_taps(self._handle(), which, out.ctypes.data, 64))
         return out[:n].copy()
+
+
+class HostResults:
+    """Pinned host buffers for one frame's results (Detector.copyResultsAsync): kpts [n,3] f32, feats [n,4] f32,
+    desc [n,128] f16, counts [2] i32 = {total, previous frame's total}. Only the first counts[0] rows are valid."""
+
+    def __init__(self, num_features: int):
+        import torch
+
+        self.kpts = torch.zeros(num_features, 3, dtype=torch.float32).pin_memory()
+        self.feats = torch.zeros(num_features, 4, dtype=torch.float32).pin_memory()
+        self.desc = torch.zeros(num_features, 128, dtype=torch.float16).pin_memory()
+        self.counts = torch.zeros(2, dtype=torch.int32).pin_memory()
+
+    @property
+    def total(self) -> int:
+        return int(self.counts[0])
+
+    def nbytes(self) -> int:
+        return self.kpts.numel() * 4 + self.feats.numel() * 4 + self.desc.numel() * 2 + 8
 
 
 def matchBruteForce(des, num_des: int, src, num_src: int, stream: int = 0, out=None):

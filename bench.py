@@ -11,7 +11,8 @@ each rank has its own frames and there is NO collective on the data path ("scali
 
   value  frames/s over all ranks, inputs resident in HBM (device-resident frames > L2 per step)
   e2e    the same through the reference-facing API with HOST buffers: detectAndCompute(host image) ->
-         copyToHost(descriptors) -> matchBruteForce -> indices to host, per frame, copies inside the timing
+         results (keypoints, features, descriptors, match indices) to pinned host memory, through the batched
+         API Detector.detectAndComputeBatch (H2D of frame i+1 overlaps the graph of frame i), copies inside the timing
   roofline       dominant kernel class, algorithmic bytes / CUDA-event time vs MEASURED_PEAKS.json
   cpu_baseline   the CPU restatement (oracle/) timed on this box's host cores on a bounded sample
   --impl reference   the UNMODIFIED reference CUDA build (oracle/_ref, its own public API and kernels)
@@ -186,29 +187,27 @@ def run_b200(args, world, rank, local):
     launches_frame = det.launches_per_frame()
     state = {"prev": 0, "kpts": 0, "launches": 0, "d2h": 0}
 
+    from another_cuda_sift_b200 import HostResults
+
+    results = [HostResults(NUM_FEATURES) for _ in range(F)]
+    match_host = [torch.empty(NUM_FEATURES, dtype=torch.int32).pin_memory() for _ in range(F)]
+    h_np = [h.numpy() for h in h_frames]
+    n_match_launches = lib.b200sift_match_launches(NUM_FEATURES, NUM_FEATURES)
+
     def step_resident():
+        # inputs already in HBM; frame graph + consecutive-frame matcher per frame, sizes stay on the device,
+        # one host synchronisation per step
         for i in range(F):
             det.detectAndComputeAsync(d_frames[i])
-            n = det.synchronize()
-            state["launches"] += launches_frame
-            if state["prev"] > 0 and n > 0:
-                matchBruteForce(det.prev_descriptor, state["prev"], det.device_descriptor, n, stream=det.stream, out=idx_dev)
-                state["launches"] += lib.b200sift_match_launches(state["prev"], n)
-            state["prev"] = n
-            state["kpts"] += n
+            det.matchConsecutiveAsync(idx_dev)
+        det.synchronize()
+        state["launches"] += F * (launches_frame + n_match_launches)
 
     def step_e2e():
-        for i in range(F):
-            det.detectAndCompute(h_frames[i].numpy())  # H2D from pinned memory inside, blocks like the reference
-            det.copyToHost(True)                        # keypoints + features + descriptors -> host
-            n = det.total_size
-            state["d2h"] += n * (12 + 16 + 256)
-            if state["prev"] > 0 and n > 0:
-                matchBruteForce(det.prev_descriptor, state["prev"], det.device_descriptor, n, stream=det.stream, out=idx_dev)
-                idx_host[: state["prev"]].copy_(idx_dev[: state["prev"]], non_blocking=True)
-                stream.synchronize()
-                state["d2h"] += state["prev"] * 4
-            state["prev"] = n
+        # the batched-frame public API with HOST buffers: pinned H2D of every frame (overlapping the previous
+        # frame's graph), keypoints + features + descriptors + match indices back to pinned host memory
+        det.detectAndComputeBatch(h_np, results, match_host)
+        state["d2h"] += F * (results[0].nbytes() + NUM_FEATURES * 4)
 
     def timed(step_fn, steps, warmup):
         with torch.cuda.stream(stream):
@@ -231,10 +230,12 @@ def run_b200(args, world, rank, local):
     sampler.start()
     ms_total, wall = timed(step_resident, args.steps, args.warmup)
     clocks = sampler.stop()
-    kpts_per_frame = state["kpts"] / (args.steps * F)
+    kpts_per_frame = 0.0
     launches = state["launches"]
     ms_e2e, _ = (ms_total, 0) if args.quick else timed(step_e2e, args.steps, args.warmup)
-    d2h_per_step = state["d2h"] / args.steps
+    d2h_per_step = state["d2h"] / args.steps if not args.quick else 0
+    if not args.quick:
+        kpts_per_frame = float(np.mean([r.total for r in results]))
 
     total_frames = sum_over_ranks(F * args.steps, world)
     value = total_frames / (ms_total * 1e-3)

@@ -112,6 +112,17 @@ B200SIFT_API int b200sift_launches_per_frame(const b200sift_detector* det);
  * bracketed by CUDA events on the detector's stream after `warmup` launches. */
 B200SIFT_API int b200sift_time_frames(b200sift_detector* det, int warmup, int iters, float* ms_per_frame);
 
+/* Pipelined (batched-frame) use, no host synchronisation per frame. After b200sift_detect_*_async:
+ *  - b200sift_match_consecutive_async: matchBruteForce(prev_descriptor, previous total, device_descriptor, this
+ *    total) exactly as tool/extract_and_match_example.cc:82 calls it, with both sizes read on the device;
+ *    d_out_idx = int[numFeatures] on the device (entries beyond the previous total are left untouched);
+ *  - b200sift_copy_results_async: all numFeatures slots of kpts / feats / desc (any may be NULL) and
+ *    counts2[0..1] = {this frame's total, previous frame's total} to (pinned) host memory.
+ * Both are enqueued on the detector's stream, i.e. after the frame and before the next one overwrites its
+ * results; host frames of later b200sift_detect_host_async calls are copied on a second stream meanwhile. */
+B200SIFT_API int b200sift_match_consecutive_async(b200sift_detector* det, int* d_out_idx);
+B200SIFT_API int b200sift_copy_results_async(b200sift_detector* det, float* kpts3, float* feats4, uint16_t* desc, int* counts2);
+
 /* Per-kernel-class device time of one frame (ms, averaged over `iters` eager frames with a CUDA event
  * after every launch on the detector's stream): ms_per_class[B200SIFT_K_COUNT]; launches_per_class (may
  * be NULL) = launches (event intervals) charged to each class per frame. bench.py's roofline figures

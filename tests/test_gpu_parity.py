@@ -196,3 +196,46 @@ def test_tiny_and_ragged_sizes_vs_cpu_oracle(cols, rows):
         assert np.array_equal(det.debug_gauss(oi).view(np.uint32), cpu.stack(oi, "gauss").view(np.uint32)), oi
         c, d = cpu.counts(oi), det.debug_counts(oi)
         assert (d["P"], d["M"]) == (c["P"], c["M"])
+
+
+def test_pipelined_batch_equals_blocking_frames():
+    """Batched frames (copy of frame i+1 overlapping the graph of frame i, device-side match sizes, one sync
+    per batch) give bit-identical results and matches to the blocking per-frame calls of the reference API."""
+    import torch
+
+    from another_cuda_sift_b200 import HostResults, matchBruteForce
+    from another_cuda_sift_b200.synth import next_frame, synth_frame
+
+    cols, rows, nf = 640, 360, 3000
+    frames = [synth_frame(rows, cols, 31)]
+    for i in range(1, 6):
+        frames.append(next_frame(frames[-1], 31 + i))
+    # blocking reference-style loop
+    det = _det(cols, rows, nf)
+    want, want_idx, prev_n = [], [], 0
+    for f in frames:
+        det.detectAndCompute(f)
+        r = _res(det)
+        want.append((r["n"], r["kpts"][:r["n"]].copy(), r["feats"][:r["n"]].copy(), r["desc"][:r["n"]].copy()))
+        if prev_n:
+            idx = matchBruteForce(det.prev_descriptor, prev_n, det.device_descriptor, r["n"],
+                                  stream=det.stream).cpu().numpy()
+            torch.cuda.synchronize()
+            want_idx.append(idx)
+        else:
+            want_idx.append(None)
+        prev_n = r["n"]
+    # pipelined batch on a fresh detector (same slot history)
+    det2 = _det(cols, rows, nf)
+    res = [HostResults(nf) for _ in frames]
+    midx = [torch.full((nf,), -7, dtype=torch.int32).pin_memory() for _ in frames]
+    pinned = [torch.from_numpy(f).pin_memory().numpy() for f in frames]
+    det2.detectAndComputeBatch(pinned, res, midx)
+    for i, (n, k, f, d) in enumerate(want):
+        assert res[i].total == n
+        assert int(res[i].counts[1]) == (want[i - 1][0] if i else 0)
+        assert np.array_equal(res[i].kpts[:n].numpy(), k) and np.array_equal(res[i].feats[:n].numpy(), f)
+        assert np.array_equal(res[i].desc[:n].numpy().view(np.uint16), d.view(np.uint16))
+        if i:
+            assert np.array_equal(midx[i][:want[i - 1][0]].numpy(), want_idx[i]), i
+            assert (want_idx[i] >= 0).mean() > 0.2
