@@ -640,6 +640,44 @@ int b200sift_profile_frame(b200sift_detector* d, int warmup, int iters, float* m
     return 0;
 }
 
+// In-graph cumulative stage times: the frame graph truncated after the pyramid (1), extrema (3), refinement
+// (4), orientation (5) and complete (7), each captured and replayed `iters` times on the last frame's input.
+int b200sift_time_stages(b200sift_detector* d, int iters, float* ms5) {
+    if (!d || !ms5 || iters <= 0) return fail(B200SIFT_EINVAL, "bad argument");
+    const int stages[5] = {1, 3, 4, 5, 7};
+    const int buf = (int)((d->frame_no + 1) & 1);
+    cudaEvent_t e0, e1;
+    CU(cudaEventCreate(&e0));
+    CU(cudaEventCreate(&e1));
+    for (int i = 0; i < 5; i++) {
+        cudaGraph_t g = nullptr;
+        cudaGraphExec_t x = nullptr;
+        CU(cudaStreamSynchronize(d->stream));
+        CU(cudaStreamBeginCapture(d->stream, cudaStreamCaptureModeThreadLocal));
+        int rc = enqueue_frame(d, d->stream, stages[i], nullptr, nullptr, buf);
+        cudaError_t e = cudaStreamEndCapture(d->stream, &g);
+        if (rc) return rc;
+        CU(e);
+        CU(cudaGraphInstantiate(&x, g, 0));
+        for (int k = 0; k < 5; k++) CU(cudaGraphLaunch(x, d->stream));
+        CU(cudaEventRecord(e0, d->stream));
+        for (int k = 0; k < iters; k++) CU(cudaGraphLaunch(x, d->stream));
+        CU(cudaEventRecord(e1, d->stream));
+        CU(cudaEventSynchronize(e1));
+        float ms = 0.f;
+        CU(cudaEventElapsedTime(&ms, e0, e1));
+        ms5[i] = ms / (float)iters;
+        cudaGraphExecDestroy(x);
+        cudaGraphDestroy(g);
+    }
+    // leave complete results behind
+    CU(cudaGraphLaunch(d->exec[buf], d->stream));
+    CU(cudaStreamSynchronize(d->stream));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return 0;
+}
+
 // ---- matcher
 namespace {
 std::mutex g_scratch_mu;

@@ -219,6 +219,12 @@ class Detector:
         check(self.lib.b200sift_profile_frame(self._handle(), warmup, iters, ms, cnt))
         return {k: dict(ms=float(ms[i]), launches=int(cnt[i])) for i, k in enumerate(self.KERNEL_CLASSES)}
 
+    def time_stages(self, iters: int = 50) -> dict:
+        """Cumulative in-graph ms after pyramid / extrema / refine / orientation / descriptor."""
+        ms = (C.c_float * 5)()
+        check(self.lib.b200sift_time_stages(self._handle(), iters, ms))
+        return dict(zip(("pyramid", "extrema", "refine", "orientation", "descriptor"), [float(v) for v in ms]))
+
     def debug_run_stages(self, image: np.ndarray, last_stage: int) -> None:
         image = np.ascontiguousarray(image, dtype=np.float32)
         check(self.lib.b200sift_debug_run_stages(self._handle(), image.ctypes.data, image.shape[0], image.shape[1], last_stage))

@@ -247,7 +247,7 @@ def run_b200(args, world, rank, local):
         det.detectAndCompute(d_frames[0])
         graph_ms = det.time_frames(5, 5 if args.quick else 100)
         prof = det.profile_frame(1 if args.quick else 3, 1 if args.quick else 20)
-        extra = dict(graph_ms=graph_ms, prof=prof, kpts=det.total_size)
+        extra = dict(graph_ms=graph_ms, prof=prof, kpts=det.total_size, stages=det.time_stages(5 if args.quick else 50))
     return dict(value=value, ms_per_step=ms_total / args.steps, wall_ms=wall, e2e_value=e2e_value,
                 e2e_ms_per_step=ms_e2e / args.steps, clocks=clocks, kpts_per_frame=kpts_per_frame,
                 launches=launches, d2h_per_step=d2h_per_step, frames=frames, det=det, extra=extra)
@@ -435,6 +435,7 @@ def main():
         "roofline_frame": {"bytes": frame_bytes, "achieved": frame_bytes / (ex["graph_ms"] * 1e-3) / 1e9,
                            "frac": frame_bytes / (ex["graph_ms"] * 1e-3) / 1e9 / hbm_peak},
         "kernel_ms_per_frame": {k: round(v["ms"], 5) for k, v in prof.items()},
+        "graph_cumulative_ms": {k: round(v, 5) for k, v in ex["stages"].items()},
     }
     if world == 1 and not args.no_cpu_baseline and not args.quick:
         line["cpu_baseline"] = cpu_port_baseline(r["frames"])

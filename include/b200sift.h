@@ -140,6 +140,10 @@ B200SIFT_API int b200sift_copy_results_async(b200sift_detector* det, float* kpts
 B200SIFT_API int b200sift_profile_frame(b200sift_detector* det, int warmup, int iters, float* ms_per_class,
                            int* launches_per_class);
 
+/* Cumulative in-graph times (ms): the frame graph truncated after the pyramid, extrema, refinement, orientation
+ * and complete, each replayed `iters` times on the last frame's input: ms5[0..4]. */
+B200SIFT_API int b200sift_time_stages(b200sift_detector* det, int iters, float* ms5);
+
 /* sift_cuda::matchBruteForce (sift_func/Match.cuh:9-14, Match.cu:8-33): for each of the nq query
  * descriptors (half[nq*128]) the index of its nearest train descriptor (half[nt*128]) under the
  * reference's half-precision L2 recipe, or -1 if the 0.8 ratio test fails. Device pointers;
