@@ -54,6 +54,7 @@ struct OctParams {
 struct FrameParams {
     OctParams oct[kMaxOctaves];
     int nOct;
+    int o_begin, o_end;  // octave range this launch works on (the frame graph runs octave 0 and the rest as parallel branches)
     int numFeatures;
     int det_tasks;       // total warp tasks of the detect kernel
     int rows_total;      // total (scale,row) entries over all octaves
@@ -72,13 +73,13 @@ void launch_u8_to_float(const uint8_t* in, size_t in_pitch, float* out, int out_
 void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s);
 void launch_downsample(const float* in, int in_pitch, int iw, int ih, float* out, int out_pitch, int ow, int oh, cudaStream_t s);
 void launch_pyramid_tail(const FrameParams& fp, const Taps* taps, int first_octave, cudaStream_t s);
-void launch_detect(const FrameParams& fp, cudaStream_t s);       // bitmask + row counts
-void launch_scan_rows(const FrameParams& fp, cudaStream_t s);    // row offsets, P
-void launch_scatter(const FrameParams& fp, cudaStream_t s);      // ordered candidate list
-void launch_refine(const FrameParams& fp, cudaStream_t s);       // Taylor refinement + tests
-void launch_compact_refined(const FrameParams& fp, cudaStream_t s);
-void launch_orientation(const FrameParams& fp, cudaStream_t s);
-void launch_compact_oriented(const FrameParams& fp, cudaStream_t s);
+void launch_detect(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);       // bitmask + row counts
+void launch_scan_rows(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);    // row offsets, P
+void launch_scatter(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);      // ordered candidate list
+void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);       // Taylor refinement + tests
+void launch_compact_refined(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
+void launch_orientation(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
+void launch_compact_oriented(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 void launch_descriptor(const FrameParams& fp, cudaStream_t s);
 
 int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s,
@@ -91,6 +92,13 @@ int match_get_path();
 size_t match_scratch_bytes(int nq, int nt);
 int match_num_launches(int nq, int nt);
 
+inline FrameParams octave_range(const FrameParams& fp, int o_begin, int o_end) {
+    FrameParams r = fp;
+    r.o_begin = o_begin;
+    r.o_end = o_end;
+    return r;
+}
+
 // reflect-101 border index (same mapping as image_func/Filter.cuh:52-66).
 __host__ __device__ inline int reflect101(int idx, int length) {
     if (length <= 1) return 0;
@@ -102,5 +110,45 @@ __host__ __device__ inline int reflect101(int idx, int length) {
     }
     return idx;
 }
+
+#ifdef __CUDACC__
+// Single-CTA (1024 threads) exclusive scan over n small integers with one barrier: warp w owns
+// the contiguous segment [w*seg, (w+1)*seg), sums it, the 32 warp totals are combined by every
+// warp from shared memory, and the segment is walked a second time (L1-resident) to hand each
+// element its exclusive prefix and the grand total. Returns the total.
+template <class Load, class Emit>
+__device__ __forceinline__ int block_scan_1024(int n, Load load, Emit emit) {
+    __shared__ int s_ws[32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int seg = ((n + 1023) >> 10) << 5;
+    const int lo = warp * seg, hi = min(n, lo + seg);
+    int local = 0;
+    for (int i = lo + lane; i < hi; i += 32) local += load(i);
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) local += __shfl_xor_sync(0xffffffffu, local, d);
+    if (lane == 0) s_ws[warp] = local;
+    __syncthreads();
+    int total = s_ws[lane];
+    int base = lane < warp ? total : 0;
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        total += __shfl_xor_sync(0xffffffffu, total, d);
+        base += __shfl_xor_sync(0xffffffffu, base, d);
+    }
+    for (int c = lo; c < hi; c += 32) {
+        const int i = c + lane;
+        const int v = i < hi ? load(i) : 0;
+        int incl = v;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const int u = __shfl_up_sync(0xffffffffu, incl, d);
+            if (lane >= d) incl += u;
+        }
+        if (i < hi) emit(i, v, base + incl - v, total);
+        base += __shfl_sync(0xffffffffu, incl, 31);
+    }
+    return total;
+}
+#endif
 
 }  // namespace b200sift

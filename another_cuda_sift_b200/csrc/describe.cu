@@ -38,11 +38,10 @@ __device__ __forceinline__ float fix_get(unsigned long long v) { return (float)(
 
 // Descriptor bins: int32, unit 2^-15. Two's-complement wrap-around makes partial sums harmless; a final bin
 // must lie within +-65536, far above what 0..255-valued pixels blurred with sigma >= 1.6 can produce
-// (|gradient| < 170, weight <= 1, a few hundred samples per bin). Quantisation: <= 1.5e-5 per vote, i.e.
+// (|gradient| < 170, weight <= 1, a few hundred samples per bin). Quantisation: <= 1.5e-5 per partial sum, i.e.
 // ~1e-6 relative on a bin -- below the fp32 rounding noise of the reference's own float accumulation.
 constexpr float kFix32 = 32768.f;
 constexpr float kUnfix32 = 1.f / 32768.f;
-__device__ __forceinline__ void fix_add32(int* slot, float v_scaled) { atomicAdd(slot, __float2int_rn(v_scaled)); }
 
 // ---------------------------------------------------------------- orientation
 // One 64-thread CTA per refined keypoint (flattened over the octaves, grid-stride). The patch loop is
@@ -62,10 +61,10 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
     __shared__ int s_peak[kOriBins];
     const int tid = threadIdx.x;
     int total = 0;
-    for (int i = 0; i < fp.nOct; i++) total += fp.oct[i].counts[1];
+    for (int i = fp.o_begin; i < fp.o_end; i++) total += fp.oct[i].counts[1];
 
     for (int g = blockIdx.x; g < total; g += gridDim.x) {
-        int oi = 0, k = g;
+        int oi = fp.o_begin, k = g;
         while (k >= fp.oct[oi].counts[1]) { k -= fp.oct[oi].counts[1]; oi++; }
         const OctParams& o = fp.oct[oi];
         const int M = o.counts[1];
@@ -175,86 +174,70 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
 // entry whose prefix equals the total T is not written (quirk Q5 again).
 __global__ void __launch_bounds__(1024)
 compact_oriented_kernel(const __grid_constant__ FrameParams fp) {
-    const OctParams& o = fp.oct[blockIdx.x];
+    const OctParams& o = fp.oct[fp.o_begin + blockIdx.x];
     const int M = o.counts[1];
-    __shared__ int warp_sums[32];
-    __shared__ int s_total, carry;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int local = 0;
-    for (int i = threadIdx.x; i < M; i += 1024) local += o.oricnt[i];
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) local += __shfl_xor_sync(0xffffffffu, local, d);
-    if (lane == 0) warp_sums[warp] = local;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int tsum = 0;
-        for (int i = 0; i < 32; i++) tsum += warp_sums[i];
-        s_total = tsum;
-        carry = 0;
-        o.counts[2] = tsum;  // T
-    }
-    __syncthreads();
-    const int total = s_total;
-    for (int base = 0; base < M; base += 1024) {
-        const int k = base + threadIdx.x;
-        const int v = k < M ? o.oricnt[k] : 0;
-        int incl = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int u = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += u;
-        }
-        __syncthreads();
-        if (lane == 31) warp_sums[warp] = incl;
-        __syncthreads();
-        if (warp == 0) {
-            int ws = warp_sums[lane];
-            int wi = ws;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int u = __shfl_up_sync(0xffffffffu, wi, d);
-                if (lane >= d) wi += u;
+    const int total = block_scan_1024(
+        M, [&](int k) { return o.oricnt[k]; },
+        [&](int k, int v, int excl, int tot) {
+            for (int c = 0; c < v; c++) {
+                const int p = excl + c;
+                if (p + 1 < tot) {
+                    const int slot = M + k * kOriBins + c;
+                    o.cand[p] = o.coll[slot];
+                    o.candF[p] = o.collF[slot];
+                }
             }
-            warp_sums[lane] = wi - ws;
-        }
-        __syncthreads();
-        const int c0 = carry;
-        const int excl = c0 + warp_sums[warp] + incl - v;
-        for (int c = 0; c < v; c++) {
-            const int p = excl + c + 1;
-            if (p < total) {
-                const int slot = M + k * kOriBins + c;
-                o.cand[p - 1] = o.coll[slot];
-                o.candF[p - 1] = o.collF[slot];
-            }
-        }
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = excl + v;
-        __syncthreads();
-    }
+        });
+    if (threadIdx.x == 0) o.counts[2] = total;  // T
 }
 
 // ---------------------------------------------------------------- descriptor
-// fast_atan2f (SiftOps.cu:403-419), contraction as in the reference SASS.
-__device__ __forceinline__ float fast_atan2f(float y, float x) {
-    const float abs_y = __fadd_rn(fabsf(y), 1e-10f);
-    float r, angle;
-    if (x < 0.0f) {
-        r = __fdiv_rn(__fadd_rn(x, abs_y), __fsub_rn(abs_y, x));
-        angle = 2.356194490f;
-    } else {
-        r = __fdiv_rn(__fsub_rn(x, abs_y), __fadd_rn(x, abs_y));
-        angle = 0.785398163f;
-    }
-    angle = __fmaf_rn(__fmaf_rn(__fmul_rn(0.1963f, r), r, -0.9817f), r, angle);
-    return (y < 0.0f) ? -angle : angle;
+constexpr int kDescThreads = 128;
+constexpr int kDescWarps = kDescThreads / 32;
+constexpr int kHistSize = 6 * 6 * 10;
+constexpr int kPrivSlots = 32;  // 2 x 2 spatial neighbours x 8 orientation bins (bin 8 is folded onto 0 here, not in the epilogue)
+
+// The 4x4 sample cells (rbin_int, cbin_int) of the descriptor window, packed as R*4+C, largest first: row and
+// column 0 cover rbin in (-1,1) (truncating modff, quirk Q13), so cell (0,0) is four units of area, the other
+// row-0 / column-0 cells two, the rest one. Warps pull cells from this queue (longest-processing-time order).
+__constant__ signed char kCellOrder[16] = {0, 1, 2, 3, 4, 8, 12, 5, 6, 7, 9, 10, 11, 13, 14, 15};
+constexpr int kRing = 64;  // per-warp ring of accepted samples (at most 31 pending + 32 appended)
+
+__device__ __forceinline__ float ex2_approx(float x) {
+    float y;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rcp_approx(float x) {  // x must be a normal number
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ float rsqrt_approx(float x) {  // x must be a normal number
+    float y;
+    asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
 }
 
-constexpr int kDescThreads = 128;
-constexpr int kHistSize = 6 * 6 * 10;
-
 // One CTA per returned keypoint (global index g over octaves in ascending order, truncated at
-// numFeatures: utils/CudaMemcpyUtils.cu:38-67). 128 threads stride over the rotated patch.
+// numFeatures: utils/CudaMemcpyUtils.cu:38-67).
+//
+// The reference (SiftOps.cu:448-604) walks the (2*radius+1)^2 bounding patch and fires 8 shared-memory
+// float atomics per sample that lands in the rotated 5x5-cell window. Shared atomics retire about one lane
+// per cycle per SM, which bounded the first version of this kernel. Here every warp OWNS whole cells of
+// the window (pulled from a CTA-wide queue, largest first):
+//   scan   the warp walks the bounding box of its cell, 32 points per step, applies the reference's
+//          acceptance test restricted to the cell and appends the accepted (i, j) to a warp-private ring
+//          (ballot + popc, no atomics);
+//   vote   whenever 32 accepted samples are pending, all 32 lanes process one each (gradient, weight,
+//          trilinear split). They all vote into the same 2x2x8 neighbourhood, so each lane accumulates
+//          into a private bank-conflict-free column of shared memory with plain LDS/FFMA/STS;
+//   flush  at the end of a cell lane s sums slot s over the 32 columns (skewed, conflict-free, fixed
+//          order), converts to 2^-15 fixed point and adds it to the CTA histogram with one integer
+//          atomic: integer sums are order-independent, so the descriptor is bit-reproducible run to run.
+// The set of samples and every per-sample coordinate (c_rot, r_rot, bins, fractions) are computed exactly
+// as in the reference; magnitude, angle and weight use the MUFU approximations (a few ulp; the result is
+// rounded to fp16).
 __global__ void __launch_bounds__(kDescThreads)
 descriptor_kernel(const __grid_constant__ FrameParams fp) {
     const int g = blockIdx.x;
@@ -271,13 +254,20 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     const OctParams& o = fp.oct[oi];
     const float3 kp = o.cand[j];
     const float4 ft = o.candF[j];
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     __shared__ int s_hist[kHistSize];
     __shared__ float s_f[kHistSize];
     __shared__ float s_desc[128];
     __shared__ float s_norm;
+    __shared__ __align__(128) float s_priv[kDescWarps][kPrivSlots][32];
+    __shared__ int s_ring[kDescWarps][kRing];
+    __shared__ int s_next;
+    if (tid == 0) s_next = 0;
     for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0;
+    float* priv = &s_priv[warp][0][lane];
+#pragma unroll
+    for (int k = 0; k < kPrivSlots; k++) priv[k * 32] = 0.f;
     __syncthreads();
 
     // unpackOctave (SiftOps.cu:389-401)
@@ -287,80 +277,157 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     octv = octv < 128 ? octv : (-128 | octv);
     const float scale = octv >= 0 ? __fdiv_rn(1.f, (float)(1 << octv)) : (float)(1 << -octv);
     const int hdim = o.pitch;
+    const int ow = o.w, oh = o.h;
     const long stack_len = (long)o.pitch * o.h * kGaussLayers;
     const long img_off = (long)((float)hdim * (float)o.h * (float)layer);
-    const float x = (float)__float2int_rn(__fmul_rn(kp.x, scale));
-    const float y = (float)__float2int_rn(__fmul_rn(kp.y, scale));
+    const int ix = __float2int_rn(__fmul_rn(kp.x, scale));
+    const int iy = __float2int_rn(__fmul_rn(kp.y, scale));
     float angle = __fsub_rn(360.f, ft.w);
     if (fabsf(__fsub_rn(angle, 360.f)) < 1e-6f) angle = 0.f;
     const float scl = __fmul_rn(__fmul_rn(ft.y, scale), 0.5f);
     constexpr float deg2rad = (float)(3.14159265358979323846 / 180.0);
-    float cos_t, sin_t;
-    __sincosf(__fmul_rn(angle, deg2rad), &sin_t, &cos_t);
+    float cos_u, sin_u;
+    __sincosf(__fmul_rn(angle, deg2rad), &sin_u, &cos_u);
     constexpr float bins_per_degree = 8 / 360.f;
     const float hist_width = __fmul_rn(3.f, scl);
     int radius = __float2int_rn(__fmul_rn(__fmul_rn(__fmul_rn(hist_width, 1.4142135623730951f), 5.f), 0.5f));
     const float diag = sqrtf(__fmaf_rn((float)o.w, (float)o.w, __fmul_rn((float)o.h, (float)o.h)));
     radius = (int)fmin((double)radius, (double)diag);
-    cos_t = __fdiv_rn(cos_t, hist_width);
-    sin_t = __fdiv_rn(sin_t, hist_width);
-    const int side = 2 * radius + 1;
-    const int total_dim = side * side;
-    const float fw = (float)o.w, fh = (float)o.h;
-    const float* stack = o.gauss;
+    const float cos_t = __fdiv_rn(cos_u, hist_width);
+    const float sin_t = __fdiv_rn(sin_u, hist_width);
+    const float* stack = o.gauss + img_off;
+    const int stack_left = (int)(stack_len - img_off);  // floats from this layer to the end of the octave's stack
+    const float ch = cos_u * hist_width, sh = sin_u * hist_width;  // window -> patch coordinates
 
-    // idx = tid + k*128 walks the patch row-major; (row, col) advance incrementally instead of idx / side, idx % side
-    const int step_r = kDescThreads / side, step_c = kDescThreads % side;
-    int prow = tid / side, pcol = tid % side;
-    for (int idx = tid; idx < total_dim; idx += kDescThreads) {
-        const int idx_i = prow - radius, idx_j = pcol - radius;
-        prow += step_r;
-        pcol += step_c;
-        if (pcol >= side) { pcol -= side; prow++; }
-        const float fi = (float)idx_i, fj = (float)idx_j;
-        const float c_rot = __fmaf_rn(fj, cos_t, -__fmul_rn(fi, sin_t));
-        const float r_rot = __fmaf_rn(fi, cos_t, __fmul_rn(fj, sin_t));
-        const float cbin = __fadd_rn(c_rot, 1.5f), rbin = __fadd_rn(r_rot, 1.5f);
-        const int base_py = (int)__fadd_rn(y, fi), base_px = (int)__fadd_rn(x, fj);
-        if (rbin > -1.f && rbin < 4.f && cbin > -1.f && cbin < 4.f && (float)base_px > 0.f && (float)base_px < fw &&
-            (float)base_py > 0.f && (float)base_py < fh) {
-            // quirk Q12: px == w-1 / py == h-1 pass the test above, so these reads may land in the
-            // row padding, the next row or the next layer; clamp only at the end of the stack.
-            const long a = img_off + (long)base_py * hdim + base_px;
-            const long a_dn = a + hdim;
-            const float v_l = __ldg(stack + a - 1), v_r = __ldg(stack + a + 1);
-            const float v_up = __ldg(stack + a - hdim);
-            const float v_dn = a_dn < stack_len ? __ldg(stack + a_dn) : 0.f;
-            const float dx = __fsub_rn(v_r, v_l);
-            const float dy = __fsub_rn(v_up, v_dn);
-            const float rbin_int = truncf(rbin), cbin_int = truncf(cbin);
-            const float rbin_frac = __fsub_rn(rbin, rbin_int), cbin_frac = __fsub_rn(cbin, cbin_int);
-            const float weight = __expf(__fmul_rn(__fmaf_rn(c_rot, c_rot, __fmul_rn(r_rot, r_rot)), -0.125f));
-            const float grad_mag = __fsqrt_rn(__fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-            float grad_ori = (float)(((double)fast_atan2f(dy, dx) / 3.14159265358979323846) * 180.0);
-            grad_ori = grad_ori < 0.f ? __fadd_rn(grad_ori, 360.f) : grad_ori;
-            const float obin = __fmul_rn(__fsub_rn(grad_ori, angle), bins_per_degree);
-            const float mag = __fmul_rn(__fmul_rn(grad_mag, weight), kFix32);  // x 2^15: exact, commutes with the roundings below
-            float obin_int = truncf(obin);
-            const float obin_frac = __fsub_rn(obin, obin_int);
-            if (obin_int < 0.f) obin_int += 8.f;
-            if (obin_int >= 8.f) obin_int -= 8.f;
-            const int hi = (int)(((rbin_int + 1.f) * 6.f + cbin_int + 1.f) * 10.f + obin_int);
-            const float v_r1 = __fmul_rn(mag, rbin_frac), v_r0 = __fmul_rn(mag, __fsub_rn(1.f, rbin_frac));
-            const float omc = __fsub_rn(1.f, cbin_frac), omo = __fsub_rn(1.f, obin_frac);
-            const float v_rc11 = __fmul_rn(v_r1, cbin_frac), v_rc10 = __fmul_rn(v_r1, omc);
-            const float v_rc01 = __fmul_rn(v_r0, cbin_frac), v_rc00 = __fmul_rn(v_r0, omc);
-            if (hi >= 0 && hi + 71 < kHistSize) {
-                fix_add32(s_hist + hi + 70, __fmul_rn(v_rc11, omo));
-                fix_add32(s_hist + hi + 71, __fmul_rn(v_rc11, obin_frac));
-                fix_add32(s_hist + hi + 60, __fmul_rn(v_rc10, omo));
-                fix_add32(s_hist + hi + 61, __fmul_rn(v_rc10, obin_frac));
-                fix_add32(s_hist + hi + 10, __fmul_rn(v_rc01, omo));
-                fix_add32(s_hist + hi + 11, __fmul_rn(v_rc01, obin_frac));
-                fix_add32(s_hist + hi, __fmul_rn(v_rc00, omo));
-                fix_add32(s_hist + hi + 1, __fmul_rn(v_rc00, obin_frac));
+    int* ring = s_ring[warp];
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned uw1 = (unsigned)(ow - 1), uh1 = (unsigned)(oh - 1);
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(&s_next, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= 16) break;
+        const int cell = kCellOrder[t];
+        const int R = cell >> 2, C = cell & 3;
+        // cell extent in rotated coordinates (r_rot = rbin - 1.5), then its bounding box in patch offsets:
+        // i = (r cos - c sin) * hist_width, j = (r sin + c cos) * hist_width. floor/ceil leave up to a pixel of
+        // slack, six orders of magnitude more than the rounding of these products
+        const float fR = (float)R, fC = (float)C;
+        const float rlo = (R == 0 ? -1.f : fR) - 1.5f, rhi = fR - 0.5f;
+        const float clo = (C == 0 ? -1.f : fC) - 1.5f, chi = fC - 0.5f;
+        const float ia = rlo * ch, ib = rhi * ch, ic = -clo * sh, id = -chi * sh;
+        const float ja = rlo * sh, jb = rhi * sh, jc = clo * ch, jd = chi * ch;
+        const int i0 = max(-radius, __float2int_rd(fminf(ia, ib) + fminf(ic, id)));
+        const int i1 = min(radius, __float2int_ru(fmaxf(ia, ib) + fmaxf(ic, id)));
+        const int j0 = max(-radius, __float2int_rd(fminf(ja, jb) + fminf(jc, jd)));
+        const int j1 = min(radius, __float2int_ru(fmaxf(ja, jb) + fmaxf(jc, jd)));
+        const int wj = j1 - j0 + 1, wi = i1 - i0 + 1;
+        if (wj <= 0 || wi <= 0) continue;
+        const int n = wi * wj;
+        // (k + 0.5) / wj is never within rounding distance of an integer, so these are exact floors
+        const float inv_wj = __frcp_rn((float)wj);
+        const int step_r = __float2int_rd(32.5f * inv_wj), step_c = 32 - step_r * wj;
+        int prow = __float2int_rd(((float)lane + 0.5f) * inv_wj), pcol = lane - prow * wj;
+        // truncf(rbin) == R written as an interval: (-1, 1) for R == 0, [R, R+1) otherwise
+        const float r_gt = R == 0 ? -1.f : __uint_as_float(__float_as_uint(fR) - 1u), r_lt = fR + 1.f;
+        const float c_gt = C == 0 ? -1.f : __uint_as_float(__float_as_uint(fC) - 1u), c_lt = fC + 1.f;
+        int head = 0, tail = 0;  // accepted / consumed sample counts of this cell (warp-uniform)
+        int scanned = 0;
+        for (;;) {
+            // ---- scan: until a full batch is pending or the box is exhausted
+            while (scanned < n && head - tail < 32) {
+                const int idx_i = i0 + prow, idx_j = j0 + pcol;
+                const bool in_box = scanned + lane < n;
+                scanned += 32;
+                prow += step_r;
+                pcol += step_c;
+                if (pcol >= wj) { pcol -= wj; prow++; }
+                const float fi = (float)idx_i, fj = (float)idx_j;
+                const float c_rot = __fmaf_rn(fj, cos_t, -__fmul_rn(fi, sin_t));
+                const float r_rot = __fmaf_rn(fi, cos_t, __fmul_rn(fj, sin_t));
+                const float cbin = __fadd_rn(c_rot, 1.5f), rbin = __fadd_rn(r_rot, 1.5f);
+                // the reference's acceptance (rbin, cbin in (-1,4), pixel strictly inside (0,w) x (0,h)),
+                // restricted to this warp's cell
+                const bool ok = in_box && rbin > r_gt && rbin < r_lt && cbin > c_gt && cbin < c_lt &&
+                                (unsigned)(ix + idx_j - 1) < uw1 && (unsigned)(iy + idx_i - 1) < uh1;
+                const unsigned b = __ballot_sync(0xffffffffu, ok);
+                if (ok) ring[(head + __popc(b & lt_mask)) & (kRing - 1)] = (idx_i & 0xffff) | (idx_j << 16);
+                head += __popc(b);
             }
+            const int pend = head - tail;
+            if (pend == 0) break;
+            __syncwarp();
+            // ---- vote: one accepted sample per lane
+            if (lane < pend) {
+                const int e = ring[(tail + lane) & (kRing - 1)];
+                const int idx_i = (int)(short)(e & 0xffff), idx_j = e >> 16;
+                const float fi = (float)idx_i, fj = (float)idx_j;
+                const float c_rot = __fmaf_rn(fj, cos_t, -__fmul_rn(fi, sin_t));
+                const float r_rot = __fmaf_rn(fi, cos_t, __fmul_rn(fj, sin_t));
+                const float cbin = __fadd_rn(c_rot, 1.5f), rbin = __fadd_rn(r_rot, 1.5f);
+                // quirk Q12: px == w-1 / py == h-1 are accepted, so these reads may land in the row
+                // padding, the next row or the next layer; clamp only at the end of the stack.
+                const int a = (iy + idx_i) * hdim + (ix + idx_j);
+                const float* pc = stack + a;
+                const float v_l = __ldg(pc - 1), v_r = __ldg(pc + 1);
+                const float v_up = __ldg(stack + (a - hdim));
+                const float v_dn = a + hdim < stack_left ? __ldg(stack + (a + hdim)) : 0.f;
+                const float dx = __fsub_rn(v_r, v_l);
+                const float dy = __fsub_rn(v_up, v_dn);
+                // rbin_int = truncf(rbin) is R (as -0.0 for rbin in (-1,0): the fraction is then negative)
+                const float rbin_frac = __fsub_rn(rbin, fR), cbin_frac = __fsub_rn(cbin, fC);
+                const float d2 = __fmaf_rn(c_rot, c_rot, __fmul_rn(r_rot, r_rot));
+                const float weight = ex2_approx(d2 * (-0.125f * 1.4426950408889634f));
+                const float g2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
+                const float grad_mag = g2 * rsqrt_approx(fmaxf(g2, 1e-30f));
+                // fast_atan2f (SiftOps.cu:403-419) with one approximate division
+                const float abs_y = fabsf(dy) + 1e-10f;
+                const bool neg = dx < 0.f;
+                const float num = neg ? dx + abs_y : dx - abs_y;
+                const float den = neg ? abs_y - dx : dx + abs_y;
+                const float q = num * rcp_approx(den);  // den >= 1e-10
+                float ang = __fmaf_rn(__fmaf_rn(0.1963f * q, q, -0.9817f), q, neg ? 2.356194490f : 0.785398163f);
+                ang = dy < 0.f ? -ang : ang;
+                float grad_ori = ang * 57.29577951308232f;
+                grad_ori = grad_ori < 0.f ? grad_ori + 360.f : grad_ori;
+                const float obin = __fmul_rn(__fsub_rn(grad_ori, angle), bins_per_degree);
+                const float mag = grad_mag * weight * kFix32;  // x 2^15: exact scaling, undone after the integer sum
+                const float obin_t = truncf(obin);
+                const float obin_frac = __fsub_rn(obin, obin_t);
+                const int ob = (int)obin_t & 7;  // -7..8 -> 0..7 (obin_int < 0: += 8, >= 8: -= 8)
+                const float v_r1 = mag * rbin_frac, v_r0 = mag * (1.f - rbin_frac);
+                const float omc = 1.f - cbin_frac, omo = 1.f - obin_frac;
+                const float v11 = v_r1 * cbin_frac, v10 = v_r1 * omc;
+                const float v01 = v_r0 * cbin_frac, v00 = v_r0 * omc;
+                float* p = priv + ob * 32;                  // slot (dr*2 + dc)*8 + ob of this lane's column
+                float* p1 = priv + ((ob + 1) & 7) * 32;     // the next orientation bin, 8 wraps to 0
+                float a0 = p[0], a1 = p1[0], a2 = p[8 * 32], a3 = p1[8 * 32];
+                float a4 = p[16 * 32], a5 = p1[16 * 32], a6 = p[24 * 32], a7 = p1[24 * 32];
+                a0 = __fmaf_rn(v00, omo, a0); a1 = __fmaf_rn(v00, obin_frac, a1);
+                a2 = __fmaf_rn(v01, omo, a2); a3 = __fmaf_rn(v01, obin_frac, a3);
+                a4 = __fmaf_rn(v10, omo, a4); a5 = __fmaf_rn(v10, obin_frac, a5);
+                a6 = __fmaf_rn(v11, omo, a6); a7 = __fmaf_rn(v11, obin_frac, a7);
+                p[0] = a0; p1[0] = a1; p[8 * 32] = a2; p1[8 * 32] = a3;
+                p[16 * 32] = a4; p1[16 * 32] = a5; p[24 * 32] = a6; p1[24 * 32] = a7;
+            }
+            tail += min(pend, 32);
+            __syncwarp();
         }
+        // ---- flush: lane s owns slot s = (dr*2 + dc)*8 + bin and sums it over the 32 lane-private columns
+        const unsigned row = (unsigned)__cvta_generic_to_shared(&s_priv[warp][lane][0]) + (lane << 2);
+        float acc = 0.f;
+#pragma unroll
+        for (int k = 0; k < 32; k++) {
+            float v;
+            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(row ^ (unsigned)(k << 2)) : "memory");
+            acc += v;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < kPrivSlots; k++) priv[k * 32] = 0.f;
+        const int tot = __float2int_rn(acc);
+        if (tot != 0) atomicAdd(s_hist + ((R + 1 + (lane >> 4)) * 6 + (C + 1 + ((lane >> 3) & 1))) * 10 + (lane & 7), tot);
+        __syncwarp();
     }
     __syncthreads();
     for (int i = tid; i < kHistSize; i += kDescThreads) s_f[i] = __fmul_rn((float)s_hist[i], kUnfix32);
@@ -370,9 +437,7 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
         const int cell = tid >> 3, k = tid & 7;
         const int ci = cell >> 2, cj = cell & 3;
         const int base = ((ci + 1) * 6 + (cj + 1)) * 10;
-        float v = s_f[base + k];
-        if (k < 2) v = __fadd_rn(v, s_f[base + 8 + k]);
-        s_desc[tid] = v;
+        s_desc[tid] = s_f[base + k];  // the wrap of bin 8 onto 0 (SiftOps.cu:431-446) already happened per vote
     }
     __syncthreads();
     if (tid == 0) {
@@ -400,10 +465,12 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
 
 }  // namespace
 
-void launch_orientation(const FrameParams& fp, cudaStream_t s) {
-    orientation_kernel<<<148 * 16, kOriThreads, 0, s>>>(fp);
+void launch_orientation(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
+    orientation_kernel<<<148 * (o_begin == 0 ? 16 : 4), kOriThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
-void launch_compact_oriented(const FrameParams& fp, cudaStream_t s) { compact_oriented_kernel<<<fp.nOct, 1024, 0, s>>>(fp); }
+void launch_compact_oriented(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
+    compact_oriented_kernel<<<o_end - o_begin, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
+}
 void launch_descriptor(const FrameParams& fp, cudaStream_t s) {
     descriptor_kernel<<<fp.numFeatures, kDescThreads, 0, s>>>(fp);
 }

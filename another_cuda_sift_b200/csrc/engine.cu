@@ -151,8 +151,33 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
     // Gaussian pyramid. Octave o+1 only needs layer 3 of octave o, so layers 4 and 5 of every big octave
     // go to a side stream (a parallel branch of the frame graph) while the main chain moves on to the next
     // octave; octaves of <= kTailPixels pixels are walked by one CTA (launch_pyramid_tail).
+    // Everything between the pyramid and the descriptor is per-octave work, so octave 0 (three quarters of
+    // the pixels and keypoints) runs its detect..orientation chain on its own branch as soon as its six
+    // layers exist, overlapping the latency-bound small octaves and the single-CTA tail.
     const bool fork = (prof == nullptr) && d->side[0] != nullptr;
-    int n_side = 0;
+    const int split = (fork && d->nOct > 1 && d->tail_first >= 1) ? 1 : 0;  // octaves [0,split) on branch A
+    auto chain = [&](int ob, int oe, cudaStream_t cs) -> int {
+        if (last_stage >= 3) {
+            launch_detect(fp, ob, oe, cs); n++; MARK(B200SIFT_K_DETECT);
+            launch_scan_rows(fp, ob, oe, cs); n++;
+            launch_scatter(fp, ob, oe, cs); n++;
+            MARK(B200SIFT_K_COMPACT);
+        }
+        if (last_stage >= 4) {
+            launch_refine(fp, ob, oe, cs); n++;
+            MARK(B200SIFT_K_REFINE);
+            launch_compact_refined(fp, ob, oe, cs); n++;
+            MARK(B200SIFT_K_COMPACT);
+        }
+        if (last_stage >= 5) {
+            launch_orientation(fp, ob, oe, cs); n++;
+            MARK(B200SIFT_K_ORIENT);
+            launch_compact_oriented(fp, ob, oe, cs); n++;
+            MARK(B200SIFT_K_COMPACT);
+        }
+        return 0;
+    };
+    bool joinA = false, joinB = false;
     for (int o = 0; o < d->nOct; o++) {
         OctParams& oc = fp.oct[o];
         const size_t ls = (size_t)oc.pitch * oc.h;
@@ -179,7 +204,7 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
         cudaStream_t ls_stream = s;
         for (int l = 1; l < kGaussLayers; l++) {
             if (l == 4 && fork && o + 1 < d->nOct) {  // layers 4,5 off the critical path
-                cudaStream_t side = d->side[n_side % kSideStreams];
+                cudaStream_t side = d->side[o < split ? 0 : 1];
                 CU(cudaEventRecord(d->ev_fork[o], s));
                 CU(cudaStreamWaitEvent(side, d->ev_fork[o], 0));
                 ls_stream = side;
@@ -188,31 +213,19 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
             MARK(o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL);
             n++;
         }
-        if (ls_stream != s) {
-            CU(cudaEventRecord(d->ev_join[o], ls_stream));
-            n_side++;
+        if (ls_stream != s) (o < split ? joinA : joinB) = true;
+        if (split && o == split - 1) {  // branch A: octave 0 is complete on side[0]
+            if (int rc = chain(0, split, ls_stream)) return rc;
         }
     }
-    if (fork)
-        for (int o = 0; o < d->nOct; o++)
-            if (o < d->tail_first && o + 1 < d->nOct) CU(cudaStreamWaitEvent(s, d->ev_join[o], 0));
-    if (last_stage >= 3) {
-        if (fp.det_tasks > 0) { launch_detect(fp, s); n++; MARK(B200SIFT_K_DETECT); }
-        launch_scan_rows(fp, s); n++;
-        launch_scatter(fp, s); n++;
-        MARK(B200SIFT_K_COMPACT);
+    if (joinB) {
+        CU(cudaEventRecord(d->ev_join[1], d->side[1]));
+        CU(cudaStreamWaitEvent(s, d->ev_join[1], 0));
     }
-    if (last_stage >= 4) {
-        launch_refine(fp, s); n++;
-        MARK(B200SIFT_K_REFINE);
-        launch_compact_refined(fp, s); n++;
-        MARK(B200SIFT_K_COMPACT);
-    }
-    if (last_stage >= 5) {
-        launch_orientation(fp, s); n++;
-        MARK(B200SIFT_K_ORIENT);
-        launch_compact_oriented(fp, s); n++;
-        MARK(B200SIFT_K_COMPACT);
+    if (int rc = chain(split, d->nOct, s)) return rc;
+    if (joinA) {
+        CU(cudaEventRecord(d->ev_join[0], d->side[0]));
+        CU(cudaStreamWaitEvent(s, d->ev_join[0], 0));
     }
     if (last_stage >= 6) {
         launch_descriptor(fp, s); n++;
@@ -251,6 +264,8 @@ int build(b200sift_detector* d) {
     FrameParams& fp = d->fp;
     std::memset(&fp, 0, sizeof(fp));
     fp.nOct = d->nOct;
+    fp.o_begin = 0;
+    fp.o_end = d->nOct;
     fp.numFeatures = c.numFeatures;
     fp.extrema_thr = (float)std::floor(0.5 * c.contrastThreshould / c.numOctaveLayers * 255 * 1.f);  // Detector.cu:362
     fp.contrast_thr = (float)c.contrastThreshould;

@@ -55,10 +55,10 @@ __device__ __forceinline__ void load_row(const OctParams& o, int y, int xc, int 
 __global__ void __launch_bounds__(kDetThreads)
 detect_kernel(const __grid_constant__ FrameParams fp) {
     const int lane = threadIdx.x & 31;
-    const int task = blockIdx.x * (kDetThreads / 32) + (threadIdx.x >> 5);
-    if (task >= fp.det_tasks) return;
-    int oi = 0;
-    while (oi + 1 < fp.nOct && task >= fp.oct[oi + 1].det_task0) oi++;
+    const int task = fp.oct[fp.o_begin].det_task0 + blockIdx.x * (kDetThreads / 32) + (threadIdx.x >> 5);
+    if (task >= (fp.o_end < fp.nOct ? fp.oct[fp.o_end].det_task0 : fp.det_tasks)) return;
+    int oi = fp.o_begin;
+    while (oi + 1 < fp.o_end && task >= fp.oct[oi + 1].det_task0) oi++;
     const OctParams& o = fp.oct[oi];
     const int t = task - o.det_task0;
     const int cs = t % o.det_cols, rs = t / o.det_cols;
@@ -104,44 +104,13 @@ detect_kernel(const __grid_constant__ FrameParams fp) {
 // One CTA per octave: exclusive scan of the (scale,row) counts.
 __global__ void __launch_bounds__(1024)
 scan_rows_kernel(const __grid_constant__ FrameParams fp) {
-    const OctParams& o = fp.oct[blockIdx.x];
-    const int n = kScales * o.h;
-    __shared__ int warp_sums[32];
-    __shared__ int carry;
-    if (threadIdx.x == 0) carry = 0;
-    __syncthreads();
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    for (int base = 0; base < n; base += 1024) {
-        const int i = base + threadIdx.x;
-        const int v = i < n ? o.rowcount[i] : 0;
-        int incl = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int u = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += u;
-        }
-        if (lane == 31) warp_sums[warp] = incl;
-        __syncthreads();
-        if (warp == 0) {
-            int ws = warp_sums[lane];
-            int wi = ws;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int u = __shfl_up_sync(0xffffffffu, wi, d);
-                if (lane >= d) wi += u;
-            }
-            warp_sums[lane] = wi - ws;  // exclusive
-        }
-        __syncthreads();
-        const int c = carry;
-        if (i < n) o.rowoff[i] = c + warp_sums[warp] + incl - v;
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = c + warp_sums[31] + incl;
-        __syncthreads();
-    }
+    const OctParams& o = fp.oct[fp.o_begin + blockIdx.x];
+    const int total = block_scan_1024(
+        kScales * o.h, [&](int i) { return o.rowcount[i]; },
+        [&](int i, int, int excl, int) { o.rowoff[i] = excl; });
     if (threadIdx.x == 0) {
-        o.counts[0] = carry;                 // P
-        o.counts[3] = min(carry, o.cap);     // candidates the refinement looks at
+        o.counts[0] = total;                 // P
+        o.counts[3] = min(total, o.cap);     // candidates the refinement looks at
     }
 }
 
@@ -149,10 +118,10 @@ scan_rows_kernel(const __grid_constant__ FrameParams fp) {
 __global__ void __launch_bounds__(256)
 scatter_kernel(const __grid_constant__ FrameParams fp) {
     const int lane = threadIdx.x & 31;
-    const int gw = blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (gw >= fp.rows_total) return;
-    int oi = 0;
-    while (oi + 1 < fp.nOct && gw >= fp.oct[oi + 1].row0) oi++;
+    const int gw = fp.oct[fp.o_begin].row0 + blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (gw >= (fp.o_end < fp.nOct ? fp.oct[fp.o_end].row0 : fp.rows_total)) return;
+    int oi = fp.o_begin;
+    while (oi + 1 < fp.o_end && gw >= fp.oct[oi + 1].row0) oi++;
     const OctParams& o = fp.oct[oi];
     const int row = gw - o.row0;
     if (o.rowcount[row] == 0) return;
@@ -232,7 +201,7 @@ __device__ __forceinline__ void solve3(const float* A, const float* b, float* x)
 
 __global__ void __launch_bounds__(128)
 refine_kernel(const __grid_constant__ FrameParams fp) {
-    const int oi = blockIdx.y;
+    const int oi = fp.o_begin + blockIdx.y;
     const OctParams& o = fp.oct[oi];
     const int idx = blockIdx.x * 128 + threadIdx.x;
     if (idx >= o.counts[3]) return;
@@ -317,77 +286,40 @@ refine_kernel(const __grid_constant__ FrameParams fp) {
 // whose prefix equals the total is not written (quirk Q5, SiftOps.cu:228).
 __global__ void __launch_bounds__(1024)
 compact_refined_kernel(const __grid_constant__ FrameParams fp) {
-    const OctParams& o = fp.oct[blockIdx.x];
-    const int n = o.counts[3];
-    __shared__ int warp_sums[32];
-    __shared__ int s_total, carry;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    int local = 0;
-    for (int i = threadIdx.x; i < n; i += 1024) local += o.flag[i];
-#pragma unroll
-    for (int d = 16; d > 0; d >>= 1) local += __shfl_xor_sync(0xffffffffu, local, d);
-    if (lane == 0) warp_sums[warp] = local;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        int tsum = 0;
-        for (int i = 0; i < 32; i++) tsum += warp_sums[i];
-        s_total = tsum;
-        carry = 0;
-        o.counts[1] = tsum;  // M
-    }
-    __syncthreads();
-    const int total = s_total;
-    for (int base = 0; base < n; base += 1024) {
-        const int i = base + threadIdx.x;
-        const int v = i < n ? o.flag[i] : 0;
-        int incl = v;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            int u = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += u;
-        }
-        __syncthreads();
-        if (lane == 31) warp_sums[warp] = incl;
-        __syncthreads();
-        if (warp == 0) {
-            int ws = warp_sums[lane];
-            int wi = ws;
-#pragma unroll
-            for (int d = 1; d < 32; d <<= 1) {
-                int u = __shfl_up_sync(0xffffffffu, wi, d);
-                if (lane >= d) wi += u;
+    const OctParams& o = fp.oct[fp.o_begin + blockIdx.x];
+    const int total = block_scan_1024(
+        o.counts[3], [&](int i) { return o.flag[i]; },
+        [&](int i, int v, int excl, int tot) {
+            if (v && excl + 1 < tot) {
+                o.coll[excl] = o.cand[i];
+                o.collF[excl] = o.candF[i];
             }
-            warp_sums[lane] = wi - ws;
-        }
-        __syncthreads();
-        const int c = carry;
-        const int p = c + warp_sums[warp] + incl;  // inclusive prefix
-        if (v && p < total) {
-            o.coll[p - 1] = o.cand[i];
-            o.collF[p - 1] = o.candF[i];
-        }
-        __syncthreads();
-        if (threadIdx.x == 1023) carry = p;
-        __syncthreads();
-    }
+        });
+    if (threadIdx.x == 0) o.counts[1] = total;  // M
 }
 
 }  // namespace
 
-void launch_detect(const FrameParams& fp, cudaStream_t s) {
+void launch_detect(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     const int warps = kDetThreads / 32;
-    if (fp.det_tasks > 0) detect_kernel<<<(fp.det_tasks + warps - 1) / warps, kDetThreads, 0, s>>>(fp);
+    const int t0 = fp.oct[o_begin].det_task0, t1 = o_end < fp.nOct ? fp.oct[o_end].det_task0 : fp.det_tasks;
+    if (t1 > t0) detect_kernel<<<(t1 - t0 + warps - 1) / warps, kDetThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
-void launch_scan_rows(const FrameParams& fp, cudaStream_t s) { scan_rows_kernel<<<fp.nOct, 1024, 0, s>>>(fp); }
-void launch_scatter(const FrameParams& fp, cudaStream_t s) {
-    scatter_kernel<<<(fp.rows_total + 7) / 8, 256, 0, s>>>(fp);
+void launch_scan_rows(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
+    scan_rows_kernel<<<o_end - o_begin, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
-void launch_refine(const FrameParams& fp, cudaStream_t s) {
+void launch_scatter(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
+    const int r0 = fp.oct[o_begin].row0, r1 = o_end < fp.nOct ? fp.oct[o_end].row0 : fp.rows_total;
+    scatter_kernel<<<(r1 - r0 + 7) / 8, 256, 0, s>>>(octave_range(fp, o_begin, o_end));
+}
+void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     int maxcap = 1;
-    for (int i = 0; i < fp.nOct; i++) maxcap = fp.oct[i].cap > maxcap ? fp.oct[i].cap : maxcap;
-    dim3 grid((maxcap + 127) / 128, fp.nOct);
-    refine_kernel<<<grid, 128, 0, s>>>(fp);
+    for (int i = o_begin; i < o_end; i++) maxcap = fp.oct[i].cap > maxcap ? fp.oct[i].cap : maxcap;
+    dim3 grid((maxcap + 127) / 128, o_end - o_begin);
+    refine_kernel<<<grid, 128, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
-void launch_compact_refined(const FrameParams& fp, cudaStream_t s) { compact_refined_kernel<<<fp.nOct, 1024, 0, s>>>(fp); }
+void launch_compact_refined(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
+    compact_refined_kernel<<<o_end - o_begin, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
+}
 
 }  // namespace b200sift
