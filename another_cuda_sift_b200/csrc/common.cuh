@@ -80,7 +80,7 @@ void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s
 void launch_compact_refined(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 void launch_orientation(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 void launch_compact_oriented(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
-void launch_descriptor(const FrameParams& fp, cudaStream_t s);
+void launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 
 int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s,
                  float* dbg = nullptr);

@@ -220,7 +220,9 @@ __device__ __forceinline__ float rsqrt_approx(float x) {  // x must be a normal 
 }
 
 // One CTA per returned keypoint (global index g over octaves in ascending order, truncated at
-// numFeatures: utils/CudaMemcpyUtils.cu:38-67).
+// numFeatures: utils/CudaMemcpyUtils.cu:38-67). A launch covers an octave range, so that the descriptors of
+// octave 0 can start while the small octaves are still being detected; the range that ends at the last
+// octave publishes the frame's keypoint count.
 //
 // The reference (SiftOps.cu:448-604) walks the (2*radius+1)^2 bounding patch and fires 8 shared-memory
 // float atomics per sample that lands in the rotated 5x5-cell window. Shared atomics retire about one lane
@@ -240,17 +242,20 @@ __device__ __forceinline__ float rsqrt_approx(float x) {  // x must be a normal 
 // rounded to fp16).
 __global__ void __launch_bounds__(kDescThreads)
 descriptor_kernel(const __grid_constant__ FrameParams fp) {
-    const int g = blockIdx.x;
-    int oi = 0, j = g, sum = 0;
+    // this launch covers octaves [o_begin, o_end); `first` keypoints of lower octaves precede it in the output
+    int first = 0;
+    for (int i = 0; i < fp.o_begin; i++) first += fp.oct[i].counts[2];
+    int oi = fp.o_begin, j = blockIdx.x, sum = first;
     bool found = false;
-    for (int i = 0; i < fp.nOct; i++) {
+    for (int i = fp.o_begin; i < fp.o_end; i++) {
         const int T = fp.oct[i].counts[2];
         if (!found && j < T) { oi = i; found = true; }
         if (!found) j -= T;
         sum += T;
     }
-    if (g == 0 && threadIdx.x == 0) *fp.total = min(sum, fp.numFeatures);
-    if (!found) return;
+    const int g = first + blockIdx.x;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && fp.o_end == fp.nOct) *fp.total = min(sum, fp.numFeatures);
+    if (!found || g >= fp.numFeatures) return;
     const OctParams& o = fp.oct[oi];
     const float3 kp = o.cand[j];
     const float4 ft = o.candF[j];
@@ -466,13 +471,20 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
 }  // namespace
 
 void launch_orientation(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
-    orientation_kernel<<<148 * (o_begin == 0 ? 16 : 4), kOriThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
+    long cap = 0;  // CTA per keypoint, grid-stride; small octave ranges cannot fill a 16-deep grid
+    for (int i = o_begin; i < o_end; i++) cap += fp.oct[i].cap;
+    const int grid = (int)(cap < 148L * 16 ? (cap > 0 ? cap : 1) : 148L * 16);
+    orientation_kernel<<<grid, kOriThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 void launch_compact_oriented(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     compact_oriented_kernel<<<o_end - o_begin, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
-void launch_descriptor(const FrameParams& fp, cudaStream_t s) {
-    descriptor_kernel<<<fp.numFeatures, kDescThreads, 0, s>>>(fp);
+void launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
+    // upper bound on the keypoints of the range: its slot capacity, and never more than the output holds
+    long cap = 0;
+    for (int i = o_begin; i < o_end; i++) cap += fp.oct[i].cap;
+    const int grid = (int)(cap < (long)fp.numFeatures ? cap : (long)fp.numFeatures);
+    descriptor_kernel<<<grid > 0 ? grid : 1, kDescThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 
 }  // namespace b200sift

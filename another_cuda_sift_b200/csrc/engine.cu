@@ -151,11 +151,21 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
     // Gaussian pyramid. Octave o+1 only needs layer 3 of octave o, so layers 4 and 5 of every big octave
     // go to a side stream (a parallel branch of the frame graph) while the main chain moves on to the next
     // octave; octaves of <= kTailPixels pixels are walked by one CTA (launch_pyramid_tail).
-    // Everything between the pyramid and the descriptor is per-octave work, so octave 0 (three quarters of
-    // the pixels and keypoints) runs its detect..orientation chain on its own branch as soon as its six
-    // layers exist, overlapping the latency-bound small octaves and the single-CTA tail.
+    // Everything after the pyramid is per-octave work, and the small octaves are a long chain of
+    // latency-bound launches. The frame graph therefore has three branches, each running
+    // detect .. orientation .. descriptor for its own octave range as soon as its layers exist:
+    //   A  octave 0 (three quarters of the pixels and keypoints)        on side[0]
+    //   B  the other multi-CTA octaves [1, tail_first)                  on side[1]
+    //   C  the tail octaves [tail_first, nOct)                          on the main stream
+    // A descriptor launch needs the keypoint counts of all lower octaves (its offset into the output), so
+    // B waits for A's orientation compaction and C for both; C publishes the frame's keypoint count.
     const bool fork = (prof == nullptr) && d->side[0] != nullptr;
-    const int split = (fork && d->nOct > 1 && d->tail_first >= 1) ? 1 : 0;  // octaves [0,split) on branch A
+    const int b_end = d->tail_first < d->nOct ? d->tail_first : d->nOct;
+    const bool split = fork && d->nOct > 1 && b_end >= 1;
+    const int a_end = split ? 1 : 0;                                   // A = [0, a_end)
+    const int c_begin = split ? (b_end < d->nOct ? b_end : 1) : 0;     // C = [c_begin, nOct) on the main stream
+    const bool has_b = split && c_begin > 1;                           // B = [1, c_begin)
+    cudaEvent_t ev_countsA = d->ev_join[2 % kMaxOctaves], ev_countsB = d->ev_join[3 % kMaxOctaves];
     auto chain = [&](int ob, int oe, cudaStream_t cs) -> int {
         if (last_stage >= 3) {
             launch_detect(fp, ob, oe, cs); n++; MARK(B200SIFT_K_DETECT);
@@ -177,7 +187,7 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
         }
         return 0;
     };
-    bool joinA = false, joinB = false;
+    bool usedA = false, usedB = false;
     for (int o = 0; o < d->nOct; o++) {
         OctParams& oc = fp.oct[o];
         const size_t ls = (size_t)oc.pitch * oc.h;
@@ -204,32 +214,51 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
         cudaStream_t ls_stream = s;
         for (int l = 1; l < kGaussLayers; l++) {
             if (l == 4 && fork && o + 1 < d->nOct) {  // layers 4,5 off the critical path
-                cudaStream_t side = d->side[o < split ? 0 : 1];
+                cudaStream_t side = d->side[o < a_end ? 0 : 1];
                 CU(cudaEventRecord(d->ev_fork[o], s));
                 CU(cudaStreamWaitEvent(side, d->ev_fork[o], 0));
                 ls_stream = side;
+                (o < a_end ? usedA : usedB) = true;
             }
             launch_blur(oc.gauss + ls * (l - 1), oc.pitch, oc.gauss + ls * l, oc.pitch, oc.w, oc.h, d->taps[l], ls_stream);
             MARK(o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL);
             n++;
         }
-        if (ls_stream != s) (o < split ? joinA : joinB) = true;
-        if (split && o == split - 1) {  // branch A: octave 0 is complete on side[0]
-            if (int rc = chain(0, split, ls_stream)) return rc;
+        if (split && o == a_end - 1) {  // branch A: octave 0 is complete on side[0]
+            if (int rc = chain(0, a_end, d->side[0])) return rc;
+            CU(cudaEventRecord(ev_countsA, d->side[0]));
+            if (last_stage >= 6) { launch_descriptor(fp, 0, a_end, d->side[0]); n++; }
+        }
+        if (has_b && o == c_begin - 1) {  // branch B: octaves [1, c_begin) are complete on side[1]
+            if (int rc = chain(a_end, c_begin, d->side[1])) return rc;
+            CU(cudaEventRecord(ev_countsB, d->side[1]));
+            if (last_stage >= 6) {
+                CU(cudaStreamWaitEvent(d->side[1], ev_countsA, 0));
+                launch_descriptor(fp, a_end, c_begin, d->side[1]);
+                n++;
+            }
         }
     }
-    if (joinB) {
+    if (usedB && !has_b) {  // side[1] only carried layers 4,5: they must be there before C's detect
         CU(cudaEventRecord(d->ev_join[1], d->side[1]));
         CU(cudaStreamWaitEvent(s, d->ev_join[1], 0));
     }
-    if (int rc = chain(split, d->nOct, s)) return rc;
-    if (joinA) {
+    if (int rc = chain(c_begin, d->nOct, s)) return rc;
+    if (last_stage >= 6) {
+        if (split) CU(cudaStreamWaitEvent(s, ev_countsA, 0));
+        if (has_b) CU(cudaStreamWaitEvent(s, ev_countsB, 0));
+        launch_descriptor(fp, c_begin, d->nOct, s); n++;
+        MARK(B200SIFT_K_DESCRIBE);
+    }
+    if (usedA) {
         CU(cudaEventRecord(d->ev_join[0], d->side[0]));
         CU(cudaStreamWaitEvent(s, d->ev_join[0], 0));
     }
+    if (has_b) {
+        CU(cudaEventRecord(d->ev_join[1], d->side[1]));
+        CU(cudaStreamWaitEvent(s, d->ev_join[1], 0));
+    }
     if (last_stage >= 6) {
-        launch_descriptor(fp, s); n++;
-        MARK(B200SIFT_K_DESCRIBE);
         CU(cudaMemcpyAsync(d->h_total, fp.total, sizeof(int), cudaMemcpyDeviceToHost, s));
         MARK(B200SIFT_K_COPY);
     }
@@ -338,7 +367,7 @@ int build(b200sift_detector* d) {
     *d->h_total = 0;
     CU(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
     for (int i = 0; i < kSideStreams; i++) CU(cudaStreamCreateWithFlags(&d->side[i], cudaStreamNonBlocking));
-    for (int o = 0; o < d->nOct; o++) {
+    for (int o = 0; o < kMaxOctaves; o++) {
         CU(cudaEventCreateWithFlags(&d->ev_fork[o], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&d->ev_join[o], cudaEventDisableTiming));
     }
