@@ -12,6 +12,7 @@
 // order independent (deterministic) and lies inside the reference's own run-to-run envelope:
 // orientation bins as 2^-32 in 64 bits (peak selection is a discrete decision, keep it as exact as
 // possible), descriptor bins as 2^-15 in 32 bits (8 votes per sample: one ATOMS.ADD each).
+#include <cstdlib>
 #include "common.cuh"
 
 namespace b200sift {
@@ -201,6 +202,7 @@ constexpr int kPrivSlots = 32;  // 2 x 2 spatial neighbours x 8 orientation bins
 // column 0 cover rbin in (-1,1) (truncating modff, quirk Q13), so cell (0,0) is four units of area, the other
 // row-0 / column-0 cells two, the rest one. Warps pull cells from this queue (longest-processing-time order).
 __constant__ signed char kCellOrder[16] = {0, 1, 2, 3, 4, 8, 12, 5, 6, 7, 9, 10, 11, 13, 14, 15};
+constexpr int kDescCtasPerSm = 7;  // register-limited residency of descriptor_kernel
 constexpr int kRing = 64;  // per-warp ring of accepted samples (at most 31 pending + 32 appended)
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -245,20 +247,10 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     // this launch covers octaves [o_begin, o_end); `first` keypoints of lower octaves precede it in the output
     int first = 0;
     for (int i = 0; i < fp.o_begin; i++) first += fp.oct[i].counts[2];
-    int oi = fp.o_begin, j = blockIdx.x, sum = first;
-    bool found = false;
-    for (int i = fp.o_begin; i < fp.o_end; i++) {
-        const int T = fp.oct[i].counts[2];
-        if (!found && j < T) { oi = i; found = true; }
-        if (!found) j -= T;
-        sum += T;
-    }
-    const int g = first + blockIdx.x;
-    if (blockIdx.x == 0 && threadIdx.x == 0 && fp.o_end == fp.nOct) *fp.total = min(sum, fp.numFeatures);
-    if (!found || g >= fp.numFeatures) return;
-    const OctParams& o = fp.oct[oi];
-    const float3 kp = o.cand[j];
-    const float4 ft = o.candF[j];
+    int range_total = 0;
+    for (int i = fp.o_begin; i < fp.o_end; i++) range_total += fp.oct[i].counts[2];
+    if (blockIdx.x == 0 && threadIdx.x == 0 && fp.o_end == fp.nOct) *fp.total = min(first + range_total, fp.numFeatures);
+    const int limit = min(range_total, fp.numFeatures - first);  // keypoints of this range that are returned
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     __shared__ int s_hist[kHistSize];
@@ -268,11 +260,19 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     __shared__ __align__(128) float s_priv[kDescWarps][kPrivSlots][32];
     __shared__ int s_ring[kDescWarps][kRing];
     __shared__ int s_next;
-    if (tid == 0) s_next = 0;
-    for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0;
     float* priv = &s_priv[warp][0][lane];
 #pragma unroll
-    for (int k = 0; k < kPrivSlots; k++) priv[k * 32] = 0.f;
+    for (int k = 0; k < kPrivSlots; k++) priv[k * 32] = 0.f;  // every flush leaves the columns zeroed again
+
+    for (int b = blockIdx.x; b < limit; b += gridDim.x) {  // persistent CTAs, grid-stride over the keypoints
+    int oi = fp.o_begin, j = b;
+    while (j >= fp.oct[oi].counts[2]) { j -= fp.oct[oi].counts[2]; oi++; }
+    const int g = first + b;
+    const OctParams& o = fp.oct[oi];
+    const float3 kp = o.cand[j];
+    const float4 ft = o.candF[j];
+    if (tid == 0) s_next = 0;
+    for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0;
     __syncthreads();
 
     // unpackOctave (SiftOps.cu:389-401)
@@ -466,6 +466,7 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
         fp.out_kpts[g] = kp;
         fp.out_feats[g] = ft;
     }
+    }  // keypoint loop (the barriers above order the reuse of the shared buffers)
 }
 
 }  // namespace
@@ -483,8 +484,23 @@ void launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cudaStream
     // upper bound on the keypoints of the range: its slot capacity, and never more than the output holds
     long cap = 0;
     for (int i = o_begin; i < o_end; i++) cap += fp.oct[i].cap;
-    const int grid = (int)(cap < (long)fp.numFeatures ? cap : (long)fp.numFeatures);
-    descriptor_kernel<<<grid > 0 ? grid : 1, kDescThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
+    long grid = cap < (long)fp.numFeatures ? cap : (long)fp.numFeatures;
+    static const long max_grid = getenv("B200SIFT_DESC_GRID") ? atol(getenv("B200SIFT_DESC_GRID")) : 148L * kDescCtasPerSm;
+    if (grid > max_grid) grid = max_grid;
+    // Lowest stream priority: the descriptor grids would otherwise fill every CTA slot and starve the short
+    // latency-bound kernels of the other graph branches (the priority is recorded in the captured node).
+    int least = 0, greatest = 0;
+    cudaDeviceGetStreamPriorityRange(&least, &greatest);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(grid > 0 ? grid : 1));
+    cfg.blockDim = dim3(kDescThreads);
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributePriority;
+    attr[0].val.priority = least;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaLaunchKernelEx(&cfg, descriptor_kernel, octave_range(fp, o_begin, o_end));
 }
 
 }  // namespace b200sift

@@ -68,7 +68,8 @@ inline int pitch_floats(int w) { return ((w * 4 + 511) / 512) * 512 / 4; }
 
 }  // namespace
 
-constexpr int kSideStreams = 2;
+constexpr int kSideStreams = 6;   // side branches of the frame graph
+constexpr int kBranchPixels = 65536;  // an octave with at least this many pixels gets a branch of its own
 
 struct b200sift_detector {
     b200sift_config cfg;
@@ -94,9 +95,13 @@ struct b200sift_detector {
     size_t match_scratch_bytes_ = 0;
     std::vector<void*> allocs;
     cudaStream_t stream = nullptr;
-    cudaStream_t side[kSideStreams] = {nullptr, nullptr};
-    cudaEvent_t ev_fork[kMaxOctaves] = {nullptr}, ev_join[kMaxOctaves] = {nullptr};
+    cudaStream_t side[kSideStreams] = {nullptr};
+    cudaEvent_t ev_fork[kMaxOctaves] = {nullptr}, ev_join[kMaxOctaves] = {nullptr}, ev_counts[kMaxOctaves] = {nullptr};
     int tail_first = 0;  // first octave handled by the single-CTA tail kernel
+    // Branches of the frame graph: octave ranges [br_begin, br_end). Branches 0 .. n_side-1 cover the
+    // multi-CTA octaves and run on side streams; the tail octaves (if any) run on the main stream.
+    int n_side = 0;
+    int br_begin[kSideStreams] = {0}, br_end[kSideStreams] = {0};
     cudaGraph_t graph[2] = {nullptr, nullptr};
     cudaGraphExec_t exec[2] = {nullptr, nullptr};
     int launches = 0;
@@ -152,20 +157,13 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
     // go to a side stream (a parallel branch of the frame graph) while the main chain moves on to the next
     // octave; octaves of <= kTailPixels pixels are walked by one CTA (launch_pyramid_tail).
     // Everything after the pyramid is per-octave work, and the small octaves are a long chain of
-    // latency-bound launches. The frame graph therefore has three branches, each running
-    // detect .. orientation .. descriptor for its own octave range as soon as its layers exist:
-    //   A  octave 0 (three quarters of the pixels and keypoints)        on side[0]
-    //   B  the other multi-CTA octaves [1, tail_first)                  on side[1]
-    //   C  the tail octaves [tail_first, nOct)                          on the main stream
+    // latency-bound launches. The frame graph therefore branches per octave range (build(): one branch
+    // per big octave, one for the remaining multi-CTA octaves, the tail octaves on the main stream); each
+    // branch runs detect .. orientation .. descriptor as soon as the six layers of its octaves exist.
     // A descriptor launch needs the keypoint counts of all lower octaves (its offset into the output), so
-    // B waits for A's orientation compaction and C for both; C publishes the frame's keypoint count.
+    // branch b waits for ev_counts[b-1], which branch b-1 records after its own wait: the dependency is
+    // transitive. The branch that ends at the last octave publishes the frame's keypoint count.
     const bool fork = (prof == nullptr) && d->side[0] != nullptr;
-    const int b_end = d->tail_first < d->nOct ? d->tail_first : d->nOct;
-    const bool split = fork && d->nOct > 1 && b_end >= 1;
-    const int a_end = split ? 1 : 0;                                   // A = [0, a_end)
-    const int c_begin = split ? (b_end < d->nOct ? b_end : 1) : 0;     // C = [c_begin, nOct) on the main stream
-    const bool has_b = split && c_begin > 1;                           // B = [1, c_begin)
-    cudaEvent_t ev_countsA = d->ev_join[2 % kMaxOctaves], ev_countsB = d->ev_join[3 % kMaxOctaves];
     auto chain = [&](int ob, int oe, cudaStream_t cs) -> int {
         if (last_stage >= 3) {
             launch_detect(fp, ob, oe, cs); n++; MARK(B200SIFT_K_DETECT);
@@ -187,7 +185,8 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
         }
         return 0;
     };
-    bool usedA = false, usedB = false;
+    int br = 0;  // branch of the current multi-CTA octave
+    bool used[kSideStreams] = {false};
     for (int o = 0; o < d->nOct; o++) {
         OctParams& oc = fp.oct[o];
         const size_t ls = (size_t)oc.pitch * oc.h;
@@ -211,53 +210,47 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
             }
             continue;
         }
+        while (o >= d->br_end[br]) br++;
+        cudaStream_t bs = fork ? d->side[br] : s;  // the branch's stream
         cudaStream_t ls_stream = s;
         for (int l = 1; l < kGaussLayers; l++) {
-            if (l == 4 && fork && o + 1 < d->nOct) {  // layers 4,5 off the critical path
-                cudaStream_t side = d->side[o < a_end ? 0 : 1];
+            if (l == 4 && fork) {  // layers 4,5 off the critical path
                 CU(cudaEventRecord(d->ev_fork[o], s));
-                CU(cudaStreamWaitEvent(side, d->ev_fork[o], 0));
-                ls_stream = side;
-                (o < a_end ? usedA : usedB) = true;
+                CU(cudaStreamWaitEvent(bs, d->ev_fork[o], 0));
+                ls_stream = bs;
+                used[br] = true;
             }
             launch_blur(oc.gauss + ls * (l - 1), oc.pitch, oc.gauss + ls * l, oc.pitch, oc.w, oc.h, d->taps[l], ls_stream);
             MARK(o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL);
             n++;
         }
-        if (split && o == a_end - 1) {  // branch A: octave 0 is complete on side[0]
-            if (int rc = chain(0, a_end, d->side[0])) return rc;
-            CU(cudaEventRecord(ev_countsA, d->side[0]));
-            if (last_stage >= 6) { launch_descriptor(fp, 0, a_end, d->side[0]); n++; }
-        }
-        if (has_b && o == c_begin - 1) {  // branch B: octaves [1, c_begin) are complete on side[1]
-            if (int rc = chain(a_end, c_begin, d->side[1])) return rc;
-            CU(cudaEventRecord(ev_countsB, d->side[1]));
+        if (o == d->br_end[br] - 1) {  // the branch's octaves are complete
+            if (int rc = chain(d->br_begin[br], d->br_end[br], bs)) return rc;
+            if (fork) {
+                if (br > 0) CU(cudaStreamWaitEvent(bs, d->ev_counts[br - 1], 0));
+                CU(cudaEventRecord(d->ev_counts[br], bs));
+            }
             if (last_stage >= 6) {
-                CU(cudaStreamWaitEvent(d->side[1], ev_countsA, 0));
-                launch_descriptor(fp, a_end, c_begin, d->side[1]);
+                launch_descriptor(fp, d->br_begin[br], d->br_end[br], bs);
                 n++;
+                MARK(B200SIFT_K_DESCRIBE);
             }
         }
     }
-    if (usedB && !has_b) {  // side[1] only carried layers 4,5: they must be there before C's detect
-        CU(cudaEventRecord(d->ev_join[1], d->side[1]));
-        CU(cudaStreamWaitEvent(s, d->ev_join[1], 0));
+    if (d->tail_first < d->nOct) {  // tail octaves on the main stream
+        if (int rc = chain(d->tail_first, d->nOct, s)) return rc;
+        if (fork && d->n_side > 0) CU(cudaStreamWaitEvent(s, d->ev_counts[d->n_side - 1], 0));
+        if (last_stage >= 6) {
+            launch_descriptor(fp, d->tail_first, d->nOct, s);
+            n++;
+            MARK(B200SIFT_K_DESCRIBE);
+        }
     }
-    if (int rc = chain(c_begin, d->nOct, s)) return rc;
-    if (last_stage >= 6) {
-        if (split) CU(cudaStreamWaitEvent(s, ev_countsA, 0));
-        if (has_b) CU(cudaStreamWaitEvent(s, ev_countsB, 0));
-        launch_descriptor(fp, c_begin, d->nOct, s); n++;
-        MARK(B200SIFT_K_DESCRIBE);
-    }
-    if (usedA) {
-        CU(cudaEventRecord(d->ev_join[0], d->side[0]));
-        CU(cudaStreamWaitEvent(s, d->ev_join[0], 0));
-    }
-    if (has_b) {
-        CU(cudaEventRecord(d->ev_join[1], d->side[1]));
-        CU(cudaStreamWaitEvent(s, d->ev_join[1], 0));
-    }
+    for (int b = 0; b < d->n_side; b++)
+        if (used[b]) {
+            CU(cudaEventRecord(d->ev_join[b], d->side[b]));
+            CU(cudaStreamWaitEvent(s, d->ev_join[b], 0));
+        }
     if (last_stage >= 6) {
         CU(cudaMemcpyAsync(d->h_total, fp.total, sizeof(int), cudaMemcpyDeviceToHost, s));
         MARK(B200SIFT_K_COPY);
@@ -365,14 +358,29 @@ int build(b200sift_detector* d) {
     }
     CU(cudaMallocHost(&d->h_total, sizeof(int)));
     *d->h_total = 0;
-    CU(cudaStreamCreateWithFlags(&d->stream, cudaStreamNonBlocking));
-    for (int i = 0; i < kSideStreams; i++) CU(cudaStreamCreateWithFlags(&d->side[i], cudaStreamNonBlocking));
+    // everything but the descriptor launches (launch_descriptor) runs at the highest stream priority
+    int prio_least = 0, prio_greatest = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+    CU(cudaStreamCreateWithPriority(&d->stream, cudaStreamNonBlocking, prio_greatest));
+    for (int i = 0; i < kSideStreams; i++) CU(cudaStreamCreateWithPriority(&d->side[i], cudaStreamNonBlocking, prio_greatest));
     for (int o = 0; o < kMaxOctaves; o++) {
         CU(cudaEventCreateWithFlags(&d->ev_fork[o], cudaEventDisableTiming));
         CU(cudaEventCreateWithFlags(&d->ev_join[o], cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&d->ev_counts[o], cudaEventDisableTiming));
     }
     d->tail_first = d->nOct;
     for (int o = d->nOct - 1; o >= 0 && tail_octave(fp.oct[o].w, fp.oct[o].h); o--) d->tail_first = o;
+    // graph branches over the multi-CTA octaves [0, tail_first): big octaves alone, the rest together
+    d->n_side = 0;
+    for (int o = 0; o < d->tail_first;) {
+        int e = o + 1;
+        const bool big = fp.oct[o].w * fp.oct[o].h >= kBranchPixels && d->n_side < kSideStreams - 1;
+        if (!big) e = d->tail_first;
+        d->br_begin[d->n_side] = o;
+        d->br_end[d->n_side] = e;
+        d->n_side++;
+        o = e;
+    }
 
     CU(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
     for (int b = 0; b < 2; b++) {
@@ -455,6 +463,7 @@ int b200sift_destroy(b200sift_detector* d) {
         if (d->side[i]) cudaStreamDestroy(d->side[i]);
     for (int o = 0; o < kMaxOctaves; o++) {
         if (d->ev_fork[o]) cudaEventDestroy(d->ev_fork[o]);
+        if (d->ev_counts[o]) cudaEventDestroy(d->ev_counts[o]);
         if (d->ev_join[o]) cudaEventDestroy(d->ev_join[o]);
     }
     delete d;
