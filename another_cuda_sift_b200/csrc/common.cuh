@@ -36,7 +36,6 @@ struct OctParams {
     float* gauss;        // [6][h][pitch]
     uint32_t* mask;      // [3][h][words] extrema bits
     int* rowcount;       // [3*h] extrema per (scale,row); zeroed every frame
-    int* rowoff;         // [3*h] exclusive prefix of rowcount
     float3* cand;        // [cap]
     float4* candF;       // [cap]
     float3* coll;        // [cap]
@@ -49,6 +48,7 @@ struct OctParams {
     int det_task0;       // first warp task of this octave in the detect kernel
     int det_cols, det_rows;  // column strips (32 px) x row strips (kDetRows rows)
     int row0;            // first (scale,row) index of this octave in the scatter kernel
+    int scat_cta0;       // first CTA of this octave in the scatter kernel (8 rows per CTA, CTAs never straddle octaves)
 };
 
 struct FrameParams {
@@ -74,8 +74,7 @@ void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w
 void launch_downsample(const float* in, int in_pitch, int iw, int ih, float* out, int out_pitch, int ow, int oh, cudaStream_t s);
 void launch_pyramid_tail(const FrameParams& fp, const Taps* taps, int first_octave, cudaStream_t s);
 void launch_detect(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);       // bitmask + row counts
-void launch_scan_rows(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);    // row offsets, P
-void launch_scatter(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);      // ordered candidate list
+void launch_scatter(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);      // row offsets, P, ordered candidate list
 void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);       // Taylor refinement + tests
 void launch_compact_refined(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 void launch_orientation(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
@@ -112,41 +111,47 @@ __host__ __device__ inline int reflect101(int idx, int length) {
 }
 
 #ifdef __CUDACC__
-// Single-CTA (1024 threads) exclusive scan over n small integers with one barrier: warp w owns
-// the contiguous segment [w*seg, (w+1)*seg), sums it, the 32 warp totals are combined by every
-// warp from shared memory, and the segment is walked a second time (L1-resident) to hand each
-// element its exclusive prefix and the grand total. Returns the total.
+// Exclusive scan over n small integers by MANY independent CTAs of 1024 threads with one barrier and no
+// inter-CTA communication: CTA `seg` owns elements [seg*1024, seg*1024+1024) and recomputes, from the whole
+// input (n is a few thousand, L2-resident), the sum of everything before its segment and the grand total.
+// emit(i, v, exclusive_prefix, total) is called for the CTA's own elements. Returns the total.
 template <class Load, class Emit>
-__device__ __forceinline__ int block_scan_1024(int n, Load load, Emit emit) {
-    __shared__ int s_ws[32];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int seg = ((n + 1023) >> 10) << 5;
-    const int lo = warp * seg, hi = min(n, lo + seg);
-    int local = 0;
-    for (int i = lo + lane; i < hi; i += 32) local += load(i);
+__device__ __forceinline__ int segment_scan_1024(int n, int seg, Load load, Emit emit) {
+    __shared__ int s_before[32], s_all[32], s_mine[32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int seg0 = seg << 10;
+    int before = 0, all = 0, mine = 0;
+    for (int i = tid; i < n; i += 1024) {
+        const int v = load(i);
+        all += v;
+        if (i < seg0) before += v;
+        if (i == seg0 + tid) mine = v;
+    }
+    int incl = mine;
 #pragma unroll
-    for (int d = 16; d > 0; d >>= 1) local += __shfl_xor_sync(0xffffffffu, local, d);
-    if (lane == 0) s_ws[warp] = local;
-    __syncthreads();
-    int total = s_ws[lane];
-    int base = lane < warp ? total : 0;
+    for (int d = 1; d < 32; d <<= 1) {
+        const int u = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += u;
+    }
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
-        total += __shfl_xor_sync(0xffffffffu, total, d);
-        base += __shfl_xor_sync(0xffffffffu, base, d);
+        before += __shfl_xor_sync(0xffffffffu, before, d);
+        all += __shfl_xor_sync(0xffffffffu, all, d);
     }
-    for (int c = lo; c < hi; c += 32) {
-        const int i = c + lane;
-        const int v = i < hi ? load(i) : 0;
-        int incl = v;
+    if (lane == 31) s_mine[warp] = incl;
+    if (lane == 0) { s_before[warp] = before; s_all[warp] = all; }
+    __syncthreads();
+    int base = s_before[lane], total = s_all[lane];
+    const int wm = s_mine[lane];
+    int woff = lane < warp ? wm : 0;
 #pragma unroll
-        for (int d = 1; d < 32; d <<= 1) {
-            const int u = __shfl_up_sync(0xffffffffu, incl, d);
-            if (lane >= d) incl += u;
-        }
-        if (i < hi) emit(i, v, base + incl - v, total);
-        base += __shfl_sync(0xffffffffu, incl, 31);
+    for (int d = 16; d > 0; d >>= 1) {
+        base += __shfl_xor_sync(0xffffffffu, base, d);
+        total += __shfl_xor_sync(0xffffffffu, total, d);
+        woff += __shfl_xor_sync(0xffffffffu, woff, d);
     }
+    const int i = seg0 + tid;
+    if (i < n) emit(i, mine, base + woff + incl - mine, total);
     return total;
 }
 #endif

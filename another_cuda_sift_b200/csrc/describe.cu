@@ -171,14 +171,15 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
     }
 }
 
-// One CTA per octave: prefix over per-keypoint peak counts -> cand/candF in (k, bin) order; the
-// entry whose prefix equals the total T is not written (quirk Q5 again).
+// CTA (blockIdx.x, octave): prefix over the per-keypoint peak counts of its 1024-keypoint segment ->
+// cand/candF in (k, bin) order; the entry whose prefix equals the total T is not written (quirk Q5 again).
 __global__ void __launch_bounds__(1024)
 compact_oriented_kernel(const __grid_constant__ FrameParams fp) {
-    const OctParams& o = fp.oct[fp.o_begin + blockIdx.x];
+    const OctParams& o = fp.oct[fp.o_begin + blockIdx.y];
     const int M = o.counts[1];
-    const int total = block_scan_1024(
-        M, [&](int k) { return o.oricnt[k]; },
+    if (blockIdx.x > 0 && (int)(blockIdx.x << 10) >= M) return;
+    const int total = segment_scan_1024(
+        M, blockIdx.x, [&](int k) { return o.oricnt[k]; },
         [&](int k, int v, int excl, int tot) {
             for (int c = 0; c < v; c++) {
                 const int p = excl + c;
@@ -189,7 +190,7 @@ compact_oriented_kernel(const __grid_constant__ FrameParams fp) {
                 }
             }
         });
-    if (threadIdx.x == 0) o.counts[2] = total;  // T
+    if (blockIdx.x == 0 && threadIdx.x == 0) o.counts[2] = total;  // T
 }
 
 // ---------------------------------------------------------------- descriptor
@@ -478,7 +479,10 @@ void launch_orientation(const FrameParams& fp, int o_begin, int o_end, cudaStrea
     orientation_kernel<<<grid, kOriThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 void launch_compact_oriented(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
-    compact_oriented_kernel<<<o_end - o_begin, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
+    int maxcap = 1;
+    for (int i = o_begin; i < o_end; i++) maxcap = fp.oct[i].cap > maxcap ? fp.oct[i].cap : maxcap;
+    dim3 grid((maxcap + 1023) / 1024, o_end - o_begin);
+    compact_oriented_kernel<<<grid, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 void launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     // upper bound on the keypoints of the range: its slot capacity, and never more than the output holds

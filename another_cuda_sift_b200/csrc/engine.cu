@@ -167,7 +167,6 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
     auto chain = [&](int ob, int oe, cudaStream_t cs) -> int {
         if (last_stage >= 3) {
             launch_detect(fp, ob, oe, cs); n++; MARK(B200SIFT_K_DETECT);
-            launch_scan_rows(fp, ob, oe, cs); n++;
             launch_scatter(fp, ob, oe, cs); n++;
             MARK(B200SIFT_K_COMPACT);
         }
@@ -301,7 +300,7 @@ int build(b200sift_detector* d) {
         if (int rc = dev_alloc(d, &d->d_input_u8[b], d->u8_pitch * c.row_width)) return rc;
     }
 
-    int rows_total = 0;
+    int rows_total = 0, scat_ctas = 0;
     for (int o = 0; o < d->nOct; o++) {
         OctParams& oc = fp.oct[o];
         oc.w = (int)roundf(c.col_width / powf(2, o));  // Detector.cu:83
@@ -312,12 +311,12 @@ int build(b200sift_detector* d) {
         oc.words = (oc.w + 31) / 32;
         oc.row0 = rows_total;
         rows_total += kScales * oc.h;
+        oc.scat_cta0 = scat_ctas;
+        scat_ctas += (kScales * oc.h + 7) / 8;
     }
     fp.rows_total = rows_total;
     if (int rc = dev_alloc(d, &d->d_rowcount_all, (size_t)rows_total)) return rc;
     d->rowcount_bytes = (size_t)rows_total * sizeof(int);
-    int* d_rowoff_all = nullptr;
-    if (int rc = dev_alloc(d, &d_rowoff_all, (size_t)rows_total)) return rc;
     int* d_counts = nullptr;
     if (int rc = dev_alloc(d, &d_counts, (size_t)4 * kMaxOctaves + 4)) return rc;
     fp.total = d_counts + 4 * kMaxOctaves;
@@ -331,7 +330,6 @@ int build(b200sift_detector* d) {
         if (int rc = dev_alloc(d, &oc.gauss, ls * kGaussLayers + oc.pitch)) return rc;
         if (int rc = dev_alloc(d, &oc.mask, (size_t)kScales * oc.h * oc.words)) return rc;
         oc.rowcount = d->d_rowcount_all + oc.row0;
-        oc.rowoff = d_rowoff_all + oc.row0;
         if (int rc = dev_alloc(d, &oc.cand, (size_t)oc.cap)) return rc;
         if (int rc = dev_alloc(d, &oc.candF, (size_t)oc.cap)) return rc;
         if (int rc = dev_alloc(d, &oc.coll, (size_t)oc.cap)) return rc;

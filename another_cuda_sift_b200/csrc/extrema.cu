@@ -101,44 +101,48 @@ detect_kernel(const __grid_constant__ FrameParams fp) {
     }
 }
 
-// One CTA per octave: exclusive scan of the (scale,row) counts.
-__global__ void __launch_bounds__(1024)
-scan_rows_kernel(const __grid_constant__ FrameParams fp) {
-    const OctParams& o = fp.oct[fp.o_begin + blockIdx.x];
-    const int total = block_scan_1024(
-        kScales * o.h, [&](int i) { return o.rowcount[i]; },
-        [&](int i, int, int excl, int) { o.rowoff[i] = excl; });
-    if (threadIdx.x == 0) {
-        o.counts[0] = total;                 // P
-        o.counts[3] = min(total, o.cap);     // candidates the refinement looks at
-    }
-}
-
-// Warp per (octave, scale, row): append the row's extrema in x order.
+// CTA per 8 consecutive (scale,row) entries of one octave, warp per row: append the row's extrema in x order.
+// The row's offset into the candidate list is the sum of the counts of all earlier rows; every CTA adds
+// those up itself (a few thousand L2-resident integers) instead of waiting for a separate scan kernel.
 __global__ void __launch_bounds__(256)
 scatter_kernel(const __grid_constant__ FrameParams fp) {
-    const int lane = threadIdx.x & 31;
-    const int gw = fp.oct[fp.o_begin].row0 + blockIdx.x * 8 + (threadIdx.x >> 5);
-    if (gw >= (fp.o_end < fp.nOct ? fp.oct[fp.o_end].row0 : fp.rows_total)) return;
+    __shared__ int s_part[8], s_cnt[8];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int cta = fp.oct[fp.o_begin].scat_cta0 + blockIdx.x;
     int oi = fp.o_begin;
-    while (oi + 1 < fp.o_end && gw >= fp.oct[oi + 1].row0) oi++;
+    while (oi + 1 < fp.o_end && cta >= fp.oct[oi + 1].scat_cta0) oi++;
     const OctParams& o = fp.oct[oi];
-    const int row = gw - o.row0;
-    if (o.rowcount[row] == 0) return;
+    const int nrows = kScales * o.h;
+    const int row_first = (cta - o.scat_cta0) * 8;
+    const int row = row_first + warp;
+    int part = 0;
+    for (int i = threadIdx.x; i < row_first; i += 256) part += o.rowcount[i];
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) part += __shfl_xor_sync(0xffffffffu, part, d);
+    const int cnt = row < nrows ? o.rowcount[row] : 0;
+    if (lane == 0) { s_part[warp] = part; s_cnt[warp] = cnt; }
+    __syncthreads();
+    int base = 0;
+#pragma unroll
+    for (int w = 0; w < 8; w++) base += s_part[w] + (w < warp ? s_cnt[w] : 0);
+    if (row == nrows - 1 && lane == 0) {
+        o.counts[0] = base + cnt;               // P
+        o.counts[3] = min(base + cnt, o.cap);   // candidates the refinement looks at
+    }
+    if (cnt == 0) return;
     const int s = row / o.h, y = row - s * o.h;
-    int base = o.rowoff[row];
     const uint32_t* m = o.mask + (size_t)row * o.words;
     for (int w0 = 0; w0 < o.words; w0 += 32) {
         const int wi = w0 + lane;
         uint32_t bits = wi < o.words ? m[wi] : 0u;
-        const int cnt = __popc(bits);
-        int incl = cnt;
+        const int c = __popc(bits);
+        int incl = c;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
             int u = __shfl_up_sync(0xffffffffu, incl, d);
             if (lane >= d) incl += u;
         }
-        int idx = base + incl - cnt;
+        int idx = base + incl - c;
         while (bits) {
             const int b = __ffs(bits) - 1;
             bits &= bits - 1;
@@ -282,20 +286,22 @@ refine_kernel(const __grid_constant__ FrameParams fp) {
     o.flag[idx] = accept;
 }
 
-// One CTA per octave: stable compaction of accepted candidates into coll/collF. The element
-// whose prefix equals the total is not written (quirk Q5, SiftOps.cu:228).
+// CTA (blockIdx.x, octave): stable compaction of the accepted candidates of its 1024-element segment into
+// coll/collF. The element whose prefix equals the total is not written (quirk Q5, SiftOps.cu:228).
 __global__ void __launch_bounds__(1024)
 compact_refined_kernel(const __grid_constant__ FrameParams fp) {
-    const OctParams& o = fp.oct[fp.o_begin + blockIdx.x];
-    const int total = block_scan_1024(
-        o.counts[3], [&](int i) { return o.flag[i]; },
+    const OctParams& o = fp.oct[fp.o_begin + blockIdx.y];
+    const int n = o.counts[3];
+    if (blockIdx.x > 0 && (int)(blockIdx.x << 10) >= n) return;
+    const int total = segment_scan_1024(
+        n, blockIdx.x, [&](int i) { return o.flag[i]; },
         [&](int i, int v, int excl, int tot) {
             if (v && excl + 1 < tot) {
                 o.coll[excl] = o.cand[i];
                 o.collF[excl] = o.candF[i];
             }
         });
-    if (threadIdx.x == 0) o.counts[1] = total;  // M
+    if (blockIdx.x == 0 && threadIdx.x == 0) o.counts[1] = total;  // M
 }
 
 }  // namespace
@@ -305,12 +311,10 @@ void launch_detect(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s
     const int t0 = fp.oct[o_begin].det_task0, t1 = o_end < fp.nOct ? fp.oct[o_end].det_task0 : fp.det_tasks;
     if (t1 > t0) detect_kernel<<<(t1 - t0 + warps - 1) / warps, kDetThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
-void launch_scan_rows(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
-    scan_rows_kernel<<<o_end - o_begin, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
-}
 void launch_scatter(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
-    const int r0 = fp.oct[o_begin].row0, r1 = o_end < fp.nOct ? fp.oct[o_end].row0 : fp.rows_total;
-    scatter_kernel<<<(r1 - r0 + 7) / 8, 256, 0, s>>>(octave_range(fp, o_begin, o_end));
+    const OctParams& last = fp.oct[o_end - 1];
+    const int c0 = fp.oct[o_begin].scat_cta0, c1 = last.scat_cta0 + (kScales * last.h + 7) / 8;
+    scatter_kernel<<<c1 - c0, 256, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     int maxcap = 1;
@@ -319,7 +323,10 @@ void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s
     refine_kernel<<<grid, 128, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 void launch_compact_refined(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
-    compact_refined_kernel<<<o_end - o_begin, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
+    int maxcap = 1;
+    for (int i = o_begin; i < o_end; i++) maxcap = fp.oct[i].cap > maxcap ? fp.oct[i].cap : maxcap;
+    dim3 grid((maxcap + 1023) / 1024, o_end - o_begin);
+    compact_refined_kernel<<<grid, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 
 }  // namespace b200sift
