@@ -79,7 +79,8 @@ void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s
 void launch_compact_refined(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 void launch_orientation(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 void launch_compact_oriented(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
-void launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
+cudaError_t descriptor_setup();
+cudaError_t launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 
 int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s,
                  float* dbg = nullptr);
@@ -111,17 +112,20 @@ __host__ __device__ inline int reflect101(int idx, int length) {
 }
 
 #ifdef __CUDACC__
-// Exclusive scan over n small integers by MANY independent CTAs of 1024 threads with one barrier and no
-// inter-CTA communication: CTA `seg` owns elements [seg*1024, seg*1024+1024) and recomputes, from the whole
-// input (n is a few thousand, L2-resident), the sum of everything before its segment and the grand total.
-// emit(i, v, exclusive_prefix, total) is called for the CTA's own elements. Returns the total.
+// Exclusive scan over n small integers by MANY independent CTAs of kScanBlock threads with one barrier and no
+// inter-CTA communication: CTA `seg` owns elements [seg*kScanBlock, (seg+1)*kScanBlock) and recomputes, from
+// the whole input (n is a few thousand, L2-resident), the sum of everything before its segment and the
+// grand total. emit(i, v, exclusive_prefix, total) is called for the CTA's own elements. Returns the total.
+// Small CTAs on purpose: they have to find room next to the descriptor CTAs of the other graph branches.
+constexpr int kScanBlock = 256;
 template <class Load, class Emit>
-__device__ __forceinline__ int segment_scan_1024(int n, int seg, Load load, Emit emit) {
-    __shared__ int s_before[32], s_all[32], s_mine[32];
+__device__ __forceinline__ int segment_scan(int n, int seg, Load load, Emit emit) {
+    constexpr int NW = kScanBlock / 32;
+    __shared__ int s_before[NW], s_all[NW], s_mine[NW];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int seg0 = seg << 10;
+    const int seg0 = seg * kScanBlock;
     int before = 0, all = 0, mine = 0;
-    for (int i = tid; i < n; i += 1024) {
+    for (int i = tid; i < n; i += kScanBlock) {
         const int v = load(i);
         all += v;
         if (i < seg0) before += v;
@@ -141,9 +145,8 @@ __device__ __forceinline__ int segment_scan_1024(int n, int seg, Load load, Emit
     if (lane == 31) s_mine[warp] = incl;
     if (lane == 0) { s_before[warp] = before; s_all[warp] = all; }
     __syncthreads();
-    int base = s_before[lane], total = s_all[lane];
-    const int wm = s_mine[lane];
-    int woff = lane < warp ? wm : 0;
+    int base = lane < NW ? s_before[lane] : 0, total = lane < NW ? s_all[lane] : 0;
+    int woff = lane < warp ? s_mine[lane] : 0;  // warp < NW
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) {
         base += __shfl_xor_sync(0xffffffffu, base, d);

@@ -12,7 +12,6 @@
 // order independent (deterministic) and lies inside the reference's own run-to-run envelope:
 // orientation bins as 2^-32 in 64 bits (peak selection is a discrete decision, keep it as exact as
 // possible), descriptor bins as 2^-15 in 32 bits (8 votes per sample: one ATOMS.ADD each).
-#include <cstdlib>
 #include "common.cuh"
 
 namespace b200sift {
@@ -171,14 +170,14 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
     }
 }
 
-// CTA (blockIdx.x, octave): prefix over the per-keypoint peak counts of its 1024-keypoint segment ->
+// CTA (blockIdx.x, octave): prefix over the per-keypoint peak counts of its kScanBlock-keypoint segment ->
 // cand/candF in (k, bin) order; the entry whose prefix equals the total T is not written (quirk Q5 again).
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(kScanBlock)
 compact_oriented_kernel(const __grid_constant__ FrameParams fp) {
     const OctParams& o = fp.oct[fp.o_begin + blockIdx.y];
     const int M = o.counts[1];
-    if (blockIdx.x > 0 && (int)(blockIdx.x << 10) >= M) return;
-    const int total = segment_scan_1024(
+    if (blockIdx.x > 0 && (int)blockIdx.x * kScanBlock >= M) return;
+    const int total = segment_scan(
         M, blockIdx.x, [&](int k) { return o.oricnt[k]; },
         [&](int k, int v, int excl, int tot) {
             for (int c = 0; c < v; c++) {
@@ -203,7 +202,8 @@ constexpr int kPrivSlots = 32;  // 2 x 2 spatial neighbours x 8 orientation bins
 // column 0 cover rbin in (-1,1) (truncating modff, quirk Q13), so cell (0,0) is four units of area, the other
 // row-0 / column-0 cells two, the rest one. Warps pull cells from this queue (longest-processing-time order).
 __constant__ signed char kCellOrder[16] = {0, 1, 2, 3, 4, 8, 12, 5, 6, 7, 9, 10, 11, 13, 14, 15};
-constexpr int kDescCtasPerSm = 7;  // register-limited residency of descriptor_kernel
+constexpr int kDescCtasPerSm = 4;  // persistent CTAs per SM and launch (up to 7 fit; several launches overlap, and
+                                   // the other graph branches need room: measured best at 1920x1200)
 constexpr int kRing = 64;  // per-warp ring of accepted samples (at most 31 pending + 32 appended)
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -481,30 +481,34 @@ void launch_orientation(const FrameParams& fp, int o_begin, int o_end, cudaStrea
 void launch_compact_oriented(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     int maxcap = 1;
     for (int i = o_begin; i < o_end; i++) maxcap = fp.oct[i].cap > maxcap ? fp.oct[i].cap : maxcap;
-    dim3 grid((maxcap + 1023) / 1024, o_end - o_begin);
-    compact_oriented_kernel<<<grid, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
+    dim3 grid((maxcap + kScanBlock - 1) / kScanBlock, o_end - o_begin);
+    compact_oriented_kernel<<<grid, kScanBlock, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
-void launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
+static int g_desc_priority = 0;
+
+cudaError_t descriptor_setup() {  // once per process, outside stream capture
+    int greatest = 0;
+    return cudaDeviceGetStreamPriorityRange(&g_desc_priority, &greatest);
+}
+
+cudaError_t launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     // upper bound on the keypoints of the range: its slot capacity, and never more than the output holds
     long cap = 0;
     for (int i = o_begin; i < o_end; i++) cap += fp.oct[i].cap;
     long grid = cap < (long)fp.numFeatures ? cap : (long)fp.numFeatures;
-    static const long max_grid = getenv("B200SIFT_DESC_GRID") ? atol(getenv("B200SIFT_DESC_GRID")) : 148L * kDescCtasPerSm;
-    if (grid > max_grid) grid = max_grid;
+    if (grid > 148L * kDescCtasPerSm) grid = 148L * kDescCtasPerSm;
     // Lowest stream priority: the descriptor grids would otherwise fill every CTA slot and starve the short
     // latency-bound kernels of the other graph branches (the priority is recorded in the captured node).
-    int least = 0, greatest = 0;
-    cudaDeviceGetStreamPriorityRange(&least, &greatest);
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3((unsigned)(grid > 0 ? grid : 1));
     cfg.blockDim = dim3(kDescThreads);
     cfg.stream = s;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributePriority;
-    attr[0].val.priority = least;
+    attr[0].val.priority = g_desc_priority;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
-    cudaLaunchKernelEx(&cfg, descriptor_kernel, octave_range(fp, o_begin, o_end));
+    return cudaLaunchKernelEx(&cfg, descriptor_kernel, octave_range(fp, o_begin, o_end));
 }
 
 }  // namespace b200sift

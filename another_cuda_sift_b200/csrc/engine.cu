@@ -230,7 +230,7 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
                 CU(cudaEventRecord(d->ev_counts[br], bs));
             }
             if (last_stage >= 6) {
-                launch_descriptor(fp, d->br_begin[br], d->br_end[br], bs);
+                CU(launch_descriptor(fp, d->br_begin[br], d->br_end[br], bs));
                 n++;
                 MARK(B200SIFT_K_DESCRIBE);
             }
@@ -240,7 +240,7 @@ int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* lau
         if (int rc = chain(d->tail_first, d->nOct, s)) return rc;
         if (fork && d->n_side > 0) CU(cudaStreamWaitEvent(s, d->ev_counts[d->n_side - 1], 0));
         if (last_stage >= 6) {
-            launch_descriptor(fp, d->tail_first, d->nOct, s);
+            CU(launch_descriptor(fp, d->tail_first, d->nOct, s));
             n++;
             MARK(B200SIFT_K_DESCRIBE);
         }
@@ -356,6 +356,7 @@ int build(b200sift_detector* d) {
     }
     CU(cudaMallocHost(&d->h_total, sizeof(int)));
     *d->h_total = 0;
+    CU(descriptor_setup());
     // everything but the descriptor launches (launch_descriptor) runs at the highest stream priority
     int prio_least = 0, prio_greatest = 0;
     CU(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));

@@ -286,14 +286,14 @@ refine_kernel(const __grid_constant__ FrameParams fp) {
     o.flag[idx] = accept;
 }
 
-// CTA (blockIdx.x, octave): stable compaction of the accepted candidates of its 1024-element segment into
+// CTA (blockIdx.x, octave): stable compaction of the accepted candidates of its kScanBlock-element segment into
 // coll/collF. The element whose prefix equals the total is not written (quirk Q5, SiftOps.cu:228).
-__global__ void __launch_bounds__(1024)
+__global__ void __launch_bounds__(kScanBlock)
 compact_refined_kernel(const __grid_constant__ FrameParams fp) {
     const OctParams& o = fp.oct[fp.o_begin + blockIdx.y];
     const int n = o.counts[3];
-    if (blockIdx.x > 0 && (int)(blockIdx.x << 10) >= n) return;
-    const int total = segment_scan_1024(
+    if (blockIdx.x > 0 && (int)blockIdx.x * kScanBlock >= n) return;
+    const int total = segment_scan(
         n, blockIdx.x, [&](int i) { return o.flag[i]; },
         [&](int i, int v, int excl, int tot) {
             if (v && excl + 1 < tot) {
@@ -325,8 +325,8 @@ void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s
 void launch_compact_refined(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     int maxcap = 1;
     for (int i = o_begin; i < o_end; i++) maxcap = fp.oct[i].cap > maxcap ? fp.oct[i].cap : maxcap;
-    dim3 grid((maxcap + 1023) / 1024, o_end - o_begin);
-    compact_refined_kernel<<<grid, 1024, 0, s>>>(octave_range(fp, o_begin, o_end));
+    dim3 grid((maxcap + kScanBlock - 1) / kScanBlock, o_end - o_begin);
+    compact_refined_kernel<<<grid, kScanBlock, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 
 }  // namespace b200sift
