@@ -44,9 +44,9 @@ struct OctParams {
     int* oricnt;         // [cap] peaks emitted per refined keypoint
     int* counts;         // [4]: P (raw extrema), M (refined), T (oriented), n = min(P, cap)
     int w, h, pitch, cap;
-    int words;           // mask words per row = ceil(w/32)
+    int words;           // mask words per row = 2*ceil(w/64)
     int det_task0;       // first warp task of this octave in the detect kernel
-    int det_cols, det_rows;  // column strips (32 px) x row strips (kDetRows rows)
+    int det_cols, det_rows;  // column strips (64 px) x row strips (kDetRows rows)
     int row0;            // first (scale,row) index of this octave in the scatter kernel
     int scat_cta0;       // first CTA of this octave in the scatter kernel (8 rows per CTA, CTAs never straddle octaves)
 };

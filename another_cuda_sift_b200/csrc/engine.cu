@@ -308,7 +308,7 @@ int build(b200sift_detector* d) {
         if (oc.w < 1 || oc.h < 1) return fail(B200SIFT_EINVAL, "octave %d is empty", o);
         oc.pitch = pitch_floats(oc.w);
         oc.cap = std::min(oc.pitch * oc.h, c.numFeatures * 10);  // KeyPoint.cu:13, Detector.cu:109
-        oc.words = (oc.w + 31) / 32;
+        oc.words = 2 * ((oc.w + 63) / 64);  // two mask words (even / odd pixels) per 64-pixel strip
         oc.row0 = rows_total;
         rows_total += kScales * oc.h;
         oc.scat_cta0 = scat_ctas;
@@ -338,7 +338,7 @@ int build(b200sift_detector* d) {
         if (int rc = dev_alloc(d, &oc.oricnt, (size_t)oc.cap)) return rc;
         oc.counts = d_counts + 4 * o;
         const int band = oc.h - 2 * kBorder;
-        oc.det_cols = (oc.w > 2 * kBorder && band > 0) ? oc.words : 0;
+        oc.det_cols = (oc.w > 2 * kBorder && band > 0) ? oc.words / 2 : 0;
         oc.det_rows = oc.det_cols ? (band + kDetRows - 1) / kDetRows : 0;
         oc.det_task0 = task0;
         task0 += oc.det_cols * oc.det_rows;

@@ -24,35 +24,29 @@ namespace b200sift {
 
 namespace {
 
-constexpr int kDetThreads = 256;
+constexpr int kDetThreads = 128;
 
-struct Row5 {  // per DoG layer: horizontal 3-max, 3-min of one row; centre value
-    float mx[5], mn[5], c[5];
+// Raw Gaussian values of one row of a 64-pixel strip: lane l owns pixels 2l, 2l+1 of the strip (one 8-byte
+// load per layer); lanes 0 and 31 also fetch the pixel left / right of the strip.
+struct RawRow {
+    float2 g[6];
+    float gh[6];
 };
 
-__device__ __forceinline__ void load_row(const OctParams& o, int y, int xc, int xh, bool halo_lane, int lane, Row5& r) {
-    const size_t ls = (size_t)o.pitch * o.h;
-    const float* base = o.gauss + (size_t)y * o.pitch;
-    float g[6], gh[6];
+__device__ __forceinline__ void load_raw(const float* __restrict__ base, size_t ls, int x, int xh, bool halo_lane, RawRow& r) {
 #pragma unroll
-    for (int l = 0; l < 6; l++) g[l] = __ldg(base + ls * l + xc);
+    for (int l = 0; l < 6; l++) r.g[l] = __ldg(reinterpret_cast<const float2*>(base + ls * l + x));
 #pragma unroll
-    for (int l = 0; l < 6; l++) gh[l] = halo_lane ? __ldg(base + ls * l + xh) : 0.f;
-#pragma unroll
-    for (int l = 0; l < 5; l++) {
-        const float d = __fsub_rn(g[l + 1], g[l]);
-        const float dh = __fsub_rn(gh[l + 1], gh[l]);
-        float left = __shfl_up_sync(0xffffffffu, d, 1);
-        float right = __shfl_down_sync(0xffffffffu, d, 1);
-        if (lane == 0) left = dh;
-        if (lane == 31) right = dh;
-        r.c[l] = d;
-        r.mx[l] = fmaxf(fmaxf(left, d), right);
-        r.mn[l] = fminf(fminf(left, d), right);
-    }
+    for (int l = 0; l < 6; l++) r.gh[l] = halo_lane ? __ldg(base + ls * l + xh) : 0.f;
 }
 
-__global__ void __launch_bounds__(kDetThreads)
+// Warp task = 64-pixel-wide column strip x kDetRows rows of one octave. Per DoG layer the warp keeps, for
+// the two pixels of every lane, the horizontal 3-max / 3-min of the previous row and of the previous two
+// rows combined, so the 3x3 in-plane extrema of the centre row cost two max and two min per new row; the
+// raw loads of the next row are issued before the current row is processed.
+// Mask layout: word 2c of a row holds the even pixels of strip c (bit l <-> x = 64c + 2l), word 2c+1 the
+// odd ones; scatter_kernel merges the two in x order.
+__global__ void __launch_bounds__(kDetThreads, 4)
 detect_kernel(const __grid_constant__ FrameParams fp) {
     const int lane = threadIdx.x & 31;
     const int task = fp.oct[fp.o_begin].det_task0 + blockIdx.x * (kDetThreads / 32) + (threadIdx.x >> 5);
@@ -62,42 +56,97 @@ detect_kernel(const __grid_constant__ FrameParams fp) {
     const OctParams& o = fp.oct[oi];
     const int t = task - o.det_task0;
     const int cs = t % o.det_cols, rs = t / o.det_cols;
-    const int x = cs * 32 + lane;
-    const int xc = min(x, o.w - 1);
-    const int xh = lane == 0 ? max(cs * 32 - 1, 0) : min(cs * 32 + 32, o.w - 1);
+    const int x = cs * 64 + 2 * lane;  // x + 1 < pitch always: the pitch is a multiple of 128 floats
+    const int xh = lane == 0 ? max(cs * 64 - 1, 0) : min(cs * 64 + 64, o.w - 1);
     const bool halo_lane = (lane == 0) || (lane == 31);
     const int ys = kBorder + rs * kDetRows;
     const int ye = min(o.h - kBorder, ys + kDetRows);
-    const bool x_ok = x >= kBorder && x < o.w - kBorder;
+    const bool ok_a = x >= kBorder && x < o.w - kBorder;
+    const bool ok_b = x + 1 >= kBorder && x + 1 < o.w - kBorder;
     const float thr = fp.extrema_thr;
+    const size_t ls = (size_t)o.pitch * o.h;
+    const float* col = o.gauss;
 
-    Row5 ra, rb, rc;  // rows y-1, y, y+1
-    load_row(o, ys - 1, xc, xh, halo_lane, lane, ra);
-    load_row(o, ys, xc, xh, halo_lane, lane, rb);
-    for (int y = ys; y < ye; y++) {
-        load_row(o, y + 1, xc, xh, halo_lane, lane, rc);
-        float vmx[5], vmn[5];
+    float pmx[5][2], pmn[5][2];  // horizontal 3-max / 3-min of the previous row
+    float qmx[5][2], qmn[5][2];  // ... of the previous two rows combined
+    float cen[3][2];             // centre-row DoG values of layers 1..3
+    float nmx[5][2], nmn[5][2], ncen[3][2];
+
+    // horizontal pass of one raw row -> nmx/nmn/ncen
+    auto horizontal = [&](const RawRow& r) {
 #pragma unroll
         for (int l = 0; l < 5; l++) {
-            vmx[l] = fmaxf(fmaxf(ra.mx[l], rb.mx[l]), rc.mx[l]);
-            vmn[l] = fminf(fminf(ra.mn[l], rb.mn[l]), rc.mn[l]);
+            const float da = __fsub_rn(r.g[l + 1].x, r.g[l].x), db = __fsub_rn(r.g[l + 1].y, r.g[l].y);
+            const float dh = __fsub_rn(r.gh[l + 1], r.gh[l]);
+            float left = __shfl_up_sync(0xffffffffu, db, 1);
+            float right = __shfl_down_sync(0xffffffffu, da, 1);
+            if (lane == 0) left = dh;
+            if (lane == 31) right = dh;
+            const float hi = fmaxf(da, db), lo = fminf(da, db);
+            nmx[l][0] = fmaxf(left, hi); nmx[l][1] = fmaxf(hi, right);
+            nmn[l][0] = fminf(left, lo); nmn[l][1] = fminf(lo, right);
+            if (l >= 1 && l <= 3) { ncen[l - 1][0] = da; ncen[l - 1][1] = db; }
+        }
+    };
+
+    RawRow raw;
+    load_raw(col + (size_t)(ys - 1) * o.pitch, ls, x, xh, halo_lane, raw);
+    horizontal(raw);
+#pragma unroll
+    for (int l = 0; l < 5; l++)
+#pragma unroll
+        for (int k = 0; k < 2; k++) { pmx[l][k] = nmx[l][k]; pmn[l][k] = nmn[l][k]; }
+    load_raw(col + (size_t)ys * o.pitch, ls, x, xh, halo_lane, raw);
+    horizontal(raw);
+#pragma unroll
+    for (int l = 0; l < 5; l++)
+#pragma unroll
+        for (int k = 0; k < 2; k++) {
+            qmx[l][k] = fmaxf(pmx[l][k], nmx[l][k]); qmn[l][k] = fminf(pmn[l][k], nmn[l][k]);
+            pmx[l][k] = nmx[l][k]; pmn[l][k] = nmn[l][k];
         }
 #pragma unroll
-        for (int s = 0; s < kScales; s++) {
-            const float v = rb.c[s + 1];
-            const float m3 = fmaxf(fmaxf(vmx[s], vmx[s + 1]), vmx[s + 2]);
-            const float n3 = fminf(fminf(vmn[s], vmn[s + 1]), vmn[s + 2]);
-            // MatOps.cu:122-143: |v| > thr, and v >= all 27 (v > 0) or v <= all 27 (v < 0).
-            const bool ext = x_ok && (fabsf(v) > thr) && ((v > 0.f) ? (v >= m3) : ((v < 0.f) && (v <= n3)));
-            const unsigned bits = __ballot_sync(0xffffffffu, ext);
-            if (lane == 0) {
-                const int row = s * o.h + y;
-                o.mask[(size_t)row * o.words + cs] = bits;
-                if (bits) atomicAdd(o.rowcount + row, __popc(bits));
+    for (int s = 0; s < 3; s++) { cen[s][0] = ncen[s][0]; cen[s][1] = ncen[s][1]; }
+    load_raw(col + (size_t)(ys + 1) * o.pitch, ls, x, xh, halo_lane, raw);
+
+    for (int y = ys; y < ye; y++) {
+        // `raw` holds row y+1; start fetching row y+2 (the last one is a harmless in-bounds re-read)
+        RawRow nxt;
+        load_raw(col + (size_t)min(y + 2, o.h - 1) * o.pitch, ls, x, xh, halo_lane, nxt);
+        horizontal(raw);
+        float vmx[5][2], vmn[5][2];
+#pragma unroll
+        for (int l = 0; l < 5; l++)
+#pragma unroll
+            for (int k = 0; k < 2; k++) {
+                vmx[l][k] = fmaxf(qmx[l][k], nmx[l][k]); vmn[l][k] = fminf(qmn[l][k], nmn[l][k]);
+                qmx[l][k] = fmaxf(pmx[l][k], nmx[l][k]); qmn[l][k] = fminf(pmn[l][k], nmn[l][k]);
+                pmx[l][k] = nmx[l][k]; pmn[l][k] = nmn[l][k];
             }
+        unsigned be[3], bo[3];
+#pragma unroll
+        for (int s = 0; s < kScales; s++) {
+            bool ext[2];
+#pragma unroll
+            for (int k = 0; k < 2; k++) {
+                const float v = cen[s][k];
+                const float m3 = fmaxf(fmaxf(vmx[s][k], vmx[s + 1][k]), vmx[s + 2][k]);
+                const float n3 = fminf(fminf(vmn[s][k], vmn[s + 1][k]), vmn[s + 2][k]);
+                // MatOps.cu:122-143: |v| > thr, and v >= all 27 (v > 0) or v <= all 27 (v < 0).
+                ext[k] = (k == 0 ? ok_a : ok_b) && (fabsf(v) > thr) && ((v > 0.f) ? (v >= m3) : ((v < 0.f) && (v <= n3)));
+            }
+            be[s] = __ballot_sync(0xffffffffu, ext[0]);
+            bo[s] = __ballot_sync(0xffffffffu, ext[1]);
+            cen[s][0] = ncen[s][0]; cen[s][1] = ncen[s][1];
         }
-        ra = rb;
-        rb = rc;
+        if (lane < kScales) {  // lane s stores scale s
+            const unsigned e = lane == 0 ? be[0] : (lane == 1 ? be[1] : be[2]);
+            const unsigned od = lane == 0 ? bo[0] : (lane == 1 ? bo[1] : bo[2]);
+            const int row = lane * o.h + y;
+            *reinterpret_cast<uint2*>(o.mask + (size_t)row * o.words + 2 * cs) = make_uint2(e, od);
+            if (e | od) atomicAdd(o.rowcount + row, __popc(e) + __popc(od));
+        }
+        raw = nxt;
     }
 }
 
@@ -131,11 +180,12 @@ scatter_kernel(const __grid_constant__ FrameParams fp) {
     }
     if (cnt == 0) return;
     const int s = row / o.h, y = row - s * o.h;
-    const uint32_t* m = o.mask + (size_t)row * o.words;
-    for (int w0 = 0; w0 < o.words; w0 += 32) {
-        const int wi = w0 + lane;
-        uint32_t bits = wi < o.words ? m[wi] : 0u;
-        const int c = __popc(bits);
+    const uint2* m = reinterpret_cast<const uint2*>(o.mask + (size_t)row * o.words);
+    const int strips = o.words >> 1;
+    for (int w0 = 0; w0 < strips; w0 += 32) {
+        const int wi = w0 + lane;  // 64-pixel strip: .x = even pixels, .y = odd pixels (detect_kernel)
+        uint2 bits = wi < strips ? m[wi] : make_uint2(0u, 0u);
+        const int c = __popc(bits.x) + __popc(bits.y);
         int incl = c;
 #pragma unroll
         for (int d = 1; d < 32; d <<= 1) {
@@ -143,10 +193,12 @@ scatter_kernel(const __grid_constant__ FrameParams fp) {
             if (lane >= d) incl += u;
         }
         int idx = base + incl - c;
-        while (bits) {
-            const int b = __ffs(bits) - 1;
-            bits &= bits - 1;
-            if (idx + 1 < o.cap) o.cand[idx] = make_float3((float)(wi * 32 + b), (float)y, (float)(s + 1));
+        while (bits.x | bits.y) {
+            const int be = bits.x ? __ffs(bits.x) - 1 : 32, bo = bits.y ? __ffs(bits.y) - 1 : 32;
+            int xx;
+            if (be <= bo) { xx = wi * 64 + 2 * be; bits.x &= bits.x - 1; }
+            else { xx = wi * 64 + 2 * bo + 1; bits.y &= bits.y - 1; }
+            if (idx + 1 < o.cap) o.cand[idx] = make_float3((float)xx, (float)y, (float)(s + 1));
             idx++;
         }
         base += __shfl_sync(0xffffffffu, incl, 31);
