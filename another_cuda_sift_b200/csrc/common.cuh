@@ -40,6 +40,8 @@ struct OctParams {
     float4* candF;       // [cap]
     float3* coll;        // [cap]
     float4* collF;       // [cap]
+    float3* fin_kp;      // [numFeatures] final keypoints of the octave (per frame slot; cand.. are shared by the slots)
+    float4* fin_ft;      // [numFeatures]
     int* flag;           // [cap] refine accept flags
     int* oricnt;         // [cap] peaks emitted per refined keypoint
     int* counts;         // [4]: P (raw extrema), M (refined), T (oriented), n = min(P, cap)
@@ -61,7 +63,7 @@ struct FrameParams {
     float3* out_kpts;    // [numFeatures]
     float4* out_feats;   // [numFeatures]
     __half* out_desc;    // [numFeatures*128]
-    int* total;          // device: total[0] = keypoints returned by the last frame, total[1] = by the frame before
+    int* total;          // device: keypoints returned by this slot's frame
     float extrema_thr;   // floor(0.5*contrast/nLayers*255) (interface/Detector.cu:362)
     float contrast_thr, edge_thr, sigma;
 };
@@ -84,7 +86,7 @@ cudaError_t launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cud
 
 int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s,
                  float* dbg = nullptr);
-int match_launch_counts(const __half* q, const __half* t, int max_n, const int* counts, int* out, void* scratch,
+int match_launch_counts(const __half* q, const __half* t, int max_n, const int* cnt_q, const int* cnt_t, int* out, void* scratch,
                         size_t scratch_bytes, cudaStream_t s);
 int match_launch_simt(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s);
 void match_set_path(int path);

@@ -182,11 +182,20 @@ compact_oriented_kernel(const __grid_constant__ FrameParams fp) {
         [&](int k, int v, int excl, int tot) {
             for (int c = 0; c < v; c++) {
                 const int p = excl + c;
+                float3 kp;
+                float4 ft;
                 if (p + 1 < tot) {
                     const int slot = M + k * kOriBins + c;
-                    o.cand[p] = o.coll[slot];
-                    o.candF[p] = o.collF[slot];
+                    kp = o.coll[slot];
+                    ft = o.collF[slot];
+                    o.cand[p] = kp;
+                    o.candF[p] = ft;
+                } else {  // quirk Q5: entry T-1 keeps whatever an earlier frame (or stage) left there
+                    kp = o.cand[p];
+                    ft = o.candF[p];
                 }
+                // the descriptor stage reads this per-slot copy: cand/candF belong to the next frame from here on
+                if (p < fp.numFeatures) { o.fin_kp[p] = kp; o.fin_ft[p] = ft; }
             }
         });
     if (blockIdx.x == 0 && threadIdx.x == 0) o.counts[2] = total;  // T
@@ -270,8 +279,8 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     while (j >= fp.oct[oi].counts[2]) { j -= fp.oct[oi].counts[2]; oi++; }
     const int g = first + b;
     const OctParams& o = fp.oct[oi];
-    const float3 kp = o.cand[j];
-    const float4 ft = o.candF[j];
+    const float3 kp = o.fin_kp[j];
+    const float4 ft = o.fin_ft[j];
     if (tid == 0) s_next = 0;
     for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0;
     __syncthreads();

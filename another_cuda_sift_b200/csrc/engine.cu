@@ -71,41 +71,55 @@ inline int pitch_floats(int w) { return ((w * 4 + 511) / 512) * 512 / 4; }
 constexpr int kSideStreams = 6;   // side branches of the frame graph
 constexpr int kBranchPixels = 65536;  // an octave with at least this many pixels gets a branch of its own
 
+constexpr int kSlots = 3;  // frames in flight
+
+// Everything one frame touches. Frame n runs in slot n % kSlots on the slot's own streams, so the frame graph
+// of frame n+1 (pyramid, extrema: latency-bound chains of small launches) overlaps the descriptor kernels of
+// frame n, and the consecutive-frame matcher can read the outputs of frames n-1 and n in place while frame
+// n+1 is already running: with three slots nothing is copied between frames.
+struct Slot {
+    FrameParams fp;
+    float* d_input = nullptr;
+    uint8_t* d_input_u8 = nullptr;
+    int* d_rowcount_all = nullptr;
+    int* h_total = nullptr;          // pinned
+    void* match_scratch = nullptr;   // survivor records of the consecutive-frame matcher
+    cudaStream_t stream = nullptr;   // main stream of the slot's frame graph
+    cudaStream_t side[kSideStreams] = {nullptr};
+    cudaEvent_t ev_fork[kMaxOctaves] = {nullptr}, ev_join[kMaxOctaves] = {nullptr}, ev_counts[kMaxOctaves] = {nullptr};
+    cudaEvent_t ev_copied = nullptr, ev_consumed = nullptr;  // input buffer hand-over with the copy stream
+    cudaEvent_t ev_done = nullptr;      // the slot's frame is complete
+    cudaEvent_t ev_matched = nullptr;   // the last matcher that read this slot as "previous frame" is complete
+    bool matched_pending = false;
+    cudaEvent_t ev_chain = nullptr;     // part B (the shared candidate lists) of the slot's frame is complete
+    cudaGraph_t graph[3] = {nullptr, nullptr, nullptr};       // parts A, B, C of the frame (enqueue_frame)
+    cudaGraphExec_t exec[3] = {nullptr, nullptr, nullptr};
+};
+
 struct b200sift_detector {
     b200sift_config cfg;
     int device = 0;
     int nOct = 0;
     Taps init_taps;
     Taps taps[kGaussLayers];
-    FrameParams fp;
-    // Two input buffers + two captured frame graphs: the H2D copy of frame i+1 runs on the copy stream while
-    // the graph of frame i runs on the main stream.
-    float* d_input[2] = {nullptr, nullptr};
+    Slot slot[kSlots];
     int in_pitch = 0;
-    uint8_t* d_input_u8[2] = {nullptr, nullptr};
     size_t u8_pitch = 0;
     cudaStream_t copy_stream = nullptr;
-    cudaEvent_t ev_copied[2] = {nullptr, nullptr}, ev_consumed[2] = {nullptr, nullptr};
-    unsigned long long frame_no = 0;
-    int* d_rowcount_all = nullptr;
+    unsigned long long frame_no = 0;  // frames enqueued so far; frame n lives in slot n % kSlots
     size_t rowcount_bytes = 0;
-    __half* d_prev_desc = nullptr;
-    int* h_total = nullptr;  // pinned
-    void* match_scratch = nullptr;  // survivor records of the consecutive-frame matcher
     size_t match_scratch_bytes_ = 0;
     std::vector<void*> allocs;
-    cudaStream_t stream = nullptr;
-    cudaStream_t side[kSideStreams] = {nullptr};
-    cudaEvent_t ev_fork[kMaxOctaves] = {nullptr}, ev_join[kMaxOctaves] = {nullptr}, ev_counts[kMaxOctaves] = {nullptr};
     int tail_first = 0;  // first octave handled by the single-CTA tail kernel
     // Branches of the frame graph: octave ranges [br_begin, br_end). Branches 0 .. n_side-1 cover the
     // multi-CTA octaves and run on side streams; the tail octaves (if any) run on the main stream.
     int n_side = 0;
     int br_begin[kSideStreams] = {0}, br_end[kSideStreams] = {0};
-    cudaGraph_t graph[2] = {nullptr, nullptr};
-    cudaGraphExec_t exec[2] = {nullptr, nullptr};
     int launches = 0;
     bool have_frame = false;
+    Slot& cur() { return slot[(frame_no + kSlots - 1) % kSlots]; }    // slot of the latest frame
+    Slot& prev() { return slot[(frame_no + kSlots - 2) % kSlots]; }   // slot of the frame before it
+    const Slot& cur() const { return slot[(frame_no + kSlots - 1) % kSlots]; }
 };
 
 namespace {
@@ -143,115 +157,124 @@ int dev_alloc(b200sift_detector* d, T** p, size_t count) {
 }
 
 // The frame pipeline, stages numbered as in Detector::detectAndCompute (Detector.cu:133-233):
-// 0 prev-descriptor copy, 1 pyramid, 3 extrema, 4 refinement, 5 orientation, 6/7 descriptor+gather.
-int enqueue_frame(b200sift_detector* d, cudaStream_t s, int last_stage, int* launches, Profiler* prof = nullptr, int buf = 0) {
-    FrameParams& fp = d->fp;
+// 1 pyramid, 3 extrema, 4 refinement, 5 orientation, 6/7 descriptor+gather. It is enqueued (and captured) in
+// three parts, because the candidate lists (cand/candF/coll/collF) are shared by the frame slots -- the
+// reference leaves stale entries in them from frame to frame (quirk Q5) and the results depend on it:
+//   A  pyramid + extrema bitmask        per-slot buffers only: overlaps anything of the previous frames
+//   B  scatter .. orientation           touches the shared lists: runs strictly in frame order
+//   C  descriptors                      per-slot buffers only (B leaves the final list in fin_kp/fin_ft)
+enum : int { kPartA = 1, kPartB = 2, kPartC = 4, kPartAll = 7 };
+
+int enqueue_frame(b200sift_detector* d, Slot& sl, int last_stage, int* launches, Profiler* prof = nullptr, int parts = kPartAll) {
+    FrameParams& fp = sl.fp;
+    cudaStream_t s = sl.stream;
     int n = 0;
-    MARK(B200SIFT_K_COPY);
-    CU(cudaMemcpyAsync(fp.total + 1, fp.total, sizeof(int), cudaMemcpyDeviceToDevice, s));  // previous frame's count
-    CU(cudaMemcpyAsync(d->d_prev_desc, fp.out_desc, (size_t)fp.numFeatures * 128 * sizeof(__half),
-                       cudaMemcpyDeviceToDevice, s));
-    CU(cudaMemsetAsync(d->d_rowcount_all, 0, d->rowcount_bytes, s));
-    MARK(B200SIFT_K_COPY);
-    // Gaussian pyramid. Octave o+1 only needs layer 3 of octave o, so layers 4 and 5 of every big octave
-    // go to a side stream (a parallel branch of the frame graph) while the main chain moves on to the next
-    // octave; octaves of <= kTailPixels pixels are walked by one CTA (launch_pyramid_tail).
-    // Everything after the pyramid is per-octave work, and the small octaves are a long chain of
-    // latency-bound launches. The frame graph therefore branches per octave range (build(): one branch
-    // per big octave, one for the remaining multi-CTA octaves, the tail octaves on the main stream); each
-    // branch runs detect .. orientation .. descriptor as soon as the six layers of its octaves exist.
-    // A descriptor launch needs the keypoint counts of all lower octaves (its offset into the output), so
-    // branch b waits for ev_counts[b-1], which branch b-1 records after its own wait: the dependency is
-    // transitive. The branch that ends at the last octave publishes the frame's keypoint count.
-    const bool fork = (prof == nullptr) && d->side[0] != nullptr;
-    auto chain = [&](int ob, int oe, cudaStream_t cs) -> int {
-        if (last_stage >= 3) {
-            launch_detect(fp, ob, oe, cs); n++; MARK(B200SIFT_K_DETECT);
-            launch_scatter(fp, ob, oe, cs); n++;
-            MARK(B200SIFT_K_COMPACT);
-        }
-        if (last_stage >= 4) {
-            launch_refine(fp, ob, oe, cs); n++;
-            MARK(B200SIFT_K_REFINE);
-            launch_compact_refined(fp, ob, oe, cs); n++;
-            MARK(B200SIFT_K_COMPACT);
-        }
-        if (last_stage >= 5) {
-            launch_orientation(fp, ob, oe, cs); n++;
-            MARK(B200SIFT_K_ORIENT);
-            launch_compact_oriented(fp, ob, oe, cs); n++;
-            MARK(B200SIFT_K_COMPACT);
-        }
+    const bool fork = (prof == nullptr) && sl.side[0] != nullptr;
+    bool used[kSideStreams] = {false};
+    auto join_sides = [&]() -> int {
+        for (int b = 0; b < d->n_side; b++)
+            if (used[b]) {
+                CU(cudaEventRecord(sl.ev_join[b], sl.side[b]));
+                CU(cudaStreamWaitEvent(s, sl.ev_join[b], 0));
+                used[b] = false;
+            }
         return 0;
     };
-    int br = 0;  // branch of the current multi-CTA octave
-    bool used[kSideStreams] = {false};
-    for (int o = 0; o < d->nOct; o++) {
-        OctParams& oc = fp.oct[o];
-        const size_t ls = (size_t)oc.pitch * oc.h;
-        const bool tail = o >= d->tail_first;
-        if (o == 0) {
-            launch_blur(d->d_input[buf], d->in_pitch, oc.gauss, oc.pitch, oc.w, oc.h, d->init_taps, s);
-            MARK(B200SIFT_K_BLUR);
-            n++;
-        } else if (!tail || o == d->tail_first) {
-            const OctParams& pv = fp.oct[o - 1];
-            const float* src = pv.gauss + (size_t)pv.pitch * pv.h * kScales;
-            launch_downsample(src, pv.pitch, pv.w, pv.h, oc.gauss, oc.pitch, oc.w, oc.h, s);
-            MARK(B200SIFT_K_DOWNSAMPLE);
-            n++;
-        }
-        if (tail) {
-            if (o == d->tail_first) {
-                launch_pyramid_tail(fp, d->taps, o, s);
-                MARK(B200SIFT_K_BLUR_SMALL);
+
+    if (parts & kPartA) {
+        MARK(B200SIFT_K_COPY);
+        CU(cudaMemsetAsync(sl.d_rowcount_all, 0, d->rowcount_bytes, s));
+        MARK(B200SIFT_K_COPY);
+        // Gaussian pyramid. Octave o+1 only needs layer 3 of octave o, so layers 4 and 5 of every big octave
+        // go to a side stream (a parallel branch of the graph) while the main chain moves on to the next
+        // octave; octaves of <= kTailPixels pixels are walked by one CTA (launch_pyramid_tail). The graph
+        // branches per octave range (build(): one branch per big octave, one for the remaining multi-CTA
+        // octaves, the tail octaves on the main stream); each branch runs its extrema detection as soon as
+        // the six layers of its octaves exist.
+        int br = 0;  // branch of the current multi-CTA octave
+        for (int o = 0; o < d->nOct; o++) {
+            OctParams& oc = fp.oct[o];
+            const size_t ls = (size_t)oc.pitch * oc.h;
+            const bool tail = o >= d->tail_first;
+            if (o == 0) {
+                launch_blur(sl.d_input, d->in_pitch, oc.gauss, oc.pitch, oc.w, oc.h, d->init_taps, s);
+                MARK(B200SIFT_K_BLUR);
+                n++;
+            } else if (!tail || o == d->tail_first) {
+                const OctParams& pv = fp.oct[o - 1];
+                const float* src = pv.gauss + (size_t)pv.pitch * pv.h * kScales;
+                launch_downsample(src, pv.pitch, pv.w, pv.h, oc.gauss, oc.pitch, oc.w, oc.h, s);
+                MARK(B200SIFT_K_DOWNSAMPLE);
                 n++;
             }
-            continue;
-        }
-        while (o >= d->br_end[br]) br++;
-        cudaStream_t bs = fork ? d->side[br] : s;  // the branch's stream
-        cudaStream_t ls_stream = s;
-        for (int l = 1; l < kGaussLayers; l++) {
-            if (l == 4 && fork) {  // layers 4,5 off the critical path
-                CU(cudaEventRecord(d->ev_fork[o], s));
-                CU(cudaStreamWaitEvent(bs, d->ev_fork[o], 0));
-                ls_stream = bs;
-                used[br] = true;
+            if (tail) {
+                if (o == d->tail_first) {
+                    launch_pyramid_tail(fp, d->taps, o, s);
+                    MARK(B200SIFT_K_BLUR_SMALL);
+                    n++;
+                }
+                continue;
             }
-            launch_blur(oc.gauss + ls * (l - 1), oc.pitch, oc.gauss + ls * l, oc.pitch, oc.w, oc.h, d->taps[l], ls_stream);
-            MARK(o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL);
-            n++;
+            while (o >= d->br_end[br]) br++;
+            cudaStream_t bs = fork ? sl.side[br] : s;  // the branch's stream
+            cudaStream_t ls_stream = s;
+            for (int l = 1; l < kGaussLayers; l++) {
+                if (l == 4 && fork) {  // layers 4,5 off the critical path
+                    CU(cudaEventRecord(sl.ev_fork[o], s));
+                    CU(cudaStreamWaitEvent(bs, sl.ev_fork[o], 0));
+                    ls_stream = bs;
+                    used[br] = true;
+                }
+                launch_blur(oc.gauss + ls * (l - 1), oc.pitch, oc.gauss + ls * l, oc.pitch, oc.w, oc.h, d->taps[l], ls_stream);
+                MARK(o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL);
+                n++;
+            }
+            if (o == d->br_end[br] - 1 && last_stage >= 3) {  // the branch's octaves are complete
+                launch_detect(fp, d->br_begin[br], d->br_end[br], bs); n++;
+                MARK(B200SIFT_K_DETECT);
+            }
         }
-        if (o == d->br_end[br] - 1) {  // the branch's octaves are complete
-            if (int rc = chain(d->br_begin[br], d->br_end[br], bs)) return rc;
+        if (d->tail_first < d->nOct && last_stage >= 3) {  // tail octaves on the main stream
+            launch_detect(fp, d->tail_first, d->nOct, s); n++;
+            MARK(B200SIFT_K_DETECT);
+        }
+        if (int rc = join_sides()) return rc;
+    }
+
+    if ((parts & kPartB) && last_stage >= 3) {
+        auto chain = [&](int ob, int oe, cudaStream_t cs) {
+            launch_scatter(fp, ob, oe, cs); n++;
+            MARK(B200SIFT_K_COMPACT);
+            if (last_stage >= 4) {
+                launch_refine(fp, ob, oe, cs); n++;
+                MARK(B200SIFT_K_REFINE);
+                launch_compact_refined(fp, ob, oe, cs); n++;
+                MARK(B200SIFT_K_COMPACT);
+            }
+            if (last_stage >= 5) {
+                launch_orientation(fp, ob, oe, cs); n++;
+                MARK(B200SIFT_K_ORIENT);
+                launch_compact_oriented(fp, ob, oe, cs); n++;
+                MARK(B200SIFT_K_COMPACT);
+            }
+        };
+        if (fork && d->n_side > 0) CU(cudaEventRecord(sl.ev_fork[0], s));
+        for (int b = 0; b < d->n_side; b++) {
+            cudaStream_t bs = fork ? sl.side[b] : s;
             if (fork) {
-                if (br > 0) CU(cudaStreamWaitEvent(bs, d->ev_counts[br - 1], 0));
-                CU(cudaEventRecord(d->ev_counts[br], bs));
+                CU(cudaStreamWaitEvent(bs, sl.ev_fork[0], 0));
+                used[b] = true;
             }
-            if (last_stage >= 6) {
-                CU(launch_descriptor(fp, d->br_begin[br], d->br_end[br], bs));
-                n++;
-                MARK(B200SIFT_K_DESCRIBE);
-            }
+            chain(d->br_begin[b], d->br_end[b], bs);
         }
+        if (d->tail_first < d->nOct) chain(d->tail_first, d->nOct, s);
+        if (int rc = join_sides()) return rc;
     }
-    if (d->tail_first < d->nOct) {  // tail octaves on the main stream
-        if (int rc = chain(d->tail_first, d->nOct, s)) return rc;
-        if (fork && d->n_side > 0) CU(cudaStreamWaitEvent(s, d->ev_counts[d->n_side - 1], 0));
-        if (last_stage >= 6) {
-            CU(launch_descriptor(fp, d->tail_first, d->nOct, s));
-            n++;
-            MARK(B200SIFT_K_DESCRIBE);
-        }
-    }
-    for (int b = 0; b < d->n_side; b++)
-        if (used[b]) {
-            CU(cudaEventRecord(d->ev_join[b], d->side[b]));
-            CU(cudaStreamWaitEvent(s, d->ev_join[b], 0));
-        }
-    if (last_stage >= 6) {
-        CU(cudaMemcpyAsync(d->h_total, fp.total, sizeof(int), cudaMemcpyDeviceToHost, s));
+
+    if ((parts & kPartC) && last_stage >= 6) {
+        CU(launch_descriptor(fp, 0, d->nOct, s)); n++;
+        MARK(B200SIFT_K_DESCRIBE);
+        CU(cudaMemcpyAsync(sl.h_total, fp.total, sizeof(int), cudaMemcpyDeviceToHost, s));
         MARK(B200SIFT_K_COPY);
     }
     CU(cudaGetLastError());
@@ -282,98 +305,115 @@ int build(b200sift_detector* d) {
     for (int i = 1; i < kGaussLayers; i++)
         if (!radius_supported(d->taps[i].n)) return fail(B200SIFT_EINVAL, "sigma %.3f: unsupported tap count %d", c.sigma, d->taps[i].n);
 
-    FrameParams& fp = d->fp;
-    std::memset(&fp, 0, sizeof(fp));
-    fp.nOct = d->nOct;
-    fp.o_begin = 0;
-    fp.o_end = d->nOct;
-    fp.numFeatures = c.numFeatures;
-    fp.extrema_thr = (float)std::floor(0.5 * c.contrastThreshould / c.numOctaveLayers * 255 * 1.f);  // Detector.cu:362
-    fp.contrast_thr = (float)c.contrastThreshould;
-    fp.edge_thr = (float)c.edgeThreshould;
-    fp.sigma = (float)c.sigma;
-
     d->in_pitch = pitch_floats(c.col_width);
     d->u8_pitch = ((size_t)c.col_width + 511) / 512 * 512;
-    for (int b = 0; b < 2; b++) {
-        if (int rc = dev_alloc(d, &d->d_input[b], (size_t)d->in_pitch * c.row_width)) return rc;
-        if (int rc = dev_alloc(d, &d->d_input_u8[b], d->u8_pitch * c.row_width)) return rc;
-    }
-
-    int rows_total = 0, scat_ctas = 0;
-    for (int o = 0; o < d->nOct; o++) {
-        OctParams& oc = fp.oct[o];
-        oc.w = (int)roundf(c.col_width / powf(2, o));  // Detector.cu:83
-        oc.h = (int)roundf(c.row_width / powf(2, o));
-        if (oc.w < 1 || oc.h < 1) return fail(B200SIFT_EINVAL, "octave %d is empty", o);
-        oc.pitch = pitch_floats(oc.w);
-        oc.cap = std::min(oc.pitch * oc.h, c.numFeatures * 10);  // KeyPoint.cu:13, Detector.cu:109
-        oc.words = 2 * ((oc.w + 63) / 64);  // two mask words (even / odd pixels) per 64-pixel strip
-        oc.row0 = rows_total;
-        rows_total += kScales * oc.h;
-        oc.scat_cta0 = scat_ctas;
-        scat_ctas += (kScales * oc.h + 7) / 8;
-    }
-    fp.rows_total = rows_total;
-    if (int rc = dev_alloc(d, &d->d_rowcount_all, (size_t)rows_total)) return rc;
-    d->rowcount_bytes = (size_t)rows_total * sizeof(int);
-    int* d_counts = nullptr;
-    if (int rc = dev_alloc(d, &d_counts, (size_t)4 * kMaxOctaves + 4)) return rc;
-    fp.total = d_counts + 4 * kMaxOctaves;
-
-    int task0 = 0;
-    for (int o = 0; o < d->nOct; o++) {
-        OctParams& oc = fp.oct[o];
-        const size_t ls = (size_t)oc.pitch * oc.h;
-        // +pitch floats of zeroed tail so that the reference's read one row past layer 5 of a
-        // stale slot stays inside the allocation
-        if (int rc = dev_alloc(d, &oc.gauss, ls * kGaussLayers + oc.pitch)) return rc;
-        if (int rc = dev_alloc(d, &oc.mask, (size_t)kScales * oc.h * oc.words)) return rc;
-        oc.rowcount = d->d_rowcount_all + oc.row0;
-        if (int rc = dev_alloc(d, &oc.cand, (size_t)oc.cap)) return rc;
-        if (int rc = dev_alloc(d, &oc.candF, (size_t)oc.cap)) return rc;
-        if (int rc = dev_alloc(d, &oc.coll, (size_t)oc.cap)) return rc;
-        if (int rc = dev_alloc(d, &oc.collF, (size_t)oc.cap)) return rc;
-        if (int rc = dev_alloc(d, &oc.flag, (size_t)oc.cap)) return rc;
-        if (int rc = dev_alloc(d, &oc.oricnt, (size_t)oc.cap)) return rc;
-        oc.counts = d_counts + 4 * o;
-        const int band = oc.h - 2 * kBorder;
-        oc.det_cols = (oc.w > 2 * kBorder && band > 0) ? oc.words / 2 : 0;
-        oc.det_rows = oc.det_cols ? (band + kDetRows - 1) / kDetRows : 0;
-        oc.det_task0 = task0;
-        task0 += oc.det_cols * oc.det_rows;
-    }
-    fp.det_tasks = task0;
-    if (int rc = dev_alloc(d, &fp.out_kpts, (size_t)c.numFeatures)) return rc;
-    if (int rc = dev_alloc(d, &fp.out_feats, (size_t)c.numFeatures)) return rc;
-    if (int rc = dev_alloc(d, &fp.out_desc, (size_t)c.numFeatures * 128)) return rc;
-    if (int rc = dev_alloc(d, &d->d_prev_desc, (size_t)c.numFeatures * 128)) return rc;
     d->match_scratch_bytes_ = match_scratch_bytes(c.numFeatures, c.numFeatures);
-    {
-        uint8_t* p = nullptr;
-        if (int rc = dev_alloc(d, &p, d->match_scratch_bytes_)) return rc;
-        d->match_scratch = p;
-    }
-    CU(cudaMallocHost(&d->h_total, sizeof(int)));
-    *d->h_total = 0;
     CU(descriptor_setup());
     // everything but the descriptor launches (launch_descriptor) runs at the highest stream priority
     int prio_least = 0, prio_greatest = 0;
     CU(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
-    CU(cudaStreamCreateWithPriority(&d->stream, cudaStreamNonBlocking, prio_greatest));
-    for (int i = 0; i < kSideStreams; i++) CU(cudaStreamCreateWithPriority(&d->side[i], cudaStreamNonBlocking, prio_greatest));
-    for (int o = 0; o < kMaxOctaves; o++) {
-        CU(cudaEventCreateWithFlags(&d->ev_fork[o], cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&d->ev_join[o], cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&d->ev_counts[o], cudaEventDisableTiming));
+    CU(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
+
+    for (int si = 0; si < kSlots; si++) {
+        Slot& sl = d->slot[si];
+        FrameParams& fp = sl.fp;
+        std::memset(&fp, 0, sizeof(fp));
+        fp.nOct = d->nOct;
+        fp.o_begin = 0;
+        fp.o_end = d->nOct;
+        fp.numFeatures = c.numFeatures;
+        fp.extrema_thr = (float)std::floor(0.5 * c.contrastThreshould / c.numOctaveLayers * 255 * 1.f);  // Detector.cu:362
+        fp.contrast_thr = (float)c.contrastThreshould;
+        fp.edge_thr = (float)c.edgeThreshould;
+        fp.sigma = (float)c.sigma;
+
+        if (int rc = dev_alloc(d, &sl.d_input, (size_t)d->in_pitch * c.row_width)) return rc;
+        if (int rc = dev_alloc(d, &sl.d_input_u8, d->u8_pitch * c.row_width)) return rc;
+
+        int rows_total = 0, scat_ctas = 0;
+        for (int o = 0; o < d->nOct; o++) {
+            OctParams& oc = fp.oct[o];
+            oc.w = (int)roundf(c.col_width / powf(2, o));  // Detector.cu:83
+            oc.h = (int)roundf(c.row_width / powf(2, o));
+            if (oc.w < 1 || oc.h < 1) return fail(B200SIFT_EINVAL, "octave %d is empty", o);
+            oc.pitch = pitch_floats(oc.w);
+            oc.cap = std::min(oc.pitch * oc.h, c.numFeatures * 10);  // KeyPoint.cu:13, Detector.cu:109
+            oc.words = 2 * ((oc.w + 63) / 64);  // two mask words (even / odd pixels) per 64-pixel strip
+            oc.row0 = rows_total;
+            rows_total += kScales * oc.h;
+            oc.scat_cta0 = scat_ctas;
+            scat_ctas += (kScales * oc.h + 7) / 8;
+        }
+        fp.rows_total = rows_total;
+        if (int rc = dev_alloc(d, &sl.d_rowcount_all, (size_t)rows_total)) return rc;
+        d->rowcount_bytes = (size_t)rows_total * sizeof(int);
+        int* d_counts = nullptr;
+        if (int rc = dev_alloc(d, &d_counts, (size_t)4 * kMaxOctaves + 4)) return rc;
+        fp.total = d_counts + 4 * kMaxOctaves;
+
+        int task0 = 0;
+        for (int o = 0; o < d->nOct; o++) {
+            OctParams& oc = fp.oct[o];
+            const size_t ls = (size_t)oc.pitch * oc.h;
+            // +pitch floats of zeroed tail so that the reference's read one row past layer 5 of a
+            // stale slot stays inside the allocation
+            if (int rc = dev_alloc(d, &oc.gauss, ls * kGaussLayers + oc.pitch)) return rc;
+            if (int rc = dev_alloc(d, &oc.mask, (size_t)kScales * oc.h * oc.words)) return rc;
+            oc.rowcount = sl.d_rowcount_all + oc.row0;
+            if (si == 0) {  // candidate lists: ONE set, handed from frame to frame (stale entries and all)
+                if (int rc = dev_alloc(d, &oc.cand, (size_t)oc.cap)) return rc;
+                if (int rc = dev_alloc(d, &oc.candF, (size_t)oc.cap)) return rc;
+                if (int rc = dev_alloc(d, &oc.coll, (size_t)oc.cap)) return rc;
+                if (int rc = dev_alloc(d, &oc.collF, (size_t)oc.cap)) return rc;
+                if (int rc = dev_alloc(d, &oc.flag, (size_t)oc.cap)) return rc;
+                if (int rc = dev_alloc(d, &oc.oricnt, (size_t)oc.cap)) return rc;
+            } else {
+                const OctParams& o0 = d->slot[0].fp.oct[o];
+                oc.cand = o0.cand; oc.candF = o0.candF; oc.coll = o0.coll; oc.collF = o0.collF;
+                oc.flag = o0.flag; oc.oricnt = o0.oricnt;
+            }
+            if (int rc = dev_alloc(d, &oc.fin_kp, (size_t)c.numFeatures)) return rc;
+            if (int rc = dev_alloc(d, &oc.fin_ft, (size_t)c.numFeatures)) return rc;
+            oc.counts = d_counts + 4 * o;
+            const int band = oc.h - 2 * kBorder;
+            oc.det_cols = (oc.w > 2 * kBorder && band > 0) ? oc.words / 2 : 0;
+            oc.det_rows = oc.det_cols ? (band + kDetRows - 1) / kDetRows : 0;
+            oc.det_task0 = task0;
+            task0 += oc.det_cols * oc.det_rows;
+        }
+        fp.det_tasks = task0;
+        if (int rc = dev_alloc(d, &fp.out_kpts, (size_t)c.numFeatures)) return rc;
+        if (int rc = dev_alloc(d, &fp.out_feats, (size_t)c.numFeatures)) return rc;
+        if (int rc = dev_alloc(d, &fp.out_desc, (size_t)c.numFeatures * 128)) return rc;
+        {
+            uint8_t* p = nullptr;
+            if (int rc = dev_alloc(d, &p, d->match_scratch_bytes_)) return rc;
+            sl.match_scratch = p;
+        }
+        CU(cudaMallocHost(&sl.h_total, sizeof(int)));
+        *sl.h_total = 0;
+        CU(cudaStreamCreateWithPriority(&sl.stream, cudaStreamNonBlocking, prio_greatest));
+        for (int i = 0; i < kSideStreams; i++) CU(cudaStreamCreateWithPriority(&sl.side[i], cudaStreamNonBlocking, prio_greatest));
+        for (int o = 0; o < kMaxOctaves; o++) {
+            CU(cudaEventCreateWithFlags(&sl.ev_fork[o], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&sl.ev_join[o], cudaEventDisableTiming));
+            CU(cudaEventCreateWithFlags(&sl.ev_counts[o], cudaEventDisableTiming));
+        }
+        CU(cudaEventCreateWithFlags(&sl.ev_copied, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&sl.ev_consumed, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&sl.ev_done, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&sl.ev_matched, cudaEventDisableTiming));
+        CU(cudaEventCreateWithFlags(&sl.ev_chain, cudaEventDisableTiming));
     }
+
+    const FrameParams& fp0 = d->slot[0].fp;
     d->tail_first = d->nOct;
-    for (int o = d->nOct - 1; o >= 0 && tail_octave(fp.oct[o].w, fp.oct[o].h); o--) d->tail_first = o;
+    for (int o = d->nOct - 1; o >= 0 && tail_octave(fp0.oct[o].w, fp0.oct[o].h); o--) d->tail_first = o;
     // graph branches over the multi-CTA octaves [0, tail_first): big octaves alone, the rest together
     d->n_side = 0;
     for (int o = 0; o < d->tail_first;) {
         int e = o + 1;
-        const bool big = fp.oct[o].w * fp.oct[o].h >= kBranchPixels && d->n_side < kSideStreams - 1;
+        const bool big = fp0.oct[o].w * fp0.oct[o].h >= kBranchPixels && d->n_side < kSideStreams - 1;
         if (!big) e = d->tail_first;
         d->br_begin[d->n_side] = o;
         d->br_end[d->n_side] = e;
@@ -381,21 +421,25 @@ int build(b200sift_detector* d) {
         o = e;
     }
 
-    CU(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
-    for (int b = 0; b < 2; b++) {
-        CU(cudaEventCreateWithFlags(&d->ev_copied[b], cudaEventDisableTiming));
-        CU(cudaEventCreateWithFlags(&d->ev_consumed[b], cudaEventDisableTiming));
+    // Three graphs per slot (parts A, B, C of the frame).
+    d->launches = 0;
+    for (int si = 0; si < kSlots; si++) {
+        Slot& sl = d->slot[si];
+        const int parts[3] = {kPartA, kPartB, kPartC};
+        int total = 0;
+        for (int g = 0; g < 3; g++) {
+            int n = 0;
+            CU(cudaStreamBeginCapture(sl.stream, cudaStreamCaptureModeThreadLocal));
+            int rc = enqueue_frame(d, sl, 7, &n, nullptr, parts[g]);
+            cudaError_t e = cudaStreamEndCapture(sl.stream, &sl.graph[g]);
+            if (rc) return rc;
+            CU(e);
+            CU(cudaGraphInstantiate(&sl.exec[g], sl.graph[g], 0));
+            total += n;
+        }
+        d->launches = total;
+        CU(cudaStreamSynchronize(sl.stream));
     }
-    // One graph for the whole frame (one instance per input buffer).
-    for (int b = 0; b < 2; b++) {
-        CU(cudaStreamBeginCapture(d->stream, cudaStreamCaptureModeThreadLocal));
-        int rc = enqueue_frame(d, d->stream, 7, &d->launches, nullptr, b);
-        cudaError_t e = cudaStreamEndCapture(d->stream, &d->graph[b]);
-        if (rc) return rc;
-        CU(e);
-        CU(cudaGraphInstantiate(&d->exec[b], d->graph[b], 0));
-    }
-    CU(cudaStreamSynchronize(d->stream));
     return 0;
 }
 
@@ -445,26 +489,39 @@ int b200sift_create(const b200sift_config* cfg, b200sift_detector** out) {
     return 0;
 }
 
+static int sync_all(b200sift_detector* d) {
+    for (int i = 0; i < kSlots; i++)
+        if (d->slot[i].stream) CU(cudaStreamSynchronize(d->slot[i].stream));
+    return 0;
+}
+
 int b200sift_destroy(b200sift_detector* d) {
     if (!d) return 0;
-    if (d->stream) cudaStreamSynchronize(d->stream);
-    for (int b = 0; b < 2; b++) {
-        if (d->exec[b]) cudaGraphExecDestroy(d->exec[b]);
-        if (d->graph[b]) cudaGraphDestroy(d->graph[b]);
-        if (d->ev_copied[b]) cudaEventDestroy(d->ev_copied[b]);
-        if (d->ev_consumed[b]) cudaEventDestroy(d->ev_consumed[b]);
+    sync_all(d);
+    if (d->copy_stream) cudaStreamSynchronize(d->copy_stream);
+    for (int si = 0; si < kSlots; si++) {
+        Slot& sl = d->slot[si];
+        for (int g = 0; g < 3; g++) {
+            if (sl.exec[g]) cudaGraphExecDestroy(sl.exec[g]);
+            if (sl.graph[g]) cudaGraphDestroy(sl.graph[g]);
+        }
+        if (sl.ev_chain) cudaEventDestroy(sl.ev_chain);
+        if (sl.ev_copied) cudaEventDestroy(sl.ev_copied);
+        if (sl.ev_consumed) cudaEventDestroy(sl.ev_consumed);
+        if (sl.ev_done) cudaEventDestroy(sl.ev_done);
+        if (sl.ev_matched) cudaEventDestroy(sl.ev_matched);
+        if (sl.h_total) cudaFreeHost(sl.h_total);
+        if (sl.stream) cudaStreamDestroy(sl.stream);
+        for (int i = 0; i < kSideStreams; i++)
+            if (sl.side[i]) cudaStreamDestroy(sl.side[i]);
+        for (int o = 0; o < kMaxOctaves; o++) {
+            if (sl.ev_fork[o]) cudaEventDestroy(sl.ev_fork[o]);
+            if (sl.ev_counts[o]) cudaEventDestroy(sl.ev_counts[o]);
+            if (sl.ev_join[o]) cudaEventDestroy(sl.ev_join[o]);
+        }
     }
     if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
     for (void* p : d->allocs) cudaFree(p);
-    if (d->h_total) cudaFreeHost(d->h_total);
-    if (d->stream) cudaStreamDestroy(d->stream);
-    for (int i = 0; i < kSideStreams; i++)
-        if (d->side[i]) cudaStreamDestroy(d->side[i]);
-    for (int o = 0; o < kMaxOctaves; o++) {
-        if (d->ev_fork[o]) cudaEventDestroy(d->ev_fork[o]);
-        if (d->ev_counts[o]) cudaEventDestroy(d->ev_counts[o]);
-        if (d->ev_join[o]) cudaEventDestroy(d->ev_join[o]);
-    }
     delete d;
     return 0;
 }
@@ -473,25 +530,43 @@ int b200sift_num_octaves(const b200sift_detector* d) { return d ? d->nOct : B200
 
 int b200sift_octave_info(const b200sift_detector* d, int o, int* dims) {
     if (!d || !dims || o < 0 || o >= d->nOct) return fail(B200SIFT_EINVAL, "bad octave");
-    const OctParams& oc = d->fp.oct[o];
+    const OctParams& oc = d->slot[0].fp.oct[o];
     dims[0] = oc.w; dims[1] = oc.h; dims[2] = oc.pitch; dims[3] = oc.cap;
     return 0;
 }
 
-// Frame i uses input buffer i & 1. Host frames are copied on the copy stream, which only waits until the
-// frame that last read this buffer (i - 2) has consumed it, so the copy overlaps the graph of frame i - 1.
-static int begin_frame(b200sift_detector* d, int* buf, bool on_copy_stream) {
-    *buf = (int)(d->frame_no & 1);
-    if (on_copy_stream) CU(cudaStreamWaitEvent(d->copy_stream, d->ev_consumed[*buf], 0));
+// Frame n runs in slot n % kSlots. Before the slot is reused, everything that read its previous contents from
+// another slot's stream (the matcher / result copies of frame n-2, which used it as "previous frame") must be
+// done; host frames are copied on the copy stream, which only waits until the frame that last used the slot
+// has consumed its input, so the copy overlaps the frames in flight.
+static int begin_frame(b200sift_detector* d, Slot** out, bool on_copy_stream) {
+    Slot& sl = d->slot[d->frame_no % kSlots];
+    if (sl.matched_pending) {
+        CU(cudaStreamWaitEvent(sl.stream, sl.ev_matched, 0));
+        sl.matched_pending = false;
+    }
+    if (on_copy_stream) CU(cudaStreamWaitEvent(d->copy_stream, sl.ev_consumed, 0));
+    *out = &sl;
     return 0;
 }
-static int launch_frame(b200sift_detector* d, int buf, bool from_copy_stream) {
+// The three graphs of one frame on the slot's stream. Part B waits for part B of the frame before it
+// (`pv`, another slot and stream): the shared candidate lists pass from frame to frame in order.
+static int launch_graphs(Slot& sl, Slot* pv) {
+    CU(cudaGraphLaunch(sl.exec[0], sl.stream));
+    CU(cudaEventRecord(sl.ev_consumed, sl.stream));  // the input image has been read
+    if (pv) CU(cudaStreamWaitEvent(sl.stream, pv->ev_chain, 0));
+    CU(cudaGraphLaunch(sl.exec[1], sl.stream));
+    CU(cudaEventRecord(sl.ev_chain, sl.stream));
+    CU(cudaGraphLaunch(sl.exec[2], sl.stream));
+    CU(cudaEventRecord(sl.ev_done, sl.stream));
+    return 0;
+}
+static int launch_frame(b200sift_detector* d, Slot& sl, bool from_copy_stream) {
     if (from_copy_stream) {
-        CU(cudaEventRecord(d->ev_copied[buf], d->copy_stream));
-        CU(cudaStreamWaitEvent(d->stream, d->ev_copied[buf], 0));
+        CU(cudaEventRecord(sl.ev_copied, d->copy_stream));
+        CU(cudaStreamWaitEvent(sl.stream, sl.ev_copied, 0));
     }
-    CU(cudaGraphLaunch(d->exec[buf], d->stream));
-    CU(cudaEventRecord(d->ev_consumed[buf], d->stream));
+    if (int rc = launch_graphs(sl, d->frame_no > 0 ? &d->cur() : nullptr)) return rc;
     d->frame_no++;
     d->have_frame = true;
     return 0;
@@ -501,17 +576,17 @@ int b200sift_detect_host_async(b200sift_detector* d, const float* img, int rows,
     if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
     if (rows != d->cfg.row_width || cols != d->cfg.col_width)
         return fail(B200SIFT_EINVAL, "image is %dx%d, detector was configured for %dx%d", cols, rows, d->cfg.col_width, d->cfg.row_width);
-    int buf = 0;
-    if (int rc = begin_frame(d, &buf, true)) return rc;
-    CU(cudaMemcpy2DAsync(d->d_input[buf], (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
+    Slot* sl = nullptr;
+    if (int rc = begin_frame(d, &sl, true)) return rc;
+    CU(cudaMemcpy2DAsync(sl->d_input, (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
                          cudaMemcpyHostToDevice, d->copy_stream));
-    return launch_frame(d, buf, true);
+    return launch_frame(d, *sl, true);
 }
 
 int b200sift_sync(b200sift_detector* d, int* total) {
     if (!d) return fail(B200SIFT_EINVAL, "null argument");
-    CU(cudaStreamSynchronize(d->stream));
-    if (total) *total = d->have_frame ? *d->h_total : 0;
+    if (int rc = sync_all(d)) return rc;
+    if (total) *total = d->have_frame ? *d->cur().h_total : 0;
     return 0;
 }
 
@@ -525,52 +600,71 @@ int b200sift_detect_device_async(b200sift_detector* d, const float* d_img, size_
     if (!d || !d_img) return fail(B200SIFT_EINVAL, "null argument");
     const int cols = d->cfg.col_width, rows = d->cfg.row_width;
     if (pitch_bytes < (size_t)cols * 4) return fail(B200SIFT_EINVAL, "pitch smaller than a row");
-    int buf = 0;
-    if (int rc = begin_frame(d, &buf, false)) return rc;
-    CU(cudaMemcpy2DAsync(d->d_input[buf], (size_t)d->in_pitch * 4, d_img, pitch_bytes, (size_t)cols * 4, rows,
-                         cudaMemcpyDeviceToDevice, d->stream));
-    return launch_frame(d, buf, false);
+    Slot* sl = nullptr;
+    if (int rc = begin_frame(d, &sl, false)) return rc;
+    CU(cudaMemcpy2DAsync(sl->d_input, (size_t)d->in_pitch * 4, d_img, pitch_bytes, (size_t)cols * 4, rows,
+                         cudaMemcpyDeviceToDevice, sl->stream));
+    return launch_frame(d, *sl, false);
 }
 
 int b200sift_detect_host_u8_async(b200sift_detector* d, const uint8_t* img, int rows, int cols) {
     if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
     if (rows != d->cfg.row_width || cols != d->cfg.col_width)
         return fail(B200SIFT_EINVAL, "image is %dx%d, detector was configured for %dx%d", cols, rows, d->cfg.col_width, d->cfg.row_width);
-    int buf = 0;
-    if (int rc = begin_frame(d, &buf, true)) return rc;
-    CU(cudaMemcpy2DAsync(d->d_input_u8[buf], d->u8_pitch, img, (size_t)cols, (size_t)cols, rows, cudaMemcpyHostToDevice, d->copy_stream));
-    launch_u8_to_float(d->d_input_u8[buf], d->u8_pitch, d->d_input[buf], d->in_pitch, cols, rows, d->copy_stream);
-    return launch_frame(d, buf, true);
+    Slot* sl = nullptr;
+    if (int rc = begin_frame(d, &sl, true)) return rc;
+    CU(cudaMemcpy2DAsync(sl->d_input_u8, d->u8_pitch, img, (size_t)cols, (size_t)cols, rows, cudaMemcpyHostToDevice, d->copy_stream));
+    launch_u8_to_float(sl->d_input_u8, d->u8_pitch, sl->d_input, d->in_pitch, cols, rows, d->copy_stream);
+    return launch_frame(d, *sl, true);
+}
+
+// Everything enqueued so far on the latest frame's stream has read the previous frame's slot: remember it, so
+// that the frame which reuses that slot (two frames from now) waits for these readers.
+static int mark_prev_read(b200sift_detector* d) {
+    Slot &cur = d->cur(), &prv = d->prev();
+    CU(cudaEventRecord(prv.ev_matched, cur.stream));
+    prv.matched_pending = true;
+    return 0;
 }
 
 int b200sift_match_consecutive_async(b200sift_detector* d, int* d_out_idx) {
     if (!d || !d_out_idx) return fail(B200SIFT_EINVAL, "null argument");
-    if (match_launch_counts(d->d_prev_desc, d->fp.out_desc, d->cfg.numFeatures, d->fp.total, d_out_idx, d->match_scratch,
-                            d->match_scratch_bytes_, d->stream))
+    Slot &cur = d->cur(), &prv = d->prev();
+    CU(cudaStreamWaitEvent(cur.stream, prv.ev_done, 0));
+    // query = previous frame's descriptors, train = this frame's; both sizes are read on the device
+    if (match_launch_counts(prv.fp.out_desc, cur.fp.out_desc, d->cfg.numFeatures, prv.fp.total, cur.fp.total, d_out_idx,
+                            cur.match_scratch, d->match_scratch_bytes_, cur.stream))
         return fail(B200SIFT_EINVAL, "matcher scratch too small");
     CU(cudaGetLastError());
-    return 0;
+    return mark_prev_read(d);
 }
 
 int b200sift_copy_results_async(b200sift_detector* d, float* kpts3, float* feats4, uint16_t* desc, int* counts2) {
     if (!d) return fail(B200SIFT_EINVAL, "null argument");
+    Slot &cur = d->cur(), &prv = d->prev();
     const size_t n = (size_t)d->cfg.numFeatures;
-    if (kpts3) CU(cudaMemcpyAsync(kpts3, d->fp.out_kpts, n * sizeof(float3), cudaMemcpyDeviceToHost, d->stream));
-    if (feats4) CU(cudaMemcpyAsync(feats4, d->fp.out_feats, n * sizeof(float4), cudaMemcpyDeviceToHost, d->stream));
-    if (desc) CU(cudaMemcpyAsync(desc, d->fp.out_desc, n * 128 * sizeof(__half), cudaMemcpyDeviceToHost, d->stream));
-    if (counts2) CU(cudaMemcpyAsync(counts2, d->fp.total, 2 * sizeof(int), cudaMemcpyDeviceToHost, d->stream));
+    if (kpts3) CU(cudaMemcpyAsync(kpts3, cur.fp.out_kpts, n * sizeof(float3), cudaMemcpyDeviceToHost, cur.stream));
+    if (feats4) CU(cudaMemcpyAsync(feats4, cur.fp.out_feats, n * sizeof(float4), cudaMemcpyDeviceToHost, cur.stream));
+    if (desc) CU(cudaMemcpyAsync(desc, cur.fp.out_desc, n * 128 * sizeof(__half), cudaMemcpyDeviceToHost, cur.stream));
+    if (counts2) {
+        CU(cudaMemcpyAsync(counts2, cur.fp.total, sizeof(int), cudaMemcpyDeviceToHost, cur.stream));
+        CU(cudaStreamWaitEvent(cur.stream, prv.ev_done, 0));
+        CU(cudaMemcpyAsync(counts2 + 1, prv.fp.total, sizeof(int), cudaMemcpyDeviceToHost, cur.stream));
+        return mark_prev_read(d);
+    }
     return 0;
 }
 
-void* b200sift_stream(b200sift_detector* d) { return d ? (void*)d->stream : nullptr; }
+void* b200sift_stream(b200sift_detector* d) { return d ? (void*)d->cur().stream : nullptr; }
 
 int b200sift_results(b200sift_detector* d, const float** kpts, const float** feats, const uint16_t** desc,
                      const uint16_t** prev_desc, int* total) {
     if (!d) return fail(B200SIFT_EINVAL, "null argument");
-    if (kpts) *kpts = reinterpret_cast<const float*>(d->fp.out_kpts);
-    if (feats) *feats = reinterpret_cast<const float*>(d->fp.out_feats);
-    if (desc) *desc = reinterpret_cast<const uint16_t*>(d->fp.out_desc);
-    if (prev_desc) *prev_desc = reinterpret_cast<const uint16_t*>(d->d_prev_desc);
+    const FrameParams& fp = d->cur().fp;
+    if (kpts) *kpts = reinterpret_cast<const float*>(fp.out_kpts);
+    if (feats) *feats = reinterpret_cast<const float*>(fp.out_feats);
+    if (desc) *desc = reinterpret_cast<const uint16_t*>(fp.out_desc);
+    if (prev_desc) *prev_desc = reinterpret_cast<const uint16_t*>(d->prev().fp.out_desc);
     if (total) return b200sift_sync(d, total);
     return 0;
 }
@@ -580,18 +674,19 @@ int b200sift_copy_to_host(b200sift_detector* d, float* kpts3, float* feats4, uin
     int total = 0;
     int rc = b200sift_sync(d, &total);
     if (rc) return rc;
-    if (kpts3) CU(cudaMemcpyAsync(kpts3, d->fp.out_kpts, (size_t)total * sizeof(float3), cudaMemcpyDeviceToHost, d->stream));
-    if (feats4) CU(cudaMemcpyAsync(feats4, d->fp.out_feats, (size_t)total * sizeof(float4), cudaMemcpyDeviceToHost, d->stream));
+    Slot& cur = d->cur();
+    if (kpts3) CU(cudaMemcpyAsync(kpts3, cur.fp.out_kpts, (size_t)total * sizeof(float3), cudaMemcpyDeviceToHost, cur.stream));
+    if (feats4) CU(cudaMemcpyAsync(feats4, cur.fp.out_feats, (size_t)total * sizeof(float4), cudaMemcpyDeviceToHost, cur.stream));
     if (with_desc && desc)
-        CU(cudaMemcpyAsync(desc, d->fp.out_desc, (size_t)total * 128 * sizeof(__half), cudaMemcpyDeviceToHost, d->stream));
-    CU(cudaStreamSynchronize(d->stream));
+        CU(cudaMemcpyAsync(desc, cur.fp.out_desc, (size_t)total * 128 * sizeof(__half), cudaMemcpyDeviceToHost, cur.stream));
+    CU(cudaStreamSynchronize(cur.stream));
     return 0;
 }
 
 int b200sift_debug_get_stack(b200sift_detector* d, int o, int which, float* out) {
     if (!d || !out || o < 0 || o >= d->nOct || which != 0) return fail(B200SIFT_EINVAL, "bad argument");
-    const OctParams& oc = d->fp.oct[o];
-    CU(cudaStreamSynchronize(d->stream));
+    const OctParams& oc = d->cur().fp.oct[o];
+    if (int rc = sync_all(d)) return rc;
     CU(cudaMemcpy2D(out, (size_t)oc.w * 4, oc.gauss, (size_t)oc.pitch * 4, (size_t)oc.w * 4, (size_t)oc.h * kGaussLayers,
                     cudaMemcpyDeviceToHost));
     return 0;
@@ -599,9 +694,9 @@ int b200sift_debug_get_stack(b200sift_detector* d, int o, int which, float* out)
 
 int b200sift_debug_get_kpt_buffer(b200sift_detector* d, int o, int which, void* out, int max_elems) {
     if (!d || !out || o < 0 || o >= d->nOct) return fail(B200SIFT_EINVAL, "bad argument");
-    const OctParams& oc = d->fp.oct[o];
+    const OctParams& oc = d->cur().fp.oct[o];
     const int n = std::min(max_elems, oc.cap);
-    CU(cudaStreamSynchronize(d->stream));
+    if (int rc = sync_all(d)) return rc;
     switch (which) {
         case 0: CU(cudaMemcpy(out, oc.cand, (size_t)n * sizeof(float3), cudaMemcpyDeviceToHost)); break;
         case 1: CU(cudaMemcpy(out, oc.candF, (size_t)n * sizeof(float4), cudaMemcpyDeviceToHost)); break;
@@ -614,9 +709,9 @@ int b200sift_debug_get_kpt_buffer(b200sift_detector* d, int o, int which, void* 
 
 int b200sift_debug_get_counts(b200sift_detector* d, int o, int* counts) {
     if (!d || !counts || o < 0 || o >= d->nOct) return fail(B200SIFT_EINVAL, "bad argument");
-    CU(cudaStreamSynchronize(d->stream));
+    if (int rc = sync_all(d)) return rc;
     int c[4];
-    CU(cudaMemcpy(c, d->fp.oct[o].counts, sizeof(c), cudaMemcpyDeviceToHost));
+    CU(cudaMemcpy(c, d->cur().fp.oct[o].counts, sizeof(c), cudaMemcpyDeviceToHost));
     counts[0] = c[0]; counts[1] = c[1]; counts[2] = c[2];
     return 0;
 }
@@ -628,33 +723,42 @@ int b200sift_debug_get_taps(b200sift_detector* d, int which, float* out, int max
     return t.n;
 }
 
+// Runs the pipeline up to `last_stage` eagerly (no graph) in the next slot, which becomes the latest frame.
 int b200sift_debug_run_stages(b200sift_detector* d, const float* img, int rows, int cols, int last_stage) {
     if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
     if (rows != d->cfg.row_width || cols != d->cfg.col_width) return fail(B200SIFT_EINVAL, "image size mismatch");
-    CU(cudaStreamSynchronize(d->stream));
-    const int buf = (int)(d->frame_no & 1);
-    CU(cudaMemcpy2DAsync(d->d_input[buf], (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
-                         cudaMemcpyHostToDevice, d->stream));
-    int rc = enqueue_frame(d, d->stream, last_stage, nullptr, nullptr, buf);
+    if (int rc = sync_all(d)) return rc;
+    Slot& sl = d->slot[d->frame_no % kSlots];
+    sl.matched_pending = false;
+    CU(cudaMemcpy2DAsync(sl.d_input, (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
+                         cudaMemcpyHostToDevice, sl.stream));
+    int rc = enqueue_frame(d, sl, last_stage, nullptr, nullptr);
     if (rc) return rc;
+    CU(cudaEventRecord(sl.ev_consumed, sl.stream));
+    CU(cudaEventRecord(sl.ev_chain, sl.stream));
+    CU(cudaEventRecord(sl.ev_done, sl.stream));
+    d->frame_no++;
     if (last_stage >= 6) d->have_frame = true;
-    CU(cudaStreamSynchronize(d->stream));
-    return 0;
+    return sync_all(d);
 }
 
 int b200sift_launches_per_frame(const b200sift_detector* d) { return d ? d->launches : B200SIFT_EINVAL; }
 
+// Latency of one frame graph: the latest frame's graph replayed back to back on its own stream.
 int b200sift_time_frames(b200sift_detector* d, int warmup, int iters, float* ms_per_frame) {
     if (!d || !ms_per_frame || iters <= 0) return fail(B200SIFT_EINVAL, "bad argument");
+    if (int rc = sync_all(d)) return rc;
+    Slot& sl = d->cur();
     cudaEvent_t e0, e1;
     CU(cudaEventCreate(&e0));
     CU(cudaEventCreate(&e1));
-    const int tb = (int)((d->frame_no + 1) & 1);  // buffer of the last frame
-    for (int i = 0; i < warmup; i++) CU(cudaGraphLaunch(d->exec[tb], d->stream));
-    CU(cudaStreamSynchronize(d->stream));
-    CU(cudaEventRecord(e0, d->stream));
-    for (int i = 0; i < iters; i++) CU(cudaGraphLaunch(d->exec[tb], d->stream));
-    CU(cudaEventRecord(e1, d->stream));
+    for (int i = 0; i < warmup; i++)
+        if (int rc = launch_graphs(sl, nullptr)) return rc;
+    CU(cudaStreamSynchronize(sl.stream));
+    CU(cudaEventRecord(e0, sl.stream));
+    for (int i = 0; i < iters; i++)
+        if (int rc = launch_graphs(sl, nullptr)) return rc;
+    CU(cudaEventRecord(e1, sl.stream));
     CU(cudaEventSynchronize(e1));
     float ms = 0.f;
     CU(cudaEventElapsedTime(&ms, e0, e1));
@@ -665,17 +769,61 @@ int b200sift_time_frames(b200sift_detector* d, int warmup, int iters, float* ms_
     return 0;
 }
 
+// Throughput of the frame graphs with kSlots frames in flight: every slot replays its graph on the latest
+// frame's input, round robin, each on its own stream.
+int b200sift_time_frames_pipelined(b200sift_detector* d, int warmup, int iters, float* ms_per_frame) {
+    if (!d || !ms_per_frame || iters <= 0) return fail(B200SIFT_EINVAL, "bad argument");
+    if (int rc = sync_all(d)) return rc;
+    Slot& src = d->cur();
+    const size_t in_bytes = (size_t)d->in_pitch * d->cfg.row_width * sizeof(float);
+    for (int i = 0; i < kSlots; i++)
+        if (&d->slot[i] != &src) CU(cudaMemcpy(d->slot[i].d_input, src.d_input, in_bytes, cudaMemcpyDeviceToDevice));
+    cudaEvent_t e0, e1[kSlots];
+    CU(cudaEventCreate(&e0));
+    for (int i = 0; i < kSlots; i++) CU(cudaEventCreate(&e1[i]));
+    const int first = (int)(d->frame_no % kSlots);
+    Slot* last = &src;
+    for (int i = 0; i < warmup; i++) {
+        Slot& sl = d->slot[(first + i) % kSlots];
+        if (int rc = launch_graphs(sl, last)) return rc;
+        last = &sl;
+    }
+    if (int rc = sync_all(d)) return rc;
+    CU(cudaEventRecord(e0, d->slot[0].stream));
+    for (int i = 1; i < kSlots; i++) CU(cudaStreamWaitEvent(d->slot[i].stream, e0, 0));
+    const int total = (iters + kSlots - 1) / kSlots * kSlots;  // a whole number of rotations
+    for (int i = 0; i < total; i++) {
+        Slot& sl = d->slot[(first + i) % kSlots];
+        if (int rc = launch_graphs(sl, last)) return rc;
+        last = &sl;
+    }
+    float ms = 0.f;
+    for (int i = 0; i < kSlots; i++) CU(cudaEventRecord(e1[i], d->slot[i].stream));
+    for (int i = 0; i < kSlots; i++) {
+        float t = 0.f;
+        CU(cudaEventSynchronize(e1[i]));
+        CU(cudaEventElapsedTime(&t, e0, e1[i]));
+        ms = std::max(ms, t);
+    }
+    cudaEventDestroy(e0);
+    for (int i = 0; i < kSlots; i++) cudaEventDestroy(e1[i]);
+    *ms_per_frame = ms / (float)total;
+    return 0;
+}
+
 int b200sift_profile_frame(b200sift_detector* d, int warmup, int iters, float* ms_per_class, int* launches_per_class) {
     if (!d || !ms_per_class || iters <= 0) return fail(B200SIFT_EINVAL, "bad argument");
+    if (int rc = sync_all(d)) return rc;
+    Slot& sl = d->cur();
     Profiler prof;
-    prof.s = d->stream;
+    prof.s = sl.stream;
     std::vector<double> acc(B200SIFT_K_COUNT, 0.0);
     std::vector<int> cnt(B200SIFT_K_COUNT, 0);
     for (int it = 0; it < warmup + iters; it++) {
         prof.used = 0;
-        int rc = enqueue_frame(d, d->stream, 7, nullptr, &prof, (int)((d->frame_no + 1) & 1));
+        int rc = enqueue_frame(d, sl, 7, nullptr, &prof);
         if (rc) return rc;
-        CU(cudaStreamSynchronize(d->stream));
+        CU(cudaStreamSynchronize(sl.stream));
         if (it < warmup) continue;
         for (size_t i = 1; i < prof.used; i++) {
             float ms = 0.f;
@@ -696,25 +844,26 @@ int b200sift_profile_frame(b200sift_detector* d, int warmup, int iters, float* m
 // (4), orientation (5) and complete (7), each captured and replayed `iters` times on the last frame's input.
 int b200sift_time_stages(b200sift_detector* d, int iters, float* ms5) {
     if (!d || !ms5 || iters <= 0) return fail(B200SIFT_EINVAL, "bad argument");
+    if (int rc = sync_all(d)) return rc;
+    Slot& sl = d->cur();
     const int stages[5] = {1, 3, 4, 5, 7};
-    const int buf = (int)((d->frame_no + 1) & 1);
     cudaEvent_t e0, e1;
     CU(cudaEventCreate(&e0));
     CU(cudaEventCreate(&e1));
     for (int i = 0; i < 5; i++) {
         cudaGraph_t g = nullptr;
         cudaGraphExec_t x = nullptr;
-        CU(cudaStreamSynchronize(d->stream));
-        CU(cudaStreamBeginCapture(d->stream, cudaStreamCaptureModeThreadLocal));
-        int rc = enqueue_frame(d, d->stream, stages[i], nullptr, nullptr, buf);
-        cudaError_t e = cudaStreamEndCapture(d->stream, &g);
+        CU(cudaStreamSynchronize(sl.stream));
+        CU(cudaStreamBeginCapture(sl.stream, cudaStreamCaptureModeThreadLocal));
+        int rc = enqueue_frame(d, sl, stages[i], nullptr, nullptr);
+        cudaError_t e = cudaStreamEndCapture(sl.stream, &g);
         if (rc) return rc;
         CU(e);
         CU(cudaGraphInstantiate(&x, g, 0));
-        for (int k = 0; k < 5; k++) CU(cudaGraphLaunch(x, d->stream));
-        CU(cudaEventRecord(e0, d->stream));
-        for (int k = 0; k < iters; k++) CU(cudaGraphLaunch(x, d->stream));
-        CU(cudaEventRecord(e1, d->stream));
+        for (int k = 0; k < 5; k++) CU(cudaGraphLaunch(x, sl.stream));
+        CU(cudaEventRecord(e0, sl.stream));
+        for (int k = 0; k < iters; k++) CU(cudaGraphLaunch(x, sl.stream));
+        CU(cudaEventRecord(e1, sl.stream));
         CU(cudaEventSynchronize(e1));
         float ms = 0.f;
         CU(cudaEventElapsedTime(&ms, e0, e1));
@@ -723,8 +872,8 @@ int b200sift_time_stages(b200sift_detector* d, int iters, float* ms5) {
         cudaGraphDestroy(g);
     }
     // leave complete results behind
-    CU(cudaGraphLaunch(d->exec[buf], d->stream));
-    CU(cudaStreamSynchronize(d->stream));
+    if (int rc = launch_graphs(sl, nullptr)) return rc;
+    CU(cudaStreamSynchronize(sl.stream));
     cudaEventDestroy(e0);
     cudaEventDestroy(e1);
     return 0;

@@ -116,10 +116,11 @@ __device__ __forceinline__ float row_norm2(const uint8_t* s, int row) {
 template <int TN, bool DBG>
 __global__ void __launch_bounds__(kFilterThreads)
 match_filter_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per,
-                    CandRec* __restrict__ rec, float* __restrict__ dbg, const int* __restrict__ counts) {
-    if (counts) {  // sizes known only on the device (consecutive-frame matching without a host round trip)
-        nt = counts[0];
-        nq = counts[1];
+                    CandRec* __restrict__ rec, float* __restrict__ dbg, const int* __restrict__ cnt_q,
+                    const int* __restrict__ cnt_t) {
+    if (cnt_q) {  // sizes known only on the device (consecutive-frame matching without a host round trip)
+        nt = *cnt_t;
+        nq = *cnt_q;
         per = (int)ceilf((float)nt / 32.f);
     }
     extern __shared__ __align__(1024) uint8_t smem[];
@@ -271,10 +272,11 @@ constexpr int kListCap = 32 * kCand;
 
 __global__ void __launch_bounds__(kRerankWarps * 32)
 match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per,
-                    const CandRec* __restrict__ rec, int* __restrict__ out_idx, const int* __restrict__ counts) {
-    if (counts) {
-        nt = counts[0];
-        nq = counts[1];
+                    const CandRec* __restrict__ rec, int* __restrict__ out_idx, const int* __restrict__ cnt_q,
+                    const int* __restrict__ cnt_t) {
+    if (cnt_q) {
+        nt = *cnt_t;
+        nq = *cnt_q;
         per = (int)ceilf((float)nt / 32.f);
     }
     __shared__ int s_col[kRerankWarps][kListCap];
@@ -375,13 +377,13 @@ constexpr size_t filter_smem(int tn) { return kTileBytes + (size_t)tn * 256 + tn
 
 template <int TN, bool DBG>
 void launch_filter(dim3 grid, const __half* q, int nq, const __half* t, int nt, int per, CandRec* rec, float* dbg, cudaStream_t s,
-                   const int* counts = nullptr) {
+                   const int* cnt_q = nullptr, const int* cnt_t = nullptr) {
     static bool attr_set = false;
     if (!attr_set) {
         cudaFuncSetAttribute(match_filter_kernel<TN, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)filter_smem(TN));
         attr_set = true;
     }
-    match_filter_kernel<TN, DBG><<<grid, kFilterThreads, filter_smem(TN), s>>>(q, nq, t, nt, per, rec, dbg, counts);
+    match_filter_kernel<TN, DBG><<<grid, kFilterThreads, filter_smem(TN), s>>>(q, nq, t, nt, per, rec, dbg, cnt_q, cnt_t);
 }
 }  // namespace
 
@@ -410,22 +412,22 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
         if (per <= 128) launch_filter<128, false>(grid, q, nq, t, nt, per, rec, dbg, s);
         else launch_filter<256, false>(grid, q, nq, t, nt, per, rec, dbg, s);
     }
-    match_rerank_kernel<<<(nq + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, nq, t, nt, per, rec, out, nullptr);
+    match_rerank_kernel<<<(nq + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, nq, t, nt, per, rec, out, nullptr, nullptr);
     return 0;
 }
 
-// Same matcher with the set sizes read on the device: counts[0] = train rows, counts[1] = query rows, both
+// Same matcher with the set sizes read on the device: *cnt_q = query rows, *cnt_t = train rows, both
 // <= max_n. Grids are sized for max_n; surplus CTAs exit at once.
-int match_launch_counts(const __half* q, const __half* t, int max_n, const int* counts, int* out, void* scratch,
+int match_launch_counts(const __half* q, const __half* t, int max_n, const int* cnt_q, const int* cnt_t, int* out, void* scratch,
                         size_t scratch_bytes, cudaStream_t s) {
     if (max_n <= 0) return 0;
     if (scratch_bytes < match_scratch_bytes(max_n, max_n)) return -1;
     CandRec* rec = static_cast<CandRec*>(scratch);
     const int per_max = (max_n + 31) / 32;
     dim3 grid((max_n + kTileM - 1) / kTileM, 32);
-    if (per_max <= 128) launch_filter<128, false>(grid, q, max_n, t, max_n, per_max, rec, nullptr, s, counts);
-    else launch_filter<256, false>(grid, q, max_n, t, max_n, per_max, rec, nullptr, s, counts);
-    match_rerank_kernel<<<(max_n + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, max_n, t, max_n, per_max, rec, out, counts);
+    if (per_max <= 128) launch_filter<128, false>(grid, q, max_n, t, max_n, per_max, rec, nullptr, s, cnt_q, cnt_t);
+    else launch_filter<256, false>(grid, q, max_n, t, max_n, per_max, rec, nullptr, s, cnt_q, cnt_t);
+    match_rerank_kernel<<<(max_n + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, max_n, t, max_n, per_max, rec, out, cnt_q, cnt_t);
     return 0;
 }
 

@@ -96,14 +96,19 @@ class Detector:
             d = (C.c_int * 4)()
             check(self.lib.b200sift_octave_info(h, o, d))
             self.octaves.append(dict(w=d[0], h=d[1], pitch=d[2], cap=d[3]))
+        self._refresh_views()
+        return True
+
+    def _refresh_views(self):
+        """The engine keeps three frames in flight, each with its own result buffers: the public device views
+        always point at the latest frame (prev_descriptor at the one before it, in place, no copy)."""
         k, f, d, p = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
-        check(self.lib.b200sift_results(h, C.byref(k), C.byref(f), C.byref(d), C.byref(p), None))
+        check(self.lib.b200sift_results(self._h, C.byref(k), C.byref(f), C.byref(d), C.byref(p), None))
         n = self.config.numFeatures
         self.device_kpts = DeviceArray(k.value, (n, 3), "<f4", self)
         self.device_features = DeviceArray(f.value, (n, 4), "<f4", self)
         self.device_descriptor = DeviceArray(d.value, (n, 128), "<f2", self)
         self.prev_descriptor = DeviceArray(p.value, (n, 128), "<f2", self)
-        return True
 
     def close(self):
         if self._h is not None:
@@ -136,7 +141,7 @@ class Detector:
             if image.stride(1) != 1:
                 raise B200SiftError("device image rows must be contiguous")
             check(self.lib.b200sift_detect_device_async(h, image.data_ptr(), image.stride(0) * 4))
-            self._keep = image
+            self._hold(image)
             return
         if hasattr(image, "numpy") and not isinstance(image, np.ndarray):
             image = image.numpy()  # CPU torch tensor (pinned or not) shares memory
@@ -147,7 +152,11 @@ class Detector:
         else:
             image = np.ascontiguousarray(image, dtype=np.float32)
             check(self.lib.b200sift_detect_host_async(h, image.ctypes.data, rows, cols))
-        self._keep = image  # must outlive the asynchronous copy
+        self._hold(image)
+
+    def _hold(self, image):
+        self._keep = (getattr(self, "_keep", None) or [])[-3:] + [image]  # inputs must outlive their asynchronous copies
+        self._refresh_views()
 
     def synchronize(self) -> int:
         t = C.c_int(0)
@@ -186,14 +195,13 @@ class Detector:
         receives the matches of frame i-1 -> frame i. One synchronisation at the end."""
         import torch
 
-        ext = torch.cuda.ExternalStream(self.stream)
-        idx = [torch.empty(self.config.numFeatures, dtype=torch.int32, device="cuda") for _ in range(2)] if match_out is not None else None
+        idx = [torch.empty(self.config.numFeatures, dtype=torch.int32, device="cuda") for _ in range(3)] if match_out is not None else None
         for i, f in enumerate(frames):
             self.detectAndComputeAsync(f)
             if match_out is not None:
-                self.matchConsecutiveAsync(idx[i & 1])
-                with torch.cuda.stream(ext):
-                    match_out[i].copy_(idx[i & 1], non_blocking=True)
+                self.matchConsecutiveAsync(idx[i % 3])
+                with torch.cuda.stream(torch.cuda.ExternalStream(self.stream)):  # the latest frame's stream
+                    match_out[i].copy_(idx[i % 3], non_blocking=True)
             self.copyResultsAsync(results[i])
         self.synchronize()
 
@@ -206,8 +214,15 @@ class Detector:
         return check(self.lib.b200sift_launches_per_frame(self._handle()))
 
     def time_frames(self, warmup: int, iters: int) -> float:
+        """Latency of one frame graph (ms): the latest frame's graph replayed back to back."""
         ms = C.c_float(0)
         check(self.lib.b200sift_time_frames(self._handle(), warmup, iters, C.byref(ms)))
+        return float(ms.value)
+
+    def time_frames_pipelined(self, warmup: int, iters: int) -> float:
+        """ms per frame with three frames in flight (every slot replays its graph, round robin)."""
+        ms = C.c_float(0)
+        check(self.lib.b200sift_time_frames_pipelined(self._handle(), warmup, iters, C.byref(ms)))
         return float(ms.value)
 
     KERNEL_CLASSES = ("copy", "blur_oct0", "blur_small", "downsample", "detect", "compact", "refine", "orient", "describe")
@@ -228,6 +243,7 @@ class Detector:
     def debug_run_stages(self, image: np.ndarray, last_stage: int) -> None:
         image = np.ascontiguousarray(image, dtype=np.float32)
         check(self.lib.b200sift_debug_run_stages(self._handle(), image.ctypes.data, image.shape[0], image.shape[1], last_stage))
+        self._refresh_views()
 
     def debug_gauss(self, o: int) -> np.ndarray:
         oc = self.octaves[o]

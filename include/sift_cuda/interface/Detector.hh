@@ -62,6 +62,18 @@ class Detector {
         c.sigma = m_config.sigma;
         c.upscale = m_config.upscale ? 1 : 0;
         check(b200sift_create(&c, &m_handle), "b200sift_create");
+        refresh_views();
+        const size_t n = size_t(m_config.numFeatures);
+        final_kpts.resize(n);        // Detector.cu:128-130
+        final_features.resize(n);
+        descriptors.resize(n * 128);
+        m_initialized = true;
+        return true;
+    }
+
+    // The engine keeps three frames in flight, each with its own result buffers: after every detect call the
+    // public views point at the latest frame, prev_descriptor at the frame before it (in place, no copy).
+    void refresh_views() {
         const float *k = nullptr, *f = nullptr;
         const uint16_t *d = nullptr, *p = nullptr;
         check(b200sift_results(m_handle, &k, &f, &d, &p, nullptr), "b200sift_results");
@@ -70,11 +82,6 @@ class Detector {
         device_features = DeviceView<float4>(reinterpret_cast<const float4*>(f), n);
         device_descriptor = DeviceView<half>(reinterpret_cast<const half*>(d), n * 128);
         prev_descriptor = DeviceView<half>(reinterpret_cast<const half*>(p), n * 128);
-        final_kpts.resize(n);        // Detector.cu:128-130
-        final_features.resize(n);
-        descriptors.resize(n * 128);
-        m_initialized = true;
-        return true;
     }
 
     // Detector.cu:133-233. The image must have the configured size (checked here, unchecked in the reference).
@@ -82,11 +89,13 @@ class Detector {
         require_init();
         check(b200sift_detect_host(m_handle, image.m_data->data(), int(image.m_image_size.row), int(image.m_image_size.col),
                                    &total_size), "b200sift_detect_host");
+        refresh_views();
     }
     // Extension: frame already resident in HBM (pitched fp32), enqueued on stream(); call synchronize().
     void detectAndComputeDevice(const float* d_image, size_t pitch_bytes) {
         require_init();
         check(b200sift_detect_device_async(m_handle, d_image, pitch_bytes), "b200sift_detect_device_async");
+        refresh_views();
     }
     int synchronize() {
         require_init();
