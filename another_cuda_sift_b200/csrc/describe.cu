@@ -12,6 +12,7 @@
 // order independent (deterministic) and lies inside the reference's own run-to-run envelope:
 // orientation bins as 2^-32 in 64 bits (peak selection is a discrete decision, keep it as exact as
 // possible), descriptor bins as 2^-15 in 32 bits (8 votes per sample: one ATOMS.ADD each).
+#include <cstdlib>
 #include "common.cuh"
 
 namespace b200sift {
@@ -211,8 +212,7 @@ constexpr int kPrivSlots = 32;  // 2 x 2 spatial neighbours x 8 orientation bins
 // column 0 cover rbin in (-1,1) (truncating modff, quirk Q13), so cell (0,0) is four units of area, the other
 // row-0 / column-0 cells two, the rest one. Warps pull cells from this queue (longest-processing-time order).
 __constant__ signed char kCellOrder[16] = {0, 1, 2, 3, 4, 8, 12, 5, 6, 7, 9, 10, 11, 13, 14, 15};
-constexpr int kDescCtasPerSm = 4;  // persistent CTAs per SM and launch (up to 7 fit; several launches overlap, and
-                                   // the other graph branches need room: measured best at 1920x1200)
+constexpr int kDescCtasPerSm = 5;  // persistent CTAs per SM (up to 7 fit): leaves room for the other frames in flight
 constexpr int kRing = 64;  // per-warp ring of accepted samples (at most 31 pending + 32 appended)
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -505,7 +505,8 @@ cudaError_t launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cud
     long cap = 0;
     for (int i = o_begin; i < o_end; i++) cap += fp.oct[i].cap;
     long grid = cap < (long)fp.numFeatures ? cap : (long)fp.numFeatures;
-    if (grid > 148L * kDescCtasPerSm) grid = 148L * kDescCtasPerSm;
+    static const long per_sm = getenv("B200SIFT_DESC_PER_SM") ? atol(getenv("B200SIFT_DESC_PER_SM")) : kDescCtasPerSm;
+    if (grid > 148L * per_sm) grid = 148L * per_sm;
     // Lowest stream priority: the descriptor grids would otherwise fill every CTA slot and starve the short
     // latency-bound kernels of the other graph branches (the priority is recorded in the captured node).
     cudaLaunchConfig_t cfg = {};
