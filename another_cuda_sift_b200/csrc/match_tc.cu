@@ -19,6 +19,7 @@
 //     A (query, chunk) whose survivor list overflows is re-scored column by column (rare, still exact).
 //
 // Roofline: tensor-bound in the limit (2*nq*nt*128 flop); at 2k x 2k it is launch/latency-bound.
+#include <algorithm>
 #include "common.cuh"
 
 namespace b200sift {
@@ -251,6 +252,225 @@ match_filter_kernel(const __half* __restrict__ des, int nq, const __half* __rest
     }
 }
 
+// ---------------------------------------------------------------- resident-chunk filter (per <= 256)
+// Squared norms of every row (fp32), once per matcher call instead of once per CTA.
+__global__ void __launch_bounds__(256)
+match_norms_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, float* __restrict__ nrm_q,
+                   float* __restrict__ nrm_t, const int* __restrict__ cnt_q, const int* __restrict__ cnt_t) {
+    if (cnt_q) { nt = *cnt_t; nq = *cnt_q; }
+    const int lane = threadIdx.x & 31;
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5);
+    if (row >= nq + nt) return;
+    const __half* p = row < nq ? des + (size_t)row * 128 : src + (size_t)(row - nq) * 128;
+    const uint2 v = __ldg(reinterpret_cast<const uint2*>(p) + lane);
+    const float2 f0 = __half22float2(*reinterpret_cast<const __half2*>(&v.x));
+    const float2 f1 = __half22float2(*reinterpret_cast<const __half2*>(&v.y));
+    float acc = __fmaf_rn(f0.x, f0.x, __fmaf_rn(f0.y, f0.y, __fmaf_rn(f1.x, f1.x, __fmul_rn(f1.y, f1.y))));
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
+    if (lane == 0) (row < nq ? nrm_q[row] : nrm_t[row - nq]) = acc;
+}
+
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
+    const int bytes = valid ? 16 : 0;  // src-size 0: the 16 bytes are zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(bytes) : "memory");
+}
+
+constexpr int kResThreads = 256;  // two groups of four warps, 128 queries each, sharing every train tile
+constexpr int kResQ = 256;        // queries per CTA
+
+// One CTA = 256 queries x `cpc` consecutive column chunks of the reference (chunk c = columns [c*per, (c+1)*per)).
+// Every chunk fits one MMA tile (TR = per rounded up to 32 <= 256 rows), so its distances stay resident in
+// TMEM (two 128 x TR accumulators, one per query half): pass 1 (second smallest) and pass 2 (survivors) both
+// read TMEM, one MMA pair per chunk. The query tiles are loaded once per CTA, pre-multiplied by -2 (exact in
+// fp16), so the accumulator is -2 a.b and a distance is one FADD with the precomputed |b|^2; |a|^2 is
+// constant per thread and only enters the threshold. The next chunk's train tile streams in with cp.async
+// while the current one is scanned.
+template <bool DBG>
+__global__ void __launch_bounds__(kResThreads)
+match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per, int TR, int cpc,
+                             CandRec* __restrict__ rec, float* __restrict__ dbg, const float* __restrict__ nrm_q,
+                             const float* __restrict__ nrm_t, const int* __restrict__ cnt_q, const int* __restrict__ cnt_t) {
+    if (cnt_q) {
+        nt = *cnt_t;
+        nq = *cnt_q;
+        per = (int)ceilf((float)nt / 32.f);
+    }
+    const int TRP = TR;  // TR is a multiple of 32: whole 32-column TMEM loads, every scanned column written by the MMA
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sQ = smem;                                     // 2 x [16][128][16 B]
+    uint8_t* sB = smem + 2 * kTileBytes;                    // 2 x [16][TR][16 B]
+    const uint32_t b_bytes = (uint32_t)TR * 256;
+    float* s_nb = reinterpret_cast<float*>(sB + 2 * b_bytes);  // 2 x [TRP]
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_nb + 2 * TRP);
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 1);
+    int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);      // [2]
+    unsigned char* s_cand = reinterpret_cast<unsigned char*>(s_tmem + 4);  // [kCand][256]: survivor columns (chunk-relative) of thread tid
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int half_id = warp >> 2;  // which 128-query tile / accumulator this warp works on
+    const int q0 = blockIdx.x * kResQ;
+    const int q = q0 + tid;
+    if (q0 >= nq) return;  // grid was sized for the largest possible query set
+    const int c_begin = blockIdx.y * cpc, c_end = min(32, c_begin + cpc);
+    const uint32_t idesc = make_idesc(TR);
+    const uint32_t kc_stride_b = (uint32_t)TR * 16;
+    const bool two_tiles = q0 + kTileM < nq;  // the second query tile holds at least one row
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(512));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (tid == 0) {
+        s_nbmax[0] = 0;
+        s_nbmax[1] = 0;
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    __syncthreads();
+    // train tile of chunk c -> buffer b (cp.async), its norms -> s_nb[b] (+inf for the padding columns)
+    auto fetch = [&](int c, int b) {
+        const int t_begin = c * per;
+        const int rows = max(0, min(nt, t_begin + per) - t_begin);
+        const uint32_t base = smem_u32(sB) + (uint32_t)b * b_bytes;
+        const int r8 = lane & 7, k4 = lane >> 3;
+        for (int u = warp; u < TR / 2; u += kResThreads / 32) {  // 16-byte pieces: 8 rows x 4 K chunks per warp step
+            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
+            const bool valid = row < rows;
+            cp_async16(base + kc * kc_stride_b + row * 16, src + (valid ? (size_t)(t_begin + row) * 128 + kc * 8 : 0), valid);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        for (int r = tid; r < TRP; r += kResThreads) {
+            const float nb = r < rows ? __ldg(nrm_t + t_begin + r) : INFINITY;
+            s_nb[b * TRP + r] = nb;
+            if (r < rows) atomicMax(s_nbmax + b, __float_as_int(nb));  // norms are >= 0: int order == float order
+        }
+    };
+    fetch(c_begin, 0);
+    {   // query tiles, scaled by -2
+        const int rows = min(kResQ, nq - q0);
+        const int r8 = lane & 7, k4 = lane >> 3;
+        const __half2 m2 = __floats2half2_rn(-2.f, -2.f);
+        for (int u = warp; u < kResQ / 2; u += kResThreads / 32) {
+            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;  // row 0..255
+            uint4 v = make_uint4(0u, 0u, 0u, 0u);
+            if (row < rows) v = __ldg(reinterpret_cast<const uint4*>(des + (size_t)(q0 + row) * 128) + kc);
+            __half2* h = reinterpret_cast<__half2*>(&v);
+#pragma unroll
+            for (int i = 0; i < 4; i++) h[i] = __hmul2(h[i], m2);
+            *reinterpret_cast<uint4*>(sQ + (row >> 7) * kTileBytes + kc * kKcStride + (row & 127) * 16) = v;
+        }
+    }
+    const float na = q < nq ? __ldg(nrm_q + q) : 0.f;
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem = *s_tmem;
+    const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)half_id * 256;
+    const uint32_t bar = smem_u32(s_bar);
+    const uint32_t aQ = smem_u32(sQ);
+    uint32_t phase = 0;
+
+    for (int c = c_begin; c < c_end; c++) {
+        const int b = (c - c_begin) & 1;
+        const int t_begin = c * per;
+        const int rows = max(0, min(nt, t_begin + per) - t_begin);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // cp.async / st.shared -> visible to the tensor core
+        __syncthreads();
+        if (tid == 0 && rows > 0) {
+            asm volatile("tcgen05.fence::after_thread_sync;");
+            const uint32_t aB = smem_u32(sB) + (uint32_t)b * b_bytes;
+            for (int hq = 0; hq < (two_tiles ? 2 : 1); hq++) {
+#pragma unroll
+                for (int k = 0; k < 8; k++) {  // K = 128 = 8 x 16; one instruction consumes 2 K chunks
+                    const uint64_t da = umma_desc(aQ + hq * kTileBytes + k * 2 * kKcStride, kKcStride, 128);
+                    const uint64_t db = umma_desc(aB + k * 2 * kc_stride_b, kc_stride_b, 128);
+                    const uint32_t acc = k > 0 ? 1u : 0u;
+                    asm volatile(
+                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                        ::"r"(tmem + hq * 256), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+                }
+            }
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+        }
+        if (c + 1 < c_end) fetch(c + 1, b ^ 1);  // the other buffer: its MMA (chunk c-1) completed before the last barrier
+        int cn = 0;
+        if (rows > 0) {
+            mbar_wait(bar, phase);
+            phase ^= 1;
+            asm volatile("tcgen05.fence::after_thread_sync;");
+            const float* nbp = s_nb + b * TRP;
+            float a1 = INFINITY, a2 = INFINITY, thr = 0.f;
+            if (half_id == 0 || two_tiles) {
+                for (int pass = 0; pass < 2; pass++) {
+                    for (int cb = 0; cb * 32 < rows; cb++) {
+                        uint32_t v[32];
+                        asm volatile(
+                            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+                            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+                            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+                            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+                              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
+                              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
+                              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+                            : "r"(taddr + cb * 32));
+                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                        const float4* nb4 = reinterpret_cast<const float4*>(nbp + cb * 32);
+                        if (pass == 0) {
+#pragma unroll
+                            for (int j4 = 0; j4 < 8; j4++) {
+                                const float4 nb = nb4[j4];
+                                const float nbv[4] = {nb.x, nb.y, nb.z, nb.w};
+#pragma unroll
+                                for (int j = 0; j < 4; j++) {
+                                    const float dd = __fadd_rn(__uint_as_float(v[j4 * 4 + j]), nbv[j]);  // |b|^2 - 2 a.b (+inf: padding)
+                                    a2 = fminf(a2, fmaxf(a1, dd));  // branch-free running top-2
+                                    a1 = fminf(a1, dd);
+                                    if (DBG) { if (q < nq && cb * 32 + j4 * 4 + j < rows) dbg[(size_t)q * nt + t_begin + cb * 32 + j4 * 4 + j] = __fadd_rn(na, dd); }
+                                }
+                            }
+                        } else {
+#pragma unroll
+                            for (int j4 = 0; j4 < 8; j4++) {
+                                const float4 nb = nb4[j4];
+                                const float nbv[4] = {nb.x, nb.y, nb.z, nb.w};
+#pragma unroll
+                                for (int j = 0; j < 4; j++) {
+                                    const float dd = __fadd_rn(__uint_as_float(v[j4 * 4 + j]), nbv[j]);
+                                    if (dd <= thr) {  // survivors are rare: one predicated shared-memory store each
+                                        if (cn < kCand) s_cand[cn * kResThreads + tid] = (unsigned char)(cb * 32 + j4 * 4 + j);
+                                        cn++;
+                                    }
+                                }
+                            }
+                        }
+                    }
+                    // survivors: D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings), + fp32 accumulation
+                    // slack; compared in the |b|^2 - 2 a.b domain, i.e. minus |a|^2
+                    const float d2nd = fmaxf(__fadd_rn(a2, na), 0.f);
+                    thr = __fsub_rn(__fmaf_rn(d2nd, 1.004f, __fmaf_rn(4e-5f, __fadd_rn(na, __int_as_float(s_nbmax[b])), 1e-3f)), na);
+                }
+            }
+        }
+        if (q < nq) {
+            int4* dst = reinterpret_cast<int4*>(rec + (size_t)q * 32 + c);
+            int cc[kCand];
+#pragma unroll
+            for (int i = 0; i < kCand; i++) cc[i] = i < cn ? t_begin + (int)s_cand[i * kResThreads + tid] : -1;
+            dst[0] = make_int4(min(cn, kCand + 1), cc[0], cc[1], cc[2]);
+            dst[1] = make_int4(cc[3], cc[4], cc[5], cc[6]);
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;");
+        __syncthreads();  // TMEM and s_nbmax[b] are free again
+        if (tid == 0) s_nbmax[b] = 0;
+    }
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
+    }
+}
+
 // The reference's per-pair score (Match.cu:93-111), warp-cooperative: lane i owns half2 i and i+32 of both
 // rows. The xor butterfly adds the same operand pairs in the same order as the reference's shfl_down tree
 // does for lane 0, and fp32 addition is commutative, so EVERY lane ends up with lane 0's exact value.
@@ -391,11 +611,35 @@ void match_set_path(int path) { g_match_path = path; }
 int match_get_path() { return g_match_path; }
 
 size_t match_scratch_bytes(int nq, int nt) {
-    (void)nt;
-    return (size_t)nq * 32 * sizeof(CandRec);  // >= the 16-byte records of the CUDA-core path
+    // survivor records (>= the 16-byte records of the CUDA-core path) + the squared norms of both sets
+    return (size_t)nq * 32 * sizeof(CandRec) + ((size_t)nq + (size_t)nt + 8) * sizeof(float);
 }
 
-int match_num_launches(int nq, int nt) { return (nq > 0 && nt >= 0) ? 2 : 0; }
+int match_num_launches(int nq, int nt) { return (nq > 0 && nt >= 0) ? ((nt + 31) / 32 <= 256 ? 3 : 2) : 0; }
+
+namespace {
+// Resident-chunk filter (every chunk of the train set fits one MMA tile): norms, then the filter.
+template <bool DBG>
+void launch_resident(const __half* q, int nq, const __half* t, int nt, int per, CandRec* rec, float* dbg, cudaStream_t s,
+                     const int* cnt_q, const int* cnt_t) {
+    float* nrm_q = reinterpret_cast<float*>(rec + (size_t)nq * 32);
+    float* nrm_t = nrm_q + nq;
+    match_norms_kernel<<<(nq + nt + 7) / 8, 256, 0, s>>>(q, nq, t, nt, nrm_q, nrm_t, cnt_q, cnt_t);
+    const int TR = std::max(32, (per + 31) & ~31);
+    // at least 116 KB so that one CTA (which owns all 512 TMEM columns) is resident per SM
+    const size_t smem = std::max<size_t>(2 * kTileBytes + (size_t)2 * TR * 256 + (size_t)2 * TR * 4 + 64 + kCand * kResThreads, 116 * 1024);
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        cudaFuncSetAttribute(match_filter_resident_kernel<DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        smem_set = smem;
+    }
+    const int tiles = (nq + kResQ - 1) / kResQ;
+    int cpc = 8;  // chunks per CTA: as many as still leave about one CTA per SM
+    while (cpc > 1 && tiles * (32 / cpc) < 140) cpc >>= 1;
+    dim3 grid(tiles, 32 / cpc);
+    match_filter_resident_kernel<DBG><<<grid, kResThreads, smem, s>>>(q, nq, t, nt, per, TR, cpc, rec, dbg, nrm_q, nrm_t, cnt_q, cnt_t);
+}
+}  // namespace
 
 int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes,
                  cudaStream_t s, float* dbg) {
@@ -404,12 +648,12 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
     if (g_match_path == 1 && !dbg) return match_launch_simt(q, nq, t, nt, out, scratch, scratch_bytes, s);
     CandRec* rec = static_cast<CandRec*>(scratch);
     const int per = (int)ceilf((float)nt / 32.f);  // Match.cu:131 (float arithmetic)
-    dim3 grid((nq + kTileM - 1) / kTileM, 32);
-    if (dbg) {
-        if (per <= 128) launch_filter<128, true>(grid, q, nq, t, nt, per, rec, dbg, s);
-        else launch_filter<256, true>(grid, q, nq, t, nt, per, rec, dbg, s);
+    if (per <= 256) {
+        if (dbg) launch_resident<true>(q, nq, t, nt, per, rec, dbg, s, nullptr, nullptr);
+        else launch_resident<false>(q, nq, t, nt, per, rec, dbg, s, nullptr, nullptr);
     } else {
-        if (per <= 128) launch_filter<128, false>(grid, q, nq, t, nt, per, rec, dbg, s);
+        dim3 grid((nq + kTileM - 1) / kTileM, 32);
+        if (dbg) launch_filter<256, true>(grid, q, nq, t, nt, per, rec, dbg, s);
         else launch_filter<256, false>(grid, q, nq, t, nt, per, rec, dbg, s);
     }
     match_rerank_kernel<<<(nq + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, nq, t, nt, per, rec, out, nullptr, nullptr);
@@ -424,9 +668,12 @@ int match_launch_counts(const __half* q, const __half* t, int max_n, const int* 
     if (scratch_bytes < match_scratch_bytes(max_n, max_n)) return -1;
     CandRec* rec = static_cast<CandRec*>(scratch);
     const int per_max = (max_n + 31) / 32;
-    dim3 grid((max_n + kTileM - 1) / kTileM, 32);
-    if (per_max <= 128) launch_filter<128, false>(grid, q, max_n, t, max_n, per_max, rec, nullptr, s, cnt_q, cnt_t);
-    else launch_filter<256, false>(grid, q, max_n, t, max_n, per_max, rec, nullptr, s, cnt_q, cnt_t);
+    if (per_max <= 256) {
+        launch_resident<false>(q, max_n, t, max_n, per_max, rec, nullptr, s, cnt_q, cnt_t);
+    } else {
+        dim3 grid((max_n + kTileM - 1) / kTileM, 32);
+        launch_filter<256, false>(grid, q, max_n, t, max_n, per_max, rec, nullptr, s, cnt_q, cnt_t);
+    }
     match_rerank_kernel<<<(max_n + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, max_n, t, max_n, per_max, rec, out, cnt_q, cnt_t);
     return 0;
 }
