@@ -286,7 +286,20 @@ constexpr int kResQ = 256;        // queries per CTA
 // fp16), so the accumulator is -2 a.b and a distance is one FADD with the precomputed |b|^2; |a|^2 is
 // constant per thread and only enters the threshold. The next chunk's train tile streams in with cp.async
 // while the current one is scanned.
-template <bool DBG>
+#define TMEM_LD32(v, addr)                                                                                     \
+    asm volatile(                                                                                              \
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "                                                              \
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "                              \
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"              \
+        : "=r"((v)[0]), "=r"((v)[1]), "=r"((v)[2]), "=r"((v)[3]), "=r"((v)[4]), "=r"((v)[5]), "=r"((v)[6]), "=r"((v)[7]),          \
+          "=r"((v)[8]), "=r"((v)[9]), "=r"((v)[10]), "=r"((v)[11]), "=r"((v)[12]), "=r"((v)[13]), "=r"((v)[14]), "=r"((v)[15]),    \
+          "=r"((v)[16]), "=r"((v)[17]), "=r"((v)[18]), "=r"((v)[19]), "=r"((v)[20]), "=r"((v)[21]), "=r"((v)[22]), "=r"((v)[23]),  \
+          "=r"((v)[24]), "=r"((v)[25]), "=r"((v)[26]), "=r"((v)[27]), "=r"((v)[28]), "=r"((v)[29]), "=r"((v)[30]), "=r"((v)[31])   \
+        : "r"(addr))
+
+// NB > 0: the chunk tile has exactly NB 32-column blocks (TR = 32*NB <= 160) and a thread keeps all its
+// distances in registers between the two passes (one TMEM read). NB == 0: any TR, TMEM is read twice.
+template <bool DBG, int NB>
 __global__ void __launch_bounds__(kResThreads)
 match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per, int TR, int cpc,
                              CandRec* __restrict__ rec, float* __restrict__ dbg, const float* __restrict__ nrm_q,
@@ -351,14 +364,23 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
         const int rows = min(kResQ, nq - q0);
         const int r8 = lane & 7, k4 = lane >> 3;
         const __half2 m2 = __floats2half2_rn(-2.f, -2.f);
-        for (int u = warp; u < kResQ / 2; u += kResThreads / 32) {
-            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;  // row 0..255
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if (row < rows) v = __ldg(reinterpret_cast<const uint4*>(des + (size_t)(q0 + row) * 128) + kc);
-            __half2* h = reinterpret_cast<__half2*>(&v);
+        constexpr int kSteps = kResQ / 2 / (kResThreads / 32);  // 16 sixteen-byte pieces per thread, all loads in flight at once
+        uint4 v[kSteps];
 #pragma unroll
-            for (int i = 0; i < 4; i++) h[i] = __hmul2(h[i], m2);
-            *reinterpret_cast<uint4*>(sQ + (row >> 7) * kTileBytes + kc * kKcStride + (row & 127) * 16) = v;
+        for (int i = 0; i < kSteps; i++) {
+            const int u = warp + i * (kResThreads / 32);
+            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;  // row 0..255
+            v[i] = make_uint4(0u, 0u, 0u, 0u);
+            if (row < rows) v[i] = __ldg(reinterpret_cast<const uint4*>(des + (size_t)(q0 + row) * 128) + kc);
+        }
+#pragma unroll
+        for (int i = 0; i < kSteps; i++) {
+            const int u = warp + i * (kResThreads / 32);
+            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
+            __half2* h = reinterpret_cast<__half2*>(&v[i]);
+#pragma unroll
+            for (int j = 0; j < 4; j++) h[j] = __hmul2(h[j], m2);
+            *reinterpret_cast<uint4*>(sQ + (row >> 7) * kTileBytes + kc * kKcStride + (row & 127) * 16) = v[i];
         }
     }
     const float na = q < nq ? __ldg(nrm_q + q) : 0.f;
@@ -402,36 +424,63 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
             phase ^= 1;
             asm volatile("tcgen05.fence::after_thread_sync;");
             const float* nbp = s_nb + b * TRP;
-            float a1 = INFINITY, a2 = INFINITY, thr = 0.f;
             if (half_id == 0 || two_tiles) {
-                for (int pass = 0; pass < 2; pass++) {
-                    for (int cb = 0; cb * 32 < rows; cb++) {
-                        uint32_t v[32];
-                        asm volatile(
-                            "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-                            "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-                            "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-                            : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
-                              "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]),
-                              "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]),
-                              "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-                            : "r"(taddr + cb * 32));
-                        asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                        const float4* nb4 = reinterpret_cast<const float4*>(nbp + cb * 32);
-                        if (pass == 0) {
+                // top-2 of a value stream with four independent (min, 2nd min) pairs: no serial dependency chain
+                float m1[4] = {INFINITY, INFINITY, INFINITY, INFINITY}, m2[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+                auto top2 = [&](int k, float dd) {
+                    m2[k] = fminf(m2[k], fmaxf(m1[k], dd));
+                    m1[k] = fminf(m1[k], dd);
+                };
+                auto merged_thr = [&]() {
+                    // {a1,a2} u {b1,b2}: min = min(a1,b1), 2nd = min(max(a1,b1), min(a2,b2))
+                    const float x2 = fminf(fmaxf(m1[0], m1[1]), fminf(m2[0], m2[1])), x1 = fminf(m1[0], m1[1]);
+                    const float y2 = fminf(fmaxf(m1[2], m1[3]), fminf(m2[2], m2[3])), y1 = fminf(m1[2], m1[3]);
+                    const float a2 = fminf(fmaxf(x1, y1), fminf(x2, y2));
+                    // survivors: D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings), + fp32 accumulation
+                    // slack; compared in the |b|^2 - 2 a.b domain, i.e. minus |a|^2
+                    const float d2nd = fmaxf(__fadd_rn(a2, na), 0.f);
+                    return __fsub_rn(__fmaf_rn(d2nd, 1.004f, __fmaf_rn(4e-5f, __fadd_rn(na, __int_as_float(s_nbmax[b])), 1e-3f)), na);
+                };
+                if constexpr (NB > 0) {
+                    uint32_t v[NB * 32];
 #pragma unroll
-                            for (int j4 = 0; j4 < 8; j4++) {
-                                const float4 nb = nb4[j4];
-                                const float nbv[4] = {nb.x, nb.y, nb.z, nb.w};
+                    for (int cb = 0; cb < NB; cb++) TMEM_LD32(v + cb * 32, taddr + cb * 32);
+                    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                    const float4* nb4 = reinterpret_cast<const float4*>(nbp);
 #pragma unroll
-                                for (int j = 0; j < 4; j++) {
-                                    const float dd = __fadd_rn(__uint_as_float(v[j4 * 4 + j]), nbv[j]);  // |b|^2 - 2 a.b (+inf: padding)
-                                    a2 = fminf(a2, fmaxf(a1, dd));  // branch-free running top-2
-                                    a1 = fminf(a1, dd);
-                                    if (DBG) { if (q < nq && cb * 32 + j4 * 4 + j < rows) dbg[(size_t)q * nt + t_begin + cb * 32 + j4 * 4 + j] = __fadd_rn(na, dd); }
-                                }
-                            }
-                        } else {
+                    for (int i4 = 0; i4 < NB * 8; i4++) {
+                        const float4 nb = nb4[i4];
+                        const float nbv[4] = {nb.x, nb.y, nb.z, nb.w};
+#pragma unroll
+                        for (int j = 0; j < 4; j++) {
+                            const float dd = __fadd_rn(__uint_as_float(v[i4 * 4 + j]), nbv[j]);  // |b|^2 - 2 a.b (+inf: padding)
+                            v[i4 * 4 + j] = __float_as_uint(dd);
+                            top2(j, dd);
+                            if (DBG) { if (q < nq && i4 * 4 + j < rows) dbg[(size_t)q * nt + t_begin + i4 * 4 + j] = __fadd_rn(na, dd); }
+                        }
+                    }
+                    const float thr = merged_thr();
+                    // survivors are rare: branch-free bit mask per 32 columns, then walk the set bits
+#pragma unroll
+                    for (int cb = 0; cb < NB; cb++) {
+                        unsigned mask = 0u;
+#pragma unroll
+                        for (int i = 0; i < 32; i++) mask |= (__uint_as_float(v[cb * 32 + i]) <= thr ? 1u : 0u) << i;
+                        while (mask) {
+                            const int i = __ffs(mask) - 1;
+                            mask &= mask - 1;
+                            if (cn < kCand) s_cand[cn * kResThreads + tid] = (unsigned char)(cb * 32 + i);
+                            cn++;
+                        }
+                    }
+                } else {
+                    float thr = 0.f;
+                    for (int pass = 0; pass < 2; pass++) {
+                        for (int cb = 0; cb * 32 < rows; cb++) {
+                            uint32_t v[32];
+                            TMEM_LD32(v, taddr + cb * 32);
+                            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                            const float4* nb4 = reinterpret_cast<const float4*>(nbp + cb * 32);
 #pragma unroll
                             for (int j4 = 0; j4 < 8; j4++) {
                                 const float4 nb = nb4[j4];
@@ -439,18 +488,18 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
 #pragma unroll
                                 for (int j = 0; j < 4; j++) {
                                     const float dd = __fadd_rn(__uint_as_float(v[j4 * 4 + j]), nbv[j]);
-                                    if (dd <= thr) {  // survivors are rare: one predicated shared-memory store each
+                                    if (pass == 0) {
+                                        top2(j, dd);
+                                        if (DBG) { if (q < nq && cb * 32 + j4 * 4 + j < rows) dbg[(size_t)q * nt + t_begin + cb * 32 + j4 * 4 + j] = __fadd_rn(na, dd); }
+                                    } else if (dd <= thr) {
                                         if (cn < kCand) s_cand[cn * kResThreads + tid] = (unsigned char)(cb * 32 + j4 * 4 + j);
                                         cn++;
                                     }
                                 }
                             }
                         }
+                        thr = merged_thr();
                     }
-                    // survivors: D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings), + fp32 accumulation
-                    // slack; compared in the |b|^2 - 2 a.b domain, i.e. minus |a|^2
-                    const float d2nd = fmaxf(__fadd_rn(a2, na), 0.f);
-                    thr = __fsub_rn(__fmaf_rn(d2nd, 1.004f, __fmaf_rn(4e-5f, __fadd_rn(na, __int_as_float(s_nbmax[b])), 1e-3f)), na);
                 }
             }
         }
@@ -619,6 +668,17 @@ int match_num_launches(int nq, int nt) { return (nq > 0 && nt >= 0) ? ((nt + 31)
 
 namespace {
 // Resident-chunk filter (every chunk of the train set fits one MMA tile): norms, then the filter.
+template <bool DBG, int NB>
+void launch_resident_nb(dim3 grid, size_t smem, const __half* q, int nq, const __half* t, int nt, int per, int TR, int cpc, CandRec* rec,
+                        float* dbg, const float* nrm_q, const float* nrm_t, cudaStream_t s, const int* cnt_q, const int* cnt_t) {
+    static size_t smem_set = 0;
+    if (smem > smem_set) {
+        cudaFuncSetAttribute(match_filter_resident_kernel<DBG, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        smem_set = smem;
+    }
+    match_filter_resident_kernel<DBG, NB><<<grid, kResThreads, smem, s>>>(q, nq, t, nt, per, TR, cpc, rec, dbg, nrm_q, nrm_t, cnt_q, cnt_t);
+}
+
 template <bool DBG>
 void launch_resident(const __half* q, int nq, const __half* t, int nt, int per, CandRec* rec, float* dbg, cudaStream_t s,
                      const int* cnt_q, const int* cnt_t) {
@@ -628,16 +688,20 @@ void launch_resident(const __half* q, int nq, const __half* t, int nt, int per, 
     const int TR = std::max(32, (per + 31) & ~31);
     // at least 116 KB so that one CTA (which owns all 512 TMEM columns) is resident per SM
     const size_t smem = std::max<size_t>(2 * kTileBytes + (size_t)2 * TR * 256 + (size_t)2 * TR * 4 + 64 + kCand * kResThreads, 116 * 1024);
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
-        cudaFuncSetAttribute(match_filter_resident_kernel<DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        smem_set = smem;
-    }
     const int tiles = (nq + kResQ - 1) / kResQ;
     int cpc = 8;  // chunks per CTA: as many as still leave about one CTA per SM
     while (cpc > 1 && tiles * (32 / cpc) < 140) cpc >>= 1;
     dim3 grid(tiles, 32 / cpc);
-    match_filter_resident_kernel<DBG><<<grid, kResThreads, smem, s>>>(q, nq, t, nt, per, TR, cpc, rec, dbg, nrm_q, nrm_t, cnt_q, cnt_t);
+#define LAUNCH_NB(NB) launch_resident_nb<DBG, NB>(grid, smem, q, nq, t, nt, per, TR, cpc, rec, dbg, nrm_q, nrm_t, s, cnt_q, cnt_t)
+    switch (TR / 32) {
+        case 1: LAUNCH_NB(1); break;
+        case 2: LAUNCH_NB(2); break;
+        case 3: LAUNCH_NB(3); break;
+        case 4: LAUNCH_NB(4); break;
+        case 5: LAUNCH_NB(5); break;
+        default: LAUNCH_NB(0); break;
+    }
+#undef LAUNCH_NB
 }
 }  // namespace
 
