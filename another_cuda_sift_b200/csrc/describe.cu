@@ -212,7 +212,7 @@ constexpr int kPrivSlots = 32;  // 2 x 2 spatial neighbours x 8 orientation bins
 // column 0 cover rbin in (-1,1) (truncating modff, quirk Q13), so cell (0,0) is four units of area, the other
 // row-0 / column-0 cells two, the rest one. Warps pull cells from this queue (longest-processing-time order).
 __constant__ signed char kCellOrder[16] = {0, 1, 2, 3, 4, 8, 12, 5, 6, 7, 9, 10, 11, 13, 14, 15};
-constexpr int kDescCtasPerSm = 5;  // persistent CTAs per SM (up to 7 fit): leaves room for the other frames in flight
+constexpr int kDescCtasPerSm = 7;  // persistent CTAs per SM (64 registers x 128 threads: register-limited at 8, shared memory at 7)
 constexpr int kRing = 64;  // per-warp ring of accepted samples (at most 31 pending + 32 appended)
 
 __device__ __forceinline__ float ex2_approx(float x) {
@@ -252,7 +252,7 @@ __device__ __forceinline__ float rsqrt_approx(float x) {  // x must be a normal 
 // The set of samples and every per-sample coordinate (c_rot, r_rot, bins, fractions) are computed exactly
 // as in the reference; magnitude, angle and weight use the MUFU approximations (a few ulp; the result is
 // rounded to fp16).
-__global__ void __launch_bounds__(kDescThreads)
+__global__ void __launch_bounds__(kDescThreads, 7)
 descriptor_kernel(const __grid_constant__ FrameParams fp) {
     // this launch covers octaves [o_begin, o_end); `first` keypoints of lower octaves precede it in the output
     int first = 0;
