@@ -100,7 +100,7 @@ class Detector:
         return True
 
     def _refresh_views(self):
-        """The engine keeps three frames in flight, each with its own result buffers: the public device views
+        """The engine keeps several frames in flight, each with its own result buffers: the public device views
         always point at the latest frame (prev_descriptor at the one before it, in place, no copy)."""
         k, f, d, p = C.c_void_p(), C.c_void_p(), C.c_void_p(), C.c_void_p()
         check(self.lib.b200sift_results(self._h, C.byref(k), C.byref(f), C.byref(d), C.byref(p), None))
@@ -155,7 +155,7 @@ class Detector:
         self._hold(image)
 
     def _hold(self, image):
-        self._keep = (getattr(self, "_keep", None) or [])[-3:] + [image]  # inputs must outlive their asynchronous copies
+        self._keep = (getattr(self, "_keep", None) or [])[-self.frames_in_flight:] + [image]  # inputs must outlive their asynchronous copies
         self._refresh_views()
 
     def synchronize(self) -> int:
@@ -195,15 +195,20 @@ class Detector:
         receives the matches of frame i-1 -> frame i. One synchronisation at the end."""
         import torch
 
-        idx = [torch.empty(self.config.numFeatures, dtype=torch.int32, device="cuda") for _ in range(3)] if match_out is not None else None
+        k = self.frames_in_flight
+        idx = [torch.empty(self.config.numFeatures, dtype=torch.int32, device="cuda") for _ in range(k)] if match_out is not None else None
         for i, f in enumerate(frames):
             self.detectAndComputeAsync(f)
             if match_out is not None:
-                self.matchConsecutiveAsync(idx[i % 3])
+                self.matchConsecutiveAsync(idx[i % k])
                 with torch.cuda.stream(torch.cuda.ExternalStream(self.stream)):  # the latest frame's stream
-                    match_out[i].copy_(idx[i % 3], non_blocking=True)
+                    match_out[i].copy_(idx[i % k], non_blocking=True)
             self.copyResultsAsync(results[i])
         self.synchronize()
+
+    @property
+    def frames_in_flight(self) -> int:
+        return int(self.lib.b200sift_frames_in_flight())
 
     @property
     def stream(self) -> int:
@@ -220,7 +225,7 @@ class Detector:
         return float(ms.value)
 
     def time_frames_pipelined(self, warmup: int, iters: int) -> float:
-        """ms per frame with three frames in flight (every slot replays its graph, round robin)."""
+        """ms per frame with every frame slot in flight (every slot replays its graph, round robin)."""
         ms = C.c_float(0)
         check(self.lib.b200sift_time_frames_pipelined(self._handle(), warmup, iters, C.byref(ms)))
         return float(ms.value)

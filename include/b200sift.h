@@ -81,13 +81,13 @@ B200SIFT_API int b200sift_detect_host_u8_async(b200sift_detector* det, const uin
 /* Waits for the frames enqueued so far; *total = keypoints of the last frame. */
 B200SIFT_API int b200sift_sync(b200sift_detector* det, int* total);
 /* The CUDA stream (cudaStream_t) of the LATEST frame, so callers can order their own work after it. The
- * engine keeps three frames in flight, each on its own stream: fetch this after every detect call. */
+ * engine keeps several frames in flight, each on its own stream: fetch this after every detect call. */
 B200SIFT_API void* b200sift_stream(b200sift_detector* det);
 
 /* Public result members of Detector (interface/Detector.hh:54-62), borrowed device pointers
  * owned by the handle. They refer to the LATEST frame (prev_desc: the frame before it, in place -- the
- * reference copies it, Detector.cu:136-141) and rotate over three internal buffers: fetch them after every
- * detect call; a pointer stays valid until the third detect call after it. kpts = float3[numFeatures]
+ * reference copies it, Detector.cu:136-141) and rotate over the internal frame slots (b200sift_frames_in_flight): fetch them after every
+ * detect call; a pointer stays valid until b200sift_frames_in_flight() - 1 further detect calls. kpts = float3[numFeatures]
  * (x, y, layer), feats = float4[numFeatures] (packed octave, size, |contrast|, angle deg),
  * desc / prev_desc = half[numFeatures*128]. Any out pointer may be NULL. */
 B200SIFT_API int b200sift_results(b200sift_detector* det, const float** kpts, const float** feats,
@@ -109,12 +109,15 @@ B200SIFT_API int b200sift_debug_get_taps(b200sift_detector* det, int which, floa
 /* Runs the frame pipeline only up to and including `last_stage` (1 pyramid, 3 extrema,
  * 4 refine, 5 orientation, 7 all) eagerly, for stage-level parity tests. Blocks. */
 B200SIFT_API int b200sift_debug_run_stages(b200sift_detector* det, const float* img, int rows, int cols, int last_stage);
+/* How many frames the engine keeps in flight (internal slots). Buffers a caller hands to the *_async calls of
+ * consecutive frames (match indices, host result buffers) should rotate over at least this many. */
+B200SIFT_API int b200sift_frames_in_flight(void);
 /* Number of kernel launches (graph kernel nodes) one frame issues. */
 B200SIFT_API int b200sift_launches_per_frame(const b200sift_detector* det);
 /* Average device time (ms) of one frame with the input resident in HBM: `iters` graph launches
  * bracketed by CUDA events on the detector's stream after `warmup` launches. */
 B200SIFT_API int b200sift_time_frames(b200sift_detector* det, int warmup, int iters, float* ms_per_frame);
-/* Same with three frames in flight (one per internal slot, each on its own stream): ms per frame of the
+/* Same with all frame slots in flight (one frame per internal slot, each on its own stream): ms per frame of the
  * pipelined engine, i.e. 1 / throughput. */
 B200SIFT_API int b200sift_time_frames_pipelined(b200sift_detector* det, int warmup, int iters, float* ms_per_frame);
 
@@ -125,7 +128,7 @@ B200SIFT_API int b200sift_time_frames_pipelined(b200sift_detector* det, int warm
  *  - b200sift_copy_results_async: all numFeatures slots of kpts / feats / desc (any may be NULL) and
  *    counts2[0..1] = {this frame's total, previous frame's total} to (pinned) host memory.
  * Both are enqueued on the latest frame's stream and are ordered before the detect call that reuses the
- * buffers they read (three frames are in flight); host frames of later b200sift_detect_host_async calls are
+ * buffers they read (several frames are in flight); host frames of later b200sift_detect_host_async calls are
  * copied on a separate copy stream meanwhile. */
 B200SIFT_API int b200sift_match_consecutive_async(b200sift_detector* det, int* d_out_idx);
 B200SIFT_API int b200sift_copy_results_async(b200sift_detector* det, float* kpts3, float* feats4, uint16_t* desc, int* counts2);

@@ -71,7 +71,7 @@ class Detector {
         return true;
     }
 
-    // The engine keeps three frames in flight, each with its own result buffers: after every detect call the
+    // The engine keeps several frames in flight (b200sift_frames_in_flight), each with its own result buffers: after every detect call the
     // public views point at the latest frame, prev_descriptor at the frame before it (in place, no copy).
     void refresh_views() {
         const float *k = nullptr, *f = nullptr;
