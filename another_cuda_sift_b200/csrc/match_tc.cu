@@ -578,26 +578,54 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
     __syncwarp();
     float mn = 1e6f, mn2 = 1e6f;   // Match.cu:125-129 sentinels (quirk Q16)
     int id = -1, id2 = -1;
-    // survivors, ascending column order inside every chunk; one pair in flight ahead of the one scored
-    __half2 b0 = a0, b1 = a1;
-    if (total > 0) {
-        const __half2* brow = reinterpret_cast<const __half2*>(src + (size_t)s_col[warp][0] * 128);
-        b0 = __ldg(brow + lane); b1 = __ldg(brow + lane + 32);
-    }
-    for (int p = 0; p < total; p++) {
-        const int col = s_col[warp][p];
-        const int ch = s_chunk[warp][p];
-        __half2 n0 = b0, n1 = b1;
-        if (p + 1 < total) {
-            const __half2* brow = reinterpret_cast<const __half2*>(src + (size_t)s_col[warp][p + 1] * 128);
-            n0 = __ldg(brow + lane); n1 = __ldg(brow + lane + 32);
+    // Survivors, ascending column order inside every chunk, FOUR per step: lane 8g+l works on survivor p+g and
+    // plays the reference's lanes l, l+8, l+16, l+24 (half2 l+8k, k = 0..7, of both rows). The reference's
+    // reduction tree (Match.cu:93-111: offsets 16, 8, 4, 2, 1) pairs lane v with v+16, then v+8: those two
+    // levels are local adds here, the last three are xor shuffles inside the 8-lane group, so every sum has
+    // the same operands in the same tree and the score is bit-identical.
+    {
+        const int g = lane >> 3, l = lane & 7;
+        __half2 a8[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a8[k] = arow[l + 8 * k];
+        const __half2 inv = __floats2half2_rn(0.25f, 0.25f);
+        auto fetch = [&](int p, __half2* b8) {
+            const int col = s_col[warp][min(p + g, total - 1)];
+            const __half2* brow = reinterpret_cast<const __half2*>(src + (size_t)col * 128);
+#pragma unroll
+            for (int k = 0; k < 8; k++) b8[k] = __ldg(brow + l + 8 * k);
+        };
+        __half2 b8[8], n8[8];
+        if (total > 0) fetch(0, b8);
+        for (int p = 0; p < total; p += 4) {
+            if (p + 4 < total) fetch(p + 4, n8);
+            float sv[4];  // partial sums of the reference's lanes l, l+8, l+16, l+24
+#pragma unroll
+            for (int v = 0; v < 4; v++) {
+                __half2 d0 = __hmul2(__hsub2(a8[v], b8[v]), inv);          // half2 index l+8v      (reference lane's first)
+                __half2 d1 = __hmul2(__hsub2(a8[v + 4], b8[v + 4]), inv);  // half2 index l+8v+32   (its second)
+                d0 = __hmul2(d0, d0);
+                d1 = __hmul2(d1, d1);
+                const float2 f0 = __half22float2(d0), f1 = __half22float2(d1);
+                sv[v] = __fadd_rn(__fadd_rn(f0.x, f0.y), __fadd_rn(f1.x, f1.y));
+            }
+            float val = __fadd_rn(__fadd_rn(sv[0], sv[2]), __fadd_rn(sv[1], sv[3]));  // offsets 16 then 8
+#pragma unroll
+            for (int off = 4; off > 0; off >>= 1) val = __fadd_rn(val, __shfl_xor_sync(0xffffffffu, val, off));
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const float vj = __shfl_sync(0xffffffffu, val, 8 * j);
+                if (p + j < total) {
+                    const int col = s_col[warp][p + j];
+                    if (lane == s_chunk[warp][p + j]) {
+                        if (vj < mn) { mn2 = mn; id2 = id; mn = vj; id = col; }
+                        else if (vj < mn2) { mn2 = vj; id2 = col; }
+                    }
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < 8; k++) b8[k] = n8[k];
         }
-        const float val = exact_score(a0, a1, b0, b1);
-        if (lane == ch) {
-            if (val < mn) { mn2 = mn; id2 = id; mn = val; id = col; }
-            else if (val < mn2) { mn2 = val; id2 = col; }
-        }
-        b0 = n0; b1 = n1;
     }
     // overflowed chunks: every column of the chunk, exactly as the reference scans them
     unsigned ovf = __ballot_sync(0xffffffffu, overflow);
