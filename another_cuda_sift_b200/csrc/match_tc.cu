@@ -549,7 +549,7 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
         per = (int)ceilf((float)nt / 32.f);
     }
     __shared__ int s_col[kRerankWarps][kListCap];
-    __shared__ unsigned char s_chunk[kRerankWarps][kListCap];
+    __shared__ float s_val[kRerankWarps][kListCap];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = blockIdx.x * kRerankWarps + warp;
     if (q >= nq) return;
@@ -573,7 +573,7 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
         const int c[kCand] = {r0.y, r0.z, r0.w, r1.x, r1.y, r1.z, r1.w};
 #pragma unroll
         for (int i = 0; i < kCand; i++)
-            if (i < mine) { s_col[warp][base + i] = c[i]; s_chunk[warp][base + i] = (unsigned char)lane; }
+            if (i < mine) s_col[warp][base + i] = c[i];
     }
     __syncwarp();
     float mn = 1e6f, mn2 = 1e6f;   // Match.cu:125-129 sentinels (quirk Q16)
@@ -612,19 +612,18 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
             float val = __fadd_rn(__fadd_rn(sv[0], sv[2]), __fadd_rn(sv[1], sv[3]));  // offsets 16 then 8
 #pragma unroll
             for (int off = 4; off > 0; off >>= 1) val = __fadd_rn(val, __shfl_xor_sync(0xffffffffu, val, off));
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const float vj = __shfl_sync(0xffffffffu, val, 8 * j);
-                if (p + j < total) {
-                    const int col = s_col[warp][p + j];
-                    if (lane == s_chunk[warp][p + j]) {
-                        if (vj < mn) { mn2 = mn; id2 = id; mn = vj; id = col; }
-                        else if (vj < mn2) { mn2 = vj; id2 = col; }
-                    }
-                }
-            }
+            if (l == 0 && p + g < total) s_val[warp][p + g] = val;
 #pragma unroll
             for (int k = 0; k < 8; k++) b8[k] = n8[k];
+        }
+        __syncwarp();
+        // lane c replays its own chunk's survivors in list (= ascending column) order, strict '<' as the reference
+        const int base = incl - mine;
+        for (int i = 0; i < mine; i++) {
+            const float v = s_val[warp][base + i];
+            const int col = s_col[warp][base + i];
+            if (v < mn) { mn2 = mn; id2 = id; mn = v; id = col; }
+            else if (v < mn2) { mn2 = v; id2 = col; }
         }
     }
     // overflowed chunks: every column of the chunk, exactly as the reference scans them
