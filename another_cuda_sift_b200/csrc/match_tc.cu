@@ -314,10 +314,10 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
     uint8_t* sQ = smem;                                     // 2 x [16][128][16 B]
     uint8_t* sB = smem + 2 * kTileBytes;                    // 2 x [16][TR][16 B]
     const uint32_t b_bytes = (uint32_t)TR * 256;
-    float* s_nb = reinterpret_cast<float*>(sB + 2 * b_bytes);  // 2 x [TRP]
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_nb + 2 * TRP);
+    float* s_nb = reinterpret_cast<float*>(sB + 2 * b_bytes);  // 3 x [TRP]: |b|^2 of the chunk being scanned, the one in the MMA, the one in flight
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_nb + 3 * TRP);
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 1);
-    int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);      // [2]
+    int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);      // largest |b|^2 over this CTA's chunks (threshold slack)
     unsigned char* s_cand = reinterpret_cast<unsigned char*>(s_tmem + 4);  // [kCand][256]: survivor columns (chunk-relative) of thread tid
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
@@ -336,16 +336,21 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
     }
     if (tid == 0) {
         s_nbmax[0] = 0;
-        s_nbmax[1] = 0;
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar)));
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
     __syncthreads();
-    // train tile of chunk c -> buffer b (cp.async), its norms -> s_nb[b] (+inf for the padding columns)
-    auto fetch = [&](int c, int b) {
+    {   // norms are >= 0: int order == float order
+        float mx = 0.f;
+        for (int t = c_begin * per + tid; t < min(nt, c_end * per); t += kResThreads) mx = fmaxf(mx, __ldg(nrm_t + t));
+        atomicMax(s_nbmax, __float_as_int(mx));
+    }
+    // train tile of chunk c -> buffer (c - c_begin) & 1 (cp.async), its norms -> s_nb[(c - c_begin) % 3]
+    // (+inf for the padding columns)
+    auto fetch = [&](int c) {
         const int t_begin = c * per;
         const int rows = max(0, min(nt, t_begin + per) - t_begin);
-        const uint32_t base = smem_u32(sB) + (uint32_t)b * b_bytes;
+        const uint32_t base = smem_u32(sB) + (uint32_t)((c - c_begin) & 1) * b_bytes;
         const int r8 = lane & 7, k4 = lane >> 3;
         for (int u = warp; u < TR / 2; u += kResThreads / 32) {  // 16-byte pieces: 8 rows x 4 K chunks per warp step
             const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
@@ -353,13 +358,10 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
             cp_async16(base + kc * kc_stride_b + row * 16, src + (valid ? (size_t)(t_begin + row) * 128 + kc * 8 : 0), valid);
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
-        for (int r = tid; r < TRP; r += kResThreads) {
-            const float nb = r < rows ? __ldg(nrm_t + t_begin + r) : INFINITY;
-            s_nb[b * TRP + r] = nb;
-            if (r < rows) atomicMax(s_nbmax + b, __float_as_int(nb));  // norms are >= 0: int order == float order
-        }
+        float* nbw = s_nb + ((c - c_begin) % 3) * TRP;
+        for (int r = tid; r < TRP; r += kResThreads) nbw[r] = r < rows ? __ldg(nrm_t + t_begin + r) : INFINITY;
     };
-    fetch(c_begin, 0);
+    fetch(c_begin);
     {   // query tiles, scaled by -2
         const int rows = min(kResQ, nq - q0);
         const int r8 = lane & 7, k4 = lane >> 3;
@@ -393,87 +395,131 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
     const uint32_t aQ = smem_u32(sQ);
     uint32_t phase = 0;
 
-    for (int c = c_begin; c < c_end; c++) {
-        const int b = (c - c_begin) & 1;
-        const int t_begin = c * per;
-        const int rows = max(0, min(nt, t_begin + per) - t_begin);
+    auto chunk_rows = [&](int c) { return max(0, min(nt, c * per + per) - c * per); };
+    auto issue_mma = [&](int c) {  // one thread: both query tiles x the train tile of chunk c, then commit
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const uint32_t aB = smem_u32(sB) + (uint32_t)((c - c_begin) & 1) * b_bytes;
+        for (int hq = 0; hq < (two_tiles ? 2 : 1); hq++) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) {  // K = 128 = 8 x 16; one instruction consumes 2 K chunks
+                const uint64_t da = umma_desc(aQ + hq * kTileBytes + k * 2 * kKcStride, kKcStride, 128);
+                const uint64_t db = umma_desc(aB + k * 2 * kc_stride_b, kc_stride_b, 128);
+                const uint32_t acc = k > 0 ? 1u : 0u;
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                    "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                    ::"r"(tmem + hq * 256), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+            }
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    };
+    auto store_rec = [&](int c, int cn) {
+        if (q < nq) {
+            int4* dst = reinterpret_cast<int4*>(rec + (size_t)q * 32 + c);
+            int cc[kCand];
+#pragma unroll
+            for (int i = 0; i < kCand; i++) cc[i] = i < cn ? c * per + (int)s_cand[i * kResThreads + tid] : -1;
+            dst[0] = make_int4(min(cn, kCand + 1), cc[0], cc[1], cc[2]);
+            dst[1] = make_int4(cc[3], cc[4], cc[5], cc[6]);
+        }
+    };
+    const float slack = __fmaf_rn(4e-5f, __fadd_rn(na, __int_as_float(s_nbmax[0])), 1e-3f);
+    const bool scans = half_id == 0 || two_tiles;
+    // top-2 of a value stream with four independent (min, 2nd min) pairs: no serial dependency chain
+    float m1[4] = {}, m2[4] = {};
+    auto top2 = [&](int k, float dd) {
+        m2[k] = fminf(m2[k], fmaxf(m1[k], dd));
+        m1[k] = fminf(m1[k], dd);
+    };
+    auto merged_thr = [&]() {
+        // {a1,a2} u {b1,b2}: min = min(a1,b1), 2nd = min(max(a1,b1), min(a2,b2))
+        const float x2 = fminf(fmaxf(m1[0], m1[1]), fminf(m2[0], m2[1])), x1 = fminf(m1[0], m1[1]);
+        const float y2 = fminf(fmaxf(m1[2], m1[3]), fminf(m2[2], m2[3])), y1 = fminf(m1[2], m1[3]);
+        const float a2 = fminf(fmaxf(x1, y1), fminf(x2, y2));
+        // survivors: D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings), + fp32 accumulation slack;
+        // compared in the |b|^2 - 2 a.b domain, i.e. minus |a|^2
+        const float d2nd = fmaxf(__fadd_rn(a2, na), 0.f);
+        return __fsub_rn(__fmaf_rn(d2nd, 1.004f, slack), na);
+    };
+
+    if constexpr (NB > 0) {
+        // The distances of a chunk move from TMEM to registers in one go, so the accumulator is free again
+        // right away: the MMA of chunk c+1 and the cp.async of chunk c+2 run under the scan of chunk c.
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // cp.async / st.shared -> visible to the tensor core
         __syncthreads();
-        if (tid == 0 && rows > 0) {
-            asm volatile("tcgen05.fence::after_thread_sync;");
-            const uint32_t aB = smem_u32(sB) + (uint32_t)b * b_bytes;
-            for (int hq = 0; hq < (two_tiles ? 2 : 1); hq++) {
-#pragma unroll
-                for (int k = 0; k < 8; k++) {  // K = 128 = 8 x 16; one instruction consumes 2 K chunks
-                    const uint64_t da = umma_desc(aQ + hq * kTileBytes + k * 2 * kKcStride, kKcStride, 128);
-                    const uint64_t db = umma_desc(aB + k * 2 * kc_stride_b, kc_stride_b, 128);
-                    const uint32_t acc = k > 0 ? 1u : 0u;
-                    asm volatile(
-                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                        ::"r"(tmem + hq * 256), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
-                }
-            }
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
-        }
-        if (c + 1 < c_end) fetch(c + 1, b ^ 1);  // the other buffer: its MMA (chunk c-1) completed before the last barrier
-        int cn = 0;
-        if (rows > 0) {
-            mbar_wait(bar, phase);
-            phase ^= 1;
-            asm volatile("tcgen05.fence::after_thread_sync;");
-            const float* nbp = s_nb + b * TRP;
-            if (half_id == 0 || two_tiles) {
-                // top-2 of a value stream with four independent (min, 2nd min) pairs: no serial dependency chain
-                float m1[4] = {INFINITY, INFINITY, INFINITY, INFINITY}, m2[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
-                auto top2 = [&](int k, float dd) {
-                    m2[k] = fminf(m2[k], fmaxf(m1[k], dd));
-                    m1[k] = fminf(m1[k], dd);
-                };
-                auto merged_thr = [&]() {
-                    // {a1,a2} u {b1,b2}: min = min(a1,b1), 2nd = min(max(a1,b1), min(a2,b2))
-                    const float x2 = fminf(fmaxf(m1[0], m1[1]), fminf(m2[0], m2[1])), x1 = fminf(m1[0], m1[1]);
-                    const float y2 = fminf(fmaxf(m1[2], m1[3]), fminf(m2[2], m2[3])), y1 = fminf(m1[2], m1[3]);
-                    const float a2 = fminf(fmaxf(x1, y1), fminf(x2, y2));
-                    // survivors: D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings), + fp32 accumulation
-                    // slack; compared in the |b|^2 - 2 a.b domain, i.e. minus |a|^2
-                    const float d2nd = fmaxf(__fadd_rn(a2, na), 0.f);
-                    return __fsub_rn(__fmaf_rn(d2nd, 1.004f, __fmaf_rn(4e-5f, __fadd_rn(na, __int_as_float(s_nbmax[b])), 1e-3f)), na);
-                };
-                if constexpr (NB > 0) {
-                    uint32_t v[NB * 32];
+        if (tid == 0 && chunk_rows(c_begin) > 0) issue_mma(c_begin);
+        if (c_begin + 1 < c_end) fetch(c_begin + 1);
+        for (int c = c_begin; c < c_end; c++) {
+            const int rows = chunk_rows(c);
+            uint32_t v[NB * 32];
+            if (rows > 0) {
+                mbar_wait(bar, phase);
+                phase ^= 1;
+                asm volatile("tcgen05.fence::after_thread_sync;");
+                if (scans) {
 #pragma unroll
                     for (int cb = 0; cb < NB; cb++) TMEM_LD32(v + cb * 32, taddr + cb * 32);
                     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-                    const float4* nb4 = reinterpret_cast<const float4*>(nbp);
+                }
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;");
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+            __syncthreads();  // accumulator drained by everybody, tile c+1 landed
+            if (c + 1 < c_end && tid == 0 && chunk_rows(c + 1) > 0) issue_mma(c + 1);
+            if (c + 2 < c_end) fetch(c + 2);  // tile buffer of chunk c (its MMA is done), norm slot (c+2) % 3
+            int cn = 0;
+            if (rows > 0 && scans) {
 #pragma unroll
-                    for (int i4 = 0; i4 < NB * 8; i4++) {
-                        const float4 nb = nb4[i4];
-                        const float nbv[4] = {nb.x, nb.y, nb.z, nb.w};
+                for (int k = 0; k < 4; k++) { m1[k] = INFINITY; m2[k] = INFINITY; }
+                const float4* nb4 = reinterpret_cast<const float4*>(s_nb + ((c - c_begin) % 3) * TRP);
 #pragma unroll
-                        for (int j = 0; j < 4; j++) {
-                            const float dd = __fadd_rn(__uint_as_float(v[i4 * 4 + j]), nbv[j]);  // |b|^2 - 2 a.b (+inf: padding)
-                            v[i4 * 4 + j] = __float_as_uint(dd);
-                            top2(j, dd);
-                            if (DBG) { if (q < nq && i4 * 4 + j < rows) dbg[(size_t)q * nt + t_begin + i4 * 4 + j] = __fadd_rn(na, dd); }
-                        }
+                for (int i4 = 0; i4 < NB * 8; i4++) {
+                    const float4 nb = nb4[i4];
+                    const float nbv[4] = {nb.x, nb.y, nb.z, nb.w};
+#pragma unroll
+                    for (int j = 0; j < 4; j++) {
+                        const float dd = __fadd_rn(__uint_as_float(v[i4 * 4 + j]), nbv[j]);  // |b|^2 - 2 a.b (+inf: padding)
+                        v[i4 * 4 + j] = __float_as_uint(dd);
+                        top2(j, dd);
+                        if (DBG) { if (q < nq && i4 * 4 + j < rows) dbg[(size_t)q * nt + c * per + i4 * 4 + j] = __fadd_rn(na, dd); }
                     }
-                    const float thr = merged_thr();
-                    // survivors are rare: branch-free bit mask per 32 columns, then walk the set bits
+                }
+                const float thr = merged_thr();
+                // survivors are rare: branch-free bit mask per 32 columns, then walk the set bits
 #pragma unroll
-                    for (int cb = 0; cb < NB; cb++) {
-                        unsigned mask = 0u;
+                for (int cb = 0; cb < NB; cb++) {
+                    unsigned mask = 0u;
 #pragma unroll
-                        for (int i = 0; i < 32; i++) mask |= (__uint_as_float(v[cb * 32 + i]) <= thr ? 1u : 0u) << i;
-                        while (mask) {
-                            const int i = __ffs(mask) - 1;
-                            mask &= mask - 1;
-                            if (cn < kCand) s_cand[cn * kResThreads + tid] = (unsigned char)(cb * 32 + i);
-                            cn++;
-                        }
+                    for (int i = 0; i < 32; i++) mask |= (__uint_as_float(v[cb * 32 + i]) <= thr ? 1u : 0u) << i;
+                    while (mask) {
+                        const int i = __ffs(mask) - 1;
+                        mask &= mask - 1;
+                        if (cn < kCand) s_cand[cn * kResThreads + tid] = (unsigned char)(cb * 32 + i);
+                        cn++;
                     }
-                } else {
+                }
+            }
+            store_rec(c, cn);
+        }
+    } else {
+        for (int c = c_begin; c < c_end; c++) {
+            const int rows = chunk_rows(c);
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // cp.async / st.shared -> visible to the tensor core
+            __syncthreads();
+            if (tid == 0 && rows > 0) issue_mma(c);
+            if (c + 1 < c_end) fetch(c + 1);  // the other tile buffer: its MMA (chunk c-1) completed before the last barrier
+            int cn = 0;
+            if (rows > 0) {
+                mbar_wait(bar, phase);
+                phase ^= 1;
+                asm volatile("tcgen05.fence::after_thread_sync;");
+                const float* nbp = s_nb + ((c - c_begin) % 3) * TRP;
+                if (scans) {
+#pragma unroll
+                    for (int k = 0; k < 4; k++) { m1[k] = INFINITY; m2[k] = INFINITY; }
                     float thr = 0.f;
                     for (int pass = 0; pass < 2; pass++) {
                         for (int cb = 0; cb * 32 < rows; cb++) {
@@ -490,7 +536,7 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
                                     const float dd = __fadd_rn(__uint_as_float(v[j4 * 4 + j]), nbv[j]);
                                     if (pass == 0) {
                                         top2(j, dd);
-                                        if (DBG) { if (q < nq && cb * 32 + j4 * 4 + j < rows) dbg[(size_t)q * nt + t_begin + cb * 32 + j4 * 4 + j] = __fadd_rn(na, dd); }
+                                        if (DBG) { if (q < nq && cb * 32 + j4 * 4 + j < rows) dbg[(size_t)q * nt + c * per + cb * 32 + j4 * 4 + j] = __fadd_rn(na, dd); }
                                     } else if (dd <= thr) {
                                         if (cn < kCand) s_cand[cn * kResThreads + tid] = (unsigned char)(cb * 32 + j4 * 4 + j);
                                         cn++;
@@ -502,19 +548,13 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
                     }
                 }
             }
+            store_rec(c, cn);
+            asm volatile("tcgen05.fence::before_thread_sync;");
+            __syncthreads();  // the accumulator is free again
         }
-        if (q < nq) {
-            int4* dst = reinterpret_cast<int4*>(rec + (size_t)q * 32 + c);
-            int cc[kCand];
-#pragma unroll
-            for (int i = 0; i < kCand; i++) cc[i] = i < cn ? t_begin + (int)s_cand[i * kResThreads + tid] : -1;
-            dst[0] = make_int4(min(cn, kCand + 1), cc[0], cc[1], cc[2]);
-            dst[1] = make_int4(cc[3], cc[4], cc[5], cc[6]);
-        }
-        asm volatile("tcgen05.fence::before_thread_sync;");
-        __syncthreads();  // TMEM and s_nbmax[b] are free again
-        if (tid == 0) s_nbmax[b] = 0;
     }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
     if (warp == 0) {
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
     }
@@ -714,7 +754,7 @@ void launch_resident(const __half* q, int nq, const __half* t, int nt, int per, 
     match_norms_kernel<<<(nq + nt + 7) / 8, 256, 0, s>>>(q, nq, t, nt, nrm_q, nrm_t, cnt_q, cnt_t);
     const int TR = std::max(32, (per + 31) & ~31);
     // at least 116 KB so that one CTA (which owns all 512 TMEM columns) is resident per SM
-    const size_t smem = std::max<size_t>(2 * kTileBytes + (size_t)2 * TR * 256 + (size_t)2 * TR * 4 + 64 + kCand * kResThreads, 116 * 1024);
+    const size_t smem = std::max<size_t>(2 * kTileBytes + (size_t)2 * TR * 256 + (size_t)3 * TR * 4 + 64 + kCand * kResThreads, 116 * 1024);
     const int tiles = (nq + kResQ - 1) / kResQ;
     int cpc = 8;  // chunks per CTA: as many as still leave about one CTA per SM
     while (cpc > 1 && tiles * (32 / cpc) < 140) cpc >>= 1;
