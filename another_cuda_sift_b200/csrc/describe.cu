@@ -12,7 +12,6 @@
 // order independent (deterministic) and lies inside the reference's own run-to-run envelope:
 // orientation bins as 2^-32 in 64 bits (peak selection is a discrete decision, keep it as exact as
 // possible), descriptor bins as 2^-15 in 32 bits (8 votes per sample: one ATOMS.ADD each).
-#include <cstdlib>
 #include "common.cuh"
 
 namespace b200sift {
@@ -428,18 +427,18 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
             tail += min(pend, 32);
             __syncwarp();
         }
-        // ---- flush: lane s owns slot s = (dr*2 + dc)*8 + bin and sums it over the 32 lane-private columns
-        const unsigned row = (unsigned)__cvta_generic_to_shared(&s_priv[warp][lane][0]) + (lane << 2);
+        // ---- flush: lane s owns slot s = (dr*2 + dc)*8 + bin, i.e. row s of the warp's [slot][lane] block: it sums
+        // the row's 32 lane-private entries with eight LDS.128 (skewed by s: conflict-free within a quarter warp,
+        // fixed order) and leaves the row zeroed for the next cell
+        float4* row4 = reinterpret_cast<float4*>(&s_priv[warp][lane][0]);
         float acc = 0.f;
 #pragma unroll
-        for (int k = 0; k < 32; k++) {
-            float v;
-            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(row ^ (unsigned)(k << 2)) : "memory");
-            acc += v;
+        for (int k = 0; k < 8; k++) {
+            float4* p4 = row4 + (k ^ (lane & 7));
+            const float4 v = *p4;
+            *p4 = make_float4(0.f, 0.f, 0.f, 0.f);
+            acc += v.x; acc += v.y; acc += v.z; acc += v.w;
         }
-        __syncwarp();
-#pragma unroll
-        for (int k = 0; k < kPrivSlots; k++) priv[k * 32] = 0.f;
         const int tot = __float2int_rn(acc);
         if (tot != 0) atomicAdd(s_hist + ((R + 1 + (lane >> 4)) * 6 + (C + 1 + ((lane >> 3) & 1))) * 10 + (lane & 7), tot);
         __syncwarp();
@@ -505,8 +504,7 @@ cudaError_t launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cud
     long cap = 0;
     for (int i = o_begin; i < o_end; i++) cap += fp.oct[i].cap;
     long grid = cap < (long)fp.numFeatures ? cap : (long)fp.numFeatures;
-    static const long per_sm = getenv("B200SIFT_DESC_PER_SM") ? atol(getenv("B200SIFT_DESC_PER_SM")) : kDescCtasPerSm;
-    if (grid > 148L * per_sm) grid = 148L * per_sm;
+    if (grid > 148L * kDescCtasPerSm) grid = 148L * kDescCtasPerSm;
     // Lowest stream priority: the descriptor grids would otherwise fill every CTA slot and starve the short
     // latency-bound kernels of the other graph branches (the priority is recorded in the captured node).
     cudaLaunchConfig_t cfg = {};

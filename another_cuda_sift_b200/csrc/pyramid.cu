@@ -8,7 +8,6 @@
 // border in both passes.
 //
 // Roofline: HBM-bound. Algorithmic bytes per layer = 8*w*h (read once, write once).
-#include <cstdlib>
 #include "common.cuh"
 
 namespace b200sift {
@@ -106,10 +105,8 @@ void launch_blur_r(const float* in, int in_pitch, float* out, int out_pitch, int
     // Taller tiles amortise the vertical halo on big images; short tiles spread small images
     // over more SMs.
     const int gx = (w + kTW - 1) / kTW;
-    static const int nb_max = getenv("B200SIFT_BLUR_NB") ? atoi(getenv("B200SIFT_BLUR_NB")) : 4;
-    static const int min_ctas = getenv("B200SIFT_BLUR_MINCTAS") ? atoi(getenv("B200SIFT_BLUR_MINCTAS")) : 2 * 148;
-    int nb = nb_max;
-    while (nb > 1 && gx * ((h + nb * kRB - 1) / (nb * kRB)) < min_ctas) nb >>= 1;
+    int nb = 4;
+    while (nb > 1 && gx * ((h + nb * kRB - 1) / (nb * kRB)) < 2 * 148) nb >>= 1;
     dim3 grid(gx, (h + nb * kRB - 1) / (nb * kRB));
     size_t smem = (size_t)nb * kRB * TWP * sizeof(float);
     blur_vh_kernel<R><<<grid, kBlurThreads, smem, s>>>(in, in_pitch, out, out_pitch, w, h, taps, nb);
