@@ -723,6 +723,76 @@ int b200sift_debug_get_taps(b200sift_detector* d, int which, float* out, int max
     return t.n;
 }
 
+// Stage dump of the latest frame (the role of Detector::setDataGen + perf/PerfData.cu:4-85 in the reference,
+// without msgpack/zlib): raw little-endian arrays + manifest.json under `dir` (which must exist).
+namespace {
+bool write_bin(const std::string& path, const void* p, size_t bytes) {
+    FILE* f = std::fopen(path.c_str(), "wb");
+    if (!f) return false;
+    const bool ok = bytes == 0 || std::fwrite(p, 1, bytes, f) == bytes;
+    return std::fclose(f) == 0 && ok;
+}
+}  // namespace
+
+int b200sift_dump_frame(b200sift_detector* d, const char* dir) {
+    if (!d || !dir) return fail(B200SIFT_EINVAL, "null argument");
+    if (d->frame_no == 0) return fail(B200SIFT_EINVAL, "no frame has been processed");
+    if (int rc = sync_all(d)) return rc;
+    Slot& sl = d->cur();
+    const std::string base = std::string(dir) + "/";
+    const int W = d->cfg.col_width, H = d->cfg.row_width;
+    std::vector<float> buf((size_t)W * H);
+    CU(cudaMemcpy2D(buf.data(), (size_t)W * 4, sl.d_input, (size_t)d->in_pitch * 4, (size_t)W * 4, H, cudaMemcpyDeviceToHost));
+    if (!write_bin(base + "input.f32", buf.data(), buf.size() * 4)) return fail(B200SIFT_EINVAL, "cannot write into the dump directory");
+    std::string man = "{\n \"format\": \"b200sift-stage-dump-1\",\n";
+    man += " \"config\": {\"col_width\": " + std::to_string(W) + ", \"row_width\": " + std::to_string(H) +
+           ", \"numFeatures\": " + std::to_string(d->cfg.numFeatures) + ", \"numOctaveLayers\": " + std::to_string(d->cfg.numOctaveLayers) +
+           ", \"contrastThreshould\": " + std::to_string(d->cfg.contrastThreshould) + ", \"edgeThreshould\": " + std::to_string(d->cfg.edgeThreshould) +
+           ", \"sigma\": " + std::to_string(d->cfg.sigma) + "},\n";
+    man += " \"frame_no\": " + std::to_string(d->frame_no) + ",\n \"octaves\": [\n";
+    for (int o = 0; o < d->nOct; o++) {
+        const OctParams& oc = sl.fp.oct[o];
+        const std::string pre = "oct" + std::to_string(o) + "_";
+        buf.resize((size_t)oc.w * oc.h * kGaussLayers);
+        CU(cudaMemcpy2D(buf.data(), (size_t)oc.w * 4, oc.gauss, (size_t)oc.pitch * 4, (size_t)oc.w * 4, (size_t)oc.h * kGaussLayers,
+                        cudaMemcpyDeviceToHost));
+        bool ok = write_bin(base + pre + "gauss.f32", buf.data(), buf.size() * 4);
+        int c[4] = {0, 0, 0, 0};
+        CU(cudaMemcpy(c, oc.counts, sizeof(c), cudaMemcpyDeviceToHost));
+        const int P = std::min(c[0], oc.cap), T = std::min(c[2], oc.cap);
+        std::vector<float> k((size_t)oc.cap * 4);
+        // refine works in place on the raw-extrema list: [0, P) holds refined values (Q10), mask decides survival
+        CU(cudaMemcpy(k.data(), oc.cand, (size_t)P * sizeof(float3), cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + pre + "cand.f32x3", k.data(), (size_t)P * sizeof(float3));
+        CU(cudaMemcpy(k.data(), oc.candF, (size_t)P * sizeof(float4), cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + pre + "candF.f32x4", k.data(), (size_t)P * sizeof(float4));
+        CU(cudaMemcpy(k.data(), oc.coll, (size_t)T * sizeof(float3), cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + pre + "coll.f32x3", k.data(), (size_t)T * sizeof(float3));
+        CU(cudaMemcpy(k.data(), oc.collF, (size_t)T * sizeof(float4), cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + pre + "collF.f32x4", k.data(), (size_t)T * sizeof(float4));
+        if (!ok) return fail(B200SIFT_EINVAL, "cannot write into the dump directory");
+        man += "  {\"w\": " + std::to_string(oc.w) + ", \"h\": " + std::to_string(oc.h) + ", \"cap\": " + std::to_string(oc.cap) +
+               ", \"raw_extrema\": " + std::to_string(c[0]) + ", \"refined\": " + std::to_string(c[1]) + ", \"oriented\": " + std::to_string(c[2]) +
+               "}" + (o + 1 < d->nOct ? ",\n" : "\n");
+    }
+    int total = 0;
+    if (d->have_frame) {
+        if (int rc = b200sift_sync(d, &total)) return rc;
+        std::vector<float> k((size_t)total * 4);
+        std::vector<uint16_t> ds((size_t)total * 128);
+        CU(cudaMemcpy(k.data(), sl.fp.out_kpts, (size_t)total * sizeof(float3), cudaMemcpyDeviceToHost));
+        bool ok = write_bin(base + "final_kpts.f32x3", k.data(), (size_t)total * sizeof(float3));
+        CU(cudaMemcpy(k.data(), sl.fp.out_feats, (size_t)total * sizeof(float4), cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + "final_features.f32x4", k.data(), (size_t)total * sizeof(float4));
+        CU(cudaMemcpy(ds.data(), sl.fp.out_desc, ds.size() * 2, cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + "final_descriptors.f16x128", ds.data(), ds.size() * 2);
+        if (!ok) return fail(B200SIFT_EINVAL, "cannot write into the dump directory");
+    }
+    man += " ],\n \"total_size\": " + std::to_string(total) + "\n}\n";
+    if (!write_bin(base + "manifest.json", man.data(), man.size())) return fail(B200SIFT_EINVAL, "cannot write into the dump directory");
+    return 0;
+}
+
 // Runs the pipeline up to `last_stage` eagerly (no graph) in the next slot, which becomes the latest frame.
 int b200sift_debug_run_stages(b200sift_detector* d, const float* img, int rows, int cols, int last_stage) {
     if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
@@ -919,25 +989,61 @@ int b200sift_match_device(const uint16_t* d_query, int nq, const uint16_t* d_tra
     return 0;
 }
 
+// Host-buffer variant (the blocking call sift_cuda::matchBruteForce makes for host data): per-device staging
+// buffers (device + pinned host) grow on demand and are kept, so a call costs two H2D copies, the matcher and one
+// D2H copy, no allocation. Calls are serialised per process (the reference's matcher is not thread-safe either).
+namespace {
+struct MatchStage {
+    uint16_t *dq = nullptr, *dt = nullptr, *hq = nullptr, *ht = nullptr;
+    int *dout = nullptr, *hout = nullptr;
+    size_t cq = 0, ct = 0;
+    cudaStream_t s = nullptr;
+};
+std::mutex g_stage_mu;
+MatchStage g_stage[64];
+
+int grow_stage(uint16_t** d, uint16_t** h, size_t* cap, size_t rows, int** dout, int** hout) {
+    if (*cap >= rows) return 0;
+    const size_t n = std::max<size_t>(rows + rows / 2, 256);
+    if (*d) { CU(cudaFree(*d)); *d = nullptr; }
+    if (*h) { CU(cudaFreeHost(*h)); *h = nullptr; }
+    *cap = 0;
+    CU(cudaMalloc(d, n * 256));
+    CU(cudaMallocHost(h, n * 256));
+    if (dout) {
+        if (*dout) { CU(cudaFree(*dout)); *dout = nullptr; }
+        if (*hout) { CU(cudaFreeHost(*hout)); *hout = nullptr; }
+        CU(cudaMalloc(dout, n * sizeof(int)));
+        CU(cudaMallocHost(hout, n * sizeof(int)));
+    }
+    *cap = n;
+    return 0;
+}
+}  // namespace
+
 int b200sift_match_host(const uint16_t* query, int nq, const uint16_t* train, int nt, int* out_idx) {
     if (nq < 0 || nt < 0 || (nq > 0 && (!query || !out_idx)) || (nt > 0 && !train)) return fail(B200SIFT_EINVAL, "bad argument");
     if (nq == 0) return 0;
-    uint16_t *dq = nullptr, *dt = nullptr;
-    int* dout = nullptr;
-    CU(cudaMalloc(&dq, (size_t)nq * 256));
-    CU(cudaMalloc(&dt, std::max<size_t>((size_t)nt * 256, 16)));
-    CU(cudaMalloc(&dout, (size_t)nq * sizeof(int)));
-    CU(cudaMemcpy(dq, query, (size_t)nq * 256, cudaMemcpyHostToDevice));
-    if (nt) CU(cudaMemcpy(dt, train, (size_t)nt * 256, cudaMemcpyHostToDevice));
-    int rc = b200sift_match_device(dq, nq, dt, nt, dout, nullptr);
-    if (!rc) {
-        cudaError_t e = cudaMemcpy(out_idx, dout, (size_t)nq * sizeof(int), cudaMemcpyDeviceToHost);
-        if (e != cudaSuccess) rc = fail(B200SIFT_ECUDA, "%s", cudaGetErrorString(e));
+    int dev = 0;
+    CU(cudaGetDevice(&dev));
+    if (dev < 0 || dev >= 64) return fail(B200SIFT_EINVAL, "device index out of range");
+    std::lock_guard<std::mutex> lk(g_stage_mu);
+    MatchStage& st = g_stage[dev];
+    if (!st.s) CU(cudaStreamCreateWithFlags(&st.s, cudaStreamNonBlocking));
+    if (int rc = grow_stage(&st.dq, &st.hq, &st.cq, (size_t)nq, &st.dout, &st.hout)) return rc;
+    if (int rc = grow_stage(&st.dt, &st.ht, &st.ct, std::max<size_t>((size_t)nt, 1), nullptr, nullptr)) return rc;
+    // pageable -> pinned on the host, then asynchronous copies: the query copy overlaps the staging of the train set
+    std::memcpy(st.hq, query, (size_t)nq * 256);
+    CU(cudaMemcpyAsync(st.dq, st.hq, (size_t)nq * 256, cudaMemcpyHostToDevice, st.s));
+    if (nt) {
+        std::memcpy(st.ht, train, (size_t)nt * 256);
+        CU(cudaMemcpyAsync(st.dt, st.ht, (size_t)nt * 256, cudaMemcpyHostToDevice, st.s));
     }
-    cudaFree(dq);
-    cudaFree(dt);
-    cudaFree(dout);
-    return rc;
+    if (int rc = b200sift_match_device(st.dq, nq, st.dt, nt, st.dout, st.s)) return rc;
+    CU(cudaMemcpyAsync(st.hout, st.dout, (size_t)nq * sizeof(int), cudaMemcpyDeviceToHost, st.s));
+    CU(cudaStreamSynchronize(st.s));
+    std::memcpy(out_idx, st.hout, (size_t)nq * sizeof(int));
+    return 0;
 }
 
 int b200sift_match_launches(int nq, int nt) { return match_num_launches(nq, nt); }

@@ -78,6 +78,7 @@ class Detector:
         self.final_features = np.zeros((n, 4), np.float32)
         self.descriptors = np.zeros((n, 128), np.float16)
         self.device_kpts = self.device_features = self.device_descriptor = self.prev_descriptor = None
+        self._dump_dir = None
 
     # -- lifecycle
     def gpuWarmUpAndAllocate(self) -> bool:
@@ -132,6 +133,20 @@ class Detector:
         total_size, like the reference (which synchronises six times inside this call)."""
         self.detectAndComputeAsync(image)
         self.synchronize()
+        if self._dump_dir:
+            self.dumpFrame(self._dump_dir)
+
+    def setDataGen(self, path: str) -> None:
+        """Detector.hh:48 / Detector.cu:145-229: once set, every blocking detectAndCompute writes the frame's
+        intermediate stages under `path` (raw arrays + manifest.json instead of the reference's msgpack+zlib;
+        tools/stage_replay.py is the counterpart of the reference's tool/perf.cu)."""
+        self._dump_dir = path or None
+
+    def dumpFrame(self, path: str) -> None:
+        import os
+
+        os.makedirs(path, exist_ok=True)
+        check(self.lib.b200sift_dump_frame(self._handle(), os.fsencode(path)))
 
     def detectAndComputeAsync(self, image) -> None:
         h = self._handle()

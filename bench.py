@@ -452,6 +452,13 @@ def main():
         "kernel_ms_per_frame": {k: round(v["ms"], 5) for k, v in prof.items()},
         "graph_cumulative_ms": {k: round(v, 5) for k, v in ex["stages"].items()},
     }
+    if not args.quick:
+        # second half of BASELINE.json's metric: latency of the 2000 x 2000 x 128 ratio-test match (seeded synthetic
+        # descriptor sets, device-resident, median of per-call CUDA-event times) + its tensor roofline
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        from bench_match import match_latency
+
+        line["match_2k2k"] = match_latency(2000, iters=200)
     if world == 1 and not args.no_cpu_baseline and not args.quick:
         line["cpu_baseline"] = cpu_port_baseline(r["frames"])
         line["opencv_cpu"] = opencv_baseline(r["frames"])

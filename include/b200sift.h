@@ -106,6 +106,13 @@ B200SIFT_API int b200sift_debug_get_kpt_buffer(b200sift_detector* det, int o, in
 B200SIFT_API int b200sift_debug_get_counts(b200sift_detector* det, int o, int* counts);
 /* Host-generated Gaussian taps: which = -1 initial blur, 0..5 layer taps. Returns tap count. */
 B200SIFT_API int b200sift_debug_get_taps(b200sift_detector* det, int which, float* out, int max_elems);
+/* Stage dump of the latest frame: what Detector::setDataGen(path) makes the reference write after every
+ * detectAndCompute (Detector.cu:145-229, perf/PerfData.cu:4-85), as raw little-endian arrays instead of
+ * msgpack+zlib. Writes into the existing directory `dir`: input.f32, oct{o}_gauss.f32 (6 x h x w),
+ * oct{o}_cand.f32x3 / candF.f32x4 (refined-in-place raw extrema, P entries), oct{o}_coll.f32x3 / collF.f32x4
+ * (oriented keypoints, T entries), final_kpts / final_features / final_descriptors and manifest.json
+ * (config, octave dims, counts). tools/stage_replay.py re-runs the stages on input.f32 and compares. Blocks. */
+B200SIFT_API int b200sift_dump_frame(b200sift_detector* det, const char* dir);
 /* Runs the frame pipeline only up to and including `last_stage` (1 pyramid, 3 extrema,
  * 4 refine, 5 orientation, 7 all) eagerly, for stage-level parity tests. Blocks. */
 B200SIFT_API int b200sift_debug_run_stages(b200sift_detector* det, const float* img, int rows, int cols, int last_stage);

@@ -8,7 +8,7 @@
 //  * device result members are sift_cuda::DeviceView<T> (borrowed, owned by the engine) instead of
 //    thrust::device_vector<T>; thrust::raw_pointer_cast is not needed, use .data();
 //  * detectAndCompute returns with the frame finished (the reference returns with its last kernel in flight);
-//  * setDataGen is accepted and ignored (the msgpack dump is out of scope);
+//  * setDataGen writes raw arrays + manifest.json (b200sift_dump_frame) instead of msgpack+zlib files;
 //  * the reference's public stage methods (createInitialImage ... collectAcrossOctaves) do not exist: the
 //    frame is one CUDA graph.
 #pragma once
@@ -90,6 +90,7 @@ class Detector {
         check(b200sift_detect_host(m_handle, image.m_data->data(), int(image.m_image_size.row), int(image.m_image_size.col),
                                    &total_size), "b200sift_detect_host");
         refresh_views();
+        if (!m_debug_path.empty()) check(b200sift_dump_frame(m_handle, m_debug_path.c_str()), "b200sift_dump_frame");
     }
     // Extension: frame already resident in HBM (pitched fp32), enqueued on stream(); call synchronize().
     void detectAndComputeDevice(const float* d_image, size_t pitch_bytes) {
@@ -112,7 +113,9 @@ class Detector {
                                     reinterpret_cast<uint16_t*>(descriptors.data()), descriptor ? 1 : 0), "b200sift_copy_to_host");
     }
 
-    void setDataGen(const std::string& path) { m_debug_path = path; }  // accepted, no dump is written
+    // Detector.hh:48: once set, every detectAndCompute dumps its intermediate stages into the (existing) directory
+    // `path`: raw arrays + manifest.json (b200sift_dump_frame) instead of the reference's msgpack+zlib files.
+    void setDataGen(const std::string& path) { m_debug_path = path; }
 
     // Results (Detector.hh:54-62)
     DeviceView<float3> device_kpts;       // x, y in full-resolution pixels, z = layer
