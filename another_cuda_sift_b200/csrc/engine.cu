@@ -759,17 +759,19 @@ int b200sift_dump_frame(b200sift_detector* d, const char* dir) {
         bool ok = write_bin(base + pre + "gauss.f32", buf.data(), buf.size() * 4);
         int c[4] = {0, 0, 0, 0};
         CU(cudaMemcpy(c, oc.counts, sizeof(c), cudaMemcpyDeviceToHost));
-        const int P = std::min(c[0], oc.cap), T = std::min(c[2], oc.cap);
+        const int M = std::min(c[1], oc.cap), T = std::min(c[2], oc.cap);
         std::vector<float> k((size_t)oc.cap * 4);
-        // refine works in place on the raw-extrema list: [0, P) holds refined values (Q10), mask decides survival
-        CU(cudaMemcpy(k.data(), oc.cand, (size_t)P * sizeof(float3), cudaMemcpyDeviceToHost));
-        ok = ok && write_bin(base + pre + "cand.f32x3", k.data(), (size_t)P * sizeof(float3));
-        CU(cudaMemcpy(k.data(), oc.candF, (size_t)P * sizeof(float4), cudaMemcpyDeviceToHost));
-        ok = ok && write_bin(base + pre + "candF.f32x4", k.data(), (size_t)P * sizeof(float4));
-        CU(cudaMemcpy(k.data(), oc.coll, (size_t)T * sizeof(float3), cudaMemcpyDeviceToHost));
-        ok = ok && write_bin(base + pre + "coll.f32x3", k.data(), (size_t)T * sizeof(float3));
-        CU(cudaMemcpy(k.data(), oc.collF, (size_t)T * sizeof(float4), cudaMemcpyDeviceToHost));
-        ok = ok && write_bin(base + pre + "collF.f32x4", k.data(), (size_t)T * sizeof(float4));
+        // after a whole frame: coll[0, M) = refined keypoints in raster order (compact_refined), cand[0, T) = the
+        // oriented keypoints in (keypoint, bin) order (compact_oriented); the last entry of each keeps whatever
+        // was in its slot before (quirk Q5)
+        CU(cudaMemcpy(k.data(), oc.coll, (size_t)M * sizeof(float3), cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + pre + "refined_kpts.f32x3", k.data(), (size_t)M * sizeof(float3));
+        CU(cudaMemcpy(k.data(), oc.collF, (size_t)M * sizeof(float4), cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + pre + "refined_features.f32x4", k.data(), (size_t)M * sizeof(float4));
+        CU(cudaMemcpy(k.data(), oc.cand, (size_t)T * sizeof(float3), cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + pre + "oriented_kpts.f32x3", k.data(), (size_t)T * sizeof(float3));
+        CU(cudaMemcpy(k.data(), oc.candF, (size_t)T * sizeof(float4), cudaMemcpyDeviceToHost));
+        ok = ok && write_bin(base + pre + "oriented_features.f32x4", k.data(), (size_t)T * sizeof(float4));
         if (!ok) return fail(B200SIFT_EINVAL, "cannot write into the dump directory");
         man += "  {\"w\": " + std::to_string(oc.w) + ", \"h\": " + std::to_string(oc.h) + ", \"cap\": " + std::to_string(oc.cap) +
                ", \"raw_extrema\": " + std::to_string(c[0]) + ", \"refined\": " + std::to_string(c[1]) + ", \"oriented\": " + std::to_string(c[2]) +

@@ -109,8 +109,9 @@ B200SIFT_API int b200sift_debug_get_taps(b200sift_detector* det, int which, floa
 /* Stage dump of the latest frame: what Detector::setDataGen(path) makes the reference write after every
  * detectAndCompute (Detector.cu:145-229, perf/PerfData.cu:4-85), as raw little-endian arrays instead of
  * msgpack+zlib. Writes into the existing directory `dir`: input.f32, oct{o}_gauss.f32 (6 x h x w),
- * oct{o}_cand.f32x3 / candF.f32x4 (refined-in-place raw extrema, P entries), oct{o}_coll.f32x3 / collF.f32x4
- * (oriented keypoints, T entries), final_kpts / final_features / final_descriptors and manifest.json
+ * oct{o}_refined_kpts.f32x3 / refined_features.f32x4 (M refined keypoints, raster order),
+ * oct{o}_oriented_kpts.f32x3 / oriented_features.f32x4 (T oriented keypoints, (keypoint, bin) order),
+ * final_kpts.f32x3 / final_features.f32x4 / final_descriptors.f16x128 and manifest.json
  * (config, octave dims, counts). tools/stage_replay.py re-runs the stages on input.f32 and compares. Blocks. */
 B200SIFT_API int b200sift_dump_frame(b200sift_detector* det, const char* dir);
 /* Runs the frame pipeline only up to and including `last_stage` (1 pyramid, 3 extrema,

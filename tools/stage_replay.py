@@ -46,11 +46,13 @@ def load_dump(path: str) -> dict:
 
     d = {"manifest": man, "input": arr("input.f32", np.float32, (cfg["row_width"], cfg["col_width"])), "oct": []}
     for o, oc in enumerate(man["octaves"]):
-        P, T = min(oc["raw_extrema"], oc["cap"]), min(oc["oriented"], oc["cap"])
+        M, T = min(oc["refined"], oc["cap"]), min(oc["oriented"], oc["cap"])
         d["oct"].append({
             "gauss": arr(f"oct{o}_gauss.f32", np.float32, (6, oc["h"], oc["w"])),
-            "cand": arr(f"oct{o}_cand.f32x3", np.float32, (P, 3)), "candF": arr(f"oct{o}_candF.f32x4", np.float32, (P, 4)),
-            "coll": arr(f"oct{o}_coll.f32x3", np.float32, (T, 3)), "collF": arr(f"oct{o}_collF.f32x4", np.float32, (T, 4))})
+            "refined_kpts": arr(f"oct{o}_refined_kpts.f32x3", np.float32, (M, 3)),
+            "refined_features": arr(f"oct{o}_refined_features.f32x4", np.float32, (M, 4)),
+            "oriented_kpts": arr(f"oct{o}_oriented_kpts.f32x3", np.float32, (T, 3)),
+            "oriented_features": arr(f"oct{o}_oriented_features.f32x4", np.float32, (T, 4))})
     n = man["total_size"]
     if os.path.exists(os.path.join(path, "final_kpts.f32x3")):
         d["final_kpts"] = arr("final_kpts.f32x3", np.float32, (n, 3))
@@ -88,19 +90,18 @@ def replay(path: str, last: str = "descriptor", verbose: bool = True) -> dict:
         elif name == "refine":
             ok = True
             for o, oc in enumerate(octs):
-                c = det.debug_counts(o)
-                P = min(oc["raw_extrema"], oc["cap"])
-                ok &= c["M"] == oc["refined"]
-                # slots of rejected candidates keep whatever the in-place refinement left there: compare all P
-                ok &= same_bits(det.debug_kpt_buffer(o, "cand")[:P], d["oct"][o]["cand"])
-                ok &= same_bits(det.debug_kpt_buffer(o, "candF")[:P], d["oct"][o]["candF"])
+                M = min(oc["refined"], oc["cap"])
+                ok &= det.debug_counts(o)["M"] == oc["refined"]
+                # the engine compacts the refined keypoints into coll[0, M) (the last slot is quirk Q5's stale one)
+                ok &= same_bits(det.debug_kpt_buffer(o, "coll")[:M], d["oct"][o]["refined_kpts"])
+                ok &= same_bits(det.debug_kpt_buffer(o, "collF")[:M], d["oct"][o]["refined_features"])
         elif name == "orientation":
             ok = True
             for o, oc in enumerate(octs):
                 T = min(oc["oriented"], oc["cap"])
                 ok &= det.debug_counts(o)["T"] == oc["oriented"]
-                ok &= same_bits(det.debug_kpt_buffer(o, "coll")[:T], d["oct"][o]["coll"])
-                ok &= same_bits(det.debug_kpt_buffer(o, "collF")[:T], d["oct"][o]["collF"])
+                ok &= same_bits(det.debug_kpt_buffer(o, "cand")[:T], d["oct"][o]["oriented_kpts"])
+                ok &= same_bits(det.debug_kpt_buffer(o, "candF")[:T], d["oct"][o]["oriented_features"])
         else:
             n = d["manifest"]["total_size"]
             ok = det.total_size == n and "final_kpts" in d
