@@ -560,6 +560,216 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
     }
 }
 
+// ---------------------------------------------------------------- streaming filter (per > 256: large train sets)
+// One CTA = 256 queries x ONE column chunk of the reference, streamed as 128-row train tiles, twice:
+//   pass 0  an upper bound of the chunk's second smallest distance per query (branch-free: the 2nd smallest of the
+//           minima of column quads is >= the true 2nd smallest, and equal to it unless both fall into one quad);
+//   pass 1  the same tiles again (MMA recomputed: cheaper than keeping 2 x 256 x per distances anywhere), every
+//           column with D <= thr(bound) is a survivor.
+// Per step the 2 x 128 x 128 accumulators are drained into registers in one go, so the MMA of tile s+1 and the
+// cp.async of tile s+2 run under the scan of tile s; the tensor pipe stays busy and the scan (2.5 - 3 issue
+// slots per distance on 8 warps) hides under it. The query tiles (scaled by -2, exact in fp16) stay in shared
+// memory for the whole chunk; |b|^2 comes precomputed from match_norms_kernel.
+constexpr int kStreamTN = 128;     // train rows per tile = TMEM columns per accumulator
+constexpr size_t kStreamSmem = 2 * kTileBytes + 2 * (size_t)kStreamTN * 256 + 3 * kStreamTN * sizeof(float) + 64 + kCand * kResThreads * sizeof(int);
+
+__global__ void __launch_bounds__(kResThreads, 1)
+match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per,
+                           CandRec* __restrict__ rec, const float* __restrict__ nrm_q, const float* __restrict__ nrm_t) {
+    constexpr int TN = kStreamTN;
+    extern __shared__ __align__(1024) uint8_t smem[];
+    uint8_t* sQ = smem;                                     // 2 x [16][128][16 B]
+    uint8_t* sB = smem + 2 * kTileBytes;                    // 2 x [16][TN][16 B]
+    constexpr uint32_t b_bytes = TN * 256;
+    float* s_nb = reinterpret_cast<float*>(sB + 2 * b_bytes);  // 3 x [TN]: |b|^2 of the tile being scanned, the one in the MMA, the one in flight
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_nb + 3 * TN);
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 1);
+    int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);
+    int* s_cand = reinterpret_cast<int*>(s_tmem + 4);       // [kCand][256]: survivor columns (chunk-relative) of thread tid
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int half_id = warp >> 2;
+    const int q0 = blockIdx.x * kResQ;
+    const int q = q0 + tid;
+    const int c = blockIdx.y;
+    const int t_begin = c * per;
+    const int crow = max(0, min(nt, t_begin + per) - t_begin);   // columns of this chunk
+    if (crow == 0) {  // uniform for the CTA
+        if (q < nq) rec[(size_t)q * 32 + c].n = 0;
+        return;
+    }
+    const int T = (crow + TN - 1) / TN, S = 2 * T;
+    constexpr uint32_t idesc = make_idesc(TN);
+    constexpr uint32_t kc_stride_b = TN * 16;
+    const bool two_tiles = q0 + kTileM < nq;
+
+    if (warp == 0) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(256));
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
+    }
+    if (tid == 0) {
+        s_nbmax[0] = 0;
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar)));
+        asm volatile("fence.mbarrier_init.release.cluster;");
+    }
+    __syncthreads();
+    {   // largest |b|^2 of the chunk (threshold slack); norms are >= 0: int order == float order
+        float mx = 0.f;
+        for (int t = tid; t < crow; t += kResThreads) mx = fmaxf(mx, __ldg(nrm_t + t_begin + t));
+        atomicMax(s_nbmax, __float_as_int(mx));
+    }
+    // step s works on tile s % T: train rows -> buffer s & 1 (cp.async, zero fill past the chunk), norms -> slot s % 3
+    auto fetch = [&](int s) {
+        const int r0 = (s >= T ? s - T : s) * TN;
+        const int rows = min(TN, crow - r0);
+        const uint32_t base = smem_u32(sB) + (uint32_t)(s & 1) * b_bytes;
+        const int r8 = lane & 7, k4 = lane >> 3;
+        const __half* g = src + (size_t)(t_begin + r0) * 128;
+#pragma unroll
+        for (int i = 0; i < TN / 2 / (kResThreads / 32); i++) {  // 16-byte pieces: 8 rows x 4 K chunks per warp step
+            const int u = warp + i * (kResThreads / 32);
+            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
+            const bool valid = row < rows;
+            cp_async16(base + kc * kc_stride_b + row * 16, g + (valid ? (size_t)row * 128 + kc * 8 : 0), valid);
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        if (tid < TN) s_nb[(s % 3) * TN + tid] = tid < rows ? __ldg(nrm_t + t_begin + r0 + tid) : INFINITY;
+    };
+    fetch(0);
+    {   // query tiles, scaled by -2
+        const int rows = min(kResQ, nq - q0);
+        const int r8 = lane & 7, k4 = lane >> 3;
+        const __half2 m2 = __floats2half2_rn(-2.f, -2.f);
+        constexpr int kSteps = kResQ / 2 / (kResThreads / 32);
+        uint4 v[kSteps];
+#pragma unroll
+        for (int i = 0; i < kSteps; i++) {
+            const int u = warp + i * (kResThreads / 32);
+            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
+            v[i] = make_uint4(0u, 0u, 0u, 0u);
+            if (row < rows) v[i] = __ldg(reinterpret_cast<const uint4*>(des + (size_t)(q0 + row) * 128) + kc);
+        }
+#pragma unroll
+        for (int i = 0; i < kSteps; i++) {
+            const int u = warp + i * (kResThreads / 32);
+            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
+            __half2* h = reinterpret_cast<__half2*>(&v[i]);
+#pragma unroll
+            for (int j = 0; j < 4; j++) h[j] = __hmul2(h[j], m2);
+            *reinterpret_cast<uint4*>(sQ + (row >> 7) * kTileBytes + kc * kKcStride + (row & 127) * 16) = v[i];
+        }
+    }
+    const float na = q < nq ? __ldg(nrm_q + q) : 0.f;
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // cp.async / st.shared -> visible to the tensor core
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t tmem = *s_tmem;
+    const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)half_id * TN;
+    const uint32_t bar = smem_u32(s_bar);
+    const uint32_t aQ = smem_u32(sQ);
+    uint32_t phase = 0;
+
+    auto issue_mma = [&](int s) {  // one thread: both query tiles x the train tile of step s, then commit
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        const uint32_t aB = smem_u32(sB) + (uint32_t)(s & 1) * b_bytes;
+        for (int hq = 0; hq < (two_tiles ? 2 : 1); hq++) {
+#pragma unroll
+            for (int k = 0; k < 8; k++) {  // K = 128 = 8 x 16; one instruction consumes 2 K chunks
+                const uint64_t da = umma_desc(aQ + hq * kTileBytes + k * 2 * kKcStride, kKcStride, 128);
+                const uint64_t db = umma_desc(aB + k * 2 * kc_stride_b, kc_stride_b, 128);
+                const uint32_t acc = k > 0 ? 1u : 0u;
+                asm volatile(
+                    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                    "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                    ::"r"(tmem + hq * TN), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+            }
+        }
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    };
+    const float slack = __fmaf_rn(4e-5f, __fadd_rn(na, __int_as_float(s_nbmax[0])), 1e-3f);
+    const bool scans = half_id == 0 || two_tiles;
+    // running (min, 2nd min) over quad minima, two independent pairs
+    float m1[2] = {INFINITY, INFINITY}, m2[2] = {INFINITY, INFINITY};
+    float thr = 0.f;
+    int cn = 0;
+
+    if (tid == 0) issue_mma(0);
+    if (S > 1) fetch(1);
+    for (int s = 0; s < S; s++) {
+        uint32_t v[TN];
+        mbar_wait(bar, phase);
+        phase ^= 1;
+        asm volatile("tcgen05.fence::after_thread_sync;");
+        if (scans) {
+#pragma unroll
+            for (int cb = 0; cb < TN / 32; cb++) TMEM_LD32(v + cb * 32, taddr + cb * 32);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+        }
+        asm volatile("tcgen05.fence::before_thread_sync;");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        __syncthreads();  // accumulators drained by everybody, tile s+1 landed
+        if (s + 1 < S && tid == 0) issue_mma(s + 1);
+        if (s + 2 < S) fetch(s + 2);  // tile buffer of step s (its MMA is done), norm slot (s+2) % 3
+        if (scans) {
+            const float4* nb4 = reinterpret_cast<const float4*>(s_nb + (s % 3) * TN);
+            if (s < T) {
+#pragma unroll
+                for (int i4 = 0; i4 < TN / 4; i4++) {
+                    const float4 nb = nb4[i4];
+                    const float d0 = __fadd_rn(__uint_as_float(v[i4 * 4 + 0]), nb.x), d1 = __fadd_rn(__uint_as_float(v[i4 * 4 + 1]), nb.y);
+                    const float d2 = __fadd_rn(__uint_as_float(v[i4 * 4 + 2]), nb.z), d3 = __fadd_rn(__uint_as_float(v[i4 * 4 + 3]), nb.w);
+                    const float qm = fminf(fminf(d0, d1), fminf(d2, d3));  // +inf on padding columns
+                    m2[i4 & 1] = fminf(m2[i4 & 1], fmaxf(m1[i4 & 1], qm));
+                    m1[i4 & 1] = fminf(m1[i4 & 1], qm);
+                }
+                if (s == T - 1) {
+                    // {a1,a2} u {b1,b2}: 2nd = min(max(a1,b1), min(a2,b2)); survivors: D <= D2nd * (1+d)/(1-d) with
+                    // d = 1.5e-3 (half roundings) + fp32 accumulation slack, compared in the |b|^2 - 2 a.b domain
+                    const float a2 = fminf(fmaxf(m1[0], m1[1]), fminf(m2[0], m2[1]));
+                    const float d2nd = fmaxf(__fadd_rn(a2, na), 0.f);
+                    thr = __fsub_rn(__fmaf_rn(d2nd, 1.004f, slack), na);
+                }
+            } else {
+                const int col0 = (s - T) * TN;
+#pragma unroll
+                for (int cb = 0; cb < TN / 32; cb++) {
+                    unsigned mask = 0u;
+#pragma unroll
+                    for (int i4 = 0; i4 < 8; i4++) {
+                        const float4 nb = nb4[cb * 8 + i4];
+                        mask |= (__fadd_rn(__uint_as_float(v[cb * 32 + i4 * 4 + 0]), nb.x) <= thr ? 1u : 0u) << (i4 * 4 + 0);
+                        mask |= (__fadd_rn(__uint_as_float(v[cb * 32 + i4 * 4 + 1]), nb.y) <= thr ? 1u : 0u) << (i4 * 4 + 1);
+                        mask |= (__fadd_rn(__uint_as_float(v[cb * 32 + i4 * 4 + 2]), nb.z) <= thr ? 1u : 0u) << (i4 * 4 + 2);
+                        mask |= (__fadd_rn(__uint_as_float(v[cb * 32 + i4 * 4 + 3]), nb.w) <= thr ? 1u : 0u) << (i4 * 4 + 3);
+                    }
+                    while (mask) {  // survivors are rare
+                        const int i = __ffs(mask) - 1;
+                        mask &= mask - 1;
+                        if (cn < kCand) s_cand[cn * kResThreads + tid] = col0 + cb * 32 + i;
+                        cn++;
+                    }
+                }
+            }
+        }
+    }
+    if (q < nq) {
+        int4* dst = reinterpret_cast<int4*>(rec + (size_t)q * 32 + c);
+        int cc[kCand];
+#pragma unroll
+        for (int i = 0; i < kCand; i++) cc[i] = i < cn ? t_begin + s_cand[i * kResThreads + tid] : -1;
+        dst[0] = make_int4(min(cn, kCand + 1), cc[0], cc[1], cc[2]);
+        dst[1] = make_int4(cc[3], cc[4], cc[5], cc[6]);
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    if (warp == 0) {
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256));
+    }
+}
+
 // The reference's per-pair score (Match.cu:93-111), warp-cooperative: lane i owns half2 i and i+32 of both
 // rows. The xor butterfly adds the same operand pairs in the same order as the reference's shfl_down tree
 // does for lane 0, and fp32 addition is commutative, so EVERY lane ends up with lane 0's exact value.
@@ -708,7 +918,7 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
 }  // namespace
 
 namespace {
-int g_match_path = 0;  // 0 = tensor-core filter + exact re-rank, 1 = all-CUDA-core exact kernel (match.cu)
+int g_match_path = 0;  // 0 = tensor-core filter + exact re-rank, 1 = all-CUDA-core exact kernel (match.cu), 2 = as 0 with the unpipelined generic filter for large train sets
 constexpr size_t filter_smem(int tn) { return kTileBytes + (size_t)tn * 256 + tn * sizeof(float) + 64 + kCand * kFilterThreads * sizeof(int); }
 
 template <int TN, bool DBG>
@@ -731,7 +941,7 @@ size_t match_scratch_bytes(int nq, int nt) {
     return (size_t)nq * 32 * sizeof(CandRec) + ((size_t)nq + (size_t)nt + 8) * sizeof(float);
 }
 
-int match_num_launches(int nq, int nt) { return (nq > 0 && nt >= 0) ? ((nt + 31) / 32 <= 256 ? 3 : 2) : 0; }
+int match_num_launches(int nq, int nt) { return (nq > 0 && nt >= 0) ? 3 : 0; }  // norms, filter, re-rank
 
 namespace {
 // Resident-chunk filter (every chunk of the train set fits one MMA tile): norms, then the filter.
@@ -782,10 +992,21 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
     if (per <= 256) {
         if (dbg) launch_resident<true>(q, nq, t, nt, per, rec, dbg, s, nullptr, nullptr);
         else launch_resident<false>(q, nq, t, nt, per, rec, dbg, s, nullptr, nullptr);
-    } else {
+    } else if (dbg || g_match_path == 2) {
         dim3 grid((nq + kTileM - 1) / kTileM, 32);
         if (dbg) launch_filter<256, true>(grid, q, nq, t, nt, per, rec, dbg, s);
         else launch_filter<256, false>(grid, q, nq, t, nt, per, rec, dbg, s);
+    } else {
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaFuncSetAttribute(match_filter_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStreamSmem);
+            attr_set = true;
+        }
+        float* nrm_q = reinterpret_cast<float*>(rec + (size_t)nq * 32);
+        float* nrm_t = nrm_q + nq;
+        match_norms_kernel<<<(nq + nt + 7) / 8, 256, 0, s>>>(q, nq, t, nt, nrm_q, nrm_t, nullptr, nullptr);
+        dim3 grid((nq + kResQ - 1) / kResQ, 32);
+        match_filter_stream_kernel<<<grid, kResThreads, kStreamSmem, s>>>(q, nq, t, nt, per, rec, nrm_q, nrm_t);
     }
     match_rerank_kernel<<<(nq + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, nq, t, nt, per, rec, out, nullptr, nullptr);
     return 0;

@@ -271,7 +271,7 @@ def cpu_port_baseline(frames, budget_s: float = 12.0):
         n_done += 1
     dt = time.perf_counter() - t0
     return dict(value=n_done / dt, unit="frames/s", cores=cores, kind="port",
-                sample=f"{n_done} consecutive 1920x1200 frames (detect + match vs previous), {dt:.1f} s, oracle/sift_oracle.cpp")
+                sample=f"{n_done} consecutive {COLS}x{ROWS} frames (detect + match vs previous), {dt:.1f} s, oracle/sift_oracle.cpp")
 
 
 def opencv_baseline(frames, budget_s: float = 10.0):
@@ -368,10 +368,18 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--frames", type=int, default=16, help="frames per step per GPU")
+    ap.add_argument("--size", default="1920x1200", help="frame size WxH: 1920x1200 is BASELINE.json's metric; 752x480 and 1600x900 are its other configs")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--quick", action="store_true", help="profiler runs: skip e2e leg, per-class profile and CPU baselines")
     args = ap.parse_args()
+    global COLS, ROWS, S_PIXELS, METRIC
+    COLS, ROWS = (int(v) for v in args.size.lower().split("x"))
+    if (COLS, ROWS) != (1920, 1200):
+        METRIC = f"detectAndCompute frames/s @{COLS}x{ROWS}"
+        n_oct = int(round(np.log(2.0 * min(COLS, ROWS)) / np.log(2.0) - 2) + 1)          # Detector.hh:27
+        rnd = lambda v: int(np.floor(v + 0.5))                                            # roundf, Detector.cu:83
+        S_PIXELS = sum(rnd(COLS / 2 ** o) * rnd(ROWS / 2 ** o) for o in range(n_oct))
     args.warmup = max(args.warmup, 3)
 
     if args.impl == "reference":
@@ -383,7 +391,7 @@ def main():
             "impl": "reference", "metric": METRIC, "value": r["value"], "unit": "frames/s", "n_gpus": 1,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "1920x1200 detectAndCompute + consecutive-frame matchBruteForce", "frames_per_step_per_gpu": args.frames,
+            "config": {"workload": f"{COLS}x{ROWS} detectAndCompute + consecutive-frame matchBruteForce", "frames_per_step_per_gpu": args.frames,
                        "numFeatures": NUM_FEATURES, "reference": "unmodified reference CUDA build (oracle/_ref) on 1 B200; "
                        "the reference is single-GPU, so the same 1-GPU figure is reported for every N"},
             "e2e": {"value": r["e2e_value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -427,10 +435,11 @@ def main():
         "metric": METRIC, "value": r["value"], "unit": "frames/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "1920x1200 detectAndCompute + consecutive-frame matchBruteForce", "frames_per_step_per_gpu": args.frames,
+        "config": {"workload": f"{COLS}x{ROWS} detectAndCompute + consecutive-frame matchBruteForce", "frames_per_step_per_gpu": args.frames,
                    "global_frames_per_step": args.frames * world, "numFeatures": NUM_FEATURES, "parallelism": f"frames x{world}", "frames_in_flight_per_gpu": r["det"].frames_in_flight,
                    "keypoints_per_frame": round(r["kpts_per_frame"], 1),
-                   "l2": f"device-resident inputs are {args.frames} distinct frames = {args.frames * COLS * ROWS * 4 / 1e6:.0f} MB per step (> 126 MB L2 when >= 14)"},
+                   "l2": f"device-resident inputs are {args.frames} distinct frames = {args.frames * COLS * ROWS * 4 / 1e6:.0f} MB per step; with the six pyramids in flight "
+                         f"({6 * 24 * S_PIXELS / 1e6:.0f} MB) the working set is {'larger' if (args.frames * COLS * ROWS * 4 + 6 * 24 * S_PIXELS) > 126e6 else 'SMALLER'} than the 126 MB L2"},
         "ms_per_frame": r["ms_per_step"] / args.frames,
         "frame_graph_ms": ex["graph_ms"],             # latency of one frame's graphs, nothing else in flight
         "frame_pipelined_ms": ex["pipe_ms"],          # per frame with every frame slot in flight (graphs only)

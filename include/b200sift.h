@@ -175,8 +175,9 @@ B200SIFT_API int b200sift_match_host(const uint16_t* query, int nq, const uint16
 B200SIFT_API int b200sift_match_launches(int nq, int nt);
 
 /* Matcher implementation: 0 (default) = tcgen05 tensor-core filter + exact re-rank (csrc/match_tc.cu),
- * 1 = all-CUDA-core exact kernel (csrc/match.cu), kept as the on-device cross-check. Both are bit-exact
- * with the reference; process-wide setting. */
+ * 1 = all-CUDA-core exact kernel (csrc/match.cu), kept as the on-device cross-check, 2 = as 0 but train sets
+ * larger than 8192 rows go through the first, unpipelined tcgen05 filter (cross-check of the streaming one).
+ * All are bit-exact with the reference; process-wide setting. */
 B200SIFT_API int b200sift_match_set_path(int path);
 /* Test access to the tensor-core stage: d_dist[nq*nt] (device) receives the fp32 squared distances
  * |a|^2 + |b|^2 - 2ab^T the filter ranks by; d_out_idx[nq] the final result. Blocks. */

@@ -23,7 +23,7 @@ def test_2000x2000_vs_golden(path):
     assert np.array_equal(matchBruteForce(q[:300], 300, q[:300], 300), g["self300"])
 
 
-@pytest.fixture(params=[0, 1], ids=["tensor-core", "cuda-core"])
+@pytest.fixture(params=[0, 1, 2], ids=["tensor-core", "cuda-core", "tensor-core-unpipelined"])
 def path(request):
     """Both matcher implementations (csrc/match_tc.cu: tcgen05 filter + exact re-rank; csrc/match.cu: exact
     CUDA-core kernel) must reproduce the reference bit for bit."""
@@ -35,9 +35,10 @@ def path(request):
     lib.b200sift_match_set_path(0)
 
 
-# (200, 5000): one 256-wide TMEM-resident tile per chunk; (150, 9000): streamed tiles, two passes
+# (200, 5000): one 256-wide TMEM-resident tile per chunk; (150, 9000) ... : streamed 128-row tiles, two passes
+# (8193 -> per 257: three tiles, the last one with a single row; 12289 -> per 385: the last chunk is short)
 @pytest.mark.parametrize("nq,nt", [(1, 1), (3, 2), (31, 32), (33, 31), (100, 257), (513, 700), (1, 4000), (700, 5),
-                                   (200, 5000), (150, 9000)])
+                                   (200, 5000), (150, 9000), (300, 8193), (129, 12289), (257, 16500)])
 def test_vs_cpu_oracle(nq, nt, path):
     from another_cuda_sift_b200 import matchBruteForce
     from another_cuda_sift_b200.synth import synth_descriptors
