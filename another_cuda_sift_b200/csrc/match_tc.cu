@@ -20,6 +20,7 @@
 //
 // Roofline: tensor-bound in the limit (2*nq*nt*128 flop); at 2k x 2k it is launch/latency-bound.
 #include <algorithm>
+#include <cuda.h>
 #include "common.cuh"
 
 namespace b200sift {
@@ -269,6 +270,36 @@ match_norms_kernel(const __half* __restrict__ des, int nq, const __half* __restr
 #pragma unroll
     for (int d = 16; d > 0; d >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, d);
     if (lane == 0) (row < nq ? nrm_q[row] : nrm_t[row - nq]) = acc;
+}
+
+// Streaming filter only: the ninth K step of its MMA. Per train row one 16-byte K chunk {h1, h2, h3, 0, 0, 0, 0, 0}
+// with |b|^2 == 2^15*h1 + 2^4*h2 + 2^-6*h3 EXACTLY (three halves cover the 24-bit fp32 mantissa; every residual is
+// an exact fp32 subtraction), so that the MMA itself adds |b|^2: the query side carries {2^15, 2^4, 2^-6, 0...} in
+// the same chunk. Representable while |b|^2 <= 65504 * 2^15 (~2.1e9); the filter falls back to the exact path
+// above that. Laid out per (chunk, 128-row tile) exactly as the tile sits in shared memory -- [2 K chunks][128
+// rows][16 B], the second K chunk zero -- so one 4 KB bulk copy brings it in; rows past the chunk (or past the
+// train set) carry {+inf, 0...}: their distance must lose.
+constexpr float kAugS1 = 32768.f, kAugS2 = 16.f, kAugS3 = 1.f / 64.f;
+__global__ void __launch_bounds__(256)
+match_aug_kernel(const float* __restrict__ nrm_t, int nt, int per, int tiles, uint4* __restrict__ aug) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= 32 * tiles * 128) return;
+    const int c = idx / (tiles * 128), rr = idx - c * (tiles * 128);
+    const int t = c * per + rr;
+    uint4 o = make_uint4(0x7c00u, 0u, 0u, 0u);  // {+inf, 0, ...}
+    if (rr < per && t < nt) {
+        const float nb = __ldg(nrm_t + t);
+        const __half h1 = __float2half_rn(__fmul_rn(nb, 1.f / kAugS1));
+        const float r1 = __fsub_rn(nb, __fmul_rn(__half2float(h1), kAugS1));
+        const __half h2 = __float2half_rn(__fmul_rn(r1, 1.f / kAugS2));
+        const float r2 = __fsub_rn(r1, __fmul_rn(__half2float(h2), kAugS2));
+        const __half h3 = __float2half_rn(__fmul_rn(r2, 1.f / kAugS3));
+        o.x = (uint32_t)__half_as_ushort(h1) | ((uint32_t)__half_as_ushort(h2) << 16);
+        o.y = (uint32_t)__half_as_ushort(h3);
+    }
+    uint4* tile = aug + ((size_t)c * tiles + (rr >> 7)) * 256;
+    tile[rr & 127] = o;
+    tile[128 + (rr & 127)] = make_uint4(0u, 0u, 0u, 0u);
 }
 
 __device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
@@ -565,208 +596,278 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
 //   pass 0  an upper bound of the chunk's second smallest distance per query (branch-free: the 2nd smallest of the
 //           minima of column quads is >= the true 2nd smallest, and equal to it unless both fall into one quad);
 //   pass 1  the same tiles again (MMA recomputed: cheaper than keeping 2 x 256 x per distances anywhere), every
-//           column with D <= thr(bound) is a survivor.
-// Per step the 2 x 128 x 128 accumulators are drained into registers in one go, so the MMA of tile s+1 and the
-// cp.async of tile s+2 run under the scan of tile s; the tensor pipe stays busy and the scan (2.5 - 3 issue
-// slots per distance on 8 warps) hides under it. The query tiles (scaled by -2, exact in fp16) stay in shared
-// memory for the whole chunk; |b|^2 comes precomputed from match_norms_kernel.
-constexpr int kStreamTN = 128;     // train rows per tile = TMEM columns per accumulator
-constexpr size_t kStreamSmem = 2 * kTileBytes + 2 * (size_t)kStreamTN * 256 + 3 * kStreamTN * sizeof(float) + 64 + kCand * kResThreads * sizeof(int);
+//           column with D <= thr(bound) is a survivor; a quad is only opened when its minimum passes.
+// Measured on B200 (tools/probes/tmem_probe.cu, elimination runs and ncu source views of earlier versions of this
+// kernel): with both operands in shared memory a M128 N128 K16 MMA takes ~83 cycles instead of 64 (8 KB of operand
+// reads per instruction saturate the 128 B/cycle shared-memory port), and streaming the train tiles with cp.async
+// bounded every version at 9-10 ms for 100k x 100k whatever the number of warps issuing it (2176 sixteen-byte copies
+// per tile, each holding its address registers until the memory system takes it). So:
+//   * the train tiles come in by TMA (one elected thread, no registers, no issue slots): two 128-row x 64-half boxes
+//     with the 128-byte swizzle (K-major SWIZZLE_128B operand layout) + one 4 KB bulk copy of the |b|^2 K chunk
+//     (match_aug_kernel), all three completing on the tile's mbarrier; four tile buffers, filled two steps ahead;
+//   * the QUERY tiles live in tensor memory (A operand from TMEM, written once per CTA with tcgen05.st: lane =
+//     query row, 32-bit column j = halves 2j, 2j+1, pre-multiplied by -2): an MMA reads only its 4 KB train slice;
+//   * K is 144, not 128: the ninth K step multiplies {2^15, 2^4, 2^-6} (query side) with the three-half split of
+//     |b|^2, so the accumulator IS |b|^2 - 2 a.b and the scan needs no addition and no norm loads;
+//   * 16 scan warps (lane quarter x query half x column half: 64 distances per thread and step, drained from TMEM
+//     into registers in one go) + one warp whose lane 0 issues the TMA loads and the MMAs. The MMA of step s+1 runs
+//     under the scan of step s.
+// TMEM columns: [0, 256) accumulators (query half h at 128 h), [256, 400) query tiles (half h at 256 + 72 h).
+// Tile buffer: [0, 16 KB) K 0..63 and [16, 32 KB) K 64..127, each [128 rows][128 B] swizzled; [32, 36 KB) the |b|^2
+// chunk and a zero chunk, [2][128 rows][16 B] unswizzled.
+constexpr int kStreamTN = 128;                         // train rows per tile = TMEM columns per accumulator
+constexpr uint32_t kStreamPanel = 128 * 128;           // one swizzled K panel: 128 rows x 64 halves
+constexpr uint32_t kStreamTile = 2 * kStreamPanel + 4096;
+constexpr int kStreamBufs = 4;
+constexpr int kStreamScan = 512;                       // 16 scan warps: (lane quarter, query half, column half)
+constexpr int kStreamThreads = kStreamScan + 32;       // + one warp whose lane 0 issues the TMA loads and the MMAs
+constexpr uint32_t kStreamAcol = 256;                  // first TMEM column of the query tiles
+constexpr uint32_t kStreamAcols = 72;                  // 32-bit columns per query tile (144 halves)
+constexpr size_t kStreamSmem = kStreamBufs * (size_t)kStreamTile + 128 + (kCand + 1) * kStreamScan * sizeof(int) + 2 * kStreamScan * sizeof(float);
+constexpr float kAugMaxNorm = 2.0e9f;                  // |b|^2 above this is not representable by the three-half split
 
-__global__ void __launch_bounds__(kResThreads, 1)
-match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per,
-                           CandRec* __restrict__ rec, const float* __restrict__ nrm_q, const float* __restrict__ nrm_t) {
+#define TMEM_ST32(addr, v)                                                                                     \
+    asm volatile(                                                                                              \
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "                                                        \
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "                             \
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"                     \
+        ::"r"(addr), "r"((v)[0]), "r"((v)[1]), "r"((v)[2]), "r"((v)[3]), "r"((v)[4]), "r"((v)[5]), "r"((v)[6]), "r"((v)[7]),        \
+          "r"((v)[8]), "r"((v)[9]), "r"((v)[10]), "r"((v)[11]), "r"((v)[12]), "r"((v)[13]), "r"((v)[14]), "r"((v)[15]),             \
+          "r"((v)[16]), "r"((v)[17]), "r"((v)[18]), "r"((v)[19]), "r"((v)[20]), "r"((v)[21]), "r"((v)[22]), "r"((v)[23]),           \
+          "r"((v)[24]), "r"((v)[25]), "r"((v)[26]), "r"((v)[27]), "r"((v)[28]), "r"((v)[29]), "r"((v)[30]), "r"((v)[31]) : "memory")
+
+// K-major SWIZZLE_128B operand: rows of 128 B, 8-row groups 1024 B apart (SBO); the K step inside the 128-byte
+// swizzle atom is taken by advancing the start address (32 B per 16 halves); tiles are 1024-byte aligned.
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+    uint64_t d = 0;
+    d |= (uint64_t)((saddr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;                    // LBO: unused by swizzled K-major layouts
+    d |= (uint64_t)(1024 >> 4) << 32;          // SBO
+    d |= (uint64_t)1 << 46;                    // descriptor version (Blackwell)
+    d |= (uint64_t)2 << 61;                    // SWIZZLE_128B
+    return d;
+}
+
+__global__ void __launch_bounds__(kStreamThreads, 1)
+match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_constant__ CUtensorMap train_map, int nt, int per,
+                           CandRec* __restrict__ rec, const float* __restrict__ nrm_q, const float* __restrict__ nrm_t,
+                           const uint4* __restrict__ aug) {
     constexpr int TN = kStreamTN;
     extern __shared__ __align__(1024) uint8_t smem[];
-    uint8_t* sQ = smem;                                     // 2 x [16][128][16 B]
-    uint8_t* sB = smem + 2 * kTileBytes;                    // 2 x [16][TN][16 B]
-    constexpr uint32_t b_bytes = TN * 256;
-    float* s_nb = reinterpret_cast<float*>(sB + 2 * b_bytes);  // 3 x [TN]: |b|^2 of the tile being scanned, the one in the MMA, the one in flight
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(s_nb + 3 * TN);
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 1);
+    uint8_t* sB = smem;                                     // 4 tile buffers
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(sB + kStreamBufs * kStreamTile);  // [0] MMA done, [1..4] tile landed
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 8);
     int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);
-    int* s_cand = reinterpret_cast<int*>(s_tmem + 4);       // [kCand][256]: survivor columns (chunk-relative) of thread tid
+    int* s_cand = reinterpret_cast<int*>(s_bar + 16);       // [kCand][512] survivor columns (chunk-relative) of thread tid, then [512] counts
+    int* s_cn = s_cand + kCand * kStreamScan;
+    float* s_pair = reinterpret_cast<float*>(s_cn + kStreamScan);  // [2][512]: (min, 2nd min) of every thread's columns after pass 0
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    const int half_id = warp >> 2;
+    const bool scanner = warp < kStreamScan / 32;
+    const int half_id = (warp >> 2) & 1;                    // which 128-query tile
+    const int col_half = (warp >> 3) & 1;                   // which 64 columns of every 128-column tile
     const int q0 = blockIdx.x * kResQ;
-    const int q = q0 + tid;
+    const int row = half_id * kTileM + (warp & 3) * 32 + lane;  // query row inside the CTA (TMEM lane = row & 127)
+    const int q = q0 + row;
     const int c = blockIdx.y;
     const int t_begin = c * per;
     const int crow = max(0, min(nt, t_begin + per) - t_begin);   // columns of this chunk
     if (crow == 0) {  // uniform for the CTA
-        if (q < nq) rec[(size_t)q * 32 + c].n = 0;
+        if (scanner && col_half == 0 && q < nq) rec[(size_t)q * 32 + c].n = 0;
         return;
     }
-    const int T = (crow + TN - 1) / TN, S = 2 * T;
+    const int T = (crow + TN - 1) / TN;
+    const int tiles = (per + TN - 1) / TN;                  // tiles per chunk in the layout of `aug`
     constexpr uint32_t idesc = make_idesc(TN);
-    constexpr uint32_t kc_stride_b = TN * 16;
     const bool two_tiles = q0 + kTileM < nq;
 
     if (warp == 0) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(256));
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(s_tmem)), "r"(512));
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;");
     }
     if (tid == 0) {
         s_nbmax[0] = 0;
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar)));
+        for (int i = 0; i < 1 + kStreamBufs; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar + i)));
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
-    __syncthreads();
-    {   // largest |b|^2 of the chunk (threshold slack); norms are >= 0: int order == float order
-        float mx = 0.f;
-        for (int t = tid; t < crow; t += kResThreads) mx = fmaxf(mx, __ldg(nrm_t + t_begin + t));
-        atomicMax(s_nbmax, __float_as_int(mx));
-    }
-    // step s works on tile s % T: train rows -> buffer s & 1 (cp.async, zero fill past the chunk), norms -> slot s % 3
-    auto fetch = [&](int s) {
-        const int r0 = (s >= T ? s - T : s) * TN;
-        const int rows = min(TN, crow - r0);
-        const uint32_t base = smem_u32(sB) + (uint32_t)(s & 1) * b_bytes;
-        const int r8 = lane & 7, k4 = lane >> 3;
-        const __half* g = src + (size_t)(t_begin + r0) * 128;
-#pragma unroll
-        for (int i = 0; i < TN / 2 / (kResThreads / 32); i++) {  // 16-byte pieces: 8 rows x 4 K chunks per warp step
-            const int u = warp + i * (kResThreads / 32);
-            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
-            const bool valid = row < rows;
-            cp_async16(base + kc * kc_stride_b + row * 16, g + (valid ? (size_t)row * 128 + kc * 8 : 0), valid);
-        }
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        if (tid < TN) s_nb[(s % 3) * TN + tid] = tid < rows ? __ldg(nrm_t + t_begin + r0 + tid) : INFINITY;
-    };
-    fetch(0);
-    {   // query tiles, scaled by -2
-        const int rows = min(kResQ, nq - q0);
-        const int r8 = lane & 7, k4 = lane >> 3;
-        const __half2 m2 = __floats2half2_rn(-2.f, -2.f);
-        constexpr int kSteps = kResQ / 2 / (kResThreads / 32);
-        uint4 v[kSteps];
-#pragma unroll
-        for (int i = 0; i < kSteps; i++) {
-            const int u = warp + i * (kResThreads / 32);
-            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
-            v[i] = make_uint4(0u, 0u, 0u, 0u);
-            if (row < rows) v[i] = __ldg(reinterpret_cast<const uint4*>(des + (size_t)(q0 + row) * 128) + kc);
-        }
-#pragma unroll
-        for (int i = 0; i < kSteps; i++) {
-            const int u = warp + i * (kResThreads / 32);
-            const int row = (u >> 2) * 8 + r8, kc = (u & 3) * 4 + k4;
-            __half2* h = reinterpret_cast<__half2*>(&v[i]);
-#pragma unroll
-            for (int j = 0; j < 4; j++) h[j] = __hmul2(h[j], m2);
-            *reinterpret_cast<uint4*>(sQ + (row >> 7) * kTileBytes + kc * kKcStride + (row & 127) * 16) = v[i];
-        }
-    }
-    const float na = q < nq ? __ldg(nrm_q + q) : 0.f;
     asm volatile("tcgen05.fence::before_thread_sync;");
-    asm volatile("cp.async.wait_group 0;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // cp.async / st.shared -> visible to the tensor core
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
     const uint32_t tmem = *s_tmem;
-    const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)half_id * TN;
+    if (scanner) {  // largest |b|^2 of the chunk (threshold slack); norms are >= 0: int order == float order
+        float mx = 0.f;
+        for (int t = tid; t < crow; t += kStreamScan) mx = fmaxf(mx, __ldg(nrm_t + t_begin + t));
+        atomicMax(s_nbmax, __float_as_int(mx));
+        // this thread's half of its query row (64 halves, x -2: exact) -> 32 TMEM columns of the row's lane; the
+        // column-half-1 thread appends K chunk 16 = the multipliers of the |b|^2 split and the zero chunk 17
+        uint32_t w[32];
+        if (q < nq) {
+            const uint4* g = reinterpret_cast<const uint4*>(des + (size_t)q * 128 + col_half * 64);
+            const __half2 m2 = __floats2half2_rn(-2.f, -2.f);
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                uint4 x = __ldg(g + i);
+                __half2* h = reinterpret_cast<__half2*>(&x);
+#pragma unroll
+                for (int j = 0; j < 4; j++) h[j] = __hmul2(h[j], m2);
+                w[4 * i] = x.x; w[4 * i + 1] = x.y; w[4 * i + 2] = x.z; w[4 * i + 3] = x.w;
+            }
+        } else {
+#pragma unroll
+            for (int i = 0; i < 32; i++) w[i] = 0u;
+        }
+        const uint32_t arow = tmem + ((uint32_t)((warp & 3) * 32) << 16) + kStreamAcol + (uint32_t)half_id * kStreamAcols;
+        TMEM_ST32(arow + col_half * 32, w);
+        if (col_half == 1) {
+            const uint32_t m01 = (uint32_t)__half_as_ushort(__float2half_rn(kAugS1)) | ((uint32_t)__half_as_ushort(__float2half_rn(kAugS2)) << 16);
+            const uint32_t m2_ = (uint32_t)__half_as_ushort(__float2half_rn(kAugS3));
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};"
+                         ::"r"(arow + 64), "r"(m01), "r"(m2_), "r"(0u), "r"(0u), "r"(0u), "r"(0u), "r"(0u), "r"(0u) : "memory");
+        }
+        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+    }
+    const float na = (scanner && q < nq) ? __ldg(nrm_q + q) : 0.f;
+    asm volatile("tcgen05.fence::before_thread_sync;");
+    __syncthreads();
+    asm volatile("tcgen05.fence::after_thread_sync;");
+    const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)half_id * TN + (uint32_t)col_half * (TN / 2);
     const uint32_t bar = smem_u32(s_bar);
-    const uint32_t aQ = smem_u32(sQ);
-    uint32_t phase = 0;
+    const float nbmax = __int_as_float(s_nbmax[0]);
+    // |b|^2 beyond the three-half split (or not finite): every record of this CTA asks for the exact whole-chunk scan
+    const bool bail = !(nbmax <= kAugMaxNorm);
+    const int S = bail ? 0 : 2 * T;
+    const bool issuer = tid == kStreamScan;
 
-    auto issue_mma = [&](int s) {  // one thread: both query tiles x the train tile of step s, then commit
+    // step s works on tile s % T -> buffer s % 4; rows past the train set are zero-filled by the TMA unit, rows past
+    // the chunk are real rows of the next chunk whose |b|^2 chunk says +inf
+    auto load_tile = [&](int s) {
+        const int ti = s >= T ? s - T : s;
+        const uint32_t dst = smem_u32(sB) + (uint32_t)(s % kStreamBufs) * kStreamTile;
+        const uint32_t full = bar + 8u * (1 + s % kStreamBufs);
+        asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"(kStreamTile) : "memory");
+#pragma unroll
+        for (int p = 0; p < 2; p++)
+            asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                         ::"r"(dst + p * kStreamPanel), "l"(&train_map), "r"(p * 64), "r"(t_begin + ti * TN), "r"(full) : "memory");
+        asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                     ::"r"(dst + 2 * kStreamPanel), "l"(aug + ((size_t)c * tiles + ti) * 256), "r"(4096u), "r"(full) : "memory");
+    };
+    auto issue_mma = [&](int s) {  // both query tiles (TMEM) x the train tile of step s (shared memory)
+        mbar_wait(bar + 8u * (1 + s % kStreamBufs), (uint32_t)(s / kStreamBufs) & 1u);
         asm volatile("tcgen05.fence::after_thread_sync;");
-        const uint32_t aB = smem_u32(sB) + (uint32_t)(s & 1) * b_bytes;
+        const uint32_t aB = smem_u32(sB) + (uint32_t)(s % kStreamBufs) * kStreamTile;
         for (int hq = 0; hq < (two_tiles ? 2 : 1); hq++) {
 #pragma unroll
-            for (int k = 0; k < 8; k++) {  // K = 128 = 8 x 16; one instruction consumes 2 K chunks
-                const uint64_t da = umma_desc(aQ + hq * kTileBytes + k * 2 * kKcStride, kKcStride, 128);
-                const uint64_t db = umma_desc(aB + k * 2 * kc_stride_b, kc_stride_b, 128);
+            for (int k = 0; k < 9; k++) {  // K = 144 = 9 x 16 halves = 9 x 8 TMEM columns of A
+                const uint32_t ta = tmem + kStreamAcol + hq * kStreamAcols + k * 8;
+                const uint64_t db = k < 8 ? umma_desc_sw128(aB + (k >> 2) * kStreamPanel + (k & 3) * 32)
+                                          : umma_desc(aB + 2 * kStreamPanel, 128 * 16, 128);
                 const uint32_t acc = k > 0 ? 1u : 0u;
                 asm volatile(
                     "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                    "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                    ::"r"(tmem + hq * TN), "l"(da), "l"(db), "r"(idesc), "r"(acc) : "memory");
+                    "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                    ::"r"(tmem + hq * TN), "r"(ta), "l"(db), "r"(idesc), "r"(acc) : "memory");
             }
         }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
     };
-    const float slack = __fmaf_rn(4e-5f, __fadd_rn(na, __int_as_float(s_nbmax[0])), 1e-3f);
-    const bool scans = half_id == 0 || two_tiles;
-    // running (min, 2nd min) over quad minima, two independent pairs
-    float m1[2] = {INFINITY, INFINITY}, m2[2] = {INFINITY, INFINITY};
+    const float slack = __fmaf_rn(4e-5f, __fadd_rn(na, nbmax), 1e-3f);
+    const bool scans = scanner && (half_id == 0 || two_tiles);
+    // running (min, 2nd min) over quad minima, four independent pairs
+    float m1[4] = {INFINITY, INFINITY, INFINITY, INFINITY}, m2[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
     float thr = 0.f;
     int cn = 0;
 
-    if (tid == 0) issue_mma(0);
-    if (S > 1) fetch(1);
+    if (issuer && S > 0) {
+        for (int s = 0; s < min(S, 3); s++) load_tile(s);
+        issue_mma(0);
+    }
     for (int s = 0; s < S; s++) {
-        uint32_t v[TN];
-        mbar_wait(bar, phase);
-        phase ^= 1;
-        asm volatile("tcgen05.fence::after_thread_sync;");
-        if (scans) {
+        uint32_t v[TN / 2];
+        if (scanner) {
+            mbar_wait(bar, (uint32_t)s & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;");
+            if (scans) {
 #pragma unroll
-            for (int cb = 0; cb < TN / 32; cb++) TMEM_LD32(v + cb * 32, taddr + cb * 32);
-            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+                for (int cb = 0; cb < TN / 64; cb++) TMEM_LD32(v + cb * 32, taddr + cb * 32);
+                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            }
+            asm volatile("tcgen05.fence::before_thread_sync;");
         }
-        asm volatile("tcgen05.fence::before_thread_sync;");
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-        __syncthreads();  // accumulators drained by everybody, tile s+1 landed
-        if (s + 1 < S && tid == 0) issue_mma(s + 1);
-        if (s + 2 < S) fetch(s + 2);  // tile buffer of step s (its MMA is done), norm slot (s+2) % 3
+        __syncthreads();  // accumulators drained by everybody; the MMA of step s is complete, so is every read of its tile
+        if (issuer) {
+            if (s + 1 < S) issue_mma(s + 1);
+            if (s + 3 < S) load_tile(s + 3);  // into the buffer of tile s-1
+        }
         if (scans) {
-            const float4* nb4 = reinterpret_cast<const float4*>(s_nb + (s % 3) * TN);
             if (s < T) {
 #pragma unroll
-                for (int i4 = 0; i4 < TN / 4; i4++) {
-                    const float4 nb = nb4[i4];
-                    const float d0 = __fadd_rn(__uint_as_float(v[i4 * 4 + 0]), nb.x), d1 = __fadd_rn(__uint_as_float(v[i4 * 4 + 1]), nb.y);
-                    const float d2 = __fadd_rn(__uint_as_float(v[i4 * 4 + 2]), nb.z), d3 = __fadd_rn(__uint_as_float(v[i4 * 4 + 3]), nb.w);
-                    const float qm = fminf(fminf(d0, d1), fminf(d2, d3));  // +inf on padding columns
-                    m2[i4 & 1] = fminf(m2[i4 & 1], fmaxf(m1[i4 & 1], qm));
-                    m1[i4 & 1] = fminf(m1[i4 & 1], qm);
+                for (int i4 = 0; i4 < TN / 8; i4++) {
+                    const float qm = fminf(fminf(__uint_as_float(v[i4 * 4 + 0]), __uint_as_float(v[i4 * 4 + 1])),
+                                           fminf(__uint_as_float(v[i4 * 4 + 2]), __uint_as_float(v[i4 * 4 + 3])));  // +inf on padding columns
+                    m2[i4 & 3] = fminf(m2[i4 & 3], fmaxf(m1[i4 & 3], qm));
+                    m1[i4 & 3] = fminf(m1[i4 & 3], qm);
                 }
-                if (s == T - 1) {
-                    // {a1,a2} u {b1,b2}: 2nd = min(max(a1,b1), min(a2,b2)); survivors: D <= D2nd * (1+d)/(1-d) with
-                    // d = 1.5e-3 (half roundings) + fp32 accumulation slack, compared in the |b|^2 - 2 a.b domain
-                    const float a2 = fminf(fmaxf(m1[0], m1[1]), fminf(m2[0], m2[1]));
+                if (s == T - 1) {  // {a1,a2} u {b1,b2}: min = min(a1,b1), 2nd = min(max(a1,b1), min(a2,b2))
+                    const float x2 = fminf(fmaxf(m1[0], m1[1]), fminf(m2[0], m2[1])), x1 = fminf(m1[0], m1[1]);
+                    const float y2 = fminf(fmaxf(m1[2], m1[3]), fminf(m2[2], m2[3])), y1 = fminf(m1[2], m1[3]);
+                    s_pair[tid] = fminf(x1, y1);
+                    s_pair[kStreamScan + tid] = fminf(fmaxf(x1, y1), fminf(x2, y2));
+                }
+            } else {
+                if (s == T) {
+                    // both column halves of the row (threads tid and tid ^ 256; ordered by the barrier above). Survivors:
+                    // D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings) + fp32 accumulation slack, compared in the
+                    // |b|^2 - 2 a.b domain
+                    const float a1 = s_pair[tid], a2v = s_pair[kStreamScan + tid];
+                    const float b1 = s_pair[tid ^ 256], b2v = s_pair[kStreamScan + (tid ^ 256)];
+                    const float a2 = fminf(fmaxf(a1, b1), fminf(a2v, b2v));
                     const float d2nd = fmaxf(__fadd_rn(a2, na), 0.f);
                     thr = __fsub_rn(__fmaf_rn(d2nd, 1.004f, slack), na);
                 }
-            } else {
-                const int col0 = (s - T) * TN;
+                const int col0 = (s - T) * TN + col_half * (TN / 2);
 #pragma unroll
-                for (int cb = 0; cb < TN / 32; cb++) {
-                    unsigned mask = 0u;
+                for (int i4 = 0; i4 < TN / 8; i4++) {
+                    const float d0 = __uint_as_float(v[i4 * 4 + 0]), d1 = __uint_as_float(v[i4 * 4 + 1]);
+                    const float d2 = __uint_as_float(v[i4 * 4 + 2]), d3 = __uint_as_float(v[i4 * 4 + 3]);
+                    if (fminf(fminf(d0, d1), fminf(d2, d3)) <= thr) {  // survivors are rare
+                        const float dd[4] = {d0, d1, d2, d3};
 #pragma unroll
-                    for (int i4 = 0; i4 < 8; i4++) {
-                        const float4 nb = nb4[cb * 8 + i4];
-                        mask |= (__fadd_rn(__uint_as_float(v[cb * 32 + i4 * 4 + 0]), nb.x) <= thr ? 1u : 0u) << (i4 * 4 + 0);
-                        mask |= (__fadd_rn(__uint_as_float(v[cb * 32 + i4 * 4 + 1]), nb.y) <= thr ? 1u : 0u) << (i4 * 4 + 1);
-                        mask |= (__fadd_rn(__uint_as_float(v[cb * 32 + i4 * 4 + 2]), nb.z) <= thr ? 1u : 0u) << (i4 * 4 + 2);
-                        mask |= (__fadd_rn(__uint_as_float(v[cb * 32 + i4 * 4 + 3]), nb.w) <= thr ? 1u : 0u) << (i4 * 4 + 3);
-                    }
-                    while (mask) {  // survivors are rare
-                        const int i = __ffs(mask) - 1;
-                        mask &= mask - 1;
-                        if (cn < kCand) s_cand[cn * kResThreads + tid] = col0 + cb * 32 + i;
-                        cn++;
+                        for (int j = 0; j < 4; j++) {
+                            if (dd[j] <= thr) {
+                                if (cn < kCand) s_cand[cn * kStreamScan + tid] = col0 + i4 * 4 + j;
+                                cn++;
+                            }
+                        }
                     }
                 }
             }
         }
     }
-    if (q < nq) {
-        int4* dst = reinterpret_cast<int4*>(rec + (size_t)q * 32 + c);
-        int cc[kCand];
-#pragma unroll
-        for (int i = 0; i < kCand; i++) cc[i] = i < cn ? t_begin + s_cand[i * kResThreads + tid] : -1;
-        dst[0] = make_int4(min(cn, kCand + 1), cc[0], cc[1], cc[2]);
-        dst[1] = make_int4(cc[3], cc[4], cc[5], cc[6]);
-    }
+    if (scanner) s_cn[tid] = cn;
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
+    if (scanner && col_half == 0 && q < nq) {
+        // merge the two column halves of the row in ascending column order (both lists already are)
+        const int pt = tid ^ 256;
+        const int na_ = min(cn, kCand), nb_ = min(s_cn[pt], kCand);
+        const int total = bail ? kCand + 1 : cn + s_cn[pt];
+        int cc[kCand];
+        int ia = 0, ib = 0;
+#pragma unroll
+        for (int i = 0; i < kCand; i++) {
+            const int ca = ia < na_ ? s_cand[ia * kStreamScan + tid] : 0x7fffffff;
+            const int cb = ib < nb_ ? s_cand[ib * kStreamScan + pt] : 0x7fffffff;
+            const int m = min(ca, cb);
+            cc[i] = (m == 0x7fffffff || bail) ? -1 : t_begin + m;
+            if (ca <= cb) ia++; else ib++;
+        }
+        int4* dst = reinterpret_cast<int4*>(rec + (size_t)q * 32 + c);
+        dst[0] = make_int4(min(total, kCand + 1), cc[0], cc[1], cc[2]);
+        dst[1] = make_int4(cc[3], cc[4], cc[5], cc[6]);
+    }
     if (warp == 0) {
-        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(256));
+        asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(512));
     }
 }
 
@@ -933,15 +1034,42 @@ void launch_filter(dim3 grid, const __half* q, int nq, const __half* t, int nt, 
 }
 }  // namespace
 
+namespace {
+// Tensor map of the train set for the streaming filter's TMA loads: [nt rows][128 halves], box = 128 rows x 64
+// halves with the 128-byte swizzle; rows past nt read as zero. cuTensorMapEncodeTiled comes from the driver through
+// the runtime's entry-point query (no link-time dependency on libcuda).
+bool encode_train_map(CUtensorMap* map, const __half* t, int nt) {
+    using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn) return false;
+        encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    const cuuint64_t dims[2] = {128, (cuuint64_t)nt};
+    const cuuint64_t strides[1] = {256};
+    const cuuint32_t box[2] = {64, (cuuint32_t)kStreamTN};
+    const cuuint32_t estr[2] = {1, 1};
+    return encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<__half*>(t), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+}  // namespace
+
 void match_set_path(int path) { g_match_path = path; }
 int match_get_path() { return g_match_path; }
 
 size_t match_scratch_bytes(int nq, int nt) {
     // survivor records (>= the 16-byte records of the CUDA-core path) + the squared norms of both sets
-    return (size_t)nq * 32 * sizeof(CandRec) + ((size_t)nq + (size_t)nt + 8) * sizeof(float);
+    // + the |b|^2 K chunks of the streaming filter (4 KB per 128-row tile of every chunk)
+    const int per = (nt + 31) / 32;
+    const size_t aug = per > 256 ? (size_t)32 * ((per + kStreamTN - 1) / kStreamTN) * 4096 : 0;
+    return (size_t)nq * 32 * sizeof(CandRec) + ((size_t)nq + (size_t)nt + 8) * sizeof(float) + aug;
 }
 
-int match_num_launches(int nq, int nt) { return (nq > 0 && nt >= 0) ? 3 : 0; }  // norms, filter, re-rank
+int match_num_launches(int nq, int nt) { return (nq > 0 && nt >= 0) ? (nt > 8192 ? 4 : 3) : 0; }  // norms, (|b|^2 chunks,) filter, re-rank
 
 namespace {
 // Resident-chunk filter (every chunk of the train set fits one MMA tile): norms, then the filter.
@@ -1002,11 +1130,17 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
             cudaFuncSetAttribute(match_filter_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStreamSmem);
             attr_set = true;
         }
-        float* nrm_q = reinterpret_cast<float*>(rec + (size_t)nq * 32);
+        // scratch: records | |b|^2 K chunks, tiled per chunk (4 KB per 128-row tile) | norms
+        const int tiles = (per + kStreamTN - 1) / kStreamTN;
+        uint4* aug = reinterpret_cast<uint4*>(rec + (size_t)nq * 32);
+        float* nrm_q = reinterpret_cast<float*>(aug + (size_t)32 * tiles * 256);
         float* nrm_t = nrm_q + nq;
+        CUtensorMap train_map;
+        if (!encode_train_map(&train_map, t, nt)) return -2;
         match_norms_kernel<<<(nq + nt + 7) / 8, 256, 0, s>>>(q, nq, t, nt, nrm_q, nrm_t, nullptr, nullptr);
+        match_aug_kernel<<<(32 * tiles * 128 + 255) / 256, 256, 0, s>>>(nrm_t, nt, per, tiles, aug);
         dim3 grid((nq + kResQ - 1) / kResQ, 32);
-        match_filter_stream_kernel<<<grid, kResThreads, kStreamSmem, s>>>(q, nq, t, nt, per, rec, nrm_q, nrm_t);
+        match_filter_stream_kernel<<<grid, kStreamThreads, kStreamSmem, s>>>(q, nq, train_map, nt, per, rec, nrm_q, nrm_t, aug);
     }
     match_rerank_kernel<<<(nq + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, nq, t, nt, per, rec, out, nullptr, nullptr);
     return 0;

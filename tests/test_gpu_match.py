@@ -84,6 +84,27 @@ def test_adversarial_ties_and_duplicates_vs_cpu_oracle(path):
     assert np.array_equal(got, CpuOracle(64, 64, 100).match(q, t))
 
 
+def test_streaming_filter_adversarial_vs_cpu_oracle(path):
+    """Large train sets (> 8192 rows: the streamed two-pass tcgen05 filter). (a) a small base repeated many times:
+    exact ties inside and across tiles and chunks, survivor lists overflow and fall back to whole-chunk scoring;
+    (b) rows whose squared norm exceeds what the three-half split of |b|^2 can carry (> 2e9): the filter hands
+    every chunk to the exact path; the half arithmetic of the reference overflows to inf there and so must ours."""
+    from another_cuda_sift_b200 import matchBruteForce
+    from oracle.pyoracle import CpuOracle
+
+    rng = np.random.default_rng(17)
+    base = (rng.random((300, 128)) * 200).astype(np.float16)
+    t = np.concatenate([base] * 30 + [base[:77]])                      # 9077 rows, per = 284
+    t[5000:5300] = (t[5000:5300].astype(np.float32) + rng.integers(-1, 2, (300, 128))).clip(0, 512).astype(np.float16)
+    q = np.concatenate([base[:48], (base[100:148].astype(np.float32) + rng.integers(-2, 3, (48, 128))).clip(0, 512).astype(np.float16)])
+    cpu = CpuOracle(64, 64, 100)
+    assert np.array_equal(matchBruteForce(q, len(q), t, len(t)), cpu.match(q, t))
+    big = (rng.random((8500, 128)) * 6000).astype(np.float16)         # |b|^2 ~ 1.5e9 .. 4e9
+    big[::7] = (rng.random((len(big[::7]), 128)) * 100).astype(np.float16)
+    qb = np.concatenate([big[:20], (rng.random((20, 128)) * 100).astype(np.float16)])
+    assert np.array_equal(matchBruteForce(qb, len(qb), big, len(big)), cpu.match(qb, big))
+
+
 def test_empty_inputs():
     from another_cuda_sift_b200 import matchBruteForce
 
