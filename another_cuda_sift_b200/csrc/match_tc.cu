@@ -655,7 +655,7 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
     constexpr int TN = kStreamTN;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sB = smem;                                     // 4 tile buffers
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(sB + kStreamBufs * kStreamTile);  // [0] MMA done, [1..4] tile landed
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(sB + kStreamBufs * kStreamTile);  // [0..1] MMA done (query half), [2..5] tile landed
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 8);
     int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);
     int* s_cand = reinterpret_cast<int*>(s_bar + 16);       // [kCand][512] survivor columns (chunk-relative) of thread tid, then [512] counts
@@ -687,7 +687,7 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
     }
     if (tid == 0) {
         s_nbmax[0] = 0;
-        for (int i = 0; i < 1 + kStreamBufs; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar + i)));
+        for (int i = 0; i < 2 + kStreamBufs; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar + i)));
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
     asm volatile("tcgen05.fence::before_thread_sync;");
@@ -736,14 +736,13 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
     // |b|^2 beyond the three-half split (or not finite): every record of this CTA asks for the exact whole-chunk scan
     const bool bail = !(nbmax <= kAugMaxNorm);
     const int S = bail ? 0 : 2 * T;
-    const bool issuer = tid == kStreamScan;
 
     // step s works on tile s % T -> buffer s % 4; rows past the train set are zero-filled by the TMA unit, rows past
     // the chunk are real rows of the next chunk whose |b|^2 chunk says +inf
     auto load_tile = [&](int s) {
         const int ti = s >= T ? s - T : s;
         const uint32_t dst = smem_u32(sB) + (uint32_t)(s % kStreamBufs) * kStreamTile;
-        const uint32_t full = bar + 8u * (1 + s % kStreamBufs);
+        const uint32_t full = bar + 8u * (2 + s % kStreamBufs);
         asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(full), "r"(kStreamTile) : "memory");
 #pragma unroll
         for (int p = 0; p < 2; p++)
@@ -752,90 +751,95 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"(dst + 2 * kStreamPanel), "l"(aug + ((size_t)c * tiles + ti) * 256), "r"(4096u), "r"(full) : "memory");
     };
-    auto issue_mma = [&](int s) {  // both query tiles (TMEM) x the train tile of step s (shared memory)
-        mbar_wait(bar + 8u * (1 + s % kStreamBufs), (uint32_t)(s / kStreamBufs) & 1u);
+    auto issue_mma = [&](int s, int hq) {  // query tile hq (TMEM) x the train tile of step s (shared memory) -> accumulator hq
+        if (hq == 0) mbar_wait(bar + 8u * (2 + s % kStreamBufs), (uint32_t)(s / kStreamBufs) & 1u);
         asm volatile("tcgen05.fence::after_thread_sync;");
         const uint32_t aB = smem_u32(sB) + (uint32_t)(s % kStreamBufs) * kStreamTile;
-        for (int hq = 0; hq < (two_tiles ? 2 : 1); hq++) {
 #pragma unroll
-            for (int k = 0; k < 9; k++) {  // K = 144 = 9 x 16 halves = 9 x 8 TMEM columns of A
-                const uint32_t ta = tmem + kStreamAcol + hq * kStreamAcols + k * 8;
-                const uint64_t db = k < 8 ? umma_desc_sw128(aB + (k >> 2) * kStreamPanel + (k & 3) * 32)
-                                          : umma_desc(aB + 2 * kStreamPanel, 128 * 16, 128);
-                const uint32_t acc = k > 0 ? 1u : 0u;
-                asm volatile(
-                    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                    "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-                    ::"r"(tmem + hq * TN), "r"(ta), "l"(db), "r"(idesc), "r"(acc) : "memory");
-            }
+        for (int k = 0; k < 9; k++) {  // K = 144 = 9 x 16 halves = 9 x 8 TMEM columns of A
+            const uint32_t ta = tmem + kStreamAcol + hq * kStreamAcols + k * 8;
+            const uint64_t db = k < 8 ? umma_desc_sw128(aB + (k >> 2) * kStreamPanel + (k & 3) * 32)
+                                      : umma_desc(aB + 2 * kStreamPanel, 128 * 16, 128);
+            const uint32_t acc = k > 0 ? 1u : 0u;
+            asm volatile(
+                "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                ::"r"(tmem + hq * TN), "r"(ta), "l"(db), "r"(idesc), "r"(acc) : "memory");
         }
-        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+        asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar + 8u * hq) : "memory");
     };
     const float slack = __fmaf_rn(4e-5f, __fadd_rn(na, nbmax), 1e-3f);
     const bool scans = scanner && (half_id == 0 || two_tiles);
-    // running (min, 2nd min) over quad minima, four independent pairs
-    float m1[4] = {INFINITY, INFINITY, INFINITY, INFINITY}, m2[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
-    float thr = 0.f;
+    const int nh = two_tiles ? 2 : 1;
     int cn = 0;
 
-    if (issuer && S > 0) {
-        for (int s = 0; s < min(S, 3); s++) load_tile(s);
-        issue_mma(0);
-    }
-    for (int s = 0; s < S; s++) {
-        uint32_t v[TN / 2];
-        if (scanner) {
-            mbar_wait(bar, (uint32_t)s & 1u);
-            asm volatile("tcgen05.fence::after_thread_sync;");
-            if (scans) {
-#pragma unroll
-                for (int cb = 0; cb < TN / 64; cb++) TMEM_LD32(v + cb * 32, taddr + cb * 32);
-                asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+    if (!scanner) {
+        // ---- issuer warp: per step and query half h, wait until the scan warps of that half have drained their
+        // accumulator (named barrier 1 + h: 256 arrivals + this warp), then queue the 9 MMAs of the next step behind
+        // whatever the tensor pipe is still working on. Draining half 0 overlaps the MMAs of half 1 and vice versa.
+        if (lane == 0 && S > 0)
+            for (int s = 0; s < min(S, kStreamBufs); s++) load_tile(s);
+        for (int s = 0; s < S; s++) {
+            for (int h = 0; h < nh; h++) {
+                if (s > 0) asm volatile("barrier.cta.sync %0, %1;" ::"r"(1 + h), "r"(kStreamScan / 2 + 32) : "memory");
+                if (lane == 0) issue_mma(s, h);
+                __syncwarp();
             }
+            // every accumulator of step s-1 has been drained, so its MMAs are complete and its tile buffer is free
+            if (lane == 0 && s > 0 && s + kStreamBufs - 1 < S) load_tile(s + kStreamBufs - 1);
+        }
+        if (S > 0)
+            for (int h = 0; h < nh; h++) asm volatile("barrier.cta.sync %0, %1;" ::"r"(1 + h), "r"(kStreamScan / 2 + 32) : "memory");
+    } else if (scans) {
+        // ---- scan warps. Running (min, 2nd min) over the minima of column octets, four independent pairs: the 2nd
+        // smallest octet minimum is >= the true 2nd smallest distance (equal unless both fall into one octet)
+        float m1[4] = {INFINITY, INFINITY, INFINITY, INFINITY}, m2[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+        float thr = 0.f;
+        const uint32_t done = bar + 8u * half_id;
+        for (int s = 0; s < S; s++) {
+            uint32_t v[TN / 2];
+            mbar_wait(done, (uint32_t)s & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;");
+#pragma unroll
+            for (int cb = 0; cb < TN / 64; cb++) TMEM_LD32(v + cb * 32, taddr + cb * 32);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
             asm volatile("tcgen05.fence::before_thread_sync;");
-        }
-        __syncthreads();  // accumulators drained by everybody; the MMA of step s is complete, so is every read of its tile
-        if (issuer) {
-            if (s + 1 < S) issue_mma(s + 1);
-            if (s + 3 < S) load_tile(s + 3);  // into the buffer of tile s-1
-        }
-        if (scans) {
+            asm volatile("barrier.cta.arrive %0, %1;" ::"r"(1 + half_id), "r"(kStreamScan / 2 + 32) : "memory");
             if (s < T) {
 #pragma unroll
-                for (int i4 = 0; i4 < TN / 8; i4++) {
-                    const float qm = fminf(fminf(__uint_as_float(v[i4 * 4 + 0]), __uint_as_float(v[i4 * 4 + 1])),
-                                           fminf(__uint_as_float(v[i4 * 4 + 2]), __uint_as_float(v[i4 * 4 + 3])));  // +inf on padding columns
-                    m2[i4 & 3] = fminf(m2[i4 & 3], fmaxf(m1[i4 & 3], qm));
-                    m1[i4 & 3] = fminf(m1[i4 & 3], qm);
+                for (int i8 = 0; i8 < TN / 16; i8++) {
+                    const float* f = reinterpret_cast<const float*>(v + i8 * 8);
+                    const float om = fminf(fminf(fminf(f[0], f[1]), fminf(f[2], f[3])), fminf(fminf(f[4], f[5]), fminf(f[6], f[7])));  // +inf on padding columns
+                    m2[i8 & 3] = fminf(m2[i8 & 3], fmaxf(m1[i8 & 3], om));
+                    m1[i8 & 3] = fminf(m1[i8 & 3], om);
                 }
-                if (s == T - 1) {  // {a1,a2} u {b1,b2}: min = min(a1,b1), 2nd = min(max(a1,b1), min(a2,b2))
+                if (s == T - 1) {
+                    // {a1,a2} u {b1,b2}: min = min(a1,b1), 2nd = min(max(a1,b1), min(a2,b2)); then the same with the other
+                    // column half of the row (thread tid ^ 256, same query half: named barrier 3 + half).
+                    // Survivors: D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings) + fp32 accumulation slack,
+                    // compared in the |b|^2 - 2 a.b domain
                     const float x2 = fminf(fmaxf(m1[0], m1[1]), fminf(m2[0], m2[1])), x1 = fminf(m1[0], m1[1]);
                     const float y2 = fminf(fmaxf(m1[2], m1[3]), fminf(m2[2], m2[3])), y1 = fminf(m1[2], m1[3]);
-                    s_pair[tid] = fminf(x1, y1);
-                    s_pair[kStreamScan + tid] = fminf(fmaxf(x1, y1), fminf(x2, y2));
-                }
-            } else {
-                if (s == T) {
-                    // both column halves of the row (threads tid and tid ^ 256; ordered by the barrier above). Survivors:
-                    // D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings) + fp32 accumulation slack, compared in the
-                    // |b|^2 - 2 a.b domain
-                    const float a1 = s_pair[tid], a2v = s_pair[kStreamScan + tid];
+                    const float a1 = fminf(x1, y1), a2v = fminf(fmaxf(x1, y1), fminf(x2, y2));
+                    s_pair[tid] = a1;
+                    s_pair[kStreamScan + tid] = a2v;
+                    asm volatile("barrier.cta.sync %0, %1;" ::"r"(3 + half_id), "r"(kStreamScan / 2) : "memory");
                     const float b1 = s_pair[tid ^ 256], b2v = s_pair[kStreamScan + (tid ^ 256)];
                     const float a2 = fminf(fmaxf(a1, b1), fminf(a2v, b2v));
                     const float d2nd = fmaxf(__fadd_rn(a2, na), 0.f);
                     thr = __fsub_rn(__fmaf_rn(d2nd, 1.004f, slack), na);
                 }
+            } else {
                 const int col0 = (s - T) * TN + col_half * (TN / 2);
 #pragma unroll
-                for (int i4 = 0; i4 < TN / 8; i4++) {
-                    const float d0 = __uint_as_float(v[i4 * 4 + 0]), d1 = __uint_as_float(v[i4 * 4 + 1]);
-                    const float d2 = __uint_as_float(v[i4 * 4 + 2]), d3 = __uint_as_float(v[i4 * 4 + 3]);
-                    if (fminf(fminf(d0, d1), fminf(d2, d3)) <= thr) {  // survivors are rare
-                        const float dd[4] = {d0, d1, d2, d3};
+                for (int i8 = 0; i8 < TN / 16; i8++) {
+                    const float* f = reinterpret_cast<const float*>(v + i8 * 8);
+                    const float om = fminf(fminf(fminf(f[0], f[1]), fminf(f[2], f[3])), fminf(fminf(f[4], f[5]), fminf(f[6], f[7])));
+                    if (om <= thr) {  // survivors are rare
 #pragma unroll
-                        for (int j = 0; j < 4; j++) {
-                            if (dd[j] <= thr) {
-                                if (cn < kCand) s_cand[cn * kStreamScan + tid] = col0 + i4 * 4 + j;
+                        for (int j = 0; j < 8; j++) {
+                            if (f[j] <= thr) {
+                                if (cn < kCand) s_cand[cn * kStreamScan + tid] = col0 + i8 * 8 + j;
                                 cn++;
                             }
                         }

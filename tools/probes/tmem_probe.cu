@@ -55,6 +55,18 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
         const uint32_t idesc = (1u << 4) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         uint32_t phase = 0;
         for (int it = 0; it < iters; it++) {
+            if (mode & 4) {  // A operand from tensor memory (columns 256..), N = 128 (mode bit 3 clear) or 64 (set)
+                const int n = (mode & 8) ? 64 : 128;
+                const uint32_t idn = (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+                for (int k = 0; k < mma_per_iter; k++) {
+                    const uint64_t db = umma_desc(smem_u32(smem) + 36864 + (k % 9) * 2 * 2048, 2048, 128);
+                    const uint32_t accf = (k % 9) > 0 ? 1u : 0u;
+                    asm volatile(
+                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                        ::"r"(tmem + ((k / 9) & 1) * 128), "r"(tmem + 256 + (k % 9) * 8), "l"(db), "r"(idn), "r"(accf) : "memory");
+                }
+            } else
             for (int k = 0; k < mma_per_iter; k++) {
                 const uint64_t da = umma_desc(smem_u32(smem) + (k % 9) * 2 * 2048, 2048, 128);
                 const uint64_t db = umma_desc(smem_u32(smem) + 36864 + (k % 9) * 2 * 2048, 2048, 128);
@@ -104,10 +116,15 @@ int main() {
         {2, 1, 36, "mma only, 36 per commit"},
         {3, 9, 18, "8 drain warps + mma 18 per commit"},
         {3, 5, 18, "4 drain warps + mma 18 per commit"},
+        {6, 1, 18, "mma A-from-TMEM N=128, 18 per commit"},
+        {6, 1, 36, "mma A-from-TMEM N=128, 36 per commit"},
+        {14, 1, 36, "mma A-from-TMEM N=64, 36 per commit"},
+        {14, 1, 72, "mma A-from-TMEM N=64, 72 per commit"},
+        {7, 9, 18, "8 drain warps + mma A-from-TMEM N=128, 18 per commit"},
     };
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
-    for (int grid : {1, 148}) {
+    for (int grid : {1}) {
         for (auto& c : cfgs) {
             const int it = grid == 1 ? iters : iters * 20;  // long enough for the power management to settle
             cudaMemset(d_out, 0, 64 * sizeof(long long));
