@@ -57,6 +57,15 @@ __host__ __device__ constexpr uint32_t make_idesc(int n) {
     return (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(kTileM >> 4) << 24);
 }
 
+// One lane of a converged warp. ptxas knows that a region guarded by elect.sync runs a single thread and keeps
+// the operands of the tcgen05 / TMA instructions inside it in uniform registers; guarded by `lane == 0` every such
+// instruction is wrapped in an ELECT + R2UR.BROADCAST uniformisation loop (13 issue slots per MMA, measured).
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(pred));
+    return pred != 0;
+}
+
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     uint32_t done = 0;
     for (uint32_t spins = 0; !done; spins++) {
@@ -777,16 +786,20 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
         // ---- issuer warp: per step and query half h, wait until the scan warps of that half have drained their
         // accumulator (named barrier 1 + h: 256 arrivals + this warp), then queue the 9 MMAs of the next step behind
         // whatever the tensor pipe is still working on. Draining half 0 overlaps the MMAs of half 1 and vice versa.
-        if (lane == 0 && S > 0)
+        if (S > 0 && elect_one())
             for (int s = 0; s < min(S, kStreamBufs); s++) load_tile(s);
+        __syncwarp();
         for (int s = 0; s < S; s++) {
             for (int h = 0; h < nh; h++) {
                 if (s > 0) asm volatile("barrier.cta.sync %0, %1;" ::"r"(1 + h), "r"(kStreamScan / 2 + 32) : "memory");
-                if (lane == 0) issue_mma(s, h);
+                if (elect_one()) issue_mma(s, h);
                 __syncwarp();
             }
             // every accumulator of step s-1 has been drained, so its MMAs are complete and its tile buffer is free
-            if (lane == 0 && s > 0 && s + kStreamBufs - 1 < S) load_tile(s + kStreamBufs - 1);
+            if (s > 0 && s + kStreamBufs - 1 < S) {
+                if (elect_one()) load_tile(s + kStreamBufs - 1);
+                __syncwarp();
+            }
         }
         if (S > 0)
             for (int h = 0; h < nh; h++) asm volatile("barrier.cta.sync %0, %1;" ::"r"(1 + h), "r"(kStreamScan / 2 + 32) : "memory");
