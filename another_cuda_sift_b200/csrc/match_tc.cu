@@ -488,7 +488,10 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
         asm volatile("cp.async.wait_group 0;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // cp.async / st.shared -> visible to the tensor core
         __syncthreads();
-        if (tid == 0 && chunk_rows(c_begin) > 0) issue_mma(c_begin);
+        if (warp == 0 && chunk_rows(c_begin) > 0) {
+            if (elect_one()) issue_mma(c_begin);
+            __syncwarp();
+        }
         if (c_begin + 1 < c_end) fetch(c_begin + 1);
         for (int c = c_begin; c < c_end; c++) {
             const int rows = chunk_rows(c);
@@ -507,7 +510,10 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
             asm volatile("cp.async.wait_group 0;" ::: "memory");
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
             __syncthreads();  // accumulator drained by everybody, tile c+1 landed
-            if (c + 1 < c_end && tid == 0 && chunk_rows(c + 1) > 0) issue_mma(c + 1);
+            if (c + 1 < c_end && warp == 0 && chunk_rows(c + 1) > 0) {
+                if (elect_one()) issue_mma(c + 1);
+                __syncwarp();
+            }
             if (c + 2 < c_end) fetch(c + 2);  // tile buffer of chunk c (its MMA is done), norm slot (c+2) % 3
             int cn = 0;
             if (rows > 0 && scans) {
@@ -549,7 +555,10 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
             asm volatile("cp.async.wait_group 0;" ::: "memory");
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // cp.async / st.shared -> visible to the tensor core
             __syncthreads();
-            if (tid == 0 && rows > 0) issue_mma(c);
+            if (warp == 0 && rows > 0) {
+                if (elect_one()) issue_mma(c);
+                __syncwarp();
+            }
             if (c + 1 < c_end) fetch(c + 1);  // the other tile buffer: its MMA (chunk c-1) completed before the last barrier
             int cn = 0;
             if (rows > 0) {

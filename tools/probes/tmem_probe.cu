@@ -45,36 +45,37 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;");
     const uint32_t tmem = s_tmem;
-    const bool mma_thread = (mode & 2) && tid == (nwarps - 1) * 32;
+    const bool mma_warp = (mode & 2) && warp == nwarps - 1;
     const bool drains = (mode & 1) && !((mode & 2) && warp == nwarps - 1);
     const uint32_t taddr = tmem + ((uint32_t)((warp & 3) * 32) << 16) + (uint32_t)((warp >> 2) & 3) * 128;
     unsigned acc = 0;
     __syncthreads();
     const long long t0 = clock64();
-    if (mma_thread) {
-        const uint32_t idesc = (1u << 4) | ((uint32_t)(128 >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+    if (mma_warp) {
+        uint32_t el;
+        asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(el));
+        if (el) {
+        const int n = (mode & 8) ? 64 : 128;
+        const uint32_t idesc = (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
         uint32_t phase = 0;
         for (int it = 0; it < iters; it++) {
-            if (mode & 4) {  // A operand from tensor memory (columns 256..), N = 128 (mode bit 3 clear) or 64 (set)
-                const int n = (mode & 8) ? 64 : 128;
-                const uint32_t idn = (1u << 4) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-                for (int k = 0; k < mma_per_iter; k++) {
-                    const uint64_t db = umma_desc(smem_u32(smem) + 36864 + (k % 9) * 2 * 2048, 2048, 128);
-                    const uint32_t accf = (k % 9) > 0 ? 1u : 0u;
-                    asm volatile(
-                        "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
-                        ::"r"(tmem + ((k / 9) & 1) * 128), "r"(tmem + 256 + (k % 9) * 8), "l"(db), "r"(idn), "r"(accf) : "memory");
+            for (int g = 0; g < mma_per_iter / 9; g++) {
+#pragma unroll
+                for (int k = 0; k < 9; k++) {
+                    const uint64_t da = umma_desc(smem_u32(smem) + k * 2 * 2048, 2048, 128);
+                    const uint64_t db = umma_desc(smem_u32(smem) + 36864 + k * 2 * 2048, 2048, 128);
+                    const uint32_t accf = k > 0 ? 1u : 0u;
+                    if (mode & 4)
+                        asm volatile(
+                            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                            "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+                            ::"r"(tmem + (g & 1) * 128), "r"(tmem + 256 + k * 8), "l"(db), "r"(idesc), "r"(accf) : "memory");
+                    else
+                        asm volatile(
+                            "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+                            "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+                            ::"r"(tmem + (g & 1) * 128), "l"(da), "l"(db), "r"(idesc), "r"(accf) : "memory");
                 }
-            } else
-            for (int k = 0; k < mma_per_iter; k++) {
-                const uint64_t da = umma_desc(smem_u32(smem) + (k % 9) * 2 * 2048, 2048, 128);
-                const uint64_t db = umma_desc(smem_u32(smem) + 36864 + (k % 9) * 2 * 2048, 2048, 128);
-                const uint32_t accf = (k % 9) > 0 ? 1u : 0u;
-                asm volatile(
-                    "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
-                    "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
-                    ::"r"(tmem + ((k / 9) & 3) * 128), "l"(da), "l"(db), "r"(idesc), "r"(accf) : "memory");
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_bar)) : "memory");
             uint32_t done = 0;
@@ -84,6 +85,8 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
             }
             phase ^= 1;
         }
+        }
+        __syncwarp();
     } else if (drains) {
         for (int it = 0; it < iters; it++) {
             uint32_t v[128];
