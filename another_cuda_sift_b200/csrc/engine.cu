@@ -984,9 +984,9 @@ int b200sift_match_device(const uint16_t* d_query, int nq, const uint16_t* d_tra
         }
         scratch = g_scratch[dev];
     }
-    if (match_launch(reinterpret_cast<const __half*>(d_query), nq, reinterpret_cast<const __half*>(d_train), nt, d_out_idx,
-                     scratch, need, s))
-        return fail(B200SIFT_EINVAL, "matcher scratch too small");
+    if (int rc = match_launch(reinterpret_cast<const __half*>(d_query), nq, reinterpret_cast<const __half*>(d_train), nt, d_out_idx,
+                              scratch, need, s))
+        return fail(B200SIFT_EINVAL, rc == -2 ? "train descriptors: tensor map rejected (the pointer must be 16-byte aligned)" : "matcher scratch too small");
     CU(cudaGetLastError());
     return 0;
 }
