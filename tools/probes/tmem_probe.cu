@@ -29,7 +29,7 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint
 __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_iter, long long* out, unsigned* sink) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
-    __shared__ uint64_t s_bar;
+    __shared__ uint64_t s_bar, s_bar2;
     const int tid = threadIdx.x, warp = tid >> 5, nwarps = blockDim.x >> 5;
     for (int i = tid; i < 3 * 36864 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
     if (warp == 0) {
@@ -38,6 +38,7 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
     }
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar2)));
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -76,6 +77,9 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
                             "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
                             ::"r"(tmem + (g & 1) * 128), "l"(da), "l"(db), "r"(idesc), "r"(accf) : "memory");
                 }
+                // mode bit 4: a commit after every group of 9 (onto a second barrier nobody waits for), as the matcher does
+                if ((mode & 16) && g + 1 < mma_per_iter / 9)
+                    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_bar2)) : "memory");
             }
             asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&s_bar)) : "memory");
             uint32_t done = 0;
@@ -124,6 +128,9 @@ int main() {
         {14, 1, 36, "mma A-from-TMEM N=64, 36 per commit"},
         {14, 1, 72, "mma A-from-TMEM N=64, 72 per commit"},
         {7, 9, 18, "8 drain warps + mma A-from-TMEM N=128, 18 per commit"},
+        {6, 1, 72, "mma A-from-TMEM N=128, 72 per wait, one commit"},
+        {22, 1, 72, "mma A-from-TMEM N=128, 72 per wait, commit every 9"},
+        {23, 9, 72, "same + 8 drain warps"},
     };
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
