@@ -47,9 +47,14 @@ blur_vh_kernel(const float* __restrict__ in, int in_pitch, float* __restrict__ o
         const int ybase = y0 + b * kRB - R;
         float v[kRB + 2 * R];
         if (ybase >= 0 && ybase + kRB + 2 * R <= h) {
+            // one 64-bit pointer stepped by the row pitch: a single IMAD.WIDE per load instead of the four address
+            // instructions (IADD3 / IMAD.X / LEA / LEA.HI.X) an element-indexed p[i * pitch] compiles to
             const float* p = in + (size_t)ybase * in_pitch + x;
 #pragma unroll
-            for (int i = 0; i < kRB + 2 * R; i++) v[i] = __ldg(p + (size_t)i * in_pitch);
+            for (int i = 0; i < kRB + 2 * R; i++) {
+                v[i] = __ldg(p);
+                asm volatile("mad.wide.s32 %0, %1, 4, %0;" : "+l"(p) : "r"(in_pitch));
+            }
         } else {
 #pragma unroll
             for (int i = 0; i < kRB + 2 * R; i++) v[i] = __ldg(in + (size_t)reflect101(ybase + i, h) * in_pitch + x);
