@@ -384,8 +384,12 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
                 const int a = (iy + idx_i) * hdim + (ix + idx_j);
                 const float* pc = stack + a;
                 const float v_l = __ldg(pc - 1), v_r = __ldg(pc + 1);
-                const float v_up = __ldg(stack + (a - hdim));
-                const float v_dn = a + hdim < stack_left ? __ldg(stack + (a + hdim)) : 0.f;
+                // the rows above / below: one IMAD.WIDE each from pc instead of a fresh 64-bit address build
+                const float *pu = pc, *pd = pc;
+                asm("mad.wide.s32 %0, %1, -4, %0;" : "+l"(pu) : "r"(hdim));
+                asm("mad.wide.s32 %0, %1, 4, %0;" : "+l"(pd) : "r"(hdim));
+                const float v_up = __ldg(pu);
+                const float v_dn = a + hdim < stack_left ? __ldg(pd) : 0.f;
                 const float dx = __fsub_rn(v_r, v_l);
                 const float dy = __fsub_rn(v_up, v_dn);
                 // rbin_int = truncf(rbin) is R (as -0.0 for rbin in (-1,0): the fraction is then negative)
