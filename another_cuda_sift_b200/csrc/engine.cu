@@ -84,6 +84,7 @@ struct Slot {
     int* d_rowcount_all = nullptr;
     int* h_total = nullptr;          // pinned
     void* match_scratch = nullptr;   // survivor records of the consecutive-frame matcher
+    int* d_match_idx = nullptr;      // match indices of b200sift_detect_batch_host (numFeatures ints)
     cudaStream_t stream = nullptr;   // main stream of the slot's frame graph
     cudaStream_t side[kSideStreams] = {nullptr};
     cudaEvent_t ev_fork[kMaxOctaves] = {nullptr}, ev_join[kMaxOctaves] = {nullptr}, ev_counts[kMaxOctaves] = {nullptr};
@@ -389,6 +390,7 @@ int build(b200sift_detector* d) {
             uint8_t* p = nullptr;
             if (int rc = dev_alloc(d, &p, d->match_scratch_bytes_)) return rc;
             sl.match_scratch = p;
+            if (int rc = dev_alloc(d, &sl.d_match_idx, (size_t)c.numFeatures)) return rc;
         }
         CU(cudaMallocHost(&sl.h_total, sizeof(int)));
         *sl.h_total = 0;
@@ -653,6 +655,27 @@ int b200sift_copy_results_async(b200sift_detector* d, float* kpts3, float* feats
         return mark_prev_read(d);
     }
     return 0;
+}
+
+int b200sift_detect_batch_host(b200sift_detector* d, const void* const* frames, int n, int rows, int cols, int is_u8,
+                               float* const* kpts3, float* const* feats4, uint16_t* const* desc, int* const* counts2,
+                               int* const* match_idx) {
+    if (!d || !frames || n < 0) return fail(B200SIFT_EINVAL, "bad argument");
+    for (int i = 0; i < n; i++) {
+        if (!frames[i]) return fail(B200SIFT_EINVAL, "frame %d is null", i);
+        int rc = is_u8 ? b200sift_detect_host_u8_async(d, static_cast<const uint8_t*>(frames[i]), rows, cols)
+                       : b200sift_detect_host_async(d, static_cast<const float*>(frames[i]), rows, cols);
+        if (rc) return rc;
+        if (match_idx && match_idx[i]) {
+            Slot& cur = d->cur();
+            if ((rc = b200sift_match_consecutive_async(d, cur.d_match_idx))) return rc;
+            CU(cudaMemcpyAsync(match_idx[i], cur.d_match_idx, (size_t)d->cfg.numFeatures * sizeof(int), cudaMemcpyDeviceToHost, cur.stream));
+        }
+        if ((rc = b200sift_copy_results_async(d, kpts3 ? kpts3[i] : nullptr, feats4 ? feats4[i] : nullptr, desc ? desc[i] : nullptr,
+                                              counts2 ? counts2[i] : nullptr)))
+            return rc;
+    }
+    return sync_all(d);
 }
 
 void* b200sift_stream(b200sift_detector* d) { return d ? (void*)d->cur().stream : nullptr; }

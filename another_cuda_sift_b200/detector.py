@@ -205,21 +205,29 @@ class Detector:
                                                    host.desc.data_ptr(), host.counts.data_ptr()))
 
     def detectAndComputeBatch(self, frames, results, match_out=None):
-        """Frames of a batch, pipelined: the host->device copy of frame i+1 overlaps the graph of frame i;
-        results[i] (HostResults) receives frame i; match_out[i] (pinned int32 torch tensors), when given,
-        receives the matches of frame i-1 -> frame i. One synchronisation at the end."""
-        import torch
-
-        k = self.frames_in_flight
-        idx = [torch.empty(self.config.numFeatures, dtype=torch.int32, device="cuda") for _ in range(k)] if match_out is not None else None
-        for i, f in enumerate(frames):
-            self.detectAndComputeAsync(f)
-            if match_out is not None:
-                self.matchConsecutiveAsync(idx[i % k])
-                with torch.cuda.stream(torch.cuda.ExternalStream(self.stream)):  # the latest frame's stream
-                    match_out[i].copy_(idx[i % k], non_blocking=True)
-            self.copyResultsAsync(results[i])
-        self.synchronize()
+        """Frames of a batch, pipelined, through ONE native call (b200sift_detect_batch_host: the loop of
+        tool/extract_and_match_example.cc:57-101 without a host synchronisation per frame): the host->device copy
+        of frame i+1 overlaps the graph of frame i; results[i] (HostResults) receives frame i; match_out[i] (pinned
+        int32 torch tensors), when given, receives the matches of frame i-1 -> frame i. `frames`: float32 or uint8
+        [rows, cols] numpy arrays / CPU torch tensors (pinned for the copies to overlap), all of one dtype."""
+        n = len(frames)
+        if n == 0:
+            return
+        arrs = [f.numpy() if (hasattr(f, "numpy") and not isinstance(f, np.ndarray)) else f for f in frames]
+        is_u8 = arrs[0].dtype == np.uint8
+        arrs = [np.ascontiguousarray(a, dtype=np.uint8 if is_u8 else np.float32) for a in arrs]
+        rows, cols = arrs[0].shape
+        if any(a.shape != (rows, cols) for a in arrs):
+            raise B200SiftError("all frames of a batch must have the same size")
+        ptrs = lambda vals: (C.c_void_p * n)(*vals)
+        check(self.lib.b200sift_detect_batch_host(
+            self._handle(), ptrs([a.ctypes.data for a in arrs]), n, rows, cols, int(is_u8),
+            ptrs([r.kpts.data_ptr() for r in results]), ptrs([r.feats.data_ptr() for r in results]),
+            ptrs([r.desc.data_ptr() for r in results]), ptrs([r.counts.data_ptr() for r in results]),
+            ptrs([m.data_ptr() for m in match_out]) if match_out is not None else None))
+        self._keep = arrs[-self.frames_in_flight:]
+        self.total_size = int(results[-1].counts[0])
+        self._refresh_views()
 
     @property
     def frames_in_flight(self) -> int:

@@ -140,6 +140,15 @@ B200SIFT_API int b200sift_time_frames_pipelined(b200sift_detector* det, int warm
  * copied on a separate copy stream meanwhile. */
 B200SIFT_API int b200sift_match_consecutive_async(b200sift_detector* det, int* d_out_idx);
 B200SIFT_API int b200sift_copy_results_async(b200sift_detector* det, float* kpts3, float* feats4, uint16_t* desc, int* counts2);
+/* The loop of tool/extract_and_match_example.cc:57-101 over a batch of n host frames in ONE call, pipelined, with a
+ * single synchronisation at the end: for every frame b200sift_detect_host_async (or the 8-bit variant when is_u8),
+ * then, where match_idx && match_idx[i], b200sift_match_consecutive_async followed by a copy of the numFeatures
+ * indices to match_idx[i] (the match of frame i-1 -> frame i), then b200sift_copy_results_async into kpts3[i] /
+ * feats4[i] / desc[i] / counts2[i] (any of the four arrays, or single entries, may be NULL). Host buffers should be
+ * pinned for the copies to overlap. Blocks until the whole batch is done. */
+B200SIFT_API int b200sift_detect_batch_host(b200sift_detector* det, const void* const* frames, int n, int rows, int cols, int is_u8,
+                                            float* const* kpts3, float* const* feats4, uint16_t* const* desc, int* const* counts2,
+                                            int* const* match_idx);
 
 /* Per-kernel-class device time of one frame (ms, averaged over `iters` eager frames with a CUDA event
  * after every launch on the detector's stream): ms_per_class[B200SIFT_K_COUNT]; launches_per_class (may

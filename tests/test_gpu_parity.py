@@ -239,3 +239,13 @@ def test_pipelined_batch_equals_blocking_frames():
         if i:
             assert np.array_equal(midx[i][:want[i - 1][0]].numpy(), want_idx[i]), i
             assert (want_idx[i] >= 0).mean() > 0.2
+    # the same batch handed over as the 8-bit frames the float images are cast from: identical results
+    det3 = _det(cols, rows, nf)
+    res8 = [HostResults(nf) for _ in frames]
+    midx8 = [torch.full((nf,), -7, dtype=torch.int32).pin_memory() for _ in frames]
+    det3.detectAndComputeBatch([torch.from_numpy(f.astype(np.uint8)).pin_memory().numpy() for f in frames], res8, midx8)
+    for i, (n, k, f, d) in enumerate(want):
+        assert res8[i].total == n
+        assert np.array_equal(res8[i].kpts[:n].numpy(), k) and np.array_equal(res8[i].desc[:n].numpy().view(np.uint16), d.view(np.uint16))
+        if i:
+            assert np.array_equal(midx8[i][:want[i - 1][0]].numpy(), want_idx[i]), i
