@@ -638,7 +638,7 @@ constexpr uint32_t kStreamPanel = 128 * 128;           // one swizzled K panel: 
 constexpr uint32_t kStreamTile = 2 * kStreamPanel + 4096;
 constexpr int kStreamBufs = 4;
 constexpr int kStreamScan = 512;                       // 16 scan warps: (lane quarter, query half, column half)
-constexpr int kStreamThreads = kStreamScan + 32;       // + one warp whose lane 0 issues the TMA loads and the MMAs
+constexpr int kStreamThreads = kStreamScan + 64;       // + one warp that issues the MMAs and one that issues the TMA loads
 constexpr uint32_t kStreamAcol = 256;                  // first TMEM column of the query tiles
 constexpr uint32_t kStreamAcols = 72;                  // 32-bit columns per query tile (144 halves)
 constexpr size_t kStreamSmem = kStreamBufs * (size_t)kStreamTile + 128 + (kCand + 1) * kStreamScan * sizeof(int) + 2 * kStreamScan * sizeof(float);
@@ -673,8 +673,8 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
     constexpr int TN = kStreamTN;
     extern __shared__ __align__(1024) uint8_t smem[];
     uint8_t* sB = smem;                                     // 4 tile buffers
-    uint64_t* s_bar = reinterpret_cast<uint64_t*>(sB + kStreamBufs * kStreamTile);  // [0..1] MMA done (query half), [2..5] tile landed
-    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 8);
+    uint64_t* s_bar = reinterpret_cast<uint64_t*>(sB + kStreamBufs * kStreamTile);  // [0..1] MMA done (query half), [2..5] tile landed, [6..9] tile buffer free
+    uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 12);
     int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);
     int* s_cand = reinterpret_cast<int*>(s_bar + 16);       // [kCand][512] survivor columns (chunk-relative) of thread tid, then [512] counts
     int* s_cn = s_cand + kCand * kStreamScan;
@@ -705,7 +705,7 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
     }
     if (tid == 0) {
         s_nbmax[0] = 0;
-        for (int i = 0; i < 2 + kStreamBufs; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar + i)));
+        for (int i = 0; i < 2 + 2 * kStreamBufs; i++) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(s_bar + i)));
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
     asm volatile("tcgen05.fence::before_thread_sync;");
@@ -755,6 +755,7 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
     const bool bail = !(nbmax <= kAugMaxNorm);
     const int S = bail ? 0 : 2 * T;
 
+    const int nh = two_tiles ? 2 : 1;
     // step s works on tile s % T -> buffer s % 4; rows past the train set are zero-filled by the TMA unit, rows past
     // the chunk are real rows of the next chunk whose |b|^2 chunk says +inf
     auto load_tile = [&](int s) {
@@ -785,28 +786,33 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
                 ::"r"(tmem + hq * TN), "r"(ta), "l"(db), "r"(idesc), "r"(acc) : "memory");
         }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar + 8u * hq) : "memory");
+        if (hq == nh - 1)  // the step's last MMAs: once they are done the tile buffer can be refilled
+            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];"
+                         ::"r"(bar + 8u * (2 + kStreamBufs + s % kStreamBufs)) : "memory");
     };
     const float slack = __fmaf_rn(4e-5f, __fadd_rn(na, nbmax), 1e-3f);
     const bool scans = scanner && (half_id == 0 || two_tiles);
-    const int nh = two_tiles ? 2 : 1;
     int cn = 0;
 
-    if (!scanner) {
+    if (warp == kStreamScan / 32 + 1) {
+        // ---- producer warp: the TMA loads have their own issuing thread. (Measured with clock64 stamps: issued from the
+        // MMA thread they queue behind its UTCHMMAs and cost it ~390 of the ~1700 cycles of a step, during which no
+        // further MMAs are queued.) Tile s goes into buffer s % 4 once the MMAs of tile s - 4 have completed.
+        if (S > 0 && elect_one()) {
+            for (int s = 0; s < S; s++) {
+                if (s >= kStreamBufs) mbar_wait(bar + 8u * (2 + kStreamBufs + s % kStreamBufs), (uint32_t)(s / kStreamBufs - 1) & 1u);
+                load_tile(s);
+            }
+        }
+        __syncwarp();
+    } else if (!scanner) {
         // ---- issuer warp: per step and query half h, wait until the scan warps of that half have drained their
         // accumulator (named barrier 1 + h: 256 arrivals + this warp), then queue the 9 MMAs of the next step behind
         // whatever the tensor pipe is still working on. Draining half 0 overlaps the MMAs of half 1 and vice versa.
-        if (S > 0 && elect_one())
-            for (int s = 0; s < min(S, kStreamBufs); s++) load_tile(s);
-        __syncwarp();
         for (int s = 0; s < S; s++) {
             for (int h = 0; h < nh; h++) {
                 if (s > 0) asm volatile("barrier.cta.sync %0, %1;" ::"r"(1 + h), "r"(kStreamScan / 2 + 32) : "memory");
                 if (elect_one()) issue_mma(s, h);
-                __syncwarp();
-            }
-            // every accumulator of step s-1 has been drained, so its MMAs are complete and its tile buffer is free
-            if (s > 0 && s + kStreamBufs - 1 < S) {
-                if (elect_one()) load_tile(s + kStreamBufs - 1);
                 __syncwarp();
             }
         }

@@ -26,10 +26,14 @@ __device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint
         : "r"(addr))
 
 // mode bit 0: warps drain TMEM (each warp 128 columns = 4 x32 loads per iteration); bit 1: thread 0 of the LAST warp issues MMAs
-__global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_iter, long long* out, unsigned* sink) {
+// bit 5 (32): the warp before the MMA warp streams 32 KB bulk copies global -> shared memory for as long as the MMA warp runs;
+// bit 6 (64): the B operand is read through K-major SWIZZLE_128B descriptors (as the matcher does) instead of the no-swizzle layout
+__global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_iter, long long* out, unsigned* sink, const uint4* gsrc) {
     extern __shared__ __align__(1024) uint8_t smem[];
     __shared__ uint32_t s_tmem;
-    __shared__ uint64_t s_bar, s_bar2;
+    __shared__ uint64_t s_bar, s_bar2, s_bar3;
+    __shared__ volatile int s_stop;
+    __shared__ int s_copies;
     const int tid = threadIdx.x, warp = tid >> 5, nwarps = blockDim.x >> 5;
     for (int i = tid; i < 3 * 36864 / 4; i += blockDim.x) reinterpret_cast<uint32_t*>(smem)[i] = 0;
     if (warp == 0) {
@@ -39,6 +43,8 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
     if (tid == 0) {
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar)));
         asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar2)));
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&s_bar3)));
+        s_stop = 0; s_copies = 0;
         asm volatile("fence.mbarrier_init.release.cluster;");
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
@@ -64,7 +70,11 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
 #pragma unroll
                 for (int k = 0; k < 9; k++) {
                     const uint64_t da = umma_desc(smem_u32(smem) + k * 2 * 2048, 2048, 128);
-                    const uint64_t db = umma_desc(smem_u32(smem) + 36864 + k * 2 * 2048, 2048, 128);
+                    uint64_t db = umma_desc(smem_u32(smem) + 36864 + k * 2 * 2048, 2048, 128);
+                    if ((mode & 64) && k < 8) {
+                        const uint32_t a = smem_u32(smem) + 36864 + (k >> 2) * 16384 + (k & 3) * 32;
+                        db = (uint64_t)((a & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+                    }
                     const uint32_t accf = k > 0 ? 1u : 0u;
                     if (mode & 4)
                         asm volatile(
@@ -89,6 +99,25 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
             }
             phase ^= 1;
         }
+        s_stop = 1;
+        }
+        __syncwarp();
+    } else if ((mode & 32) && warp == nwarps - 2) {
+        uint32_t el;
+        asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.u32 %0, 1, 0, p;\n\t}" : "=r"(el));
+        if (el) {
+            uint32_t ph = 0; int n = 0;
+            while (!s_stop) {
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(&s_bar3)), "r"(32768u) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                             ::"r"(smem_u32(smem) + 2 * 36864), "l"(gsrc + (size_t)(n & 255) * 2048), "r"(32768u), "r"(smem_u32(&s_bar3)) : "memory");
+                uint32_t done = 0;
+                while (!done)
+                    asm volatile("{\n\t.reg .pred p;\n\tmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\tselp.u32 %0, 1, 0, p;\n\t}"
+                                 : "=r"(done) : "r"(smem_u32(&s_bar3)), "r"(ph) : "memory");
+                ph ^= 1; n++;
+            }
+            s_copies = n;
         }
         __syncwarp();
     } else if (drains) {
@@ -103,6 +132,8 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
     }
     const long long t1 = clock64();
     if ((tid & 31) == 0 && blockIdx.x == 0) out[warp] = t1 - t0;
+    __syncthreads();
+    if (tid == 0 && blockIdx.x == 0) out[63] = s_copies;
     if (acc == 0x12345678u) sink[0] = acc;
     asm volatile("tcgen05.fence::before_thread_sync;");
     __syncthreads();
@@ -112,6 +143,7 @@ __global__ void __launch_bounds__(1024) probe(int mode, int iters, int mma_per_i
 int main() {
     long long* d_out; unsigned* d_sink;
     cudaMalloc(&d_out, 64 * sizeof(long long)); cudaMalloc(&d_sink, 4);
+    uint4* d_src; cudaMalloc(&d_src, 256 * 32768); cudaMemset(d_src, 0, 256 * 32768);
     const size_t smem = 3 * 36864;
     cudaFuncSetAttribute(probe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     const int iters = 2000;
@@ -131,6 +163,10 @@ int main() {
         {6, 1, 72, "mma A-from-TMEM N=128, 72 per wait, one commit"},
         {22, 1, 72, "mma A-from-TMEM N=128, 72 per wait, commit every 9"},
         {23, 9, 72, "same + 8 drain warps"},
+        {6 + 64, 1, 72, "mma A-from-TMEM N=128, 72 per wait, B through SWIZZLE_128B"},
+        {6 + 32, 2, 72, "mma A-from-TMEM N=128 (no-swizzle B) + bulk-copy stream"},
+        {6 + 64 + 32, 2, 72, "mma A-from-TMEM N=128, SWIZZLE_128B B + bulk-copy stream"},
+        {7 + 64 + 32, 10, 72, "same + 8 drain warps"},
     };
     cudaEvent_t e0, e1;
     cudaEventCreate(&e0); cudaEventCreate(&e1);
@@ -139,7 +175,7 @@ int main() {
             const int it = grid == 1 ? iters : iters * 20;  // long enough for the power management to settle
             cudaMemset(d_out, 0, 64 * sizeof(long long));
             cudaEventRecord(e0);
-            probe<<<grid, c.warps * 32, smem>>>(c.mode, it, c.mma, d_out, d_sink);
+            probe<<<grid, c.warps * 32, smem>>>(c.mode, it, c.mma, d_out, d_sink, d_src);
             cudaEventRecord(e1);
             cudaError_t e = cudaDeviceSynchronize();
             float ms = 0.f;
@@ -148,6 +184,7 @@ int main() {
             cudaMemcpy(h, d_out, sizeof(h), cudaMemcpyDeviceToHost);
             printf("grid %3d  %-52s err=%s  cycles/iter: warp0 %.1f  last warp %.1f   %.2f ms -> %.0f MHz\n", grid, c.name, cudaGetErrorString(e),
                    (double)h[0] / it, (double)h[c.warps - 1] / it, ms, (double)h[c.warps - 1] / (ms * 1e3));
+            if (c.mode & 32) printf("          bulk copies: %lld x 32 KB = %.1f B/cycle\n", h[63], (double)h[63] * 32768 / (double)h[c.warps - 1]);
         }
     }
     return 0;
