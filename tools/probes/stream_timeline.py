@@ -1,3 +1,12 @@
+"""Development probe (not product, not run by the tests): prints the clock64 stamps of one CTA of the streaming
+matcher filter -- when the MMA-issuing thread starts waiting for a drained accumulator, passes the barrier and has
+issued its 9 MMAs; when a scan warp starts waiting for the MMAs, sees them done and has released the accumulator.
+
+It needs an INSTRUMENTED build of csrc/match_tc.cu: a `__device__ long long g_tl[1024]` written at those six points
+(index step * 16 + {0,1,2} issuer half 0, {4,5,6} issuer half 1, {8,9,10} scan warp half 0, {12,13,14} half 1) for
+one (blockIdx.x, blockIdx.y), and an exported `int b200sift_debug_timeline(long long* out)` that copies it out with
+cudaMemcpyFromSymbol. The stock library does not export that symbol and this script then fails at the lookup.
+profiles/r1_match_stream.md quotes what it showed."""
 import sys, ctypes as C, numpy as np, torch
 sys.path.insert(0, '/root/repo')
 from another_cuda_sift_b200 import matchBruteForce, _lib
