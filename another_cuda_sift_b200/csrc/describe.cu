@@ -291,6 +291,8 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     __shared__ __align__(128) float s_priv[kDescWarps][kPrivSlots][32];
     __shared__ int s_ring[kDescWarps][kRing];
     __shared__ int s_next;
+    __shared__ int4 s_cbox[16];
+    __shared__ int2 s_cstep[16];
     float* priv = &s_priv[warp][0][lane];
 #pragma unroll
     for (int k = 0; k < kPrivSlots; k++) priv[k * 32] = 0.f;  // every flush leaves the columns zeroed again
@@ -303,8 +305,7 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     const float3 kp = o.fin_kp[j];
     const float4 ft = o.fin_ft[j];
     if (tid == 0) s_next = 0;
-    for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0;
-    __syncthreads();
+    for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0;  // the barrier after the cell boxes below covers these
 
     // unpackOctave (SiftOps.cu:389-401)
     const int packed = (int)ft.x;
@@ -335,19 +336,13 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     const int stack_left = (int)(stack_len - img_off);  // floats from this layer to the end of the octave's stack
     const float ch = cos_u * hist_width, sh = sin_u * hist_width;  // window -> patch coordinates
 
-    int* ring = s_ring[warp];
-    const unsigned lt_mask = (1u << lane) - 1u;
-    const unsigned uw1 = (unsigned)(ow - 1), uh1 = (unsigned)(oh - 1);
-    for (;;) {
-        int t = 0;
-        if (lane == 0) t = atomicAdd(&s_next, 1);
-        t = __shfl_sync(0xffffffffu, t, 0);
-        if (t >= 16) break;
-        const int cell = kCellOrder[t];
+    if (tid < 16) {
+        // cell t of the queue: its extent in rotated coordinates (r_rot = rbin - 1.5), then its bounding box in patch
+        // offsets: i = (r cos - c sin) * hist_width, j = (r sin + c cos) * hist_width. floor/ceil leave up to a pixel of
+        // slack, six orders of magnitude more than the rounding of these products. One thread per cell, once per
+        // keypoint (the warps that own the cells used to recompute this, 83 warp instructions per cell).
+        const int cell = kCellOrder[tid];
         const int R = cell >> 2, C = cell & 3;
-        // cell extent in rotated coordinates (r_rot = rbin - 1.5), then its bounding box in patch offsets:
-        // i = (r cos - c sin) * hist_width, j = (r sin + c cos) * hist_width. floor/ceil leave up to a pixel of
-        // slack, six orders of magnitude more than the rounding of these products
         const float fR = (float)R, fC = (float)C;
         const float rlo = (R == 0 ? -1.f : fR) - 1.5f, rhi = fR - 0.5f;
         const float clo = (C == 0 ? -1.f : fC) - 1.5f, chi = fC - 0.5f;
@@ -358,12 +353,32 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
         const int j0 = max(-radius, __float2int_rd(fminf(ja, jb) + fminf(jc, jd)));
         const int j1 = min(radius, __float2int_ru(fmaxf(ja, jb) + fmaxf(jc, jd)));
         const int wj = j1 - j0 + 1, wi = i1 - i0 + 1;
-        if (wj <= 0 || wi <= 0) continue;
-        const int n = wi * wj;
-        // (k + 0.5) / wj is never within rounding distance of an integer, so these are exact floors
-        const float inv_wj = __frcp_rn((float)wj);
-        const int step_r = __float2int_rd(32.5f * inv_wj), step_c = 32 - step_r * wj;
-        int prow = __float2int_rd(((float)lane + 0.5f) * inv_wj), pcol = lane - prow * wj;
+        const bool empty = wj <= 0 || wi <= 0;
+        // (k + 0.5) / wj is never within rounding distance of an integer, so this is an exact floor
+        const int step_r = empty ? 0 : __float2int_rd(32.5f * __frcp_rn((float)wj));
+        s_cbox[tid] = make_int4(i0, j0, wj, empty ? 0 : wi * wj);
+        s_cstep[tid] = make_int2(step_r, 32 - step_r * wj);
+    }
+    __syncthreads();
+
+    int* ring = s_ring[warp];
+    const unsigned lt_mask = (1u << lane) - 1u;
+    const unsigned uw1 = (unsigned)(ow - 1), uh1 = (unsigned)(oh - 1);
+    for (;;) {
+        int t = 0;
+        if (lane == 0) t = atomicAdd(&s_next, 1);
+        t = __shfl_sync(0xffffffffu, t, 0);
+        if (t >= 16) break;
+        const int cell = kCellOrder[t];
+        const int R = cell >> 2, C = cell & 3;
+        const float fR = (float)R, fC = (float)C;
+        const int4 cbox = s_cbox[t];  // bounding box and scan steps, computed once per keypoint by 16 threads (below)
+        const int i0 = cbox.x, j0 = cbox.y, wj = cbox.z, n = cbox.w;
+        if (n <= 0) continue;
+        const int2 cstep = s_cstep[t];
+        const int step_r = cstep.x, step_c = cstep.y;
+        // (k + 0.5) / wj is never within rounding distance of an integer, so this is an exact floor
+        int prow = __float2int_rd(((float)lane + 0.5f) * __frcp_rn((float)wj)), pcol = lane - prow * wj;
         // truncf(rbin) == R written as an interval: (-1, 1) for R == 0, [R, R+1) otherwise
         const float r_gt = R == 0 ? -1.f : __uint_as_float(__float_as_uint(fR) - 1u), r_lt = fR + 1.f;
         const float c_gt = C == 0 ? -1.f : __uint_as_float(__float_as_uint(fC) - 1u), c_lt = fC + 1.f;
