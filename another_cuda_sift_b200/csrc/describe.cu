@@ -88,11 +88,15 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
         const float* g0 = o.gauss + ls * layer;  // DoG[layer] = G[layer+1] - G[layer]
         const float fh1 = (float)o.h - 1.f, fw1 = (float)o.w - 1.f;
 
+        // idx / side without an integer division: (idx + 0.5) / side is at least 0.5 / side >= 4.9e-4 away from an integer,
+        // the float product is off by < 1.3e-4 (idx < 2^20, side <= 1024), so the floor is exact
+        const float inv_side = __frcp_rn((float)side);
         auto geometry = [&](int idx, int& px_off, int& py_off, const float*& p) -> bool {
             if (idx >= total_dim) return false;
-            py_off = (int)__fsub_rn((float)(idx / side), radius);
+            const int row = __float2int_rd(__fmul_rn((float)idx + 0.5f, inv_side));
+            py_off = (int)__fsub_rn((float)row, radius);
             const int py = base_py + py_off;
-            px_off = (int)__fsub_rn((float)(idx % side), radius);
+            px_off = (int)__fsub_rn((float)(idx - row * side), radius);
             const int px = base_px + px_off;
             if (py < 1 || (float)py >= fh1 || px < 1 || (float)px >= fw1) return false;
             p = g0 + (size_t)py * h_dim + px;

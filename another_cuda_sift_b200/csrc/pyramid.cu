@@ -173,8 +173,10 @@ __device__ __forceinline__ void tail_layer(const Taps& t, float* s_cur, float* s
     float tap[NT];
 #pragma unroll
     for (int k = 0; k < NT; k++) tap[k] = t.v[k];
+    // i / w without an integer division: n <= 4096, so the float floor of (i + 0.5) / w is exact
+    const float inv_w = __frcp_rn((float)w);
     for (int i = tid; i < n; i += kTailThreads) {
-        const int y = i / w, x = i - y * w;
+        const int y = __float2int_rd(((float)i + 0.5f) * inv_w), x = i - y * w;
         const int* rt = s_rtab + (y - R + kTailR);
         float v[NT];
 #pragma unroll
@@ -186,7 +188,7 @@ __device__ __forceinline__ void tail_layer(const Taps& t, float* s_cur, float* s
     }
     __syncthreads();
     for (int i = tid; i < n; i += kTailThreads) {
-        const int y = i / w, x = i - y * w;
+        const int y = __float2int_rd(((float)i + 0.5f) * inv_w), x = i - y * w;
         const int* ct = s_ctab + (x - R + kTailR);
         const float* row = s_tmp + y * w;
         float v[NT];
