@@ -453,6 +453,18 @@ def main():
     gms = {g: sum(prof[k]["ms"] for k in ks) for g, ks in groups.items()}
     dom = max(gms, key=gms.get)
     dom_ms = gms[dom]
+    eager_ms = dom_ms
+    how = ("CUDA events around every launch of one frame run eagerly on a single stream (b200sift_profile_frame); "
+           "in the frame graph these launches overlap")
+    if dom == "blur_vh_kernel":
+        # The blur launches as the product runs them: the frame GRAPH truncated after the pyramid, replayed and timed with
+        # CUDA events on its stream (b200sift_time_stages). That interval also holds the 5 downsample launches and the tail
+        # kernel on the blur chain's critical path, so the blur rate derived from it is a lower bound; the eager per-launch
+        # figure (5-6 us of launch latency per dependent small kernel) is kept as eager_ms_per_frame.
+        dom_ms = ex["stages"]["pyramid"]
+        how = ("the frame graph truncated after the pyramid (27 blur launches + 5 downsample + tail kernel), replayed and timed "
+               "with CUDA events on its stream (b200sift_time_stages): a lower bound of the blur rate; eager_ms_per_frame is the "
+               "sum over the same launches run eagerly with an event after each")
     dom_bytes = sum(cb[k] for k in groups[dom])
     dom_launches = sum(prof[k]["launches"] for k in groups[dom])
     achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
@@ -486,8 +498,7 @@ def main():
                      "bytes_per_launch": dom_bytes / max(dom_launches, 1), "us_per_launch": dom_ms * 1e3 / max(dom_launches, 1),
                      "by_kernel": {g: {"ms_per_frame": round(gms[g], 5),
                                        "GB/s": round(sum(cb[k] for k in groups[g]) / (gms[g] * 1e-3) / 1e9, 1)} for g in groups},
-                     "note": "per-launch times from CUDA events around every launch of one frame run on a single stream "
-                             "(b200sift_profile_frame); in the frame graph these launches overlap"},
+                     "eager_ms_per_frame": eager_ms, "note": how},
         "roofline_frame": {"bytes": frame_bytes, "achieved": frame_bytes / (ex["pipe_ms"] * 1e-3) / 1e9,
                            "frac": frame_bytes / (ex["pipe_ms"] * 1e-3) / 1e9 / hbm_peak,
                            "note": "SURVEY 8(d) algorithmic bytes of one frame / pipelined frame time"},
