@@ -45,7 +45,7 @@ SIGNATURES = {
     "b200sift_octave_info": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int)]),
     "b200sift_detect_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_int)]),
     "b200sift_detect_host_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
-    "b200sift_detect_device_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t]),
+    "b200sift_detect_device_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p]),
     "b200sift_detect_host_u8_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int]),
     "b200sift_sync": (C.c_int, [C.c_void_p, C.POINTER(C.c_int)]),
     "b200sift_stream": (C.c_void_p, [C.c_void_p]),

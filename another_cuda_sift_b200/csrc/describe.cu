@@ -256,6 +256,20 @@ __device__ __forceinline__ float rsqrt_approx(float x) {  // x must be a normal 
     return y;
 }
 
+// obin of one descriptor sample exactly as the reference computes it (fast_atan2f, SiftOps.cu:403-419, and
+// `fast_atan2f(dy, dx) / M_PI * 180.f`, `(grad_ori - angle) * bins_per_degree`, :565-568), in the instruction
+// sequence of its sm_100a SASS: r by IEEE division, FMUL(r, 0.1963) -> FFMA(., r, -0.9817) -> FFMA(., r, base),
+// the degree conversion in double. Out of line: it runs for a few samples in 10,000 and must not cost the vote
+// loop registers.
+__device__ __noinline__ float exact_obin(float dx, float dy, float abs_y, bool neg, float angle) {
+    const float r = neg ? __fdiv_rn(__fadd_rn(dx, abs_y), __fsub_rn(abs_y, dx)) : __fdiv_rn(__fsub_rn(dx, abs_y), __fadd_rn(dx, abs_y));
+    float a = __fmaf_rn(__fmaf_rn(__fmul_rn(r, 0.1963f), r, -0.9817f), r, neg ? 2.356194490f : 0.785398163f);
+    a = dy < 0.f ? -a : a;
+    float grad_ori = (float)((double)a / 3.14159265358979323846 * 180.0);
+    if (grad_ori < 0.f) grad_ori = __fadd_rn(grad_ori, 360.f);
+    return __fmul_rn(__fsub_rn(grad_ori, angle), 8 / 360.f);
+}
+
 // One CTA per returned keypoint (global index g over octaves in ascending order, truncated at
 // numFeatures: utils/CudaMemcpyUtils.cu:38-67). A launch covers an octave range, so that the descriptors of
 // octave 0 can start while the small octaves are still being detected; the range that ends at the last
@@ -449,7 +463,14 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
                 ang = dy < 0.f ? -ang : ang;
                 float grad_ori = ang * 57.29577951308232f;
                 grad_ori = grad_ori < 0.f ? grad_ori + 360.f : grad_ori;
-                const float obin = __fmul_rn(__fsub_rn(grad_ori, angle), bins_per_degree);
+                float obin = __fmul_rn(__fsub_rn(grad_ori, angle), bins_per_degree);
+                // The vote is a discontinuous function of the angle in two places: where fast_atan2f changes sign (the
+                // +360 wrap meets the truncating modff: obin and obin - 8 do not vote alike, quirk Q11) and where obin
+                // crosses a (negative) integer. The approximations above are good to ~2e-6 bins, so within 1e-4 bins /
+                // 1e-5 rad of either the reference's own instruction sequence decides (SASS of SiftOps.cu:403-419,565:
+                // IEEE division, FMUL + 2 FFMA, then double / pi * 180): identical bins, ~2 samples in 10,000.
+                if (fabsf(ang) < 1e-5f || fabsf(__fsub_rn(obin, rintf(obin))) < 1e-4f)
+                    obin = exact_obin(dx, dy, abs_y, neg, angle);
                 const float mag = grad_mag * weight * kFix32;  // x 2^15: exact scaling, undone after the integer sum
                 const float obin_t = truncf(obin);
                 const float obin_frac = __fsub_rn(obin, obin_t);

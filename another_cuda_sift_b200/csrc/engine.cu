@@ -107,6 +107,7 @@ struct b200sift_detector {
     int in_pitch = 0;
     size_t u8_pitch = 0;
     cudaStream_t copy_stream = nullptr;
+    cudaEvent_t ev_user = nullptr;    // orders a caller's stream before the engine's use of a caller-owned device buffer
     unsigned long long frame_no = 0;  // frames enqueued so far; frame n lives in slot n % kSlots
     size_t rowcount_bytes = 0;
     size_t match_scratch_bytes_ = 0;
@@ -314,6 +315,7 @@ int build(b200sift_detector* d) {
     int prio_least = 0, prio_greatest = 0;
     CU(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
     CU(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
+    CU(cudaEventCreateWithFlags(&d->ev_user, cudaEventDisableTiming));
 
     for (int si = 0; si < kSlots; si++) {
         Slot& sl = d->slot[si];
@@ -523,6 +525,7 @@ int b200sift_destroy(b200sift_detector* d) {
         }
     }
     if (d->copy_stream) cudaStreamDestroy(d->copy_stream);
+    if (d->ev_user) cudaEventDestroy(d->ev_user);
     for (void* p : d->allocs) cudaFree(p);
     delete d;
     return 0;
@@ -598,12 +601,16 @@ int b200sift_detect_host(b200sift_detector* d, const float* img, int rows, int c
     return b200sift_sync(d, total);
 }
 
-int b200sift_detect_device_async(b200sift_detector* d, const float* d_img, size_t pitch_bytes) {
+int b200sift_detect_device_async(b200sift_detector* d, const float* d_img, size_t pitch_bytes, void* producer_stream) {
     if (!d || !d_img) return fail(B200SIFT_EINVAL, "null argument");
     const int cols = d->cfg.col_width, rows = d->cfg.row_width;
     if (pitch_bytes < (size_t)cols * 4) return fail(B200SIFT_EINVAL, "pitch smaller than a row");
     Slot* sl = nullptr;
     if (int rc = begin_frame(d, &sl, false)) return rc;
+    // The slot streams are cudaStreamNonBlocking: nothing orders them against the stream that produced the image
+    // (not even the legacy default stream), so the copy below waits for an event recorded there.
+    CU(cudaEventRecord(d->ev_user, static_cast<cudaStream_t>(producer_stream)));
+    CU(cudaStreamWaitEvent(sl->stream, d->ev_user, 0));
     CU(cudaMemcpy2DAsync(sl->d_input, (size_t)d->in_pitch * 4, d_img, pitch_bytes, (size_t)cols * 4, rows,
                          cudaMemcpyDeviceToDevice, sl->stream));
     return launch_frame(d, *sl, false);
@@ -631,6 +638,7 @@ static int mark_prev_read(b200sift_detector* d) {
 
 int b200sift_match_consecutive_async(b200sift_detector* d, int* d_out_idx) {
     if (!d || !d_out_idx) return fail(B200SIFT_EINVAL, "null argument");
+    if (d->frame_no == 0) return fail(B200SIFT_ESTATE, "no frame has been processed");
     Slot &cur = d->cur(), &prv = d->prev();
     CU(cudaStreamWaitEvent(cur.stream, prv.ev_done, 0));
     // query = previous frame's descriptors, train = this frame's; both sizes are read on the device
@@ -978,9 +986,15 @@ int b200sift_time_stages(b200sift_detector* d, int iters, float* ms5) {
 
 // ---- matcher
 namespace {
+// One cached scratch buffer per device, shared by every b200sift_match_device call on that device. Calls on
+// different streams are serialised through an event recorded after each call's last kernel (the next user of the
+// scratch, on whatever stream, waits for it), so concurrent matchers cannot overwrite each other's survivor records.
 std::mutex g_scratch_mu;
 void* g_scratch[64] = {nullptr};
 size_t g_scratch_bytes[64] = {0};
+cudaEvent_t g_scratch_ev[64] = {nullptr};
+cudaStream_t g_scratch_last[64] = {nullptr};
+bool g_scratch_used[64] = {false};
 }  // namespace
 
 int b200sift_match_device(const uint16_t* d_query, int nq, const uint16_t* d_train, int nt, int* d_out_idx, void* stream) {
@@ -1006,11 +1020,16 @@ int b200sift_match_device(const uint16_t* d_query, int nq, const uint16_t* d_tra
             g_scratch_bytes[dev] = need;
         }
         scratch = g_scratch[dev];
+        if (!g_scratch_ev[dev]) CU(cudaEventCreateWithFlags(&g_scratch_ev[dev], cudaEventDisableTiming));
+        if (g_scratch_used[dev] && g_scratch_last[dev] != s) CU(cudaStreamWaitEvent(s, g_scratch_ev[dev], 0));
+        if (int rc = match_launch(reinterpret_cast<const __half*>(d_query), nq, reinterpret_cast<const __half*>(d_train), nt, d_out_idx,
+                                  scratch, need, s))
+            return fail(B200SIFT_EINVAL, rc == -2 ? "train descriptors: tensor map rejected (the pointer must be 16-byte aligned)" : "matcher scratch too small");
+        CU(cudaGetLastError());
+        CU(cudaEventRecord(g_scratch_ev[dev], s));
+        g_scratch_last[dev] = s;
+        g_scratch_used[dev] = true;
     }
-    if (int rc = match_launch(reinterpret_cast<const __half*>(d_query), nq, reinterpret_cast<const __half*>(d_train), nt, d_out_idx,
-                              scratch, need, s))
-        return fail(B200SIFT_EINVAL, rc == -2 ? "train descriptors: tensor map rejected (the pointer must be 16-byte aligned)" : "matcher scratch too small");
-    CU(cudaGetLastError());
     return 0;
 }
 

@@ -926,6 +926,7 @@ __global__ void __launch_bounds__(kRerankWarps * 32)
 match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __restrict__ src, int nt, int per,
                     const CandRec* __restrict__ rec, int* __restrict__ out_idx, const int* __restrict__ cnt_q,
                     const int* __restrict__ cnt_t) {
+    const int max_q = nq;
     if (cnt_q) {
         nt = *cnt_t;
         nq = *cnt_q;
@@ -935,7 +936,10 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
     __shared__ float s_val[kRerankWarps][kListCap];
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int q = blockIdx.x * kRerankWarps + warp;
-    if (q >= nq) return;
+    if (q >= nq) {  // device-side sizes: the grid covers max_n rows, rows past the query count report "no match"
+        if (q < max_q && lane == 0) out_idx[q] = -1;
+        return;
+    }
     const __half2* arow = reinterpret_cast<const __half2*>(des + (size_t)q * 128);
     const __half2 a0 = arow[lane], a1 = arow[lane + 32];
     // lane c <- survivors of chunk c
@@ -1051,16 +1055,27 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
 }  // namespace
 
 namespace {
+constexpr int kMaxDevices = 64;
+// Device the calling thread launches on (index into the per-device attribute tables below). One thread per GPU may
+// run concurrently: every table entry is only ever touched by the threads whose current device it belongs to, and
+// setting an attribute twice is harmless.
+int current_device() {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    return (dev >= 0 && dev < kMaxDevices) ? dev : 0;
+}
 int g_match_path = 0;  // 0 = tensor-core filter + exact re-rank, 1 = all-CUDA-core exact kernel (match.cu), 2 = as 0 with the unpipelined generic filter for large train sets
 constexpr size_t filter_smem(int tn) { return kTileBytes + (size_t)tn * 256 + tn * sizeof(float) + 64 + kCand * kFilterThreads * sizeof(int); }
 
 template <int TN, bool DBG>
 void launch_filter(dim3 grid, const __half* q, int nq, const __half* t, int nt, int per, CandRec* rec, float* dbg, cudaStream_t s,
                    const int* cnt_q = nullptr, const int* cnt_t = nullptr) {
-    static bool attr_set = false;
-    if (!attr_set) {
+    // the attribute belongs to the (device, context) pair, not to the process: track it per device
+    static size_t smem_set[kMaxDevices] = {0};
+    const int dev = current_device();
+    if (smem_set[dev] < filter_smem(TN)) {
         cudaFuncSetAttribute(match_filter_kernel<TN, DBG>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)filter_smem(TN));
-        attr_set = true;
+        smem_set[dev] = filter_smem(TN);
     }
     match_filter_kernel<TN, DBG><<<grid, kFilterThreads, filter_smem(TN), s>>>(q, nq, t, nt, per, rec, dbg, cnt_q, cnt_t);
 }
@@ -1108,10 +1123,11 @@ namespace {
 template <bool DBG, int NB>
 void launch_resident_nb(dim3 grid, size_t smem, const __half* q, int nq, const __half* t, int nt, int per, int TR, int cpc, CandRec* rec,
                         float* dbg, const float* nrm_q, const float* nrm_t, cudaStream_t s, const int* cnt_q, const int* cnt_t) {
-    static size_t smem_set = 0;
-    if (smem > smem_set) {
+    static size_t smem_set[kMaxDevices] = {0};
+    const int dev = current_device();
+    if (smem > smem_set[dev]) {
         cudaFuncSetAttribute(match_filter_resident_kernel<DBG, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        smem_set = smem;
+        smem_set[dev] = smem;
     }
     match_filter_resident_kernel<DBG, NB><<<grid, kResThreads, smem, s>>>(q, nq, t, nt, per, TR, cpc, rec, dbg, nrm_q, nrm_t, cnt_q, cnt_t);
 }
@@ -1157,10 +1173,11 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
         if (dbg) launch_filter<256, true>(grid, q, nq, t, nt, per, rec, dbg, s);
         else launch_filter<256, false>(grid, q, nq, t, nt, per, rec, dbg, s);
     } else {
-        static bool attr_set = false;
-        if (!attr_set) {
+        static bool attr_set[kMaxDevices] = {false};
+        const int dev = current_device();
+        if (!attr_set[dev]) {
             cudaFuncSetAttribute(match_filter_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStreamSmem);
-            attr_set = true;
+            attr_set[dev] = true;
         }
         // scratch: records | |b|^2 K chunks, tiled per chunk (4 KB per 128-row tile) | norms
         const int tiles = (per + kStreamTN - 1) / kStreamTN;

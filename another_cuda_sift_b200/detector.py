@@ -155,8 +155,13 @@ class Detector:
                 raise B200SiftError("device image must be float32 [rows, cols]")
             if image.stride(1) != 1:
                 raise B200SiftError("device image rows must be contiguous")
-            check(self.lib.b200sift_detect_device_async(h, image.data_ptr(), image.stride(0) * 4))
+            import torch
+
+            # the engine orders its copy after the stream that produced the tensor (torch's current stream)
+            check(self.lib.b200sift_detect_device_async(h, image.data_ptr(), image.stride(0) * 4,
+                                                        C.c_void_p(torch.cuda.current_stream().cuda_stream)))
             self._hold(image)
+            image.record_stream(torch.cuda.ExternalStream(self.stream))  # keep the allocator off it until the copy ran
             return
         if hasattr(image, "numpy") and not isinstance(image, np.ndarray):
             image = image.numpy()  # CPU torch tensor (pinned or not) shares memory
@@ -191,12 +196,14 @@ class Detector:
         """matchBruteForce(prev_descriptor, previous total, device_descriptor, this total) as
         tool/extract_and_match_example.cc:82 calls it, enqueued behind the current frame with both sizes
         read on the device. Returns a torch int32 CUDA tensor [numFeatures]; entries beyond the previous
-        frame's total are left untouched."""
+        frame's total are -1. The tensor is written on the engine's stream (Detector.stream): order your own reads
+        after it (synchronize(), or wait on that stream)."""
         import torch
 
         if out is None:
-            out = torch.full((self.config.numFeatures,), -1, dtype=torch.int32, device="cuda")
+            out = torch.empty((self.config.numFeatures,), dtype=torch.int32, device="cuda")
         check(self.lib.b200sift_match_consecutive_async(self._handle(), out.data_ptr()))
+        out.record_stream(torch.cuda.ExternalStream(self.stream))  # the caching allocator must not recycle it under the matcher
         return out
 
     def copyResultsAsync(self, host: "HostResults") -> None:

@@ -84,6 +84,20 @@ def next_frame(prev: np.ndarray, frame_index: int) -> np.ndarray:
     return np.floor(np.clip(out, 0, 255)).astype(np.float32)
 
 
+def blocks_frame(rows: int, cols: int, seed: int) -> np.ndarray:
+    """Axis-aligned rectangles of random grey levels: gradients point exactly along the axes, i.e. the orientation
+    samples sit ON histogram bin edges (0 / 90 / 180 / 270 degrees) and the descriptor samples where the vote is
+    discontinuous in the gradient angle -- the cases the fast paths of orientation_kernel / descriptor_kernel must
+    hand to the reference's own expressions."""
+    rng = np.random.default_rng(seed)
+    img = np.full((rows, cols), 96, np.float32)
+    for _ in range(260):
+        h, w = rng.integers(6, 60, 2)
+        y, x = rng.integers(0, rows - h), rng.integers(0, cols - w)
+        img[y:y + h, x:x + w] = float(rng.integers(0, 256))
+    return img
+
+
 def _encode(v: np.ndarray) -> np.ndarray:
     v = v / np.maximum(np.linalg.norm(v, axis=1, keepdims=True), 1e-7)
     v = np.minimum(v, 0.2)

@@ -74,8 +74,11 @@ B200SIFT_API int b200sift_octave_info(const b200sift_detector* det, int o, int* 
 B200SIFT_API int b200sift_detect_host(b200sift_detector* det, const float* img, int rows, int cols, int* total);
 B200SIFT_API int b200sift_detect_host_async(b200sift_detector* det, const float* img, int rows, int cols);
 /* Same frame, input already resident in HBM (`pitch_bytes` between rows); copied device to
- * device into the detector's input image on the detector's stream. */
-B200SIFT_API int b200sift_detect_device_async(b200sift_detector* det, const float* d_img, size_t pitch_bytes);
+ * device into the detector's input image on the frame's own stream. `producer_stream` (a cudaStream_t, NULL = the
+ * legacy default stream) is the stream whose work produced `d_img`: the engine records an event there and makes its
+ * copy wait for it -- its own streams are non-blocking and would otherwise not be ordered after the producer.
+ * The image may be overwritten once b200sift_sync (or any later event on b200sift_stream) has completed. */
+B200SIFT_API int b200sift_detect_device_async(b200sift_detector* det, const float* d_img, size_t pitch_bytes, void* producer_stream);
 /* 8-bit input: converted to float on the device, 4x less PCIe traffic. */
 B200SIFT_API int b200sift_detect_host_u8_async(b200sift_detector* det, const uint8_t* img, int rows, int cols);
 /* Waits for the frames enqueued so far; *total = keypoints of the last frame. */
@@ -132,7 +135,9 @@ B200SIFT_API int b200sift_time_frames_pipelined(b200sift_detector* det, int warm
 /* Pipelined (batched-frame) use, no host synchronisation per frame. After b200sift_detect_*_async:
  *  - b200sift_match_consecutive_async: matchBruteForce(prev_descriptor, previous total, device_descriptor, this
  *    total) exactly as tool/extract_and_match_example.cc:82 calls it, with both sizes read on the device;
- *    d_out_idx = int[numFeatures] on the device (entries beyond the previous total are left untouched);
+ *    d_out_idx = int[numFeatures] on the device, written entirely by the engine on the latest frame's stream
+ *    (entries beyond the previous frame's total are set to -1): the caller must not touch it on another stream
+ *    until an event recorded on b200sift_stream after this call has completed;
  *  - b200sift_copy_results_async: all numFeatures slots of kpts / feats / desc (any may be NULL) and
  *    counts2[0..1] = {this frame's total, previous frame's total} to (pinned) host memory.
  * Both are enqueued on the latest frame's stream and are ordered before the detect call that reuses the
@@ -175,7 +180,10 @@ B200SIFT_API int b200sift_time_stages(b200sift_detector* det, int iters, float* 
  * descriptors (half[nq*128]) the index of its nearest train descriptor (half[nt*128]) under the
  * reference's half-precision L2 recipe, or -1 if the 0.8 ratio test fails. Device pointers;
  * out_idx = int[nq] on the device. `stream` is a cudaStream_t (NULL = legacy default stream).
- * Asynchronous; scratch memory is cached per device and grown on demand. */
+ * Asynchronous. Scratch memory is ONE cached buffer per device, grown on demand: calls on different streams are
+ * serialised through an event (a call waits for the previous call's kernels, whatever stream they ran on), and a call
+ * that has to grow the buffer synchronises the device first -- so the first call of a size class must not be made
+ * during stream capture. One host thread per device may call concurrently with threads of other devices. */
 B200SIFT_API int b200sift_match_device(const uint16_t* d_query, int nq, const uint16_t* d_train, int nt,
                           int* d_out_idx, void* stream);
 /* Host-buffer convenience (copies in, matches, copies out, blocks). */

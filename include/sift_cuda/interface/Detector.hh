@@ -92,10 +92,11 @@ class Detector {
         refresh_views();
         if (!m_debug_path.empty()) check(b200sift_dump_frame(m_handle, m_debug_path.c_str()), "b200sift_dump_frame");
     }
-    // Extension: frame already resident in HBM (pitched fp32), enqueued on stream(); call synchronize().
-    void detectAndComputeDevice(const float* d_image, size_t pitch_bytes) {
+    // Extension: frame already resident in HBM (pitched fp32), produced on `producer` (NULL = legacy default stream);
+    // the engine orders its copy after that stream and enqueues the frame on stream(); call synchronize().
+    void detectAndComputeDevice(const float* d_image, size_t pitch_bytes, cudaStream_t producer = nullptr) {
         require_init();
-        check(b200sift_detect_device_async(m_handle, d_image, pitch_bytes), "b200sift_detect_device_async");
+        check(b200sift_detect_device_async(m_handle, d_image, pitch_bytes, producer), "b200sift_detect_device_async");
         refresh_views();
     }
     int synchronize() {

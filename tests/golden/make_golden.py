@@ -16,7 +16,7 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
-from another_cuda_sift_b200.synth import next_frame, synth_descriptors, synth_frame  # noqa: E402
+from another_cuda_sift_b200.synth import blocks_frame, next_frame, synth_descriptors, synth_frame  # noqa: E402
 from oracle.pyoracle import RefOracle  # noqa: E402
 
 
@@ -83,9 +83,9 @@ def run_frames(cols, rows, nframes, keep_stacks=0, density=1.0, num_features=500
     return out
 
 
-def envelope(cols, rows, runs=3):
+def envelope(cols, rows, runs=3, kind="texture"):
     """The reference's own run-to-run spread (float shared-memory atomics in orientation / descriptor)."""
-    img = synth_frame(rows, cols, 0)
+    img = blocks_frame(rows, cols, 5) if kind == "blocks" else synth_frame(rows, cols, 0)
     res = []
     for _ in range(runs):
         ref = RefOracle(cols, rows, 5000)
@@ -104,9 +104,22 @@ def envelope(cols, rows, runs=3):
     return dict(totals=np.array(n), same_keypoints=same_kp, desc_max_abs=dmax, desc_l2_max=l2max)
 
 
+def envelopes(outdir):
+    """Run-to-run envelopes of the reference on the frames where the descriptor bar is asserted: the 752x480 texture,
+    the axis-aligned blocks frame (tests/test_gpu_parity.py) and 1920x1200."""
+    for name, args in (("envelope_752x480", (752, 480)), ("envelope_blocks_640x360", (640, 360, 3, "blocks")),
+                       ("envelope_1920x1200", (1920, 1200))):
+        env = envelope(*args)
+        np.savez_compressed(os.path.join(outdir, name + ".npz"), **env)
+        print(name, {k: (v.tolist() if hasattr(v, "tolist") else v) for k, v in env.items()})
+
+
 def main():
-    outdir = sys.argv[1] if len(sys.argv) > 1 else os.path.dirname(os.path.abspath(__file__))
+    args = [a for a in sys.argv[1:] if not a.startswith("--")]
+    outdir = args[0] if args else os.path.dirname(os.path.abspath(__file__))
     os.makedirs(outdir, exist_ok=True)
+    if "--envelopes-only" in sys.argv:
+        return envelopes(outdir)
     ref = RefOracle(64, 64, 100)
     taps = {f"taps{i}": ref.taps(i) for i in range(-1, 6)}
     np.savez_compressed(os.path.join(outdir, "taps.npz"), **taps)
@@ -125,9 +138,8 @@ def main():
     m["self300"] = ref.match(q[:300], q[:300])
     np.savez_compressed(os.path.join(outdir, "match.npz"), **m)
 
-    env = envelope(752, 480)
-    np.savez_compressed(os.path.join(outdir, "envelope_752x480.npz"), **env)
-    print("golden written to", outdir, {k: (v.tolist() if hasattr(v, "tolist") else v) for k, v in env.items()})
+    envelopes(outdir)
+    print("golden written to", outdir)
 
 
 if __name__ == "__main__":

@@ -11,9 +11,10 @@ from util import check_results
 pytestmark = pytest.mark.gpu
 
 # Bars (BASELINE.json north_star): extrema and refined positions bit-exact; >= 99.5% keypoint-set agreement;
-# size 1e-3 relative; descriptors 1e-3 L2 -- asserted for DESC_FRAC of the keypoints because the reference
-# itself is not run-to-run reproducible there (float shared-memory atomics; envelope_752x480.npz).
-DESC_TOL, DESC_FRAC = 1e-3, 0.995
+# size 1e-3 relative; normalised descriptors within 1e-3 L2 for EVERY paired keypoint whose reference descriptor is
+# defined (tests/util.py:touches_padding lists the ones that read uninitialised row padding in the reference; the
+# excluded fraction is recorded in gpurun_out/parity_metrics.jsonl and capped).
+DESC_TOL, DESC_FRAC = 1e-3, 1.0
 
 
 def _det(cols, rows, nf=5000):
@@ -60,7 +61,7 @@ def test_frames_vs_golden(name):
             c = det.debug_counts(oi)
             assert (c["P"], c["M"]) == (counts[0][oi], counts[1][oi]), (fr, oi, c)
         want = dict(n=int(g[f"f{fr}_total"]), kpts=g[f"f{fr}_kpts"], feats=g[f"f{fr}_feats"], desc=g[f"f{fr}_desc"])
-        info = check_results(_res(det), want, desc_tol=DESC_TOL, desc_frac=DESC_FRAC, octaves=g["octaves"])
+        info = check_results(_res(det), want, desc_tol=DESC_TOL, desc_frac=DESC_FRAC, octaves=g["octaves"], tag=f"golden/{name}/f{fr}")
         print(name, fr, info)
 
 
@@ -79,14 +80,33 @@ def test_extrema_and_refinement_bit_exact_vs_golden():
         assert np.array_equal(det.debug_kpt_buffer(oi, "coll")[:n], want)
         gotF = det.debug_kpt_buffer(oi, "collF")[:n, :3]
         assert np.array_equal(gotF.view(np.uint32), wantF.view(np.uint32)), oi  # incl. powf: same libdevice
+    # Oriented stage, every octave, unconditionally. The reference sums its 36-bin histograms with float atomics in
+    # an order that changes from run to run, so a peak that sits on the 0.8*max / neighbour threshold may flip and
+    # T may differ by a few; the (keypoint, feature) rows are therefore compared as multisets: per octave |T - T_ref|
+    # <= max(2, 1%), over the frame >= 99.5% of the rows identical, and where T agrees the order must agree too.
     det.debug_run_stages(img, 5)
+    rows_got, rows_want, t_got, t_want = [], [], [], []
     for oi in range(det.n_octaves):
         want, wantF = g[f"f0_oriented{oi}"], g[f"f0_orientedF{oi}"]
         got, gotF = det.debug_kpt_buffer(oi, "cand"), det.debug_kpt_buffer(oi, "candF")
-        n = len(want)
-        if det.debug_counts(oi)["T"] == int(g["f0_counts"][2][oi]):
-            same = np.all(got[:n] == want, axis=1) & np.all(gotF[:n] == wantF, axis=1)
-            assert same.mean() >= 0.99 if n else True
+        T, T_ref = det.debug_counts(oi)["T"], int(g["f0_counts"][2][oi])
+        t_got.append(T)
+        t_want.append(T_ref)
+        assert abs(T - T_ref) <= max(2, T_ref // 100), (oi, T, T_ref)
+        n = len(want)                       # T_ref - 1: the last slot is never written (quirk Q5)
+        m = max(min(T, det.octaves[oi]["cap"]) - 1, 0)
+        a = np.concatenate([got[:m], gotF[:m]], axis=1)
+        b = np.concatenate([want, wantF], axis=1)
+        rows_got.append(a)
+        rows_want.append(b)
+        if T == T_ref and n:
+            same = np.all(a == b, axis=1)
+            assert same.mean() >= 0.99, (oi, float(same.mean()))
+    from util import record, rows_agreement
+
+    agree = rows_agreement(np.concatenate(rows_got), np.concatenate(rows_want))
+    record("golden/frames_752x480.npz/oriented", dict(agree=agree, T=t_got, T_ref=t_want))
+    assert agree >= 0.995, agree
 
 
 @pytest.mark.parametrize("cols,rows", [(160, 120), (203, 151), (752, 480)])
@@ -129,7 +149,8 @@ def test_live_reference_when_available():
         for oi in range(det.n_octaves):
             assert np.array_equal(det.debug_gauss(oi).view(np.uint32), ref.stack(oi, "gauss").view(np.uint32)), (fr, oi)
         det.detectAndCompute(img)
-        info = check_results(_res(det), ref.results(), desc_tol=DESC_TOL, desc_frac=DESC_FRAC)
+        octs = [(o["w"], o["h"], o["pitch"], o["cap"]) for o in det.octaves]
+        info = check_results(_res(det), ref.results(), desc_tol=DESC_TOL, desc_frac=DESC_FRAC, octaves=octs, tag=f"live/640x360/f{fr}")
         print("live", fr, info)
 
 
@@ -252,16 +273,9 @@ def test_pipelined_batch_equals_blocking_frames():
 
 
 def _blocks_frame(rows, cols, seed):
-    """Axis-aligned rectangles of random grey levels: gradients point exactly along the axes, i.e. the orientation
-    samples sit ON histogram bin edges (0 / 90 / 180 / 270 degrees) -- the case the polynomial-atan2 fast path of
-    orientation_kernel must hand to the reference's own expression."""
-    rng = np.random.default_rng(seed)
-    img = np.full((rows, cols), 96, np.float32)
-    for _ in range(260):
-        h, w = rng.integers(6, 60, 2)
-        y, x = rng.integers(0, rows - h), rng.integers(0, cols - w)
-        img[y:y + h, x:x + w] = float(rng.integers(0, 256))
-    return img
+    from another_cuda_sift_b200.synth import blocks_frame
+
+    return blocks_frame(rows, cols, seed)
 
 
 @pytest.mark.parametrize("cols,rows,kind", [(640, 360, "blocks"), (1600, 900, "texture")])
@@ -283,11 +297,81 @@ def test_live_reference_bin_edges_and_1600x900(cols, rows, kind):
             assert np.array_equal(det.debug_gauss(oi).view(np.uint32), ref.stack(oi, "gauss").view(np.uint32)), (fr, oi)
         det.detectAndCompute(img)
         octs = [(o["w"], o["h"], o["pitch"], o["cap"]) for o in det.octaves]
-        # "blocks": the keypoint sets must agree exactly (that is what the case is for). Its gradients also sit on the
-        # 45-degree edges of the 8 descriptor orientation bins and on integer window coordinates, where the reference's
-        # fast_atan2f and the reciprocal approximation used here may put a vote on either side of an edge: a few
-        # descriptors differ by more than 1e-3 (observed 4 of 320, max 7e-3), so the descriptor bar is 97% there.
+        # "blocks": the keypoint sets must agree exactly (that is what the case is for). Its gradients also sit where
+        # the descriptor vote is discontinuous in the gradient angle (fast_atan2f changing sign, obin on a negative
+        # integer): descriptor_kernel hands those samples to the reference's own instruction sequence (exact_obin),
+        # so the bar is the same as everywhere else: every defined descriptor within 1e-3.
         info = check_results(_res(det), ref.results(), min_agree=1.0 if kind == "blocks" else 0.995, desc_tol=DESC_TOL,
-                             desc_frac=0.97 if kind == "blocks" else DESC_FRAC, octaves=octs)
+                             desc_frac=DESC_FRAC, octaves=octs, tag=f"live/{kind}_{cols}x{rows}/f{fr}")
         assert info["n_got"] > 50, info
         print("live", kind, fr, info)
+
+
+@pytest.mark.parametrize("nf", [3000, 150], ids=["nf3000", "nf150-slot-cap-overflow"])
+def test_slot_wraparound_pipelines_equal_blocking(nf):
+    """More frames than twice the engine's frame slots, so every slot is reused while work is in flight: the
+    ev_matched / ev_consumed / ev_chain hand-overs across a wrap. Three drivers on fresh detectors (same slot history):
+    (a) blocking per-frame calls, (b) the batched host call (float and 8-bit frames), (c) the asynchronous loop
+    bench.py times (device-resident frames, device-side matcher sizes, no per-frame synchronisation). All results --
+    counts, keypoints, features, descriptors, match indices -- must be bit-identical. nf = 150 makes the busy octaves
+    overflow their slot capacity (cap = 10 * numFeatures) and truncates the output, so the stale-slot state of quirks
+    Q5 / Q6 / Q7 crosses the wraps too."""
+    import torch
+
+    from another_cuda_sift_b200 import HostResults, matchBruteForce
+    from another_cuda_sift_b200.synth import next_frame, synth_frame
+
+    cols, rows = 640, 360
+    det = _det(cols, rows, nf)
+    n_frames = 2 * det.frames_in_flight + 2
+    frames = [synth_frame(rows, cols, 51)]
+    for i in range(1, n_frames):
+        frames.append(next_frame(frames[-1], 51 + i))
+    want, want_idx, prev_n = [], [], 0
+    for f in frames:
+        det.detectAndCompute(f)
+        r = _res(det)
+        want.append((r["n"], r["kpts"][:r["n"]].copy(), r["feats"][:r["n"]].copy(), r["desc"][:r["n"]].copy()))
+        idx = None
+        if prev_n:
+            idx = matchBruteForce(det.prev_descriptor, prev_n, det.device_descriptor, r["n"], stream=det.stream).cpu().numpy()
+            torch.cuda.synchronize()
+        want_idx.append(idx)
+        prev_n = r["n"]
+    if nf == 150:
+        assert all(w[0] == nf for w in want), [w[0] for w in want]   # truncated at numFeatures (Q7)
+
+    def compare(res, midx, tag):
+        for i, (n, k, f, d) in enumerate(want):
+            assert res[i].total == n, (tag, i)
+            assert int(res[i].counts[1]) == (want[i - 1][0] if i else 0), (tag, i)
+            assert np.array_equal(res[i].kpts[:n].numpy(), k) and np.array_equal(res[i].feats[:n].numpy(), f), (tag, i)
+            assert np.array_equal(res[i].desc[:n].numpy().view(np.uint16), d.view(np.uint16)), (tag, i)
+            if i:
+                pn = want[i - 1][0]
+                assert np.array_equal(midx[i][:pn].numpy(), want_idx[i]), (tag, i)
+                assert bool((midx[i][pn:] == -1).all()), (tag, i)   # rows past the previous total are -1
+
+    for tag, conv in (("batch-f32", lambda f: torch.from_numpy(f).pin_memory().numpy()),
+                      ("batch-u8", lambda f: torch.from_numpy(f.astype(np.uint8)).pin_memory().numpy())):
+        d2 = _det(cols, rows, nf)
+        res = [HostResults(nf) for _ in frames]
+        midx = [torch.full((nf,), -7, dtype=torch.int32).pin_memory() for _ in frames]
+        d2.detectAndComputeBatch([conv(f) for f in frames], res, midx)
+        compare(res, midx, tag)
+
+    # (c) the asynchronous loop: frames produced on torch's current stream right before the call (the engine must
+    # order its copy after that stream), match indices into rotating device buffers, results to pinned host memory
+    d3 = _det(cols, rows, nf)
+    res = [HostResults(nf) for _ in frames]
+    midx_dev = [torch.full((nf,), -7, dtype=torch.int32, device="cuda") for _ in frames]
+    host = [torch.from_numpy(f).pin_memory() for f in frames]
+    for i in range(n_frames):
+        img = host[i].cuda(non_blocking=True) * 1.0      # produced asynchronously on the current stream
+        d3.detectAndComputeAsync(img)
+        if i:
+            d3.matchConsecutiveAsync(midx_dev[i])
+        d3.copyResultsAsync(res[i])
+    d3.synchronize()
+    torch.cuda.synchronize()
+    compare(res, [m.cpu() for m in midx_dev], "async-device")
