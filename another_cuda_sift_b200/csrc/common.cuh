@@ -2,12 +2,12 @@
 //
 // Data layout in HBM (one slab per detector, allocated once):
 //   * input image            : pitched float, pitch = round_up(w*4, 512) bytes
-//   * Gaussian stack/octave  : 6 layers, layer-major then row-major, row pitch rounded up to
+//   * Gaussian stack/octave  : numOctaveLayers + 3 layers, layer-major then row-major, row pitch rounded up to
 //                              512 B, layer stride pitch*h floats -- the layout the reference gets
 //                              from cudaMallocPitch (types/CudaImage.cu:192-207), kept because its
 //                              descriptor kernel reads one element past a row / layer (quirk Q12)
 //   * no DoG stack           : DoG[l] = G[l+1]-G[l] is one exact FADD, recomputed where needed
-//   * extrema bitmask        : 1 bit per pixel per scale (3 scales), + per-row popcounts
+//   * extrema bitmask        : 1 bit per pixel per scale (numOctaveLayers scales), + per-row popcounts
 //   * keypoint slots/octave  : cand/candF/coll/collF with the reference's slot semantics
 //                              (types/KeyPoint.cuh:9-29)
 #pragma once
@@ -18,11 +18,13 @@
 namespace b200sift {
 
 constexpr int kMaxOctaves = 16;
-constexpr int kGaussLayers = 6;   // numOctaveLayers + 3
-constexpr int kScales = 3;        // numOctaveLayers
+// numOctaveLayers (n) and sigma are runtime parameters, as in the reference (interface/Detector.cu:63-94: n + 3 Gaussian
+// layers, n + 2 DoG layers, n scales per octave; utils/GaussianUtils.cc:39-67: any tap count). Bounds of this engine:
+constexpr int kMaxScales = 6;                  // numOctaveLayers <= 6
+constexpr int kMaxLayers = kMaxScales + 3;
 constexpr int kBorder = 5;        // SIFT_IMG_BORDER (sift_func/SiftOps.cuh:8)
 constexpr int kOriBins = 36;      // sift_func/SiftOps.cu:261
-constexpr int kMaxTaps = 21;
+constexpr int kMaxTaps = 85;      // blur radius <= 42, i.e. layer sigma <= ~13.9 (numOctaveLayers = 1 at sigma 1.6 needs 67 taps)
 constexpr int kTailPixels = 4096;  // octaves up to this many pixels (and kTailMaxDim per side) go to the single-CTA tail kernel
 constexpr int kTailMaxDim = 1024;
 inline bool tail_octave(int w, int h) { return w * h <= kTailPixels && w <= kTailMaxDim && h <= kTailMaxDim; }
@@ -33,9 +35,9 @@ struct Taps {
 };
 
 struct OctParams {
-    float* gauss;        // [6][h][pitch]
-    uint32_t* mask;      // [3][h][words] extrema bits
-    int* rowcount;       // [3*h] extrema per (scale,row); zeroed every frame
+    float* gauss;        // [nLayers][h][pitch]
+    uint32_t* mask;      // [nScales][h][words] extrema bits
+    int* rowcount;       // [nScales*h] extrema per (scale,row); zeroed every frame
     float3* cand;        // [cap]
     float4* candF;       // [cap]
     float3* coll;        // [cap]
@@ -56,6 +58,7 @@ struct OctParams {
 struct FrameParams {
     OctParams oct[kMaxOctaves];
     int nOct;
+    int nScales, nLayers;  // numOctaveLayers, numOctaveLayers + 3
     int o_begin, o_end;  // octave range this launch works on (the frame graph runs octave 0 and the rest as parallel branches)
     int numFeatures;
     int det_tasks;       // total warp tasks of the detect kernel
@@ -72,9 +75,25 @@ constexpr int kDetRows = 16;  // rows per warp task in the detect kernel
 
 // ---- stage launchers (each enqueues on `s`; no host synchronisation inside) ----
 void launch_u8_to_float(const uint8_t* in, size_t in_pitch, float* out, int out_pitch, int w, int h, cudaStream_t s);
+// Pyramid launchers (pyramid.cu). `chain`: up to three successive blurs in ONE launch (2-D tiles with recomputed
+// halos), optionally fed by the bilinear 2x resample of the previous octave; every stage's layer is stored.
+struct BlurStage {
+    float* out;     // the layer this stage writes (same pitch / dims as the octave)
+    const Taps* taps;
+};
+bool blur_chain_supported(bool from_prev_octave, const BlurStage* st, int n_stages);
+cudaError_t pyramid_setup();  // once per device, outside stream capture (opt-in shared-memory sizes)
+// src: the layer to blur (pitch src_pitch); or, with from_prev_octave, layer n of the previous octave (src_w x src_h),
+// resampled on the fly, the resampled base layer also being written to `base_out`.
+void launch_blur_chain(const float* src, int src_pitch, int src_w, int src_h, bool from_prev_octave, float* base_out,
+                       const BlurStage* st, int n_stages, int pitch, int w, int h, cudaStream_t s);
 void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s);
 void launch_downsample(const float* in, int in_pitch, int iw, int ih, float* out, int out_pitch, int ow, int oh, cudaStream_t s);
-void launch_pyramid_tail(const FrameParams& fp, const Taps* taps, int first_octave, cudaStream_t s);
+// Single-CTA walk over the octaves [first_octave, nOct) (all of at most kTailPixels pixels): layers [l_begin, l_end)
+// of each; with l_begin == 0 the base layer comes from the previous octave (or, for octave 0, from `input` blurred
+// with `init_taps`), otherwise layer l_begin - 1 is read back from the stack.
+void launch_pyramid_tail(const FrameParams& fp, const Taps* taps, const Taps& init_taps, const float* input, int in_pitch,
+                         int first_octave, int l_begin, int l_end, cudaStream_t s);
 void launch_detect(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);       // bitmask + row counts
 void launch_scatter(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);      // row offsets, P, ordered candidate list
 void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);       // Taylor refinement + tests

@@ -84,7 +84,7 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
         const int total_dim = side * side;
         const float weight_factor = __fdiv_rn(-0.5f, __fmul_rn(scale, scale));
         int layer = (int)kp.z;
-        layer = min(max(layer, 0), 4);
+        layer = min(max(layer, 0), fp.nScales + 1);
         const float* g0 = o.gauss + ls * layer;  // DoG[layer] = G[layer+1] - G[layer]
         const float fh1 = (float)o.h - 1.f, fw1 = (float)o.w - 1.f;
 
@@ -333,7 +333,7 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     const float scale = octv >= 0 ? __fdiv_rn(1.f, (float)(1 << octv)) : (float)(1 << -octv);
     const int hdim = o.pitch;
     const int ow = o.w, oh = o.h;
-    const long stack_len = (long)o.pitch * o.h * kGaussLayers;
+    const long stack_len = (long)o.pitch * o.h * fp.nLayers;
     const long img_off = (long)((float)hdim * (float)o.h * (float)layer);
     const int ix = __float2int_rn(__fmul_rn(kp.x, scale));
     const int iy = __float2int_rn(__fmul_rn(kp.y, scale));

@@ -59,10 +59,7 @@ Taps gaussian_taps(float sigma) {
     return t;
 }
 
-bool radius_supported(int n) {
-    const int r = n / 2;
-    return (n & 1) && (r == 4 || r == 5 || r == 6 || r == 8 || r == 10);
-}
+bool taps_supported(const Taps& t) { return (t.n & 1) && t.n >= 3 && t.n <= kMaxTaps; }
 
 inline int pitch_floats(int w) { return ((w * 4 + 511) / 512) * 512 / 4; }
 
@@ -101,8 +98,9 @@ struct b200sift_detector {
     b200sift_config cfg;
     int device = 0;
     int nOct = 0;
+    int nScales = 3, nLayers = 6;     // numOctaveLayers, numOctaveLayers + 3
     Taps init_taps;
-    Taps taps[kGaussLayers];
+    Taps taps[kMaxLayers];
     Slot slot[kSlots];
     int in_pitch = 0;
     size_t u8_pitch = 0;
@@ -193,48 +191,73 @@ int enqueue_frame(b200sift_detector* d, Slot& sl, int last_stage, int* launches,
         // branches per octave range (build(): one branch per big octave, one for the remaining multi-CTA
         // octaves, the tail octaves on the main stream); each branch runs its extrema detection as soon as
         // the six layers of its octaves exist.
+        // Launches per octave of the default configuration: octave 0 = one single-stage launch per layer (initial blur,
+        // L1..Ln on the main chain, L(n+1), L(n+2) on the branch); octaves >= 1 = ONE fused launch on the main chain
+        // (2x resample of the previous octave's layer n + L1..Ln) and ONE on the branch (L(n+1), L(n+2)). Radii without a
+        // fused instantiation fall back to resample + one launch per layer.
+        const int nL = d->nLayers, nS = d->nScales;
         int br = 0;  // branch of the current multi-CTA octave
-        for (int o = 0; o < d->nOct; o++) {
+        for (int o = 0; o < d->tail_first; o++) {
             OctParams& oc = fp.oct[o];
             const size_t ls = (size_t)oc.pitch * oc.h;
-            const bool tail = o >= d->tail_first;
+            const int cls = o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL;
+            BlurStage st[kMaxLayers];
+            for (int l = 1; l < nL; l++) st[l] = BlurStage{oc.gauss + ls * l, &d->taps[l]};
+            bool fused_main = false;
             if (o == 0) {
                 launch_blur(sl.d_input, d->in_pitch, oc.gauss, oc.pitch, oc.w, oc.h, d->init_taps, s);
                 MARK(B200SIFT_K_BLUR);
                 n++;
-            } else if (!tail || o == d->tail_first) {
+            } else {
                 const OctParams& pv = fp.oct[o - 1];
-                const float* src = pv.gauss + (size_t)pv.pitch * pv.h * kScales;
-                launch_downsample(src, pv.pitch, pv.w, pv.h, oc.gauss, oc.pitch, oc.w, oc.h, s);
-                MARK(B200SIFT_K_DOWNSAMPLE);
+                const float* src = pv.gauss + (size_t)pv.pitch * pv.h * nS;
+                fused_main = nS <= 3 && blur_chain_supported(true, st + 1, nS);
+                if (fused_main) {
+                    launch_blur_chain(src, pv.pitch, pv.w, pv.h, true, oc.gauss, st + 1, nS, oc.pitch, oc.w, oc.h, s);
+                    MARK(cls);
+                } else {
+                    launch_downsample(src, pv.pitch, pv.w, pv.h, oc.gauss, oc.pitch, oc.w, oc.h, s);
+                    MARK(B200SIFT_K_DOWNSAMPLE);
+                }
                 n++;
             }
-            if (tail) {
-                if (o == d->tail_first) {
-                    launch_pyramid_tail(fp, d->taps, o, s);
-                    MARK(B200SIFT_K_BLUR_SMALL);
+            if (!fused_main)
+                for (int l = 1; l <= nS; l++) {
+                    launch_blur(oc.gauss + ls * (l - 1), oc.pitch, st[l].out, oc.pitch, oc.w, oc.h, d->taps[l], s);
+                    MARK(cls);
                     n++;
                 }
-                continue;
-            }
             while (o >= d->br_end[br]) br++;
             cudaStream_t bs = fork ? sl.side[br] : s;  // the branch's stream
-            cudaStream_t ls_stream = s;
-            for (int l = 1; l < kGaussLayers; l++) {
-                if (l == 4 && fork) {  // layers 4,5 off the critical path
-                    CU(cudaEventRecord(sl.ev_fork[o], s));
-                    CU(cudaStreamWaitEvent(bs, sl.ev_fork[o], 0));
-                    ls_stream = bs;
-                    used[br] = true;
-                }
-                launch_blur(oc.gauss + ls * (l - 1), oc.pitch, oc.gauss + ls * l, oc.pitch, oc.w, oc.h, d->taps[l], ls_stream);
-                MARK(o == 0 ? B200SIFT_K_BLUR : B200SIFT_K_BLUR_SMALL);
+            if (fork) {  // layers n+1, n+2 off the critical path
+                CU(cudaEventRecord(sl.ev_fork[o], s));
+                CU(cudaStreamWaitEvent(bs, sl.ev_fork[o], 0));
+                used[br] = true;
+            }
+            if (o > 0 && blur_chain_supported(false, st + nS + 1, 2)) {
+                launch_blur_chain(oc.gauss + ls * nS, oc.pitch, oc.w, oc.h, false, nullptr, st + nS + 1, 2, oc.pitch, oc.w, oc.h, bs);
+                MARK(cls);
                 n++;
+            } else {
+                for (int l = nS + 1; l < nL; l++) {
+                    launch_blur(oc.gauss + ls * (l - 1), oc.pitch, st[l].out, oc.pitch, oc.w, oc.h, d->taps[l], bs);
+                    MARK(cls);
+                    n++;
+                }
             }
             if (o == d->br_end[br] - 1 && last_stage >= 3) {  // the branch's octaves are complete
                 launch_detect(fp, d->br_begin[br], d->br_end[br], bs); n++;
                 MARK(B200SIFT_K_DETECT);
             }
+        }
+        if (d->tail_first < d->nOct) {
+            // tail octaves: one CTA walks resample + L0..Ln of all of them (a dependency chain), then one CTA per octave
+            // adds L(n+1), L(n+2)
+            launch_pyramid_tail(fp, d->taps, d->init_taps, sl.d_input, d->in_pitch, d->tail_first, 0, nS + 1, s);
+            MARK(B200SIFT_K_BLUR_SMALL);
+            launch_pyramid_tail(fp, d->taps, d->init_taps, sl.d_input, d->in_pitch, d->tail_first, nS + 1, nL, s);
+            MARK(B200SIFT_K_BLUR_SMALL);
+            n += 2;
         }
         if (d->tail_first < d->nOct && last_stage >= 3) {  // tail octaves on the main stream
             launch_detect(fp, d->tail_first, d->nOct, s); n++;
@@ -294,23 +317,30 @@ int build(b200sift_detector* d) {
     // Detector.cu:54-59 and :63-77
     float sigma_diff = sqrtf(fmax(c.sigma * c.sigma - 0.5f * 0.5f * 4, 0.01f));
     d->init_taps = gaussian_taps(sigma_diff);
-    std::vector<float> sigmas(kGaussLayers);
+    d->nScales = c.numOctaveLayers;
+    d->nLayers = c.numOctaveLayers + 3;
+    const int nL = d->nLayers, nS = d->nScales;
+    std::vector<float> sigmas(nL);
     sigmas[0] = (float)c.sigma;
     double k = std::pow(2., 1. / c.numOctaveLayers);
-    for (int i = 1; i < kGaussLayers; i++) {
+    for (int i = 1; i < nL; i++) {
         double sig_prev = std::pow(k, (double)(i - 1)) * c.sigma;
         double sig_total = sig_prev * k;
         sigmas[i] = (float)std::sqrt(sig_total * sig_total - sig_prev * sig_prev);
     }
-    for (int i = 0; i < kGaussLayers; i++) d->taps[i] = gaussian_taps(sigmas[i]);
-    if (!radius_supported(d->init_taps.n)) return fail(B200SIFT_EINVAL, "sigma %.3f: unsupported tap count %d", c.sigma, d->init_taps.n);
-    for (int i = 1; i < kGaussLayers; i++)
-        if (!radius_supported(d->taps[i].n)) return fail(B200SIFT_EINVAL, "sigma %.3f: unsupported tap count %d", c.sigma, d->taps[i].n);
+    for (int i = 0; i < nL; i++) d->taps[i] = gaussian_taps(sigmas[i]);
+    if (!taps_supported(d->init_taps))
+        return fail(B200SIFT_EINVAL, "sigma %.3f: the initial blur needs %d taps (supported: 3..%d)", c.sigma, d->init_taps.n, kMaxTaps);
+    for (int i = 1; i < nL; i++)
+        if (!taps_supported(d->taps[i]))
+            return fail(B200SIFT_EINVAL, "sigma %.3f, numOctaveLayers %d: layer %d needs %d taps (supported: 3..%d)", c.sigma,
+                        c.numOctaveLayers, i, d->taps[i].n, kMaxTaps);
 
     d->in_pitch = pitch_floats(c.col_width);
     d->u8_pitch = ((size_t)c.col_width + 511) / 512 * 512;
     d->match_scratch_bytes_ = match_scratch_bytes(c.numFeatures, c.numFeatures);
     CU(descriptor_setup());
+    CU(pyramid_setup());
     // everything but the descriptor launches (launch_descriptor) runs at the highest stream priority
     int prio_least = 0, prio_greatest = 0;
     CU(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
@@ -322,6 +352,8 @@ int build(b200sift_detector* d) {
         FrameParams& fp = sl.fp;
         std::memset(&fp, 0, sizeof(fp));
         fp.nOct = d->nOct;
+        fp.nScales = nS;
+        fp.nLayers = nL;
         fp.o_begin = 0;
         fp.o_end = d->nOct;
         fp.numFeatures = c.numFeatures;
@@ -343,9 +375,9 @@ int build(b200sift_detector* d) {
             oc.cap = std::min(oc.pitch * oc.h, c.numFeatures * 10);  // KeyPoint.cu:13, Detector.cu:109
             oc.words = 2 * ((oc.w + 63) / 64);  // two mask words (even / odd pixels) per 64-pixel strip
             oc.row0 = rows_total;
-            rows_total += kScales * oc.h;
+            rows_total += nS * oc.h;
             oc.scat_cta0 = scat_ctas;
-            scat_ctas += (kScales * oc.h + 7) / 8;
+            scat_ctas += (nS * oc.h + 7) / 8;
         }
         fp.rows_total = rows_total;
         if (int rc = dev_alloc(d, &sl.d_rowcount_all, (size_t)rows_total)) return rc;
@@ -360,8 +392,8 @@ int build(b200sift_detector* d) {
             const size_t ls = (size_t)oc.pitch * oc.h;
             // +pitch floats of zeroed tail so that the reference's read one row past layer 5 of a
             // stale slot stays inside the allocation
-            if (int rc = dev_alloc(d, &oc.gauss, ls * kGaussLayers + oc.pitch)) return rc;
-            if (int rc = dev_alloc(d, &oc.mask, (size_t)kScales * oc.h * oc.words)) return rc;
+            if (int rc = dev_alloc(d, &oc.gauss, ls * nL + oc.pitch)) return rc;
+            if (int rc = dev_alloc(d, &oc.mask, (size_t)nS * oc.h * oc.words)) return rc;
             oc.rowcount = sl.d_rowcount_all + oc.row0;
             if (si == 0) {  // candidate lists: ONE set, handed from frame to frame (stale entries and all)
                 if (int rc = dev_alloc(d, &oc.cand, (size_t)oc.cap)) return rc;
@@ -473,7 +505,9 @@ int b200sift_create(const b200sift_config* cfg, b200sift_detector** out) {
     if (cfg->col_width <= 0 || cfg->row_width <= 0)
         return fail(B200SIFT_EINVAL, "Image width or height not set.");  // Detector.cu:22-25
     if (cfg->upscale) return fail(B200SIFT_EINVAL, "upscale=true is broken in the reference (CudaSiftConfig.hh:12) and unsupported");
-    if (cfg->numOctaveLayers != 3) return fail(B200SIFT_EINVAL, "numOctaveLayers must be 3");
+    if (cfg->numOctaveLayers < 1 || cfg->numOctaveLayers > kMaxScales)
+        return fail(B200SIFT_EINVAL, "numOctaveLayers must be in 1..%d", kMaxScales);
+    if (!(cfg->sigma > 0)) return fail(B200SIFT_EINVAL, "sigma must be positive");
     if (cfg->numFeatures <= 0) return fail(B200SIFT_EINVAL, "numFeatures must be positive");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
@@ -718,9 +752,9 @@ int b200sift_debug_get_stack(b200sift_detector* d, int o, int which, float* out)
     if (!d || !out || o < 0 || o >= d->nOct || which != 0) return fail(B200SIFT_EINVAL, "bad argument");
     const OctParams& oc = d->cur().fp.oct[o];
     if (int rc = sync_all(d)) return rc;
-    CU(cudaMemcpy2D(out, (size_t)oc.w * 4, oc.gauss, (size_t)oc.pitch * 4, (size_t)oc.w * 4, (size_t)oc.h * kGaussLayers,
+    CU(cudaMemcpy2D(out, (size_t)oc.w * 4, oc.gauss, (size_t)oc.pitch * 4, (size_t)oc.w * 4, (size_t)oc.h * d->nLayers,
                     cudaMemcpyDeviceToHost));
-    return 0;
+    return d->nLayers;
 }
 
 int b200sift_debug_get_kpt_buffer(b200sift_detector* d, int o, int which, void* out, int max_elems) {
@@ -748,7 +782,7 @@ int b200sift_debug_get_counts(b200sift_detector* d, int o, int* counts) {
 }
 
 int b200sift_debug_get_taps(b200sift_detector* d, int which, float* out, int max_elems) {
-    if (!d || which < -1 || which >= kGaussLayers) return fail(B200SIFT_EINVAL, "bad argument");
+    if (!d || which < -1 || which >= d->nLayers) return fail(B200SIFT_EINVAL, "bad argument");
     const Taps& t = which < 0 ? d->init_taps : d->taps[which];
     if (out && t.n <= max_elems) std::memcpy(out, t.v, t.n * sizeof(float));
     return t.n;
@@ -784,8 +818,8 @@ int b200sift_dump_frame(b200sift_detector* d, const char* dir) {
     for (int o = 0; o < d->nOct; o++) {
         const OctParams& oc = sl.fp.oct[o];
         const std::string pre = "oct" + std::to_string(o) + "_";
-        buf.resize((size_t)oc.w * oc.h * kGaussLayers);
-        CU(cudaMemcpy2D(buf.data(), (size_t)oc.w * 4, oc.gauss, (size_t)oc.pitch * 4, (size_t)oc.w * 4, (size_t)oc.h * kGaussLayers,
+        buf.resize((size_t)oc.w * oc.h * d->nLayers);
+        CU(cudaMemcpy2D(buf.data(), (size_t)oc.w * 4, oc.gauss, (size_t)oc.pitch * 4, (size_t)oc.w * 4, (size_t)oc.h * d->nLayers,
                         cudaMemcpyDeviceToHost));
         bool ok = write_bin(base + pre + "gauss.f32", buf.data(), buf.size() * 4);
         int c[4] = {0, 0, 0, 0};

@@ -28,34 +28,30 @@ constexpr int kDetThreads = 128;
 
 // Raw Gaussian values of one row of a 64-pixel strip: lane l owns pixels 2l, 2l+1 of the strip (one 8-byte
 // load per layer); lanes 0 and 31 also fetch the pixel left / right of the strip.
+template <int NG>
 struct RawRow {
-    float2 g[6];
-    float gh[6];
+    float2 g[NG];
+    float gh[NG];
 };
 
-__device__ __forceinline__ void load_raw(const float* __restrict__ base, size_t ls, int x, int xh, bool halo_lane, RawRow& r) {
+template <int NG>
+__device__ __forceinline__ void load_raw(const float* __restrict__ base, size_t ls, int x, int xh, bool halo_lane, RawRow<NG>& r) {
 #pragma unroll
-    for (int l = 0; l < 6; l++) r.g[l] = __ldg(reinterpret_cast<const float2*>(base + ls * l + x));
+    for (int l = 0; l < NG; l++) r.g[l] = __ldg(reinterpret_cast<const float2*>(base + ls * l + x));
 #pragma unroll
-    for (int l = 0; l < 6; l++) r.gh[l] = halo_lane ? __ldg(base + ls * l + xh) : 0.f;
+    for (int l = 0; l < NG; l++) r.gh[l] = halo_lane ? __ldg(base + ls * l + xh) : 0.f;
 }
 
-// Warp task = 64-pixel-wide column strip x kDetRows rows of one octave. Per DoG layer the warp keeps, for
-// the two pixels of every lane, the horizontal 3-max / 3-min of the previous row and of the previous two
-// rows combined, so the 3x3 in-plane extrema of the centre row cost two max and two min per new row; the
-// raw loads of the next row are issued before the current row is processed.
+// Warp task = 64-pixel-wide column strip x kDetRows rows of one octave, for NS consecutive scales starting at scale
+// s0 (NS + 2 DoG layers from NS + 3 Gaussian layers). Per DoG layer the warp keeps, for the two pixels of every lane,
+// the horizontal 3-max / 3-min of the previous row and of the previous two rows combined, so the 3x3 in-plane extrema
+// of the centre row cost two max and two min per new row; the raw loads of the next row are issued before the current
+// row is processed.
 // Mask layout: word 2c of a row holds the even pixels of strip c (bit l <-> x = 64c + 2l), word 2c+1 the
 // odd ones; scatter_kernel merges the two in x order.
-__global__ void __launch_bounds__(kDetThreads, 4)
-detect_kernel(const __grid_constant__ FrameParams fp) {
-    const int lane = threadIdx.x & 31;
-    const int task = fp.oct[fp.o_begin].det_task0 + blockIdx.x * (kDetThreads / 32) + (threadIdx.x >> 5);
-    if (task >= (fp.o_end < fp.nOct ? fp.oct[fp.o_end].det_task0 : fp.det_tasks)) return;
-    int oi = fp.o_begin;
-    while (oi + 1 < fp.o_end && task >= fp.oct[oi + 1].det_task0) oi++;
-    const OctParams& o = fp.oct[oi];
-    const int t = task - o.det_task0;
-    const int cs = t % o.det_cols, rs = t / o.det_cols;
+template <int NS>
+__device__ __forceinline__ void detect_strip(const FrameParams& fp, const OctParams& o, int cs, int rs, int s0, int lane) {
+    constexpr int ND = NS + 2, NG = NS + 3;
     const int x = cs * 64 + 2 * lane;  // x + 1 < pitch always: the pitch is a multiple of 128 floats
     const int xh = lane == 0 ? max(cs * 64 - 1, 0) : min(cs * 64 + 64, o.w - 1);
     const bool halo_lane = (lane == 0) || (lane == 31);
@@ -65,17 +61,17 @@ detect_kernel(const __grid_constant__ FrameParams fp) {
     const bool ok_b = x + 1 >= kBorder && x + 1 < o.w - kBorder;
     const float thr = fp.extrema_thr;
     const size_t ls = (size_t)o.pitch * o.h;
-    const float* col = o.gauss;
+    const float* col = o.gauss + ls * s0;
 
-    float pmx[5][2], pmn[5][2];  // horizontal 3-max / 3-min of the previous row
-    float qmx[5][2], qmn[5][2];  // ... of the previous two rows combined
-    float cen[3][2];             // centre-row DoG values of layers 1..3
-    float nmx[5][2], nmn[5][2], ncen[3][2];
+    float pmx[ND][2], pmn[ND][2];  // horizontal 3-max / 3-min of the previous row
+    float qmx[ND][2], qmn[ND][2];  // ... of the previous two rows combined
+    float cen[NS][2];              // centre-row DoG values of the NS middle layers
+    float nmx[ND][2], nmn[ND][2], ncen[NS][2];
 
     // horizontal pass of one raw row -> nmx/nmn/ncen
-    auto horizontal = [&](const RawRow& r) {
+    auto horizontal = [&](const RawRow<NG>& r) {
 #pragma unroll
-        for (int l = 0; l < 5; l++) {
+        for (int l = 0; l < ND; l++) {
             const float da = __fsub_rn(r.g[l + 1].x, r.g[l].x), db = __fsub_rn(r.g[l + 1].y, r.g[l].y);
             const float dh = __fsub_rn(r.gh[l + 1], r.gh[l]);
             float left = __shfl_up_sync(0xffffffffu, db, 1);
@@ -85,47 +81,47 @@ detect_kernel(const __grid_constant__ FrameParams fp) {
             const float hi = fmaxf(da, db), lo = fminf(da, db);
             nmx[l][0] = fmaxf(left, hi); nmx[l][1] = fmaxf(hi, right);
             nmn[l][0] = fminf(left, lo); nmn[l][1] = fminf(lo, right);
-            if (l >= 1 && l <= 3) { ncen[l - 1][0] = da; ncen[l - 1][1] = db; }
+            if (l >= 1 && l <= NS) { ncen[l - 1][0] = da; ncen[l - 1][1] = db; }
         }
     };
 
-    RawRow raw;
-    load_raw(col + (size_t)(ys - 1) * o.pitch, ls, x, xh, halo_lane, raw);
+    RawRow<NG> raw;
+    load_raw<NG>(col + (size_t)(ys - 1) * o.pitch, ls, x, xh, halo_lane, raw);
     horizontal(raw);
 #pragma unroll
-    for (int l = 0; l < 5; l++)
+    for (int l = 0; l < ND; l++)
 #pragma unroll
         for (int k = 0; k < 2; k++) { pmx[l][k] = nmx[l][k]; pmn[l][k] = nmn[l][k]; }
-    load_raw(col + (size_t)ys * o.pitch, ls, x, xh, halo_lane, raw);
+    load_raw<NG>(col + (size_t)ys * o.pitch, ls, x, xh, halo_lane, raw);
     horizontal(raw);
 #pragma unroll
-    for (int l = 0; l < 5; l++)
+    for (int l = 0; l < ND; l++)
 #pragma unroll
         for (int k = 0; k < 2; k++) {
             qmx[l][k] = fmaxf(pmx[l][k], nmx[l][k]); qmn[l][k] = fminf(pmn[l][k], nmn[l][k]);
             pmx[l][k] = nmx[l][k]; pmn[l][k] = nmn[l][k];
         }
 #pragma unroll
-    for (int s = 0; s < 3; s++) { cen[s][0] = ncen[s][0]; cen[s][1] = ncen[s][1]; }
-    load_raw(col + (size_t)(ys + 1) * o.pitch, ls, x, xh, halo_lane, raw);
+    for (int s = 0; s < NS; s++) { cen[s][0] = ncen[s][0]; cen[s][1] = ncen[s][1]; }
+    load_raw<NG>(col + (size_t)(ys + 1) * o.pitch, ls, x, xh, halo_lane, raw);
 
     for (int y = ys; y < ye; y++) {
         // `raw` holds row y+1; start fetching row y+2 (the last one is a harmless in-bounds re-read)
-        RawRow nxt;
-        load_raw(col + (size_t)min(y + 2, o.h - 1) * o.pitch, ls, x, xh, halo_lane, nxt);
+        RawRow<NG> nxt;
+        load_raw<NG>(col + (size_t)min(y + 2, o.h - 1) * o.pitch, ls, x, xh, halo_lane, nxt);
         horizontal(raw);
-        float vmx[5][2], vmn[5][2];
+        float vmx[ND][2], vmn[ND][2];
 #pragma unroll
-        for (int l = 0; l < 5; l++)
+        for (int l = 0; l < ND; l++)
 #pragma unroll
             for (int k = 0; k < 2; k++) {
                 vmx[l][k] = fmaxf(qmx[l][k], nmx[l][k]); vmn[l][k] = fminf(qmn[l][k], nmn[l][k]);
                 qmx[l][k] = fmaxf(pmx[l][k], nmx[l][k]); qmn[l][k] = fminf(pmn[l][k], nmn[l][k]);
                 pmx[l][k] = nmx[l][k]; pmn[l][k] = nmn[l][k];
             }
-        unsigned be[3], bo[3];
+        unsigned be[NS], bo[NS];
 #pragma unroll
-        for (int s = 0; s < kScales; s++) {
+        for (int s = 0; s < NS; s++) {
             bool ext[2];
 #pragma unroll
             for (int k = 0; k < 2; k++) {
@@ -139,14 +135,38 @@ detect_kernel(const __grid_constant__ FrameParams fp) {
             bo[s] = __ballot_sync(0xffffffffu, ext[1]);
             cen[s][0] = ncen[s][0]; cen[s][1] = ncen[s][1];
         }
-        if (lane < kScales) {  // lane s stores scale s
-            const unsigned e = lane == 0 ? be[0] : (lane == 1 ? be[1] : be[2]);
-            const unsigned od = lane == 0 ? bo[0] : (lane == 1 ? bo[1] : bo[2]);
-            const int row = lane * o.h + y;
+        if (lane < NS) {  // lane s stores scale s0 + s
+            unsigned e = be[0], od = bo[0];
+#pragma unroll
+            for (int s = 1; s < NS; s++)
+                if (lane == s) { e = be[s]; od = bo[s]; }
+            const int row = (s0 + lane) * o.h + y;
             *reinterpret_cast<uint2*>(o.mask + (size_t)row * o.words + 2 * cs) = make_uint2(e, od);
             if (e | od) atomicAdd(o.rowcount + row, __popc(e) + __popc(od));
         }
         raw = nxt;
+    }
+}
+
+// grid.x: warp tasks (strip x row block) of the octave range, grid.y: groups of up to three scales -- scale group g
+// covers scales [3g, min(nScales, 3g + 3)) and reads the Gaussian layers 3g .. 3g + ns + 2 (numOctaveLayers = 3: one
+// group, every layer read once).
+__global__ void __launch_bounds__(kDetThreads, 4)
+detect_kernel(const __grid_constant__ FrameParams fp) {
+    const int lane = threadIdx.x & 31;
+    const int task = fp.oct[fp.o_begin].det_task0 + blockIdx.x * (kDetThreads / 32) + (threadIdx.x >> 5);
+    if (task >= (fp.o_end < fp.nOct ? fp.oct[fp.o_end].det_task0 : fp.det_tasks)) return;
+    int oi = fp.o_begin;
+    while (oi + 1 < fp.o_end && task >= fp.oct[oi + 1].det_task0) oi++;
+    const OctParams& o = fp.oct[oi];
+    const int t = task - o.det_task0;
+    const int cs = t % o.det_cols, rs = t / o.det_cols;
+    const int s0 = 3 * blockIdx.y;
+    switch (min(3, fp.nScales - s0)) {
+        case 3: detect_strip<3>(fp, o, cs, rs, s0, lane); break;
+        case 2: detect_strip<2>(fp, o, cs, rs, s0, lane); break;
+        case 1: detect_strip<1>(fp, o, cs, rs, s0, lane); break;
+        default: break;
     }
 }
 
@@ -161,7 +181,7 @@ scatter_kernel(const __grid_constant__ FrameParams fp) {
     int oi = fp.o_begin;
     while (oi + 1 < fp.o_end && cta >= fp.oct[oi + 1].scat_cta0) oi++;
     const OctParams& o = fp.oct[oi];
-    const int nrows = kScales * o.h;
+    const int nrows = fp.nScales * o.h;
     const int row_first = (cta - o.scat_cta0) * 8;
     const int row = row_first + warp;
     int part = 0;
@@ -272,7 +292,8 @@ refine_kernel(const __grid_constant__ FrameParams fp) {
     int accept = 1;
     // A stale slot (only reachable when an octave overflows its cap, appendix A.1) can hold
     // anything; the reference would read outside its DoG block there. Reject instead.
-    if (l < 1 || l > 3 || r < 1 || r >= o.h - 1 || c < 1 || c >= o.w - 1) { accept = 0; it = 5; }
+    const int nS = fp.nScales;
+    if (l < 1 || l > nS || r < 1 || r >= o.h - 1 || c < 1 || c >= o.w - 1) { accept = 0; it = 5; }
     for (; it < 5; it++) {
         const float c_c = D(l, r, c);
         const float c_xp = D(l, r, c + 1), c_xm = D(l, r, c - 1);
@@ -297,7 +318,7 @@ refine_kernel(const __grid_constant__ FrameParams fp) {
         l = (int)__fsub_rn((float)l, roundf(x[2]));
         r = (int)__fsub_rn((float)r, roundf(x[1]));
         c = (int)__fsub_rn((float)c, roundf(x[0]));
-        if (l < 1 || l > 3) { accept = 0; break; }
+        if (l < 1 || l > nS) { accept = 0; break; }  // SiftOps.cu:154: l > size.z - 2, size.z = n + 2 DoG layers
         if ((float)r < 5.f || (float)r >= sy - 5.f || (float)c < 5.f || (float)c >= sx - 5.f) { accept = 0; break; }
     }
     if (it >= 5) accept = 0;
@@ -311,7 +332,7 @@ refine_kernel(const __grid_constant__ FrameParams fp) {
         // reference SASS: t = fma(d2,x2, fma(d0,x0, d1*x1)); contrast = fma(v, 1/255, t*-0.5)
         const float t = __fmaf_rn(d2, x[2], __fmaf_rn(d0, x[0], __fmul_rn(d1, x[1])));
         const float contrast = __fmaf_rn(c_c, img_scale, __fmul_rn(t, -0.5f));
-        if (__fmul_rn(fabsf(contrast), (float)kScales) < fp.contrast_thr) accept = 0;
+        if (__fmul_rn(fabsf(contrast), (float)nS) < fp.contrast_thr) accept = 0;
         if (accept) {
             const float v2 = __fadd_rn(c_c, c_c);
             const float dxx = __fmul_rn(__fsub_rn(__fadd_rn(c_xp, c_xm), v2), second);
@@ -328,7 +349,7 @@ refine_kernel(const __grid_constant__ FrameParams fp) {
             o.cand[idx] = make_float3((float)(c * (1 << oi)), (float)(r * (1 << oi)), (float)l);
             float4 f = o.candF[idx];
             f.x = (float)(oi + (l << 8) + ((int)__fmul_rn(roundf(__fadd_rn(x[2], 0.5f)), 255.f) << 16));
-            const float pw = powf(2.f, __fdiv_rn(__fsub_rn((float)l, x[2]), (float)kScales));
+            const float pw = powf(2.f, __fdiv_rn(__fsub_rn((float)l, x[2]), (float)nS));
             const float sp = __fmul_rn(__fmul_rn(fp.sigma, pw), (float)(1 << oi));
             f.y = __fadd_rn(sp, sp);
             f.z = fabsf(contrast);
@@ -361,11 +382,12 @@ compact_refined_kernel(const __grid_constant__ FrameParams fp) {
 void launch_detect(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     const int warps = kDetThreads / 32;
     const int t0 = fp.oct[o_begin].det_task0, t1 = o_end < fp.nOct ? fp.oct[o_end].det_task0 : fp.det_tasks;
-    if (t1 > t0) detect_kernel<<<(t1 - t0 + warps - 1) / warps, kDetThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
+    dim3 grid((t1 - t0 + warps - 1) / warps, (fp.nScales + 2) / 3);
+    if (t1 > t0) detect_kernel<<<grid, kDetThreads, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 void launch_scatter(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
     const OctParams& last = fp.oct[o_end - 1];
-    const int c0 = fp.oct[o_begin].scat_cta0, c1 = last.scat_cta0 + (kScales * last.h + 7) / 8;
+    const int c0 = fp.oct[o_begin].scat_cta0, c1 = last.scat_cta0 + (fp.nScales * last.h + 7) / 8;
     scatter_kernel<<<c1 - c0, 256, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {

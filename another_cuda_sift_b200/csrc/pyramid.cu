@@ -1,121 +1,32 @@
-// Gaussian scale-space kernels: fused separable blur (vertical then horizontal in ONE launch,
-// the intermediate never leaves shared memory) and the bilinear 2x downsample.
+// Gaussian scale-space kernels.
 //
-// Replaces image_func/Filter.cu:8-51 + FilterImpl.cuh:6-45 (two global-memory passes per layer)
-// and image_func/Resize.cu:6-64. Arithmetic is bit-identical to the reference: every output is
-// the same in-order chain acc = fmaf(pixel, tap, acc) over offsets -r..+r starting from 0, first
-// over rows, then over columns of the row-filtered image, with reflect-101 indices at the image
-// border in both passes.
+// Replaces image_func/Filter.cu:8-51 + FilterImpl.cuh:6-45 (two global-memory passes per layer),
+// image_func/Resize.cu:6-64 and the per-layer launch loop of interface/Detector.cu:274-305.
 //
-// Roofline: HBM-bound. Algorithmic bytes per layer = 8*w*h (read once, write once).
+// Arithmetic is bit-identical to the reference: every blurred value is the same in-order chain
+// acc = fmaf(pixel, tap, acc) over offsets -r..+r starting from 0, first over rows, then over columns of
+// the row-filtered image, with reflect-101 indices at the image border in both passes; the 2x resample is
+// the reference's expression tree with the FMA contraction of its sm_100a SASS.
+//
+//  blur_chain_kernel   K <= 3 successive blurs of one octave in ONE launch, 2-D tiles: the CTA computes stage k
+//                      on its output tile grown by the radii of the later stages (the halo is recomputed, never
+//                      exchanged), every intermediate lives in shared memory, every stage's tile goes to its
+//                      layer of the Gaussian stack. Stage 0 is either a plain layer or the bilinear 2x resample
+//                      of the previous octave's layer n, computed on the fly (and stored as the base layer).
+//                      The frame graph runs one such launch per octave on the critical path
+//                      (resample + L1..Ln) and one on a side branch (L(n+1), L(n+2)); octave 0 uses single-stage
+//                      launches (its 2.3 Mpx are throughput-, not latency-bound).
+//  blur_generic_kernel any radius <= 42 at run time (uncommon sigma / numOctaveLayers), one stage.
+//  pyramid_tail_kernel ONE CTA walks every octave of <= 4096 pixels.
+//
+// Roofline: HBM/L2-bound in the limit. Algorithmic bytes per layer = 8*w*h (read once, write once).
+#include <type_traits>
+
 #include "common.cuh"
 
 namespace b200sift {
 
 namespace {
-
-constexpr int kTW = 128;      // output columns per CTA (one warp row = 32 lanes x 4 outputs)
-constexpr int kRB = 16;       // output rows per vertical register block
-constexpr int kBlurThreads = 320;  // 10 warps: one vertical-pass sweep covers the 128 + 2R columns of two row blocks
-
-// One CTA: TH = nb*kRB output rows x kTW output columns.
-//  pass 1 (vertical):   each thread owns one column of one row block, keeps kRB+2R input pixels
-//                       in registers (all loads issued up front) and emits kRB row-filtered
-//                       values into shared memory. Columns cover the tile plus an R-wide halo,
-//                       taken at reflect-101 positions, because the horizontal pass of the
-//                       reference reads the row-filtered image at reflected columns.
-//  pass 2 (horizontal): each lane produces 4 consecutive outputs from 4+2R shared-memory values
-//                       fetched as conflict-free LDS.128, stores one STG.128.
-template <int R>
-__global__ void __launch_bounds__(kBlurThreads)
-blur_vh_kernel(const float* __restrict__ in, int in_pitch, float* __restrict__ out, int out_pitch,
-               int w, int h, const __grid_constant__ Taps taps, int nb) {
-    constexpr int RP = (R + 3) & ~3;       // halo rounded up so that rows stay 16-byte aligned
-    constexpr int TWP = kTW + 2 * RP;      // shared row length
-    constexpr int NC = kTW + 2 * R;        // columns that are really needed
-    constexpr int NT = 2 * R + 1;
-    extern __shared__ __align__(16) float tmp[];  // [nb*kRB][TWP]
-
-    const int x0 = blockIdx.x * kTW;
-    const int y0 = blockIdx.y * nb * kRB;
-    const int tid = threadIdx.x;
-
-    for (int t = tid; t < NC * nb; t += kBlurThreads) {
-        const int b = t / NC;
-        const int c = (RP - R) + (t - b * NC);
-        const int x = reflect101(x0 - RP + c, w);
-        const int ybase = y0 + b * kRB - R;
-        float v[kRB + 2 * R];
-        if (ybase >= 0 && ybase + kRB + 2 * R <= h) {
-            // one 64-bit pointer stepped by the row pitch: a single IMAD.WIDE per load instead of the four address
-            // instructions (IADD3 / IMAD.X / LEA / LEA.HI.X) an element-indexed p[i * pitch] compiles to
-            const float* p = in + (size_t)ybase * in_pitch + x;
-#pragma unroll
-            for (int i = 0; i < kRB + 2 * R; i++) {
-                v[i] = __ldg(p);
-                asm volatile("mad.wide.s32 %0, %1, 4, %0;" : "+l"(p) : "r"(in_pitch));
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < kRB + 2 * R; i++) v[i] = __ldg(in + (size_t)reflect101(ybase + i, h) * in_pitch + x);
-        }
-        float* dst = tmp + (size_t)(b * kRB) * TWP + c;
-#pragma unroll
-        for (int r = 0; r < kRB; r++) {
-            float acc = 0.f;
-#pragma unroll
-            for (int k = 0; k < NT; k++) acc = __fmaf_rn(v[r + k], taps.v[k], acc);
-            dst[r * TWP] = acc;
-        }
-    }
-    __syncthreads();
-
-    const int warp = tid >> 5, lane = tid & 31;
-    const int TH = nb * kRB;
-    const int xo = 4 * lane;
-    const int x = x0 + xo;
-    if (x >= w) return;
-    for (int row = warp; row < TH; row += kBlurThreads / 32) {
-        const int y = y0 + row;
-        if (y >= h) break;
-        constexpr int NV = (2 * RP + 4) / 4;
-        float q[NV * 4];
-        const float4* src = reinterpret_cast<const float4*>(tmp + (size_t)row * TWP + xo);
-#pragma unroll
-        for (int m = 0; m < NV; m++) {
-            float4 f = src[m];
-            q[4 * m] = f.x; q[4 * m + 1] = f.y; q[4 * m + 2] = f.z; q[4 * m + 3] = f.w;
-        }
-        float o[4];
-#pragma unroll
-        for (int j = 0; j < 4; j++) {
-            float acc = 0.f;
-#pragma unroll
-            for (int k = 0; k < NT; k++) acc = __fmaf_rn(q[RP - R + j + k], taps.v[k], acc);
-            o[j] = acc;
-        }
-        float* dst = out + (size_t)y * out_pitch + x;
-        if (x + 3 < w) {
-            *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
-        } else {
-            for (int j = 0; j < 4 && x + j < w; j++) dst[j] = o[j];
-        }
-    }
-}
-
-template <int R>
-void launch_blur_r(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
-    constexpr int RP = (R + 3) & ~3;
-    constexpr int TWP = kTW + 2 * RP;
-    // Taller tiles amortise the vertical halo on big images; short tiles spread small images
-    // over more SMs.
-    const int gx = (w + kTW - 1) / kTW;
-    int nb = 4;
-    while (nb > 1 && gx * ((h + nb * kRB - 1) / (nb * kRB)) < 2 * 148) nb >>= 1;
-    dim3 grid(gx, (h + nb * kRB - 1) / (nb * kRB));
-    size_t smem = (size_t)nb * kRB * TWP * sizeof(float);
-    blur_vh_kernel<R><<<grid, kBlurThreads, smem, s>>>(in, in_pitch, out, out_pitch, w, h, taps, nb);
-}
 
 // Bilinear resample with the reference's exact expression tree (image_func/Resize.cu:26-63);
 // the tail is the contraction ptxas chose for the reference on sm_100a:
@@ -134,11 +45,253 @@ __device__ __forceinline__ float bilinear_sample(const float* __restrict__ in, i
     int y2 = yf == 0.f ? y1 + 1 : __float2int_ru(coord_y);
     y2 = min(max_y, max(0, y2));
     const float x2e = __fsub_rn(1.f, xf), y2e = __fsub_rn(1.f, yf);
-    const float v11 = in[(size_t)y1 * in_pitch + x1], v21 = in[(size_t)y1 * in_pitch + x2];
-    const float v12 = in[(size_t)y2 * in_pitch + x1], v22 = in[(size_t)y2 * in_pitch + x2];
+    const float v11 = __ldg(in + (size_t)y1 * in_pitch + x1), v21 = __ldg(in + (size_t)y1 * in_pitch + x2);
+    const float v12 = __ldg(in + (size_t)y2 * in_pitch + x1), v22 = __ldg(in + (size_t)y2 * in_pitch + x2);
     const float a = __fmaf_rn(v11, x2e, __fmul_rn(v21, xf));
     const float r12 = __fmul_rn(__fmaf_rn(v12, x2e, __fmul_rn(v22, xf)), yf);
     return __fmaf_rn(a, y2e, r12);
+}
+
+// ---------------------------------------------------------------- fused blur chain
+struct ChainParams {
+    const float* src;        // plain: the layer to blur; resample: layer n of the previous octave
+    int src_pitch, src_w, src_h;
+    float* base_out;         // resample only: the octave's base layer
+    float* out[3];           // layer written by stage 1..3
+    int pitch, w, h;         // this octave
+    Taps taps[3];
+};
+
+__host__ __device__ constexpr int round_up4(int v) { return (v + 3) & ~3; }
+
+// Geometry shared by kernel and launcher. All shared-memory buffers use ONE coordinate frame: buffer column
+// x - BX, buffer row y - BY with BX = (tx0 - E0 - 6) rounded down to a multiple of 4 (so that image columns that are
+// multiples of 4 sit on 16-byte boundaries and every LDS.128 window of the horizontal pass stays inside the buffer)
+// and BY = ty0 - E0, E0 = R1 + R2 + R3 the halo of stage 0.
+template <int TW, int TH, int RB, int R1, int R2, int R3>
+struct ChainGeom {
+    static constexpr int K = (R2 < 0) ? 1 : (R3 < 0 ? 2 : 3);
+    static constexpr int E0 = R1 + (R2 < 0 ? 0 : R2) + (R3 < 0 ? 0 : R3);
+    static constexpr int E1 = E0 - R1;
+    static constexpr int SW = round_up4(TW + 2 * E0 + 16);   // row stride of every buffer (floats)
+    static constexpr int SH = TH + 2 * E0;                   // rows of the stage-0 region
+    static constexpr int SHV = TH + 2 * E1;                  // rows of the largest row-filtered intermediate
+    static constexpr int kLutRows = SH + RB + 8, kLutCols = SW + 8;
+    // [S even | S odd (K > 1)] [V] [slack rows: partial register blocks read past their region] [row / column tables]
+    static constexpr size_t kFloats = (size_t)SW * SH * (K > 1 ? 2 : 1) + (size_t)SW * SHV + (size_t)SW * RB;
+    static constexpr size_t kSmem = kFloats * sizeof(float) + (size_t)(kLutRows + kLutCols) * sizeof(int);
+};
+
+// Vertical pass of one stage: V(x, y) = chain over rows of S(x, reflect(y + d)) for the columns [xa, xb) and the rows
+// [ya, yb) (image coordinates). A thread owns one column of one RB-row block: RB + 2R values in registers (compile
+// time shared-memory offsets in the interior; through the reflect table at the top / bottom image border), RB
+// in-order chains.
+template <int R, int RB, int SW, int NT>
+__device__ __forceinline__ void chain_vpass(const float* __restrict__ S, float* __restrict__ V, const Taps& t, int xa, int xb,
+                                            int ya, int yb, int BX, int BY, int BYV, bool border, const int* __restrict__ rowlut, int tid) {
+    constexpr int NTAP = 2 * R + 1;
+    const int ncols = xb - xa;
+    const int nblk = (yb - ya + RB - 1) / RB;
+    const float inv_ncols = __frcp_rn((float)ncols);
+    const int items = ncols * nblk;
+    for (int it = tid; it < items; it += NT) {
+        // it / ncols without an integer division: items < 2^16, (it + 0.5) / ncols is never within rounding distance of an integer
+        const int blk = __float2int_rd(((float)it + 0.5f) * inv_ncols);
+        const int c = xa + (it - blk * ncols) - BX;
+        const int y0 = ya + blk * RB;
+        float v[RB + 2 * R];
+        if (!border) {
+            const float* p = S + (y0 - R - BY) * SW + c;
+#pragma unroll
+            for (int i = 0; i < RB + 2 * R; i++) v[i] = p[i * SW];
+        } else {
+            const int* lut = rowlut + blk * RB;
+#pragma unroll
+            for (int i = 0; i < RB + 2 * R; i++) v[i] = S[lut[i] + c];
+        }
+        float* dst = V + (y0 - BYV) * SW + c;
+#pragma unroll
+        for (int r = 0; r < RB; r++) {
+            float acc = 0.f;
+#pragma unroll
+            for (int k = 0; k < NTAP; k++) acc = __fmaf_rn(v[r + k], t.v[k], acc);
+            if (y0 + r < yb) dst[r * SW] = acc;
+        }
+    }
+}
+
+// Horizontal pass: out(x, y) = chain over columns of V(reflect(x + d), y) for the quads [xq0, xq1) (multiples of 4) and
+// rows [ya, yb). A thread produces 4 consecutive outputs from 4 + 2R row-filtered values (LDS.128 in the interior,
+// through the reflect table at the left / right image border), stores them into the next stage's buffer (Snext, may
+// be null) and -- for the part inside the CTA's tile and the image -- into the layer `out`.
+template <int R, int SW, int NT>
+__device__ __forceinline__ void chain_hpass(const float* __restrict__ V, float* __restrict__ Snext, float* __restrict__ out, int pitch,
+                                            const Taps& t, int xq0, int xq1, int ya, int yb, int BX, int BY, int BYV, bool border,
+                                            const int* __restrict__ collut, int tx0, int tx1, int ty0, int ty1, int tid) {
+    constexpr int NTAP = 2 * R + 1;
+    constexpr int RP = round_up4(R);
+    const int nq = (xq1 - xq0) >> 2;
+    const float inv_nq = __frcp_rn((float)nq);
+    const int items = nq * (yb - ya);
+    for (int it = tid; it < items; it += NT) {
+        const int row = __float2int_rd(((float)it + 0.5f) * inv_nq);
+        const int x = xq0 + 4 * (it - row * nq);
+        const int y = ya + row;
+        const float* vrow = V + (y - BYV) * SW;
+        float o[4];
+        if (!border) {
+            constexpr int NV = (2 * RP + 4) / 4;
+            float q[NV * 4];
+            const float4* src = reinterpret_cast<const float4*>(vrow + (x - RP - BX));
+#pragma unroll
+            for (int m = 0; m < NV; m++) {
+                const float4 f = src[m];
+                q[4 * m] = f.x; q[4 * m + 1] = f.y; q[4 * m + 2] = f.z; q[4 * m + 3] = f.w;
+            }
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                float acc = 0.f;
+#pragma unroll
+                for (int k = 0; k < NTAP; k++) acc = __fmaf_rn(q[RP - R + j + k], t.v[k], acc);
+                o[j] = acc;
+            }
+        } else {
+            float q[4 + 2 * R];
+            const int* lut = collut + (x - xq0);
+#pragma unroll
+            for (int i = 0; i < 4 + 2 * R; i++) q[i] = vrow[lut[i]];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                float acc = 0.f;
+#pragma unroll
+                for (int k = 0; k < NTAP; k++) acc = __fmaf_rn(q[j + k], t.v[k], acc);
+                o[j] = acc;
+            }
+        }
+        if (Snext) *reinterpret_cast<float4*>(Snext + (y - BY) * SW + (x - BX)) = make_float4(o[0], o[1], o[2], o[3]);
+        if (y >= ty0 && y < ty1 && x >= tx0 && x < tx1) {   // tx0, tx1 and x are multiples of 4: a quad is inside or outside as a whole
+            float* dst = out + (size_t)y * pitch + x;
+            if (x + 3 < tx1) {
+                *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+            } else {
+                for (int j = 0; j < 4 && x + j < tx1; j++) dst[j] = o[j];
+            }
+        }
+    }
+}
+
+template <bool DOWN, int NT, int TW, int TH, int RB, int R1, int R2, int R3>
+__global__ void __launch_bounds__(NT, 2)
+blur_chain_kernel(const __grid_constant__ ChainParams p) {
+    using G = ChainGeom<TW, TH, RB, R1, R2, R3>;
+    constexpr int K = G::K, E0 = G::E0, SW = G::SW, SH = G::SH;
+    extern __shared__ __align__(16) float smem[];
+    float* S0 = smem;
+    float* S1 = smem + (size_t)SW * SH;                                   // only when K > 1
+    float* Vb = smem + (size_t)SW * SH * (K > 1 ? 2 : 1);
+    int* rowlut = reinterpret_cast<int*>(smem + G::kFloats);
+    int* collut = rowlut + G::kLutRows;
+
+    const int tid = threadIdx.x;
+    const int w = p.w, h = p.h;
+    const int tx0 = blockIdx.x * TW, ty0 = blockIdx.y * TH;
+    const int tx1 = min(w, tx0 + TW), ty1 = min(h, ty0 + TH);  // tx1 may be ragged; tx0 is a multiple of 4
+    const int BX = (tx0 - E0 - 6) & ~3, BY = ty0 - E0;
+    const int BYV = ty0 - G::E1;   // row origin of the row-filtered intermediate (it never needs more than the stage-1 rows)
+
+    // ---- stage 0: the region of the source this tile depends on -> S0
+    {
+        const int xa = max(0, tx0 - E0), xb = min(w, tx0 + TW + E0);
+        const int ya = max(0, ty0 - E0), yb = min(h, ty0 + TH + E0);
+        if constexpr (DOWN) {
+            const int ncols = xb - xa;
+            const float inv = __frcp_rn((float)ncols);
+            const int items = ncols * (yb - ya);
+            for (int it = tid; it < items; it += NT) {
+                const int r = __float2int_rd(((float)it + 0.5f) * inv);
+                const int x = xa + (it - r * ncols), y = ya + r;
+                const float v = bilinear_sample(p.src, p.src_pitch, p.src_w, p.src_h, w, h, x, y);
+                S0[(y - BY) * SW + (x - BX)] = v;
+                if (x >= tx0 && x < tx1 && y >= ty0 && y < ty1) p.base_out[(size_t)y * p.pitch + x] = v;
+            }
+        } else {
+            // whole quads (the pitch is a multiple of 4 floats and >= w: reading a little row padding is harmless)
+            const int xqa = xa & ~3, xqb = (xb + 3) & ~3;
+            const int nq = (xqb - xqa) >> 2;
+            const float inv = __frcp_rn((float)nq);
+            const int items = nq * (yb - ya);
+            for (int it = tid; it < items; it += NT) {
+                const int r = __float2int_rd(((float)it + 0.5f) * inv);
+                const int x = xqa + 4 * (it - r * nq), y = ya + r;
+                const float4 v = __ldg(reinterpret_cast<const float4*>(p.src + (size_t)y * p.src_pitch + x));
+                *reinterpret_cast<float4*>(S0 + (y - BY) * SW + (x - BX)) = v;
+            }
+        }
+    }
+
+    // ---- stages 1..K
+    auto stage = [&](auto rtag, int k, const Taps& t, const float* S, float* Snext, float* out, int Ek) {
+        constexpr int R = decltype(rtag)::value;
+        // stage k is needed on the tile grown by Ek (the radii of the later stages), clipped to the image; its row-filtered
+        // intermediate on the columns of that region grown by R (clipped): everything a reflected read can land on
+        const int xa = max(0, tx0 - Ek), xb = min(w, tx0 + TW + Ek);
+        const int ya = max(0, ty0 - Ek), yb = min(h, ty0 + TH + Ek);
+        const int vxa = max(0, xa - R), vxb = min(w, xb + R);
+        const bool vborder = (ya - R < 0) || (yb + R > h);
+        const int xq0 = xa & ~3, xq1 = (xb + 3) & ~3;
+        const bool hborder = (xq0 - R < 0) || (xq1 + R > w);
+        __syncthreads();   // S complete (previous stage / stage 0); the tables of the previous stage are no longer read
+        if (vborder) {
+            const int nrows = ((yb - ya + RB - 1) / RB) * RB + 2 * R;
+            for (int j = tid; j < nrows; j += NT) rowlut[j] = min(max(reflect101(ya - R + j, h) - BY, 0), SH - 1) * SW;
+        }
+        if (hborder) {
+            const int ncols = (xq1 - xq0) + 2 * R;
+            for (int j = tid; j < ncols; j += NT) collut[j] = min(max(reflect101(xq0 - R + j, w) - BX, 0), SW - 1);
+        }
+        if (vborder || hborder) __syncthreads();
+        chain_vpass<R, RB, SW, NT>(S, Vb, t, vxa, vxb, ya, yb, BX, BY, BYV, vborder, rowlut, tid);
+        __syncthreads();
+        chain_hpass<R, SW, NT>(Vb, Snext, out, p.pitch, t, xq0, xq1, ya, yb, BX, BY, BYV, hborder, collut, tx0, tx1, ty0, ty1, tid);
+        (void)k;
+    };
+    stage(std::integral_constant<int, R1>{}, 1, p.taps[0], S0, K > 1 ? S1 : nullptr, p.out[0], E0 - R1);
+    if constexpr (K >= 2) stage(std::integral_constant<int, (R2 < 0 ? 1 : R2)>{}, 2, p.taps[1], S1, K > 2 ? S0 : nullptr, p.out[1], E0 - R1 - R2);
+    if constexpr (K >= 3) stage(std::integral_constant<int, (R3 < 0 ? 1 : R3)>{}, 3, p.taps[2], S0, nullptr, p.out[2], 0);
+}
+
+// ---------------------------------------------------------------- generic single-stage blur (any radius <= 42)
+constexpr int kGenTW = 64, kGenTH = 32, kGenThreads = 256;
+constexpr int kGenMaxR = (kMaxTaps - 1) / 2;
+
+__global__ void __launch_bounds__(kGenThreads)
+blur_generic_kernel(const float* __restrict__ in, int in_pitch, float* __restrict__ out, int out_pitch, int w, int h,
+                    const __grid_constant__ Taps taps) {
+    extern __shared__ __align__(16) float smem[];
+    const int R = taps.n / 2;
+    const int CW = kGenTW + 2 * R;           // columns of the row-filtered tile
+    float* V = smem;                         // [kGenTH][CW]
+    const int tid = threadIdx.x;
+    const int tx0 = blockIdx.x * kGenTW, ty0 = blockIdx.y * kGenTH;
+    for (int it = tid; it < CW * kGenTH; it += kGenThreads) {
+        const int r = it / CW, c = it - r * CW;
+        const int y = ty0 + r;
+        const int x = reflect101(tx0 - R + c, w);   // the horizontal pass reads the row-filtered image at reflected columns
+        float acc = 0.f;
+        if (y < h)
+            for (int k = 0; k < taps.n; k++) acc = __fmaf_rn(__ldg(in + (size_t)reflect101(y - R + k, h) * in_pitch + x), taps.v[k], acc);
+        V[it] = acc;
+    }
+    __syncthreads();
+    for (int it = tid; it < kGenTW * kGenTH; it += kGenThreads) {
+        const int r = it / kGenTW, c = it - r * kGenTW;
+        const int x = tx0 + c, y = ty0 + r;
+        if (x >= w || y >= h) continue;
+        const float* row = V + r * CW + c;
+        float acc = 0.f;
+        for (int k = 0; k < taps.n; k++) acc = __fmaf_rn(row[k], taps.v[k], acc);
+        out[(size_t)y * out_pitch + x] = acc;
+    }
 }
 
 __global__ void __launch_bounds__(256)
@@ -151,56 +304,93 @@ downsample_kernel(const float* __restrict__ in, int in_pitch, int iw, int ih,
 }
 
 // ---------------------------------------------------------------- pyramid tail
-// Octaves of at most kTailPixels pixels are pure launch latency as separate kernels (5 blurs + 1 resample
-// each, a few microseconds of dependent launches per layer). ONE CTA walks all of them instead: the
-// current layer and the row-filtered intermediate live in shared memory, every layer is also written to
-// its place in the Gaussian stack. Arithmetic is the same in-order fmaf chain as blur_vh_kernel.
+// Octaves of at most kTailPixels pixels are pure launch latency as separate kernels. ONE CTA walks all of them
+// instead: the current layer and the row-filtered intermediate live in shared memory, every layer is also written to
+// its place in the Gaussian stack. Arithmetic is the same in-order fmaf chain as above.
 struct TailParams {
-    Taps taps[kGaussLayers];
+    Taps taps[kMaxLayers];
+    Taps init_taps;
+    const float* input;      // the frame (only read when the tail starts at octave 0)
+    int in_pitch;
     float* gauss[kMaxOctaves];
     int w[kMaxOctaves], h[kMaxOctaves], pitch[kMaxOctaves];
-    int first, nOct;
+    int first, nOct, nScales;
+    int l_begin, l_end;
 };
 
 constexpr int kTailThreads = 1024;
-constexpr int kTailR = 10;  // largest blur radius (21 taps)
+constexpr int kTailR = kGenMaxR;  // largest blur radius the reflect tables cover
 
 // One blur layer of the tail: vertical pass s_cur -> s_tmp, horizontal pass s_tmp -> s_cur (+ global).
+// R > 0: compile-time radius, both passes fully unrolled; R == 0: the radius is read from the taps.
 template <int R>
 __device__ __forceinline__ void tail_layer(const Taps& t, float* s_cur, float* s_tmp, const int* s_rtab, const int* s_ctab,
                                            float* __restrict__ dst, int w, int pitch, int n, int tid) {
-    constexpr int NT = 2 * R + 1;
-    float tap[NT];
-#pragma unroll
-    for (int k = 0; k < NT; k++) tap[k] = t.v[k];
     // i / w without an integer division: n <= 4096, so the float floor of (i + 0.5) / w is exact
     const float inv_w = __frcp_rn((float)w);
-    for (int i = tid; i < n; i += kTailThreads) {
-        const int y = __float2int_rd(((float)i + 0.5f) * inv_w), x = i - y * w;
-        const int* rt = s_rtab + (y - R + kTailR);
-        float v[NT];
+    if constexpr (R > 0) {
+        constexpr int NT = 2 * R + 1;
+        float tap[NT];
 #pragma unroll
-        for (int k = 0; k < NT; k++) v[k] = s_cur[rt[k] + x];
-        float acc = 0.f;
+        for (int k = 0; k < NT; k++) tap[k] = t.v[k];
+        for (int i = tid; i < n; i += kTailThreads) {
+            const int y = __float2int_rd(((float)i + 0.5f) * inv_w), x = i - y * w;
+            const int* rt = s_rtab + (y - R + kTailR);
+            float v[NT];
 #pragma unroll
-        for (int k = 0; k < NT; k++) acc = __fmaf_rn(v[k], tap[k], acc);
-        s_tmp[i] = acc;
+            for (int k = 0; k < NT; k++) v[k] = s_cur[rt[k] + x];
+            float acc = 0.f;
+#pragma unroll
+            for (int k = 0; k < NT; k++) acc = __fmaf_rn(v[k], tap[k], acc);
+            s_tmp[i] = acc;
+        }
+        __syncthreads();
+        for (int i = tid; i < n; i += kTailThreads) {
+            const int y = __float2int_rd(((float)i + 0.5f) * inv_w), x = i - y * w;
+            const int* ct = s_ctab + (x - R + kTailR);
+            const float* row = s_tmp + y * w;
+            float v[NT];
+#pragma unroll
+            for (int k = 0; k < NT; k++) v[k] = row[ct[k]];
+            float acc = 0.f;
+#pragma unroll
+            for (int k = 0; k < NT; k++) acc = __fmaf_rn(v[k], tap[k], acc);
+            s_cur[i] = acc;
+            dst[(size_t)y * pitch + x] = acc;
+        }
+    } else {
+        const int nt = t.n, r = t.n / 2;
+        for (int i = tid; i < n; i += kTailThreads) {
+            const int y = __float2int_rd(((float)i + 0.5f) * inv_w), x = i - y * w;
+            const int* rt = s_rtab + (y - r + kTailR);
+            float acc = 0.f;
+            for (int k = 0; k < nt; k++) acc = __fmaf_rn(s_cur[rt[k] + x], t.v[k], acc);
+            s_tmp[i] = acc;
+        }
+        __syncthreads();
+        for (int i = tid; i < n; i += kTailThreads) {
+            const int y = __float2int_rd(((float)i + 0.5f) * inv_w), x = i - y * w;
+            const int* ct = s_ctab + (x - r + kTailR);
+            const float* row = s_tmp + y * w;
+            float acc = 0.f;
+            for (int k = 0; k < nt; k++) acc = __fmaf_rn(row[ct[k]], t.v[k], acc);
+            s_cur[i] = acc;
+            dst[(size_t)y * pitch + x] = acc;
+        }
     }
-    __syncthreads();
-    for (int i = tid; i < n; i += kTailThreads) {
-        const int y = __float2int_rd(((float)i + 0.5f) * inv_w), x = i - y * w;
-        const int* ct = s_ctab + (x - R + kTailR);
-        const float* row = s_tmp + y * w;
-        float v[NT];
-#pragma unroll
-        for (int k = 0; k < NT; k++) v[k] = row[ct[k]];
-        float acc = 0.f;
-#pragma unroll
-        for (int k = 0; k < NT; k++) acc = __fmaf_rn(v[k], tap[k], acc);
-        s_cur[i] = acc;
-        dst[(size_t)y * pitch + x] = acc;
+    __syncthreads();  // also orders this CTA's global writes of layer n before the next octave reads them
+}
+
+__device__ __forceinline__ void tail_layer_any(const Taps& t, float* s_cur, float* s_tmp, const int* s_rtab, const int* s_ctab,
+                                               float* __restrict__ dst, int w, int pitch, int n, int tid) {
+    switch (t.n / 2) {  // the radii of the default configuration get unrolled code
+        case 4: tail_layer<4>(t, s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
+        case 5: tail_layer<5>(t, s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
+        case 6: tail_layer<6>(t, s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
+        case 8: tail_layer<8>(t, s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
+        case 10: tail_layer<10>(t, s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
+        default: tail_layer<0>(t, s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
     }
-    __syncthreads();  // also orders this CTA's global writes of layer 3 before the next octave reads them
 }
 
 __global__ void __launch_bounds__(kTailThreads)
@@ -212,34 +402,36 @@ pyramid_tail_kernel(const __grid_constant__ TailParams tp) {
     __shared__ int s_rtab[kTailMaxDim + 2 * kTailR];
     __shared__ int s_ctab[kTailMaxDim + 2 * kTailR];
     const int tid = threadIdx.x;
-    for (int o = tp.first; o < tp.nOct; o++) {
+    // l_begin == 0: the octaves depend on each other (one CTA walks them all); l_begin > 0: every octave continues from
+    // its own stored layer l_begin - 1, CTA b takes octave first + b
+    const int o_lo = tp.l_begin > 0 ? tp.first + (int)blockIdx.x : tp.first;
+    const int o_hi = tp.l_begin > 0 ? o_lo + 1 : tp.nOct;
+    for (int o = o_lo; o < o_hi; o++) {
         const int w = tp.w[o], h = tp.h[o], pitch = tp.pitch[o], n = w * h;
         float* g = tp.gauss[o];
         const size_t ls = (size_t)pitch * h;
         for (int j = tid; j < h + 2 * kTailR; j += kTailThreads) s_rtab[j] = reflect101(j - kTailR, h) * w;
         for (int j = tid; j < w + 2 * kTailR; j += kTailThreads) s_ctab[j] = reflect101(j - kTailR, w);
-        if (o == tp.first) {  // base layer was produced by the launch before this kernel
-            for (int i = tid; i < n; i += kTailThreads) s_cur[i] = g[(size_t)(i / w) * pitch + i % w];
-        } else {              // bilinear resample of the previous octave's layer 3 (written by this CTA)
-            const float* src = tp.gauss[o - 1] + (size_t)tp.pitch[o - 1] * tp.h[o - 1] * kScales;
+        if (tp.l_begin > 0) {    // continue from a layer that an earlier launch left in the stack
+            const float* src = g + ls * (tp.l_begin - 1);
+            for (int i = tid; i < n; i += kTailThreads) s_cur[i] = src[(size_t)(i / w) * pitch + i % w];
+            __syncthreads();
+        } else if (o == 0) {     // the frame itself: initial blur (interface/Detector.cu:253-258) -> layer 0
+            for (int i = tid; i < n; i += kTailThreads) s_cur[i] = tp.input[(size_t)(i / w) * tp.in_pitch + i % w];
+            __syncthreads();
+            tail_layer_any(tp.init_taps, s_cur, s_tmp, s_rtab, s_ctab, g, w, pitch, n, tid);
+        } else {                 // bilinear resample of the previous octave's layer n (written by this CTA or by the launch before)
+            const float* src = tp.gauss[o - 1] + (size_t)tp.pitch[o - 1] * tp.h[o - 1] * tp.nScales;
             for (int i = tid; i < n; i += kTailThreads) {
                 const int y = i / w, x = i - y * w;
                 const float v = bilinear_sample(src, tp.pitch[o - 1], tp.w[o - 1], tp.h[o - 1], w, h, x, y);
                 s_cur[i] = v;
                 g[(size_t)y * pitch + x] = v;
             }
+            __syncthreads();
         }
-        __syncthreads();
-        for (int l = 1; l < kGaussLayers; l++) {
-            float* dst = g + ls * l;
-            switch (tp.taps[l].n / 2) {  // compile-time radius: both passes fully unrolled
-                case 4: tail_layer<4>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
-                case 5: tail_layer<5>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
-                case 6: tail_layer<6>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
-                case 8: tail_layer<8>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
-                default: tail_layer<10>(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, dst, w, pitch, n, tid); break;
-            }
-        }
+        for (int l = max(1, tp.l_begin); l < tp.l_end; l++)
+            tail_layer_any(tp.taps[l], s_cur, s_tmp, s_rtab, s_ctab, g + ls * l, w, pitch, n, tid);
     }
 }
 
@@ -258,17 +450,111 @@ u8_to_float_kernel(const uint8_t* __restrict__ in, size_t in_pitch, float* __res
     }
 }
 
+// ---- launch tables -------------------------------------------------------------------------------------------
+// Single-stage tiles: 128 x 64 (two CTAs of 320 threads per SM) when that fills the GPU, else 128 x 32.
+constexpr int kOneThreads = 320, kOneTW = 128, kOneRB = 16;
+// Fused chains: 64 x 32 tiles, 256 threads, 8-row register blocks.
+constexpr int kFuseThreads = 256, kFuseTW = 64, kFuseTH = 32, kFuseRB = 8;
+
+template <bool DOWN, int NT, int TW, int TH, int RB, int R1, int R2, int R3>
+void launch_chain_inst(const ChainParams& p, cudaStream_t s) {
+    using G = ChainGeom<TW, TH, RB, R1, R2, R3>;
+    dim3 grid((p.w + TW - 1) / TW, (p.h + TH - 1) / TH);
+    blur_chain_kernel<DOWN, NT, TW, TH, RB, R1, R2, R3><<<grid, NT, G::kSmem, s>>>(p);
+}
+template <bool DOWN, int NT, int TW, int TH, int RB, int R1, int R2, int R3>
+cudaError_t setup_chain_inst() {
+    using G = ChainGeom<TW, TH, RB, R1, R2, R3>;
+    return cudaFuncSetAttribute(blur_chain_kernel<DOWN, NT, TW, TH, RB, R1, R2, R3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::kSmem);
+}
+
+constexpr int kMaxOneR = 16;  // single-stage instantiations exist for every radius 1..16
+
+template <int R>
+void launch_one_r(const ChainParams& p, cudaStream_t s) {
+    // taller tiles amortise the vertical halo; take them when they still give every SM its two CTAs' worth of work
+    const int gx = (p.w + kOneTW - 1) / kOneTW;
+    if (gx * ((p.h + 63) / 64) >= 148) launch_chain_inst<false, kOneThreads, kOneTW, 64, kOneRB, R, -1, -1>(p, s);
+    else launch_chain_inst<false, kOneThreads, kOneTW, 32, kOneRB, R, -1, -1>(p, s);
+}
+template <int R>
+cudaError_t setup_one_r() {
+    cudaError_t e = setup_chain_inst<false, kOneThreads, kOneTW, 64, kOneRB, R, -1, -1>();
+    if (e != cudaSuccess) return e;
+    return setup_chain_inst<false, kOneThreads, kOneTW, 32, kOneRB, R, -1, -1>();
+}
+template <int R>
+struct OneTable {
+    static void launch(int r, const ChainParams& p, cudaStream_t s) {
+        if (r == R) launch_one_r<R>(p, s);
+        else OneTable<R - 1>::launch(r, p, s);
+    }
+    static cudaError_t setup() {
+        cudaError_t e = setup_one_r<R>();
+        return e != cudaSuccess ? e : OneTable<R - 1>::setup();
+    }
+};
+template <>
+struct OneTable<0> {
+    static void launch(int, const ChainParams&, cudaStream_t) {}
+    static cudaError_t setup() { return cudaSuccess; }
+};
+
+// the fused chains of the default configuration (sigma 1.6, numOctaveLayers 3): resample + 9/11/13 taps, 17/21 taps
+bool is_radii(const BlurStage* st, int n, int a, int b, int c) {
+    const int want[3] = {a, b, c};
+    int k = 0;
+    while (k < 3 && want[k] >= 0) k++;
+    if (n != k) return false;
+    for (int i = 0; i < n; i++)
+        if (st[i].taps->n != 2 * want[i] + 1) return false;
+    return true;
+}
+
 }  // namespace
 
-void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
-    switch (taps.n / 2) {
-        case 4: launch_blur_r<4>(in, in_pitch, out, out_pitch, w, h, taps, s); break;
-        case 5: launch_blur_r<5>(in, in_pitch, out, out_pitch, w, h, taps, s); break;
-        case 6: launch_blur_r<6>(in, in_pitch, out, out_pitch, w, h, taps, s); break;
-        case 8: launch_blur_r<8>(in, in_pitch, out, out_pitch, w, h, taps, s); break;
-        case 10: launch_blur_r<10>(in, in_pitch, out, out_pitch, w, h, taps, s); break;
-        default: break;  // engine.cu rejects other sigmas at create time
+cudaError_t pyramid_setup() {
+    cudaError_t e = OneTable<kMaxOneR>::setup();
+    if (e != cudaSuccess) return e;
+    e = setup_chain_inst<true, kFuseThreads, kFuseTW, kFuseTH, kFuseRB, 4, 5, 6>();
+    if (e != cudaSuccess) return e;
+    e = setup_chain_inst<false, kFuseThreads, kFuseTW, kFuseTH, kFuseRB, 8, 10, -1>();
+    if (e != cudaSuccess) return e;
+    return cudaFuncSetAttribute(blur_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                (int)((kGenTW + 2 * kGenMaxR) * kGenTH * sizeof(float)));
+}
+
+bool blur_chain_supported(bool from_prev_octave, const BlurStage* st, int n) {
+    if (from_prev_octave) return is_radii(st, n, 4, 5, 6);
+    if (n == 1) return (st[0].taps->n & 1) && st[0].taps->n / 2 >= 1 && st[0].taps->n / 2 <= kMaxOneR;
+    return is_radii(st, n, 8, 10, -1);
+}
+
+void launch_blur_chain(const float* src, int src_pitch, int src_w, int src_h, bool from_prev_octave, float* base_out,
+                       const BlurStage* st, int n, int pitch, int w, int h, cudaStream_t s) {
+    ChainParams p;
+    p.src = src; p.src_pitch = src_pitch; p.src_w = src_w; p.src_h = src_h;
+    p.base_out = base_out;
+    p.pitch = pitch; p.w = w; p.h = h;
+    for (int i = 0; i < 3; i++) {
+        p.out[i] = i < n ? st[i].out : nullptr;
+        if (i < n) p.taps[i] = *st[i].taps;
+        else p.taps[i].n = 0;
     }
+    if (from_prev_octave) launch_chain_inst<true, kFuseThreads, kFuseTW, kFuseTH, kFuseRB, 4, 5, 6>(p, s);
+    else if (n == 1) OneTable<kMaxOneR>::launch(st[0].taps->n / 2, p, s);
+    else launch_chain_inst<false, kFuseThreads, kFuseTW, kFuseTH, kFuseRB, 8, 10, -1>(p, s);
+}
+
+void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
+    BlurStage st{out, &taps};
+    if (blur_chain_supported(false, &st, 1) && in_pitch % 4 == 0) {
+        launch_blur_chain(in, in_pitch, w, h, false, nullptr, &st, 1, out_pitch, w, h, s);
+        return;
+    }
+    const int R = taps.n / 2;
+    dim3 grid((w + kGenTW - 1) / kGenTW, (h + kGenTH - 1) / kGenTH);
+    blur_generic_kernel<<<grid, kGenThreads, (size_t)(kGenTW + 2 * R) * kGenTH * sizeof(float), s>>>(in, in_pitch, out, out_pitch, w, h, taps);
 }
 
 void launch_downsample(const float* in, int in_pitch, int iw, int ih, float* out, int out_pitch, int ow, int oh, cudaStream_t s) {
@@ -276,16 +562,28 @@ void launch_downsample(const float* in, int in_pitch, int iw, int ih, float* out
     downsample_kernel<<<grid, 256, 0, s>>>(in, in_pitch, iw, ih, out, out_pitch, ow, oh);
 }
 
-void launch_pyramid_tail(const FrameParams& fp, const Taps* taps, int first, cudaStream_t s) {
+void launch_pyramid_tail(const FrameParams& fp, const Taps* taps, const Taps& init_taps, const float* input, int in_pitch,
+                         int first, int l_begin, int l_end, cudaStream_t s) {
     TailParams tp;
-    for (int l = 0; l < kGaussLayers; l++) tp.taps[l] = taps[l];
-    for (int o = 0; o < fp.nOct; o++) {
-        tp.gauss[o] = fp.oct[o].gauss;
-        tp.w[o] = fp.oct[o].w; tp.h[o] = fp.oct[o].h; tp.pitch[o] = fp.oct[o].pitch;
+    for (int l = 0; l < kMaxLayers; l++) {
+        if (l < fp.nLayers) tp.taps[l] = taps[l];
+        else tp.taps[l].n = 0;
+    }
+    tp.init_taps = init_taps;
+    tp.input = input;
+    tp.in_pitch = in_pitch;
+    for (int o = 0; o < kMaxOctaves; o++) {
+        tp.gauss[o] = o < fp.nOct ? fp.oct[o].gauss : nullptr;
+        tp.w[o] = o < fp.nOct ? fp.oct[o].w : 0;
+        tp.h[o] = o < fp.nOct ? fp.oct[o].h : 0;
+        tp.pitch[o] = o < fp.nOct ? fp.oct[o].pitch : 0;
     }
     tp.first = first;
     tp.nOct = fp.nOct;
-    pyramid_tail_kernel<<<1, kTailThreads, 0, s>>>(tp);
+    tp.nScales = fp.nScales;
+    tp.l_begin = l_begin;
+    tp.l_end = l_end;
+    pyramid_tail_kernel<<<l_begin > 0 ? fp.nOct - first : 1, kTailThreads, 0, s>>>(tp);
 }
 
 void launch_u8_to_float(const uint8_t* in, size_t in_pitch, float* out, int out_pitch, int w, int h, cudaStream_t s) {

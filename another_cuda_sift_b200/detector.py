@@ -160,8 +160,7 @@ class Detector:
             # the engine orders its copy after the stream that produced the tensor (torch's current stream)
             check(self.lib.b200sift_detect_device_async(h, image.data_ptr(), image.stride(0) * 4,
                                                         C.c_void_p(torch.cuda.current_stream().cuda_stream)))
-            self._hold(image)
-            image.record_stream(torch.cuda.ExternalStream(self.stream))  # keep the allocator off it until the copy ran
+            self._hold(image)  # the reference keeps the caching allocator off the tensor until its copy has long run
             return
         if hasattr(image, "numpy") and not isinstance(image, np.ndarray):
             image = image.numpy()  # CPU torch tensor (pinned or not) shares memory
@@ -203,7 +202,9 @@ class Detector:
         if out is None:
             out = torch.empty((self.config.numFeatures,), dtype=torch.int32, device="cuda")
         check(self.lib.b200sift_match_consecutive_async(self._handle(), out.data_ptr()))
-        out.record_stream(torch.cuda.ExternalStream(self.stream))  # the caching allocator must not recycle it under the matcher
+        # the matcher writes `out` on the engine's stream, which torch's caching allocator knows nothing about: keep a
+        # reference for as many frames as the engine has in flight, so the memory cannot be recycled under the kernel
+        self._keep_out = (getattr(self, "_keep_out", None) or [])[-self.frames_in_flight:] + [out]
         return out
 
     def copyResultsAsync(self, host: "HostResults") -> None:
@@ -238,7 +239,9 @@ class Detector:
 
     @property
     def frames_in_flight(self) -> int:
-        return int(self.lib.b200sift_frames_in_flight())
+        if getattr(self, "_fif", None) is None:
+            self._fif = int(self.lib.b200sift_frames_in_flight())
+        return self._fif
 
     @property
     def stream(self) -> int:
@@ -282,7 +285,7 @@ class Detector:
 
     def debug_gauss(self, o: int) -> np.ndarray:
         oc = self.octaves[o]
-        out = np.zeros((6, oc["h"], oc["w"]), np.float32)
+        out = np.zeros((self.config.numOctaveLayers + 3, oc["h"], oc["w"]), np.float32)
         check(self.lib.b200sift_debug_get_stack(self._handle(), o, 0, out.ctypes.data))
         return out
 
@@ -299,8 +302,8 @@ class Detector:
         return dict(P=c[0], M=c[1], T=c[2])
 
     def debug_taps(self, which: int) -> np.ndarray:
-        out = np.zeros(64, np.float32)
-        n = check(self.lib.b200sift_debug_get_taps(self._handle(), which, out.ctypes.data, 64))
+        out = np.zeros(128, np.float32)
+        n = check(self.lib.b200sift_debug_get_taps(self._handle(), which, out.ctypes.data, 128))
         return out[:n].copy()
 
 

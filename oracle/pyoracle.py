@@ -45,11 +45,14 @@ class _Oracle:
     prefix = ""
     lib_path = ""
 
-    def __init__(self, cols: int, rows: int, num_features: int = 5000):
+    def __init__(self, cols: int, rows: int, num_features: int = 5000, num_octave_layers: int = 3,
+                 contrast: float = 0.04, edge: float = 10.0, sigma: float = 1.6):
         self.lib = C.CDLL(self.lib_path)
         self.cols, self.rows, self.num_features = cols, rows, num_features
+        self.n_layers = num_octave_layers + 3
         f = self._fn
         f("create", C.c_void_p, [C.c_int, C.c_int, C.c_int])
+        f("create_cfg", C.c_void_p, [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double])
         f("destroy", None, [C.c_void_p])
         f("num_octaves", C.c_int, [C.c_void_p])
         f("octave_info", None, [C.c_void_p, C.c_int, C.c_void_p])
@@ -63,7 +66,10 @@ class _Oracle:
         f("get_counts", None, [C.c_void_p, C.c_int, C.c_void_p])
         f("get_taps", C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int])
         f("match", C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p])
-        self.h = self._create(cols, rows, num_features)
+        if (num_octave_layers, contrast, edge, sigma) == (3, 0.04, 10.0, 1.6):
+            self.h = self._create(cols, rows, num_features)
+        else:
+            self.h = self._create_cfg(cols, rows, num_features, num_octave_layers, contrast, edge, sigma)
         if not self.h:
             raise RuntimeError("oracle create failed")
         self.n_octaves = self._num_octaves(self.h)
@@ -115,7 +121,7 @@ class _Oracle:
 
     # --- stage level
     def stack(self, o: int, which: str) -> np.ndarray:
-        layers = 6 if which == "gauss" else 5
+        layers = self.n_layers if which == "gauss" else self.n_layers - 1
         oc = self.octaves[o]
         out = np.zeros((layers, oc["h"], oc["w"]), np.float32)
         rc = self._get_stack(self.h, o, 0 if which == "gauss" else 1, out.ctypes.data)
@@ -133,8 +139,8 @@ class _Oracle:
         return out
 
     def taps(self, which: int) -> np.ndarray:
-        out = np.zeros(64, np.float32)
-        n = self._get_taps(self.h, which, out.ctypes.data, 64)
+        out = np.zeros(128, np.float32)
+        n = self._get_taps(self.h, which, out.ctypes.data, 128)
         return out[:n].copy()
 
     def match(self, des: np.ndarray, src: np.ndarray) -> np.ndarray:
@@ -148,9 +154,9 @@ class _Oracle:
 class CpuOracle(_Oracle):
     prefix = "oracle_"
 
-    def __init__(self, cols, rows, num_features=5000):
+    def __init__(self, cols, rows, num_features=5000, **cfg):
         self.lib_path = build_cpu()
-        super().__init__(cols, rows, num_features)
+        super().__init__(cols, rows, num_features, **cfg)
 
     def counts(self, o: int):
         c = (C.c_int * 3)()

@@ -56,12 +56,36 @@ int copy_dev(const thrust::device_vector<T>& v, void* out, size_t max_elems) {
 
 extern "C" {
 
+static void* ref_create_from(const CudaSiftConfig& cfg);
+
 void* ref_create(int cols, int rows, int num_features) {
     CudaSiftConfig cfg;
     cfg.col_width = cols;
     cfg.row_width = rows;
     cfg.numFeatures = num_features;
     cfg.upscale = false;
+    return ref_create_from(cfg);
+}
+
+// every field of CudaSiftConfig (types/CudaSiftConfig.hh:3-14) except upscale: the reference is parametric in
+// numOctaveLayers and sigma (Detector.cu:63-94), these entry points let the tests drive it there
+void* ref_create_cfg(int cols, int rows, int num_features, int num_octave_layers, double contrast, double edge, double sigma) {
+    CudaSiftConfig cfg;
+    cfg.col_width = cols;
+    cfg.row_width = rows;
+    cfg.numFeatures = num_features;
+    cfg.numOctaveLayers = num_octave_layers;
+    cfg.contrastThreshould = contrast;
+    cfg.edgeThreshould = edge;
+    cfg.sigma = sigma;
+    cfg.upscale = false;
+    return ref_create_from(cfg);
+}
+
+int ref_num_layers(void* p) { return static_cast<RefHandle*>(p)->det->m_config.numOctaveLayers + 3; }
+
+static void* ref_create_from(const CudaSiftConfig& cfg) {
+    const int rows = cfg.row_width, cols = cfg.col_width;
     auto* h = new RefHandle;
     h->rows = rows;
     h->cols = cols;
