@@ -34,12 +34,26 @@ class Config(C.Structure):
     ]
 
 
+class Options(C.Structure):
+    """b200sift_options (include/b200sift.h): engine options without a counterpart in CudaSiftConfig."""
+
+    _fields_ = [
+        ("frames_in_flight", C.c_int),
+        ("remove_duplicates", C.c_int),
+        ("interpolate_orientation", C.c_int),
+        ("working_upscale", C.c_int),
+        ("reserved", C.c_int * 4),
+    ]
+
+
 # name -> (restype, argtypes); every symbol include/b200sift.h declares
 SIGNATURES = {
     "b200sift_default_config": (None, [C.POINTER(Config)]),
     "b200sift_last_error": (C.c_char_p, []),
     "b200sift_version": (C.c_char_p, []),
     "b200sift_create": (C.c_int, [C.POINTER(Config), C.POINTER(C.c_void_p)]),
+    "b200sift_default_options": (None, [C.POINTER(Options)]),
+    "b200sift_create_ex": (C.c_int, [C.POINTER(Config), C.POINTER(Options), C.POINTER(C.c_void_p)]),
     "b200sift_destroy": (C.c_int, [C.c_void_p]),
     "b200sift_num_octaves": (C.c_int, [C.c_void_p]),
     "b200sift_octave_info": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int)]),
@@ -58,7 +72,7 @@ SIGNATURES = {
     "b200sift_debug_get_taps": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int]),
     "b200sift_debug_run_stages": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "b200sift_dump_frame": (C.c_int, [C.c_void_p, C.c_char_p]),
-    "b200sift_frames_in_flight": (C.c_int, []),
+    "b200sift_frames_in_flight": (C.c_int, [C.c_void_p]),
     "b200sift_launches_per_frame": (C.c_int, [C.c_void_p]),
     "b200sift_time_frames": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]),
     "b200sift_time_frames_pipelined": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]),
@@ -71,6 +85,14 @@ SIGNATURES = {
     "b200sift_match_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "b200sift_match_host": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
     "b200sift_match_launches": (C.c_int, [C.c_int, C.c_int]),
+    "b200sift_nccl_unique_id": (C.c_int, [C.c_void_p]),
+    "b200sift_comm_create": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),
+    "b200sift_comm_destroy": (C.c_int, [C.c_void_p]),
+    "b200sift_comm_info": (C.c_int, [C.c_void_p, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "b200sift_shard_rows": (C.c_int, [C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int)]),
+    "b200sift_match_sharded": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
+    "b200sift_match_sharded_profile": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p,
+                                                 C.POINTER(C.c_float)]),
     "b200sift_match_set_path": (C.c_int, [C.c_int]),
     "b200sift_debug_match_dist": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
 }

@@ -69,6 +69,8 @@ struct FrameParams {
     int* total;          // device: keypoints returned by this slot's frame
     float extrema_thr;   // floor(0.5*contrast/nLayers*255) (interface/Detector.cu:362)
     float contrast_thr, edge_thr, sigma;
+    // opt-in fixes (b200sift_options; all 0 = the reference's behaviour)
+    int opt_dedup, opt_ori_interp, opt_upscale;
 };
 
 constexpr int kDetRows = 16;  // rows per warp task in the detect kernel
@@ -83,6 +85,7 @@ struct BlurStage {
 };
 bool blur_chain_supported(bool from_prev_octave, const BlurStage* st, int n_stages);
 cudaError_t pyramid_setup();  // once per device, outside stream capture (opt-in shared-memory sizes)
+bool pyramid_failed();        // true (once) if a launcher could not encode its TMA tensor map since the last call
 // src: the layer to blur (pitch src_pitch); or, with from_prev_octave, layer n of the previous octave (src_w x src_h),
 // resampled on the fly, the resampled base layer also being written to `base_out`.
 void launch_blur_chain(const float* src, int src_pitch, int src_w, int src_h, bool from_prev_octave, float* base_out,
@@ -100,11 +103,12 @@ void launch_refine(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s
 void launch_compact_refined(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 void launch_orientation(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 void launch_compact_oriented(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
+void launch_dedup(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);            // opt-in: two launches
 cudaError_t descriptor_setup();
 cudaError_t launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s);
 
 int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s,
-                 float* dbg = nullptr);
+                 float* dbg = nullptr, cudaEvent_t* marks = nullptr);
 int match_launch_counts(const __half* q, const __half* t, int max_n, const int* cnt_q, const int* cnt_t, int* out, void* scratch,
                         size_t scratch_bytes, cudaStream_t s);
 int match_launch_simt(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes, cudaStream_t s);

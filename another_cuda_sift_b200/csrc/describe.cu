@@ -75,10 +75,12 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
         if (tid < kOriBins) s_hist[tid] = 0ull;
         __syncthreads();
         // SiftOps.cu:271-297
-        const float scale = __fdiv_rn(__fmul_rn(1.5f, ft.y), (float)(1 << (oi + 1)));
+        // opt_upscale: SiftOps.cu:260,269 (mod = upscaled ? 0 : 1) with the halved size, and positions back in octave pixels
+        const float scale = __fdiv_rn(__fmul_rn(1.5f, ft.y), (float)(1 << (oi + (fp.opt_upscale ? 0 : 1))));
         const float radius = roundf(__fmul_rn(3.f, scale));
-        const int base_px = (int)roundf(__fdiv_rn(kp.x, (float)(1 << oi)));
-        const int base_py = (int)roundf(__fdiv_rn(kp.y, (float)(1 << oi)));
+        const float pos_mul = fp.opt_upscale ? 2.f : 1.f;
+        const int base_px = (int)roundf(__fdiv_rn(__fmul_rn(kp.x, pos_mul), (float)(1 << oi)));
+        const int base_py = (int)roundf(__fdiv_rn(__fmul_rn(kp.y, pos_mul), (float)(1 << oi)));
         int side = (int)__fmaf_rn(2.f, radius, 1.f);
         if (side > 1024) side = 1024;  // only a corrupt stale slot could ask for more
         const int total_dim = side * side;
@@ -185,6 +187,16 @@ orientation_kernel(const __grid_constant__ FrameParams fp) {
                 o.coll[slot] = kp;
                 float4 f = ft;
                 f.w = __fsub_rn(360.f, __fmul_rn(__fdiv_rn((float)tid, 36.f), 360.f));
+                if (fp.opt_ori_interp) {
+                    // opt-in (SiftOps.cu:359 "TODO: interpolate the peak"): parabola through the peak and its neighbours of the
+                    // smoothed histogram, as OpenCV does (features2d/src/sift.simd.hpp:555-557)
+                    const int l = tid > 0 ? tid - 1 : kOriBins - 1, r = tid < kOriBins - 1 ? tid + 1 : 0;
+                    const float hl = s_smooth[l], hc = s_smooth[tid], hr = s_smooth[r];
+                    float bin = (float)tid + 0.5f * (hl - hr) / (hl - 2.f * hc + hr);
+                    bin = bin < 0.f ? (float)kOriBins + bin : (bin >= (float)kOriBins ? bin - (float)kOriBins : bin);
+                    f.w = 360.f - (360.f / (float)kOriBins) * bin;
+                    if (fabsf(f.w - 360.f) < 1.1920929e-7f) f.w = 0.f;
+                }
                 o.collF[slot] = f;
             }
             if (tid == kOriBins - 1) {
@@ -225,6 +237,67 @@ compact_oriented_kernel(const __grid_constant__ FrameParams fp) {
             }
         });
     if (blockIdx.x == 0 && threadIdx.x == 0) o.counts[2] = total;  // T
+}
+
+// ---------------------------------------------------------------- duplicate removal (opt-in)
+// interface/Detector.cu:220 "TODO: remove duplicate". A keypoint is a duplicate when an EARLIER keypoint of the same octave
+// has the same x, y, size and angle (what OpenCV's KeyPointsFilter::removeDuplicated compares); the first one is kept, the
+// order of the survivors is unchanged. Two launches after compact_oriented: flags (each CTA compares its 256 entries with
+// all earlier ones, tiled through shared memory), then a stable compaction into the slot's final list.
+__global__ void __launch_bounds__(kScanBlock)
+dedup_flag_kernel(const __grid_constant__ FrameParams fp) {
+    const OctParams& o = fp.oct[fp.o_begin + blockIdx.y];
+    const int T = min(o.counts[2], o.cap);
+    const int i0 = blockIdx.x * kScanBlock;
+    if (i0 >= T) return;
+    __shared__ float4 s_key[kScanBlock];
+    const int i = i0 + threadIdx.x;
+    float4 mine = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (i < T) {
+        const float3 k = o.cand[i];
+        const float4 f = o.candF[i];
+        mine = make_float4(k.x, k.y, f.y, f.w);
+    }
+    bool dup = false;
+    for (int j0 = 0; j0 <= i0; j0 += kScanBlock) {
+        const int j = j0 + threadIdx.x;
+        if (j < T) {
+            const float3 k = o.cand[j];
+            const float4 f = o.candF[j];
+            s_key[threadIdx.x] = make_float4(k.x, k.y, f.y, f.w);
+        }
+        __syncthreads();
+        const int n = min(kScanBlock, min(T, i) - j0);   // only entries before i
+        for (int t = 0; t < n; t++) {
+            const float4 q = s_key[t];
+            dup |= (q.x == mine.x) & (q.y == mine.y) & (q.z == mine.z) & (q.w == mine.w);
+        }
+        __syncthreads();
+    }
+    if (i < T) o.flag[i] = dup ? 0 : 1;
+}
+
+__global__ void __launch_bounds__(kScanBlock)
+dedup_compact_kernel(const __grid_constant__ FrameParams fp) {
+    const OctParams& o = fp.oct[fp.o_begin + blockIdx.y];
+    const int T = min(o.counts[2], o.cap);
+    if (blockIdx.x > 0 && (int)blockIdx.x * kScanBlock >= T) return;
+    const int total = segment_scan(
+        T, blockIdx.x, [&](int i) { return o.flag[i]; },
+        [&](int i, int v, int excl, int tot) {
+            if (v && excl < fp.numFeatures) {
+                o.fin_kp[excl] = o.cand[i];
+                o.fin_ft[excl] = o.candF[i];
+            }
+        });
+    // the other CTAs of this launch still read counts[2] (T): the new count is parked in counts[3] (free after the
+    // refinement stage) and moved by dedup_publish_kernel
+    if (blockIdx.x == 0 && threadIdx.x == 0) o.counts[3] = total;
+}
+
+__global__ void dedup_publish_kernel(const __grid_constant__ FrameParams fp) {
+    const int oi = fp.o_begin + threadIdx.x;
+    if (oi < fp.o_end) fp.oct[oi].counts[2] = fp.oct[oi].counts[3];
 }
 
 // ---------------------------------------------------------------- descriptor
@@ -557,6 +630,14 @@ void launch_compact_oriented(const FrameParams& fp, int o_begin, int o_end, cuda
     for (int i = o_begin; i < o_end; i++) maxcap = fp.oct[i].cap > maxcap ? fp.oct[i].cap : maxcap;
     dim3 grid((maxcap + kScanBlock - 1) / kScanBlock, o_end - o_begin);
     compact_oriented_kernel<<<grid, kScanBlock, 0, s>>>(octave_range(fp, o_begin, o_end));
+}
+void launch_dedup(const FrameParams& fp, int o_begin, int o_end, cudaStream_t s) {
+    int maxcap = 1;
+    for (int i = o_begin; i < o_end; i++) maxcap = fp.oct[i].cap > maxcap ? fp.oct[i].cap : maxcap;
+    dim3 grid((maxcap + kScanBlock - 1) / kScanBlock, o_end - o_begin);
+    dedup_flag_kernel<<<grid, kScanBlock, 0, s>>>(octave_range(fp, o_begin, o_end));
+    dedup_compact_kernel<<<grid, kScanBlock, 0, s>>>(octave_range(fp, o_begin, o_end));
+    dedup_publish_kernel<<<1, 32, 0, s>>>(octave_range(fp, o_begin, o_end));
 }
 static int g_desc_priority = 0;
 

@@ -31,6 +31,23 @@ int fail(int code, const char* fmt, ...) {
     return code;
 }
 
+}  // namespace
+
+namespace b200sift {
+// last-error setter for the other translation units behind the C ABI (shard.cu)
+int set_error(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return code;
+}
+}  // namespace b200sift
+
+namespace {
+
 #define CU(call)                                                                                  \
     do {                                                                                          \
         cudaError_t e_ = (call);                                                                  \
@@ -68,15 +85,18 @@ inline int pitch_floats(int w) { return ((w * 4 + 511) / 512) * 512 / 4; }
 constexpr int kSideStreams = 6;   // side branches of the frame graph
 constexpr int kBranchPixels = 65536;  // an octave with at least this many pixels gets a branch of its own
 
-constexpr int kSlots = 6;  // frames in flight (measured at 1920x1200: 3 -> 3290, 4 -> 3680, 6 -> 3850 frames/s; ~85 MB per slot)
+// Frames in flight: a create-time option (b200sift_options::frames_in_flight, 3..8). Measured at 1920x1200: 3 -> 3290,
+// 4 -> 3680, 6 -> 3850 frames/s; ~85 MB of device memory per slot there.
+constexpr int kDefaultSlots = 6, kMinSlots = 3, kMaxSlots = 8;
 
-// Everything one frame touches. Frame n runs in slot n % kSlots on the slot's own streams, so the frame graph
+// Everything one frame touches. Frame n runs in slot n % nslots on the slot's own streams, so the frame graph
 // of frame n+1 (pyramid, extrema: latency-bound chains of small launches) overlaps the descriptor kernels of
 // frame n, and the consecutive-frame matcher can read the outputs of frames n-1 and n in place while frame
 // n+1 is already running: with three slots nothing is copied between frames.
 struct Slot {
     FrameParams fp;
     float* d_input = nullptr;
+    float* d_up = nullptr;           // the doubled frame (working upscale only)
     uint8_t* d_input_u8 = nullptr;
     int* d_rowcount_all = nullptr;
     int* h_total = nullptr;          // pinned
@@ -101,8 +121,12 @@ struct b200sift_detector {
     int nScales = 3, nLayers = 6;     // numOctaveLayers, numOctaveLayers + 3
     Taps init_taps;
     Taps taps[kMaxLayers];
-    Slot slot[kSlots];
+    Slot slot[kMaxSlots];
+    int nslots = kDefaultSlots;
+    b200sift_options opt;
     int in_pitch = 0;
+    bool upscaled = false;            // cfg.upscale with b200sift_options::working_upscale
+    int base_w = 0, base_h = 0, up_pitch = 0;   // dimensions of octave 0 (2x the frame when upscaled)
     size_t u8_pitch = 0;
     cudaStream_t copy_stream = nullptr;
     cudaEvent_t ev_user = nullptr;    // orders a caller's stream before the engine's use of a caller-owned device buffer
@@ -117,9 +141,9 @@ struct b200sift_detector {
     int br_begin[kSideStreams] = {0}, br_end[kSideStreams] = {0};
     int launches = 0;
     bool have_frame = false;
-    Slot& cur() { return slot[(frame_no + kSlots - 1) % kSlots]; }    // slot of the latest frame
-    Slot& prev() { return slot[(frame_no + kSlots - 2) % kSlots]; }   // slot of the frame before it
-    const Slot& cur() const { return slot[(frame_no + kSlots - 1) % kSlots]; }
+    Slot& cur() { return slot[(frame_no + nslots - 1) % nslots]; }    // slot of the latest frame
+    Slot& prev() { return slot[(frame_no + nslots - 2) % nslots]; }   // slot of the frame before it
+    const Slot& cur() const { return slot[(frame_no + nslots - 1) % nslots]; }
 };
 
 namespace {
@@ -205,7 +229,16 @@ int enqueue_frame(b200sift_detector* d, Slot& sl, int last_stage, int* launches,
             for (int l = 1; l < nL; l++) st[l] = BlurStage{oc.gauss + ls * l, &d->taps[l]};
             bool fused_main = false;
             if (o == 0) {
-                launch_blur(sl.d_input, d->in_pitch, oc.gauss, oc.pitch, oc.w, oc.h, d->init_taps, s);
+                const float* base = sl.d_input;
+                int base_pitch = d->in_pitch;
+                if (d->upscaled) {  // working upscale (opt-in): the frame doubled with the reference's bilinear resize (Detector.cu:236-244)
+                    launch_downsample(sl.d_input, d->in_pitch, d->cfg.col_width, d->cfg.row_width, sl.d_up, d->up_pitch, oc.w, oc.h, s);
+                    MARK(B200SIFT_K_DOWNSAMPLE);
+                    n++;
+                    base = sl.d_up;
+                    base_pitch = d->up_pitch;
+                }
+                launch_blur(base, base_pitch, oc.gauss, oc.pitch, oc.w, oc.h, d->init_taps, s);
                 MARK(B200SIFT_K_BLUR);
                 n++;
             } else {
@@ -253,9 +286,16 @@ int enqueue_frame(b200sift_detector* d, Slot& sl, int last_stage, int* launches,
         if (d->tail_first < d->nOct) {
             // tail octaves: one CTA walks resample + L0..Ln of all of them (a dependency chain), then one CTA per octave
             // adds L(n+1), L(n+2)
-            launch_pyramid_tail(fp, d->taps, d->init_taps, sl.d_input, d->in_pitch, d->tail_first, 0, nS + 1, s);
+            const float* base = d->upscaled ? sl.d_up : sl.d_input;
+            const int base_pitch = d->upscaled ? d->up_pitch : d->in_pitch;
+            if (d->upscaled && d->tail_first == 0) {
+                launch_downsample(sl.d_input, d->in_pitch, d->cfg.col_width, d->cfg.row_width, sl.d_up, d->up_pitch, fp.oct[0].w, fp.oct[0].h, s);
+                MARK(B200SIFT_K_DOWNSAMPLE);
+                n++;
+            }
+            launch_pyramid_tail(fp, d->taps, d->init_taps, base, base_pitch, d->tail_first, 0, nS + 1, s);
             MARK(B200SIFT_K_BLUR_SMALL);
-            launch_pyramid_tail(fp, d->taps, d->init_taps, sl.d_input, d->in_pitch, d->tail_first, nS + 1, nL, s);
+            launch_pyramid_tail(fp, d->taps, d->init_taps, base, base_pitch, d->tail_first, nS + 1, nL, s);
             MARK(B200SIFT_K_BLUR_SMALL);
             n += 2;
         }
@@ -281,6 +321,10 @@ int enqueue_frame(b200sift_detector* d, Slot& sl, int last_stage, int* launches,
                 MARK(B200SIFT_K_ORIENT);
                 launch_compact_oriented(fp, ob, oe, cs); n++;
                 MARK(B200SIFT_K_COMPACT);
+                if (fp.opt_dedup) {
+                    launch_dedup(fp, ob, oe, cs); n += 3;
+                    MARK(B200SIFT_K_COMPACT);
+                }
             }
         };
         if (fork && d->n_side > 0) CU(cudaEventRecord(sl.ev_fork[0], s));
@@ -303,6 +347,7 @@ int enqueue_frame(b200sift_detector* d, Slot& sl, int last_stage, int* launches,
         MARK(B200SIFT_K_COPY);
     }
     CU(cudaGetLastError());
+    if (pyramid_failed()) return fail(B200SIFT_ECUDA, "cuTensorMapEncodeTiled rejected a Gaussian layer (driver too old for TMA?)");
     if (launches) *launches = n;
     return 0;
 }
@@ -337,6 +382,10 @@ int build(b200sift_detector* d) {
                         c.numOctaveLayers, i, d->taps[i].n, kMaxTaps);
 
     d->in_pitch = pitch_floats(c.col_width);
+    d->upscaled = c.upscale != 0;   // b200sift_create_ex only lets it through with working_upscale
+    d->base_w = d->upscaled ? 2 * c.col_width : c.col_width;   // Detector.cu:44-50
+    d->base_h = d->upscaled ? 2 * c.row_width : c.row_width;
+    d->up_pitch = pitch_floats(d->base_w);
     d->u8_pitch = ((size_t)c.col_width + 511) / 512 * 512;
     d->match_scratch_bytes_ = match_scratch_bytes(c.numFeatures, c.numFeatures);
     CU(descriptor_setup());
@@ -347,7 +396,7 @@ int build(b200sift_detector* d) {
     CU(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&d->ev_user, cudaEventDisableTiming));
 
-    for (int si = 0; si < kSlots; si++) {
+    for (int si = 0; si < d->nslots; si++) {
         Slot& sl = d->slot[si];
         FrameParams& fp = sl.fp;
         std::memset(&fp, 0, sizeof(fp));
@@ -361,15 +410,20 @@ int build(b200sift_detector* d) {
         fp.contrast_thr = (float)c.contrastThreshould;
         fp.edge_thr = (float)c.edgeThreshould;
         fp.sigma = (float)c.sigma;
+        fp.opt_dedup = d->opt.remove_duplicates ? 1 : 0;
+        fp.opt_ori_interp = d->opt.interpolate_orientation ? 1 : 0;
+        fp.opt_upscale = d->upscaled ? 1 : 0;
 
         if (int rc = dev_alloc(d, &sl.d_input, (size_t)d->in_pitch * c.row_width)) return rc;
         if (int rc = dev_alloc(d, &sl.d_input_u8, d->u8_pitch * c.row_width)) return rc;
+        if (d->upscaled)
+            if (int rc = dev_alloc(d, &sl.d_up, (size_t)d->up_pitch * d->base_h)) return rc;
 
         int rows_total = 0, scat_ctas = 0;
         for (int o = 0; o < d->nOct; o++) {
             OctParams& oc = fp.oct[o];
-            oc.w = (int)roundf(c.col_width / powf(2, o));  // Detector.cu:83
-            oc.h = (int)roundf(c.row_width / powf(2, o));
+            oc.w = (int)roundf(d->base_w / powf(2, o));  // Detector.cu:83 (m_init_col / m_init_row: doubled when upscaled)
+            oc.h = (int)roundf(d->base_h / powf(2, o));
             if (oc.w < 1 || oc.h < 1) return fail(B200SIFT_EINVAL, "octave %d is empty", o);
             oc.pitch = pitch_floats(oc.w);
             oc.cap = std::min(oc.pitch * oc.h, c.numFeatures * 10);  // KeyPoint.cu:13, Detector.cu:109
@@ -459,7 +513,7 @@ int build(b200sift_detector* d) {
 
     // Three graphs per slot (parts A, B, C of the frame).
     d->launches = 0;
-    for (int si = 0; si < kSlots; si++) {
+    for (int si = 0; si < d->nslots; si++) {
         Slot& sl = d->slot[si];
         const int parts[3] = {kPartA, kPartB, kPartC};
         int total = 0;
@@ -499,12 +553,27 @@ void b200sift_default_config(b200sift_config* cfg) {
 const char* b200sift_last_error(void) { return g_err.c_str(); }
 const char* b200sift_version(void) { return "b200sift 0.1 (sm_100a)"; }
 
-int b200sift_create(const b200sift_config* cfg, b200sift_detector** out) {
+void b200sift_default_options(b200sift_options* opt) {
+    if (!opt) return;
+    std::memset(opt, 0, sizeof(*opt));
+    opt->frames_in_flight = kDefaultSlots;
+}
+
+int b200sift_create(const b200sift_config* cfg, b200sift_detector** out) { return b200sift_create_ex(cfg, nullptr, out); }
+
+int b200sift_create_ex(const b200sift_config* cfg, const b200sift_options* opt, b200sift_detector** out) {
     if (!cfg || !out) return fail(B200SIFT_EINVAL, "null argument");
     *out = nullptr;
+    b200sift_options o;
+    b200sift_default_options(&o);
+    if (opt) o = *opt;
+    if (o.frames_in_flight == 0) o.frames_in_flight = kDefaultSlots;
+    if (o.frames_in_flight < kMinSlots || o.frames_in_flight > kMaxSlots)
+        return fail(B200SIFT_EINVAL, "frames_in_flight must be in %d..%d", kMinSlots, kMaxSlots);
     if (cfg->col_width <= 0 || cfg->row_width <= 0)
         return fail(B200SIFT_EINVAL, "Image width or height not set.");  // Detector.cu:22-25
-    if (cfg->upscale) return fail(B200SIFT_EINVAL, "upscale=true is broken in the reference (CudaSiftConfig.hh:12) and unsupported");
+    if (cfg->upscale && !o.working_upscale)
+        return fail(B200SIFT_EINVAL, "upscale=true is broken in the reference (CudaSiftConfig.hh:12): set b200sift_options::working_upscale to opt into the fixed version");
     if (cfg->numOctaveLayers < 1 || cfg->numOctaveLayers > kMaxScales)
         return fail(B200SIFT_EINVAL, "numOctaveLayers must be in 1..%d", kMaxScales);
     if (!(cfg->sigma > 0)) return fail(B200SIFT_EINVAL, "sigma must be positive");
@@ -516,6 +585,8 @@ int b200sift_create(const b200sift_config* cfg, b200sift_detector** out) {
     }
     b200sift_detector* d = new b200sift_detector;
     d->cfg = *cfg;
+    d->opt = o;
+    d->nslots = o.frames_in_flight;
     int rc = build(d);
     if (rc) {
         std::string keep = g_err;
@@ -528,7 +599,7 @@ int b200sift_create(const b200sift_config* cfg, b200sift_detector** out) {
 }
 
 static int sync_all(b200sift_detector* d) {
-    for (int i = 0; i < kSlots; i++)
+    for (int i = 0; i < d->nslots; i++)
         if (d->slot[i].stream) CU(cudaStreamSynchronize(d->slot[i].stream));
     return 0;
 }
@@ -537,7 +608,7 @@ int b200sift_destroy(b200sift_detector* d) {
     if (!d) return 0;
     sync_all(d);
     if (d->copy_stream) cudaStreamSynchronize(d->copy_stream);
-    for (int si = 0; si < kSlots; si++) {
+    for (int si = 0; si < d->nslots; si++) {
         Slot& sl = d->slot[si];
         for (int g = 0; g < 3; g++) {
             if (sl.exec[g]) cudaGraphExecDestroy(sl.exec[g]);
@@ -574,12 +645,12 @@ int b200sift_octave_info(const b200sift_detector* d, int o, int* dims) {
     return 0;
 }
 
-// Frame n runs in slot n % kSlots. Before the slot is reused, everything that read its previous contents from
+// Frame n runs in slot n % nslots. Before the slot is reused, everything that read its previous contents from
 // another slot's stream (the matcher / result copies of frame n-2, which used it as "previous frame") must be
 // done; host frames are copied on the copy stream, which only waits until the frame that last used the slot
 // has consumed its input, so the copy overlaps the frames in flight.
 static int begin_frame(b200sift_detector* d, Slot** out, bool on_copy_stream) {
-    Slot& sl = d->slot[d->frame_no % kSlots];
+    Slot& sl = d->slot[d->frame_no % d->nslots];
     if (sl.matched_pending) {
         CU(cudaStreamWaitEvent(sl.stream, sl.ev_matched, 0));
         sl.matched_pending = false;
@@ -865,7 +936,7 @@ int b200sift_debug_run_stages(b200sift_detector* d, const float* img, int rows, 
     if (!d || !img) return fail(B200SIFT_EINVAL, "null argument");
     if (rows != d->cfg.row_width || cols != d->cfg.col_width) return fail(B200SIFT_EINVAL, "image size mismatch");
     if (int rc = sync_all(d)) return rc;
-    Slot& sl = d->slot[d->frame_no % kSlots];
+    Slot& sl = d->slot[d->frame_no % d->nslots];
     sl.matched_pending = false;
     CU(cudaMemcpy2DAsync(sl.d_input, (size_t)d->in_pitch * 4, img, (size_t)cols * 4, (size_t)cols * 4, rows,
                          cudaMemcpyHostToDevice, sl.stream));
@@ -881,7 +952,7 @@ int b200sift_debug_run_stages(b200sift_detector* d, const float* img, int rows, 
 
 int b200sift_launches_per_frame(const b200sift_detector* d) { return d ? d->launches : B200SIFT_EINVAL; }
 
-int b200sift_frames_in_flight(void) { return kSlots; }
+int b200sift_frames_in_flight(const b200sift_detector* d) { return d ? d->nslots : kDefaultSlots; }
 
 // Latency of one frame graph: the latest frame's graph replayed back to back on its own stream.
 int b200sift_time_frames(b200sift_detector* d, int warmup, int iters, float* ms_per_frame) {
@@ -908,44 +979,45 @@ int b200sift_time_frames(b200sift_detector* d, int warmup, int iters, float* ms_
     return 0;
 }
 
-// Throughput of the frame graphs with kSlots frames in flight: every slot replays its graph on the latest
+// Throughput of the frame graphs with all frame slots in flight: every slot replays its graph on the latest
 // frame's input, round robin, each on its own stream.
 int b200sift_time_frames_pipelined(b200sift_detector* d, int warmup, int iters, float* ms_per_frame) {
     if (!d || !ms_per_frame || iters <= 0) return fail(B200SIFT_EINVAL, "bad argument");
     if (int rc = sync_all(d)) return rc;
+    const int nslots = d->nslots;
     Slot& src = d->cur();
     const size_t in_bytes = (size_t)d->in_pitch * d->cfg.row_width * sizeof(float);
-    for (int i = 0; i < kSlots; i++)
+    for (int i = 0; i < nslots; i++)
         if (&d->slot[i] != &src) CU(cudaMemcpy(d->slot[i].d_input, src.d_input, in_bytes, cudaMemcpyDeviceToDevice));
-    cudaEvent_t e0, e1[kSlots];
+    cudaEvent_t e0, e1[kMaxSlots];
     CU(cudaEventCreate(&e0));
-    for (int i = 0; i < kSlots; i++) CU(cudaEventCreate(&e1[i]));
-    const int first = (int)(d->frame_no % kSlots);
+    for (int i = 0; i < nslots; i++) CU(cudaEventCreate(&e1[i]));
+    const int first = (int)(d->frame_no % nslots);
     Slot* last = &src;
     for (int i = 0; i < warmup; i++) {
-        Slot& sl = d->slot[(first + i) % kSlots];
+        Slot& sl = d->slot[(first + i) % nslots];
         if (int rc = launch_graphs(sl, last)) return rc;
         last = &sl;
     }
     if (int rc = sync_all(d)) return rc;
     CU(cudaEventRecord(e0, d->slot[0].stream));
-    for (int i = 1; i < kSlots; i++) CU(cudaStreamWaitEvent(d->slot[i].stream, e0, 0));
-    const int total = (iters + kSlots - 1) / kSlots * kSlots;  // a whole number of rotations
+    for (int i = 1; i < nslots; i++) CU(cudaStreamWaitEvent(d->slot[i].stream, e0, 0));
+    const int total = (iters + nslots - 1) / nslots * nslots;  // a whole number of rotations
     for (int i = 0; i < total; i++) {
-        Slot& sl = d->slot[(first + i) % kSlots];
+        Slot& sl = d->slot[(first + i) % nslots];
         if (int rc = launch_graphs(sl, last)) return rc;
         last = &sl;
     }
     float ms = 0.f;
-    for (int i = 0; i < kSlots; i++) CU(cudaEventRecord(e1[i], d->slot[i].stream));
-    for (int i = 0; i < kSlots; i++) {
+    for (int i = 0; i < nslots; i++) CU(cudaEventRecord(e1[i], d->slot[i].stream));
+    for (int i = 0; i < nslots; i++) {
         float t = 0.f;
         CU(cudaEventSynchronize(e1[i]));
         CU(cudaEventElapsedTime(&t, e0, e1[i]));
         ms = std::max(ms, t);
     }
     cudaEventDestroy(e0);
-    for (int i = 0; i < kSlots; i++) cudaEventDestroy(e1[i]);
+    for (int i = 0; i < nslots; i++) cudaEventDestroy(e1[i]);
     *ms_per_frame = ms / (float)total;
     return 0;
 }

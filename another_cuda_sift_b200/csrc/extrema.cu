@@ -346,12 +346,16 @@ refine_kernel(const __grid_constant__ FrameParams fp) {
         }
         if (accept) {
             // SiftOps.cu:201-207 (quirk Q10: integer position, sub-pixel offset not added)
-            o.cand[idx] = make_float3((float)(c * (1 << oi)), (float)(r * (1 << oi)), (float)l);
+            // opt_upscale (working upscale, opt-in): octave oi of the doubled frame is octave oi - 1 of the input:
+            // positions halved (as the reference does, SiftOps.cu:200-202), and -- the fix -- size and packed octave too
+            const float inv_mod = fp.opt_upscale ? 0.5f : 1.f;
+            o.cand[idx] = make_float3(__fmul_rn((float)(c * (1 << oi)), inv_mod), __fmul_rn((float)(r * (1 << oi)), inv_mod), (float)l);
             float4 f = o.candF[idx];
-            f.x = (float)(oi + (l << 8) + ((int)__fmul_rn(roundf(__fadd_rn(x[2], 0.5f)), 255.f) << 16));
+            const int octave_field = fp.opt_upscale ? ((oi - 1) & 255) : oi;
+            f.x = (float)(octave_field + (l << 8) + ((int)__fmul_rn(roundf(__fadd_rn(x[2], 0.5f)), 255.f) << 16));
             const float pw = powf(2.f, __fdiv_rn(__fsub_rn((float)l, x[2]), (float)nS));
             const float sp = __fmul_rn(__fmul_rn(fp.sigma, pw), (float)(1 << oi));
-            f.y = __fadd_rn(sp, sp);
+            f.y = __fmul_rn(__fadd_rn(sp, sp), inv_mod);
             f.z = fabsf(contrast);
             o.candF[idx] = f;
         }

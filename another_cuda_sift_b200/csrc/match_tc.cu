@@ -1159,7 +1159,9 @@ void launch_resident(const __half* q, int nq, const __half* t, int nt, int per, 
 }  // namespace
 
 int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, void* scratch, size_t scratch_bytes,
-                 cudaStream_t s, float* dbg) {
+                 cudaStream_t s, float* dbg, cudaEvent_t* marks) {
+    // marks (profiling only): [0] after the norm (+ |b|^2 chunk) kernels, [1] after the filter, [2] after the re-rank
+    auto mark = [&](int i) { if (marks) cudaEventRecord(marks[i], s); };
     if (nq <= 0) return 0;
     if (scratch_bytes < match_scratch_bytes(nq, nt)) return -1;
     if (g_match_path == 1 && !dbg) return match_launch_simt(q, nq, t, nt, out, scratch, scratch_bytes, s);
@@ -1188,10 +1190,14 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
         if (!encode_train_map(&train_map, t, nt)) return -2;
         match_norms_kernel<<<(nq + nt + 7) / 8, 256, 0, s>>>(q, nq, t, nt, nrm_q, nrm_t, nullptr, nullptr);
         match_aug_kernel<<<(32 * tiles * 128 + 255) / 256, 256, 0, s>>>(nrm_t, nt, per, tiles, aug);
+        mark(0);
         dim3 grid((nq + kResQ - 1) / kResQ, 32);
         match_filter_stream_kernel<<<grid, kStreamThreads, kStreamSmem, s>>>(q, nq, train_map, nt, per, rec, nrm_q, nrm_t, aug);
     }
+    if (per <= 256 || dbg || g_match_path == 2) mark(0);  // those paths compute their norms inside / right before the filter
+    mark(1);
     match_rerank_kernel<<<(nq + kRerankWarps - 1) / kRerankWarps, kRerankWarps * 32, 0, s>>>(q, nq, t, nt, per, rec, out, nullptr, nullptr);
+    mark(2);
     return 0;
 }
 

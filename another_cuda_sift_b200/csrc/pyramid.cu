@@ -20,6 +20,9 @@
 //  pyramid_tail_kernel ONE CTA walks every octave of <= 4096 pixels.
 //
 // Roofline: HBM/L2-bound in the limit. Algorithmic bytes per layer = 8*w*h (read once, write once).
+#include <cuda.h>
+
+#include <cstring>
 #include <type_traits>
 
 #include "common.cuh"
@@ -52,6 +55,25 @@ __device__ __forceinline__ float bilinear_sample(const float* __restrict__ in, i
     return __fmaf_rn(a, y2e, r12);
 }
 
+// The same resample, split: the per-axis part (indices and fraction depend on one coordinate only) ...
+__device__ __forceinline__ void bilinear_axis(int i, int in_dim, int out_dim, int& i1, int& i2, float& f) {
+    const float coord = __fsub_rn(__fdiv_rn(__fmul_rn(__fadd_rn((float)i, 0.5f), (float)in_dim), (float)out_dim), 0.5f);
+    const int mx = in_dim - 1;
+    i1 = min(mx, max(0, __float2int_rd(coord)));
+    f = __fsub_rn(coord, truncf(coord));
+    i2 = f == 0.f ? i1 + 1 : __float2int_ru(coord);
+    i2 = min(mx, max(0, i2));
+}
+// ... and the combination of the four samples (identical operations in identical order)
+__device__ __forceinline__ float bilinear_combine(float v11, float v21, float v12, float v22, float xf, float yf) {
+    const float x2e = __fsub_rn(1.f, xf), y2e = __fsub_rn(1.f, yf);
+    const float a = __fmaf_rn(v11, x2e, __fmul_rn(v21, xf));
+    const float r12 = __fmul_rn(__fmaf_rn(v12, x2e, __fmul_rn(v22, xf)), yf);
+    return __fmaf_rn(a, y2e, r12);
+}
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
 // ---------------------------------------------------------------- fused blur chain
 struct ChainParams {
     const float* src;        // plain: the layer to blur; resample: layer n of the previous octave
@@ -77,9 +99,10 @@ struct ChainGeom {
     static constexpr int SH = TH + 2 * E0;                   // rows of the stage-0 region
     static constexpr int SHV = TH + 2 * E1;                  // rows of the largest row-filtered intermediate
     static constexpr int kLutRows = SH + RB + 8, kLutCols = SW + 8;
+    static constexpr int kResampleTab = 3 * (SW + SH);       // per column / row of the stage-0 region: first index, second index, fraction
     // [S even | S odd (K > 1)] [V] [slack rows: partial register blocks read past their region] [row / column tables]
     static constexpr size_t kFloats = (size_t)SW * SH * (K > 1 ? 2 : 1) + (size_t)SW * SHV + (size_t)SW * RB;
-    static constexpr size_t kSmem = kFloats * sizeof(float) + (size_t)(kLutRows + kLutCols) * sizeof(int);
+    static constexpr size_t kSmem = kFloats * sizeof(float) + (size_t)(kLutRows + kLutCols + kResampleTab) * sizeof(int) + 16;
 };
 
 // Vertical pass of one stage: V(x, y) = chain over rows of S(x, reflect(y + d)) for the columns [xa, xb) and the rows
@@ -182,15 +205,17 @@ __device__ __forceinline__ void chain_hpass(const float* __restrict__ V, float* 
 
 template <bool DOWN, int NT, int TW, int TH, int RB, int R1, int R2, int R3>
 __global__ void __launch_bounds__(NT, 2)
-blur_chain_kernel(const __grid_constant__ ChainParams p) {
+blur_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__ CUtensorMap src_map) {
     using G = ChainGeom<TW, TH, RB, R1, R2, R3>;
     constexpr int K = G::K, E0 = G::E0, SW = G::SW, SH = G::SH;
-    extern __shared__ __align__(16) float smem[];
+    extern __shared__ __align__(128) float smem[];
     float* S0 = smem;
     float* S1 = smem + (size_t)SW * SH;                                   // only when K > 1
     float* Vb = smem + (size_t)SW * SH * (K > 1 ? 2 : 1);
     int* rowlut = reinterpret_cast<int*>(smem + G::kFloats);
     int* collut = rowlut + G::kLutRows;
+    int* rtab = collut + G::kLutCols;                                     // resample tables (DOWN only)
+    uint64_t* bar = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(rtab + G::kResampleTab) + 7) & ~uintptr_t(7));
 
     const int tid = threadIdx.x;
     const int w = p.w, h = p.h;
@@ -204,28 +229,68 @@ blur_chain_kernel(const __grid_constant__ ChainParams p) {
         const int xa = max(0, tx0 - E0), xb = min(w, tx0 + TW + E0);
         const int ya = max(0, ty0 - E0), yb = min(h, ty0 + TH + E0);
         if constexpr (DOWN) {
-            const int ncols = xb - xa;
+            // per-column / per-row terms of the resample once per CTA, then four pixels (16 loads) in flight per thread
+            const int ncols = xb - xa, nrows = yb - ya;
+            int* cx1 = rtab; int* cx2 = rtab + SW; float* cxf = reinterpret_cast<float*>(rtab + 2 * SW);
+            int* ry1 = rtab + 3 * SW; int* ry2 = ry1 + SH; float* ryf = reinterpret_cast<float*>(ry1 + 2 * SH);
+            for (int j = tid; j < ncols + nrows; j += NT) {
+                int i1, i2;
+                float f;
+                if (j < ncols) {
+                    bilinear_axis(xa + j, p.src_w, w, i1, i2, f);
+                    cx1[j] = i1; cx2[j] = i2; cxf[j] = f;
+                } else {
+                    bilinear_axis(ya + j - ncols, p.src_h, h, i1, i2, f);
+                    ry1[j - ncols] = i1 * p.src_pitch; ry2[j - ncols] = i2 * p.src_pitch; ryf[j - ncols] = f;
+                }
+            }
+            __syncthreads();
             const float inv = __frcp_rn((float)ncols);
-            const int items = ncols * (yb - ya);
-            for (int it = tid; it < items; it += NT) {
-                const int r = __float2int_rd(((float)it + 0.5f) * inv);
-                const int x = xa + (it - r * ncols), y = ya + r;
-                const float v = bilinear_sample(p.src, p.src_pitch, p.src_w, p.src_h, w, h, x, y);
-                S0[(y - BY) * SW + (x - BX)] = v;
-                if (x >= tx0 && x < tx1 && y >= ty0 && y < ty1) p.base_out[(size_t)y * p.pitch + x] = v;
+            const int items = ncols * nrows;
+            for (int it0 = tid; it0 < items; it0 += 4 * NT) {
+                float v[4][4], xf[4], yf[4];
+                int cc[4], rr[4];
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    const int it = min(it0 + u * NT, items - 1);
+                    rr[u] = __float2int_rd(((float)it + 0.5f) * inv);
+                    cc[u] = it - rr[u] * ncols;
+                    const float* r1 = p.src + ry1[rr[u]];
+                    const float* r2 = p.src + ry2[rr[u]];
+                    const int x1 = cx1[cc[u]], x2 = cx2[cc[u]];
+                    v[u][0] = __ldg(r1 + x1); v[u][1] = __ldg(r1 + x2); v[u][2] = __ldg(r2 + x1); v[u][3] = __ldg(r2 + x2);
+                    xf[u] = cxf[cc[u]]; yf[u] = ryf[rr[u]];
+                }
+#pragma unroll
+                for (int u = 0; u < 4; u++) {
+                    if (it0 + u * NT >= items) break;
+                    const int x = xa + cc[u], y = ya + rr[u];
+                    const float val = bilinear_combine(v[u][0], v[u][1], v[u][2], v[u][3], xf[u], yf[u]);
+                    S0[(y - BY) * SW + (x - BX)] = val;
+                    if (x >= tx0 && x < tx1 && y >= ty0 && y < ty1) p.base_out[(size_t)y * p.pitch + x] = val;
+                }
             }
         } else {
-            // whole quads (the pitch is a multiple of 4 floats and >= w: reading a little row padding is harmless)
-            const int xqa = xa & ~3, xqb = (xb + 3) & ~3;
-            const int nq = (xqb - xqa) >> 2;
-            const float inv = __frcp_rn((float)nq);
-            const int items = nq * (yb - ya);
-            for (int it = tid; it < items; it += NT) {
-                const int r = __float2int_rd(((float)it + 0.5f) * inv);
-                const int x = xqa + 4 * (it - r * nq), y = ya + r;
-                const float4 v = __ldg(reinterpret_cast<const float4*>(p.src + (size_t)y * p.src_pitch + x));
-                *reinterpret_cast<float4*>(S0 + (y - BY) * SW + (x - BX)) = v;
+            // ONE TMA tile load brings the whole SW x SH box of the source layer (origin (BX, BY), zero fill outside the
+            // image) into S0: no address arithmetic, no registers, full memory-level parallelism
+            if (tid == 0) {
+                asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_addr(bar)));
+                asm volatile("fence.mbarrier_init.release.cluster;");
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"((uint32_t)(SW * SH * sizeof(float))) : "memory");
+                asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];"
+                             ::"r"(smem_addr(S0)), "l"(&src_map), "r"(BX), "r"(BY), "r"(smem_addr(bar)) : "memory");
             }
+            __syncthreads();  // the barrier is initialised before anybody polls it
+            uint32_t done = 0;
+            for (uint32_t spins = 0; !done; spins++) {
+                if (spins > (1u << 28)) __trap();  // a lost TMA must fail loudly, never hang the GPU
+                asm volatile(
+                    "{\n\t.reg .pred q;\n\t"
+                    "mbarrier.try_wait.parity.shared::cta.b64 q, [%1], %2;\n\t"
+                    "selp.u32 %0, 1, 0, q;\n\t}"
+                    : "=r"(done) : "r"(smem_addr(bar)), "r"(0u) : "memory");
+            }
+            (void)xa; (void)xb; (void)ya; (void)yb;
         }
     }
 
@@ -267,7 +332,7 @@ constexpr int kGenMaxR = (kMaxTaps - 1) / 2;
 __global__ void __launch_bounds__(kGenThreads)
 blur_generic_kernel(const float* __restrict__ in, int in_pitch, float* __restrict__ out, int out_pitch, int w, int h,
                     const __grid_constant__ Taps taps) {
-    extern __shared__ __align__(16) float smem[];
+    extern __shared__ __align__(128) float smem[];
     const int R = taps.n / 2;
     const int CW = kGenTW + 2 * R;           // columns of the row-filtered tile
     float* V = smem;                         // [kGenTH][CW]
@@ -451,16 +516,44 @@ u8_to_float_kernel(const uint8_t* __restrict__ in, size_t in_pitch, float* __res
 }
 
 // ---- launch tables -------------------------------------------------------------------------------------------
+extern bool g_pyramid_error;
 // Single-stage tiles: 128 x 64 (two CTAs of 320 threads per SM) when that fills the GPU, else 128 x 32.
 constexpr int kOneThreads = 320, kOneTW = 128, kOneRB = 16;
 // Fused chains: 64 x 32 tiles, 256 threads, 8-row register blocks.
 constexpr int kFuseThreads = 256, kFuseTW = 64, kFuseTH = 32, kFuseRB = 8;
 
+// Tensor map of a w x h float layer with row pitch `pitch` floats; box = the CTA's stage-0 region. The encode function
+// comes from the driver through the runtime's entry-point query (no link-time dependency on libcuda).
+bool encode_layer_map(CUtensorMap* map, const float* base, int w, int h, int pitch, int box_w, int box_h) {
+    using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = nullptr;
+    if (!encode) {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qres;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qres) != cudaSuccess || !fn) return false;
+        encode = reinterpret_cast<EncodeFn>(fn);
+    }
+    const cuuint64_t dims[2] = {(cuuint64_t)w, (cuuint64_t)h};
+    const cuuint64_t strides[1] = {(cuuint64_t)pitch * sizeof(float)};
+    const cuuint32_t box[2] = {(cuuint32_t)box_w, (cuuint32_t)box_h};
+    const cuuint32_t estr[2] = {1, 1};
+    return encode(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 template <bool DOWN, int NT, int TW, int TH, int RB, int R1, int R2, int R3>
 void launch_chain_inst(const ChainParams& p, cudaStream_t s) {
     using G = ChainGeom<TW, TH, RB, R1, R2, R3>;
     dim3 grid((p.w + TW - 1) / TW, (p.h + TH - 1) / TH);
-    blur_chain_kernel<DOWN, NT, TW, TH, RB, R1, R2, R3><<<grid, NT, G::kSmem, s>>>(p);
+    CUtensorMap map;
+    std::memset(&map, 0, sizeof(map));
+    if (!DOWN && !encode_layer_map(&map, p.src, p.w, p.h, p.src_pitch, G::SW, G::SH)) {
+        g_pyramid_error = true;  // reported by pyramid_check() (engine.cu turns it into an error of the enqueueing call)
+        return;
+    }
+    blur_chain_kernel<DOWN, NT, TW, TH, RB, R1, R2, R3><<<grid, NT, G::kSmem, s>>>(p, map);
 }
 template <bool DOWN, int NT, int TW, int TH, int RB, int R1, int R2, int R3>
 cudaError_t setup_chain_inst() {
@@ -468,6 +561,7 @@ cudaError_t setup_chain_inst() {
     return cudaFuncSetAttribute(blur_chain_kernel<DOWN, NT, TW, TH, RB, R1, R2, R3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G::kSmem);
 }
 
+bool g_pyramid_error = false;
 constexpr int kMaxOneR = 16;  // single-stage instantiations exist for every radius 1..16
 
 template <int R>
@@ -512,6 +606,12 @@ bool is_radii(const BlurStage* st, int n, int a, int b, int c) {
 }
 
 }  // namespace
+
+bool pyramid_failed() {
+    const bool f = g_pyramid_error;
+    g_pyramid_error = false;
+    return f;
+}
 
 cudaError_t pyramid_setup() {
     cudaError_t e = OneTable<kMaxOneR>::setup();

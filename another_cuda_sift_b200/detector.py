@@ -66,9 +66,13 @@ def _device_ptr(x) -> int:
 class Detector:
     """`sift_cuda::Detector` (reference sift_cuda/interface/Detector.hh:24-96)."""
 
-    def __init__(self, config: CudaSiftConfig):
+    def __init__(self, config: CudaSiftConfig, *, frames_in_flight: int = 0, remove_duplicates: bool = False,
+                 interpolate_orientation: bool = False, working_upscale: bool = False):
+        """`config` is the reference's struct; the keyword arguments are b200sift_options (include/b200sift.h): engine
+        options without a reference counterpart, all off = the reference's behaviour."""
         self.lib = _lib.load()
         self.config = config
+        self.options = _lib.Options(frames_in_flight, int(remove_duplicates), int(interpolate_orientation), int(working_upscale))
         self._h = None
         self.total_size = 0
         self.max_kpts = 5000
@@ -89,7 +93,7 @@ class Detector:
             return False
         h = C.c_void_p()
         cfg = self.config.to_c()
-        check(self.lib.b200sift_create(C.byref(cfg), C.byref(h)))
+        check(self.lib.b200sift_create_ex(C.byref(cfg), C.byref(self.options), C.byref(h)))
         self._h = h
         self.n_octaves = self.lib.b200sift_num_octaves(h)
         self.octaves = []
@@ -240,7 +244,7 @@ class Detector:
     @property
     def frames_in_flight(self) -> int:
         if getattr(self, "_fif", None) is None:
-            self._fif = int(self.lib.b200sift_frames_in_flight())
+            self._fif = int(self.lib.b200sift_frames_in_flight(self._h))
         return self._fif
 
     @property

@@ -35,20 +35,35 @@ extern "C" {
 #define B200SIFT_ESTATE (-3) /* call order violated (e.g. results before any frame) */
 
 /* Mirrors `struct CudaSiftConfig` (sift_cuda/types/CudaSiftConfig.hh:3-14), same field order,
- * names (including the reference's spellings) and defaults. `upscale` must be 0: the reference
- * documents it as broken (CudaSiftConfig.hh:12) and this engine rejects it. */
+ * names (including the reference's spellings) and defaults. `upscale` must be 0 unless
+ * b200sift_options::working_upscale is set: the reference documents it as broken (CudaSiftConfig.hh:12). */
 typedef struct b200sift_config {
     int col_width;
     int row_width;
     int numFeatures;           /* 5000 */
-    int numOctaveLayers;       /* 3 (only value supported, as in the reference's kernels) */
+    int numOctaveLayers;       /* 3; 1..6 supported (runtime parameter, as in the reference: Detector.cu:63-94) */
     double contrastThreshould; /* 0.04 */
     double edgeThreshould;     /* 10 */
-    double sigma;              /* 1.6 */
+    double sigma;              /* 1.6; any value whose layer blurs need <= 85 taps (GaussianUtils.cc:39-67) */
     int upscale;               /* 0 */
 } b200sift_config;
 
 typedef struct b200sift_detector b200sift_detector; /* opaque handle */
+
+/* Engine options that have no counterpart in CudaSiftConfig. All zero (b200sift_default_options sets frames_in_flight
+ * to its default) = the reference's behaviour, bit for bit. The three fixes are the TODOs the reference itself lists;
+ * they change results and are therefore opt-in. */
+typedef struct b200sift_options {
+    int frames_in_flight;        /* internal frame slots, 3..8 (0 = default 6): throughput vs ~85 MB of HBM per slot at 1920x1200 */
+    int remove_duplicates;       /* interface/Detector.cu:220 "TODO: remove duplicate": drop keypoints whose (x, y, size, angle)
+                                    equal an earlier keypoint of the same octave before description (first one kept) */
+    int interpolate_orientation; /* sift_func/SiftOps.cu:359 "TODO: interpolate the peak": parabolic peak interpolation of the
+                                    orientation histogram instead of angle = 360 - 10 * bin */
+    int working_upscale;         /* types/CudaSiftConfig.hh:11-12 "broken if set to true": with cfg.upscale = 1 the frame is
+                                    doubled (bilinear, the reference's resize) and keypoints are reported in input pixels with
+                                    octave -1 conventions (position, size and packed octave consistent) */
+    int reserved[4];
+} b200sift_options;
 
 B200SIFT_API void b200sift_default_config(b200sift_config* cfg);
 B200SIFT_API const char* b200sift_last_error(void);
@@ -58,6 +73,9 @@ B200SIFT_API const char* b200sift_version(void);
  * interface/Detector.cu:17-131): allocates every device / pinned buffer once and captures the
  * per-frame CUDA graph. Fails with EINVAL when col_width or row_width is 0 (Detector.cu:22-25). */
 B200SIFT_API int b200sift_create(const b200sift_config* cfg, b200sift_detector** out);
+B200SIFT_API void b200sift_default_options(b200sift_options* opt);
+/* b200sift_create with options (opt == NULL: defaults). */
+B200SIFT_API int b200sift_create_ex(const b200sift_config* cfg, const b200sift_options* opt, b200sift_detector** out);
 B200SIFT_API int b200sift_destroy(b200sift_detector* det);
 
 /* Geometry the reference derives in Detector.hh:27 and Detector.cu:83,109. */
@@ -120,9 +138,9 @@ B200SIFT_API int b200sift_dump_frame(b200sift_detector* det, const char* dir);
 /* Runs the frame pipeline only up to and including `last_stage` (1 pyramid, 3 extrema,
  * 4 refine, 5 orientation, 7 all) eagerly, for stage-level parity tests. Blocks. */
 B200SIFT_API int b200sift_debug_run_stages(b200sift_detector* det, const float* img, int rows, int cols, int last_stage);
-/* How many frames the engine keeps in flight (internal slots). Buffers a caller hands to the *_async calls of
- * consecutive frames (match indices, host result buffers) should rotate over at least this many. */
-B200SIFT_API int b200sift_frames_in_flight(void);
+/* How many frames the engine keeps in flight (internal slots; det == NULL: the default). Buffers a caller hands to the
+ * *_async calls of consecutive frames (match indices, host result buffers) should rotate over at least this many. */
+B200SIFT_API int b200sift_frames_in_flight(const b200sift_detector* det);
 /* Number of kernel launches (graph kernel nodes) one frame issues. */
 B200SIFT_API int b200sift_launches_per_frame(const b200sift_detector* det);
 /* Average device time (ms) of one frame with the input resident in HBM: `iters` graph launches
@@ -190,6 +208,34 @@ B200SIFT_API int b200sift_match_device(const uint16_t* d_query, int nq, const ui
 B200SIFT_API int b200sift_match_host(const uint16_t* query, int nq, const uint16_t* train, int nt, int* out_idx);
 /* Kernel launches issued by one b200sift_match_device call for this problem size. */
 B200SIFT_API int b200sift_match_launches(int nq, int nt);
+
+/* ---- Query-row sharded matching over the GPUs of one box (BASELINE.json "100k x 100k ... query-row
+ * sharded across 8xB200 with NCCL gather"). The sharded semantic is sift_cuda::matchBruteForce (sift_func/Match.cu:8-33):
+ * the train set is replicated, rank r owns the query rows [r*per, min(nq, (r+1)*per)), per = ceil(nq / world).
+ * One process (or thread) per GPU; NCCL is loaded at run time (libnccl.so.2), only by these calls.
+ *   b200sift_nccl_unique_id   ncclGetUniqueId on one rank; the caller ships the 128 bytes to the other ranks
+ *                             (torch.distributed / MPI / a file -- rendezvous is the host's business)
+ *   b200sift_comm_create      ncclCommInitRank on the CURRENT device; collective over all ranks
+ *   b200sift_shard_rows       the row block of `rank` ([*begin, *end)); returns per
+ *   b200sift_match_sharded    enqueues on `stream`, with no host synchronisation in between:
+ *                               ncclBroadcast of d_train (nt x 128 halves, in place) from rank train_root
+ *                                 (train_root < 0: every rank already holds the train set),
+ *                               the matcher on this rank's rows (d_query_block = its first row),
+ *                               ncclAllGather of `per` int32 per rank into d_out_all (world * per ints on every rank;
+ *                                 the first nq_total are matchBruteForce's result, the padding is -1).
+ *                             Collective: every rank must call it with the same nq_total / nt / train_root. */
+typedef struct b200sift_comm b200sift_comm;
+B200SIFT_API int b200sift_nccl_unique_id(uint8_t* id128);
+B200SIFT_API int b200sift_comm_create(const uint8_t* id128, int rank, int world, b200sift_comm** out);
+B200SIFT_API int b200sift_comm_destroy(b200sift_comm* comm);
+B200SIFT_API int b200sift_comm_info(const b200sift_comm* comm, int* rank, int* world, int* nccl_version);
+B200SIFT_API int b200sift_shard_rows(int n_rows, int world, int rank, int* begin, int* end);
+B200SIFT_API int b200sift_match_sharded(b200sift_comm* comm, const uint16_t* d_query_block, int nq_total, uint16_t* d_train, int nt,
+                                        int train_root, int* d_out_all, void* stream);
+/* The same call with a CUDA event between its stages; blocks, ms5 = {broadcast, norms (+ |b|^2 chunks), tcgen05 filter,
+ * exact re-rank, all-gather} in milliseconds on this rank (bench.py's per-stage breakdown). */
+B200SIFT_API int b200sift_match_sharded_profile(b200sift_comm* comm, const uint16_t* d_query_block, int nq_total, uint16_t* d_train,
+                                                int nt, int train_root, int* d_out_all, void* stream, float* ms5);
 
 /* Matcher implementation: 0 (default) = tcgen05 tensor-core filter + exact re-rank (csrc/match_tc.cu),
  * 1 = all-CUDA-core exact kernel (csrc/match.cu), kept as the on-device cross-check, 2 = as 0 but train sets

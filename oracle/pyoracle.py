@@ -66,7 +66,12 @@ class _Oracle:
         f("get_counts", None, [C.c_void_p, C.c_int, C.c_void_p])
         f("get_taps", C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int])
         f("match", C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p])
-        if (num_octave_layers, contrast, edge, sigma) == (3, 0.04, 10.0, 1.6):
+        if getattr(self, "_opts", 0):
+            fn = self.lib.oracle_create_opts
+            fn.restype = C.c_void_p
+            fn.argtypes = [C.c_int, C.c_int, C.c_int, C.c_int, C.c_double, C.c_double, C.c_double, C.c_int]
+            self.h = fn(cols, rows, num_features, num_octave_layers, contrast, edge, sigma, self._opts)
+        elif (num_octave_layers, contrast, edge, sigma) == (3, 0.04, 10.0, 1.6):
             self.h = self._create(cols, rows, num_features)
         else:
             self.h = self._create_cfg(cols, rows, num_features, num_octave_layers, contrast, edge, sigma)
@@ -154,8 +159,10 @@ class _Oracle:
 class CpuOracle(_Oracle):
     prefix = "oracle_"
 
-    def __init__(self, cols, rows, num_features=5000, **cfg):
+    def __init__(self, cols, rows, num_features=5000, remove_duplicates=False, interpolate_orientation=False,
+                 working_upscale=False, **cfg):
         self.lib_path = build_cpu()
+        self._opts = int(remove_duplicates) | (int(interpolate_orientation) << 1) | (int(working_upscale) << 2)
         super().__init__(cols, rows, num_features, **cfg)
 
     def counts(self, o: int):

@@ -5,8 +5,8 @@
         tools/bench_match.py --large 100000                       # 100k x 100k, query rows sharded over N GPUs
 
 Prints one JSON line (rank 0). Times are CUDA events on the launching stream, after warm-up, max over ranks;
-the large problem's timed region contains the matcher on this rank's row block AND the NCCL all-gather of the
-int32 indices. The descriptor sets are the seeded synthetic ones of SURVEY.md 8(d) (seed 42 / 43).
+the large problem's timed region contains the ncclBroadcast of the train set, the matcher on this rank's row block AND
+the ncclAllGather of the int32 indices (native call b200sift_match_sharded). The descriptor sets are the seeded synthetic ones of SURVEY.md 8(d) (seed 42 / 43).
 Roofline of the matcher: tensor-bound, flops = 2*nq*nt*128 against MEASURED_PEAKS.json's dense bf16 figure.
 """
 from __future__ import annotations
@@ -87,47 +87,101 @@ def match_latency(n: int, iters: int = 200, warmup: int = 20, rotate: int = 8):
                          "frac": flops / (stream_ms * 1e-3) / 1e12 / peak, "peak_kind": kind}}
 
 
-def large_sharded(n: int, world: int, rank: int, iters: int = 3):
-    import torch
-    import torch.distributed as dist
+def large_sharded(n: int, world: int, rank: int, iters: int = 5, check_rows: int = 64):
+    """BASELINE.json configs[4]: n x n descriptors, query rows sharded over the ranks, through the native call
+    b200sift_match_sharded. Rank 0 owns the train set: the timed region contains its ncclBroadcast, the matcher on this
+    rank's row block and the ncclAllGather of the int32 indices, all on one stream (CUDA events, max over ranks, median
+    of `iters`). Correctness: `check_rows` sampled rows of every rank's block against the CPU restatement of
+    Match.cu:35-177 (oracle/, bit-exact: the SURVEY 8(c) oracle for this size) + all ranks hold the same result."""
+    import time
 
-    from another_cuda_sift_b200.sharding import row_shard, sharded_match
+    import torch
+
+    from another_cuda_sift_b200.sharding import ShardedMatcher
     from another_cuda_sift_b200.synth import synth_descriptors
 
     q, t = synth_descriptors(n, n)
-    dq = torch.from_numpy(q.view(np.int16)).cuda()
-    dt = torch.from_numpy(t.view(np.int16)).cuda()
-    full = sharded_match(dq, n, dt, n)  # warm-up (also NCCL communicator set-up)
-    torch.cuda.synchronize()
-    times = []
-    for _ in range(iters):
+    sm = ShardedMatcher()
+    lo, hi = sm.rows(n)
+    dq = torch.from_numpy(q[lo:hi].copy().view(np.int16)).cuda()            # this rank's query rows only
+    dt_src = torch.from_numpy(t.view(np.int16)).cuda() if rank == 0 else None  # the train set lives on rank 0
+    dt = torch.empty((n, 128), dtype=torch.int16, device="cuda")               # receive buffer (rank 0: working copy)
+    root = 0 if world > 1 else -1
+
+    def barrier():
+        torch.cuda.synchronize()
         if world > 1:
+            import torch.distributed as dist
+
             dist.barrier()
         torch.cuda.synchronize()
+
+    def reset():  # the receivers forget the train set, so that every timed call really needs the broadcast
+        if rank == 0:
+            dt.copy_(dt_src)
+        else:
+            dt.zero_()
+
+    times, full = [], None
+    for it in range(iters + 2):
+        reset()
+        barrier()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
-        full = sharded_match(dq, n, dt, n)
+        full = sm.match(dq, n, dt, n, train_root=root)
         b.record()
         torch.cuda.synchronize()
         ms = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device="cuda")
         if world > 1:
+            import torch.distributed as dist
+
             dist.all_reduce(ms, op=dist.ReduceOp.MAX)
-        times.append(float(ms.item()))
-    idx = full.cpu().numpy()
-    # size-independent checks: every rank holds the same full result; accepted matches of noisy copies point
-    # back at a train row whose source is this query for the overwhelming majority
-    chk = torch.tensor([int(np.bitwise_xor.reduce(idx.astype(np.int64) * 2654435761 % (1 << 31)))], dtype=torch.int64, device="cuda")
-    same = True
+        if it >= 2:
+            times.append(float(ms.item()))
+    reset()
+    barrier()
+    stages = sm.profile(dq, n, dt, n, train_root=root)
     if world > 1:
-        lo = chk.clone(); hi = chk.clone()
-        dist.all_reduce(lo, op=dist.ReduceOp.MIN); dist.all_reduce(hi, op=dist.ReduceOp.MAX)
-        same = bool(lo.item() == hi.item())
-    lo_r, hi_r = row_shard(n, world, rank)
+        import torch.distributed as dist
+
+        st = torch.tensor(list(stages.values()), dtype=torch.float64, device="cuda")
+        dist.all_reduce(st, op=dist.ReduceOp.MAX)
+        stages = dict(zip(stages.keys(), [float(v) for v in st.tolist()]))
+    idx = full.cpu().numpy()
+    # correctness against the oracle on sampled rows of THIS rank's block
+    from oracle.pyoracle import CpuOracle
+
+    rows = lo + np.sort(np.random.default_rng(100 + rank).choice(hi - lo, size=min(check_rows, hi - lo), replace=False))
+    t0 = time.perf_counter()
+    cpu = CpuOracle(64, 64, 100)
+    if world > 1:
+        cpu.set_threads(max(1, (os.cpu_count() or 8) // world))
+    want = cpu.match(q[rows], t)
+    oracle_s = time.perf_counter() - t0
+    bad = int((want != idx[rows]).sum())
+    chk = torch.tensor([int(np.bitwise_xor.reduce(idx.astype(np.int64) * 2654435761 % (1 << 31))), bad], dtype=torch.int64, device="cuda")
+    same, bad_total = True, bad
+    if world > 1:
+        import torch.distributed as dist
+
+        lo_c, hi_c = chk[:1].clone(), chk[:1].clone()
+        dist.all_reduce(lo_c, op=dist.ReduceOp.MIN)
+        dist.all_reduce(hi_c, op=dist.ReduceOp.MAX)
+        same = bool(lo_c.item() == hi_c.item())
+        tot = chk[1:].clone()
+        dist.all_reduce(tot, op=dist.ReduceOp.SUM)
+        bad_total = int(tot.item())
     ms = sorted(times)[len(times) // 2]
     peak, kind = tensor_peak_tflops()
     flops = 2.0 * n * n * 128
-    return {"n": n, "n_gpus": world, "rows_per_rank": hi_r - lo_r, "ms": ms, "ms_all": times, "matches": int((idx >= 0).sum()),
-            "all_ranks_identical": same, "gather_bytes_per_rank": 4 * (hi_r - lo_r),
+    sm.close()
+    return {"n": n, "n_gpus": world, "rows_per_rank": hi - lo, "ms": ms, "ms_all": times, "matches": int((idx >= 0).sum()),
+            "stages_ms_max_over_ranks": {k: round(v, 4) for k, v in stages.items()},
+            "timed_region": "ncclBroadcast of the 25.6 MB train set from rank 0 + matcher on this rank's rows + ncclAllGather of int32 indices, one stream, "
+                            "CUDA events, max over ranks" if world > 1 else "matcher on all rows (one rank: no collective)",
+            "oracle_check": {"rows_per_rank": int(len(rows)), "ranks": world, "mismatches": bad_total, "oracle": "oracle/sift_oracle.cpp match (Match.cu:35-177 restated, bit-exact)",
+                             "oracle_seconds_rank0": round(oracle_s, 1)},
+            "all_ranks_identical": same, "broadcast_bytes": n * 256, "gather_bytes_per_rank": 4 * (hi - lo),
             "roofline": {"bound": "tensor", "achieved": flops / (ms * 1e-3) / 1e12, "peak": peak * world, "unit": "TFLOP/s",
                          "frac": flops / (ms * 1e-3) / 1e12 / (peak * world), "peak_kind": kind}}
 
