@@ -72,6 +72,7 @@ SIGNATURES = {
     "b200sift_debug_get_taps": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int]),
     "b200sift_debug_run_stages": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int]),
     "b200sift_dump_frame": (C.c_int, [C.c_void_p, C.c_char_p]),
+    "b200sift_rerun_stages": (C.c_int, [C.c_void_p, C.c_int]),
     "b200sift_frames_in_flight": (C.c_int, [C.c_void_p]),
     "b200sift_launches_per_frame": (C.c_int, [C.c_void_p]),
     "b200sift_time_frames": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]),

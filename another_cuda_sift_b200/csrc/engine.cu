@@ -950,6 +950,26 @@ int b200sift_debug_run_stages(b200sift_detector* d, const float* img, int rows, 
     return sync_all(d);
 }
 
+// Re-runs the pipeline on the latest frame's input up to `last_stage` (the compat shims of the reference's public stage
+// methods, Detector.hh:36-43). Eager, blocking; the re-run becomes the latest frame.
+int b200sift_rerun_stages(b200sift_detector* d, int last_stage) {
+    if (!d) return fail(B200SIFT_EINVAL, "null argument");
+    if (d->frame_no == 0) return fail(B200SIFT_ESTATE, "no frame has been processed");
+    if (int rc = sync_all(d)) return rc;
+    Slot& src = d->cur();
+    Slot& sl = d->slot[d->frame_no % d->nslots];
+    sl.matched_pending = false;
+    CU(cudaMemcpyAsync(sl.d_input, src.d_input, (size_t)d->in_pitch * d->cfg.row_width * sizeof(float), cudaMemcpyDeviceToDevice, sl.stream));
+    int rc = enqueue_frame(d, sl, last_stage, nullptr, nullptr);
+    if (rc) return rc;
+    CU(cudaEventRecord(sl.ev_consumed, sl.stream));
+    CU(cudaEventRecord(sl.ev_chain, sl.stream));
+    CU(cudaEventRecord(sl.ev_done, sl.stream));
+    d->frame_no++;
+    if (last_stage >= 6) d->have_frame = true;
+    return sync_all(d);
+}
+
 int b200sift_launches_per_frame(const b200sift_detector* d) { return d ? d->launches : B200SIFT_EINVAL; }
 
 int b200sift_frames_in_flight(const b200sift_detector* d) { return d ? d->nslots : kDefaultSlots; }

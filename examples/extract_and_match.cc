@@ -33,6 +33,7 @@ int main(int argc, char** argv) {
     cudaDeviceSynchronize();
 
     int prev_size = 0;
+    std::vector<int> want_kpts, want_good;
     for (size_t idx = 0; idx < host_img.size(); idx++) {
         detector.detectAndCompute(host_img[idx]);
         detector.copyToHost(false);
@@ -46,6 +47,37 @@ int main(int argc, char** argv) {
         std::printf("frame %zu: %d keypoints, %d matches to the previous frame; first kpt (%.0f, %.0f)\n", idx, curr_size, good,
                     curr_size ? detector.final_kpts[0].x : 0.f, curr_size ? detector.final_kpts[0].y : 0.f);
         prev_size = curr_size;
+        want_kpts.push_back(curr_size);
+        want_good.push_back(good);
+    }
+
+    // the reference's public stage methods (Detector.hh:36-43), here compatibility shims over the latest frame
+    detector.getGaussianPyramid();
+    detector.getKeyPoints();
+    detector.adjustKpts();
+    detector.adjustOrientationAndCleanup();
+    detector.extractDescriptor();
+    detector.collectAcrossOctaves();
+    if (detector.total_size != want_kpts.back()) {
+        std::fprintf(stderr, "stage shims: %d keypoints, expected %d\n", detector.total_size, want_kpts.back());
+        return 2;
+    }
+
+    // the same frames through the pipelined batch call on a fresh detector (same slot history), engine options spelled out
+    b200sift_options opt;
+    b200sift_default_options(&opt);
+    opt.frames_in_flight = 4;
+    sift_cuda::Detector batch_detector(config, opt);
+    if (!batch_detector.gpuWarmUpAndAllocate()) return 1;
+    const auto res = batch_detector.detectAndComputeBatch(host_img, true, true);
+    for (size_t idx = 0; idx < res.size(); idx++) {
+        int good = 0;
+        for (int m : res[idx].matches_from_previous) good += m >= 0;
+        std::printf("batch frame %zu: %d keypoints, %d matches to the previous frame\n", idx, res[idx].total_size, good);
+        if (res[idx].total_size != want_kpts[idx] || good != want_good[idx]) {
+            std::fprintf(stderr, "batch frame %zu differs from the blocking loop\n", idx);
+            return 3;
+        }
     }
     return 0;
 }

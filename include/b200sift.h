@@ -138,6 +138,10 @@ B200SIFT_API int b200sift_dump_frame(b200sift_detector* det, const char* dir);
 /* Runs the frame pipeline only up to and including `last_stage` (1 pyramid, 3 extrema,
  * 4 refine, 5 orientation, 7 all) eagerly, for stage-level parity tests. Blocks. */
 B200SIFT_API int b200sift_debug_run_stages(b200sift_detector* det, const float* img, int rows, int cols, int last_stage);
+/* The reference's public stage methods (createInitialImage ... collectAcrossOctaves, interface/Detector.hh:36-43) as a
+ * compat shim: re-runs the pipeline on the LATEST frame's input up to and including `last_stage` (numbering as above).
+ * Eager, blocking; ESTATE before the first frame. */
+B200SIFT_API int b200sift_rerun_stages(b200sift_detector* det, int last_stage);
 /* How many frames the engine keeps in flight (internal slots; det == NULL: the default). Buffers a caller hands to the
  * *_async calls of consecutive frames (match indices, host result buffers) should rotate over at least this many. */
 B200SIFT_API int b200sift_frames_in_flight(const b200sift_detector* det);

@@ -9,8 +9,12 @@
 //    thrust::device_vector<T>; thrust::raw_pointer_cast is not needed, use .data();
 //  * detectAndCompute returns with the frame finished (the reference returns with its last kernel in flight);
 //  * setDataGen writes raw arrays + manifest.json (b200sift_dump_frame) instead of msgpack+zlib files;
-//  * the reference's public stage methods (createInitialImage ... collectAcrossOctaves) do not exist: the
-//    frame is one CUDA graph.
+//  * the reference's public stage methods (createInitialImage ... collectAcrossOctaves, Detector.hh:36-43) exist as
+//    compatibility shims: the frame is three CUDA graphs here, so each shim re-runs the pipeline on the latest frame's
+//    input up to and including its stage (eagerly, blocking) -- what calling them after detectAndCompute does in the
+//    reference, at the cost of redoing the earlier stages;
+//  * extensions: detectAndComputeBatch (pipelined frames, one synchronisation), detectAndComputeDevice, engine options
+//    (second constructor argument, include/b200sift.h: b200sift_options).
 #pragma once
 #include <algorithm>
 #include <cmath>
@@ -18,6 +22,7 @@
 #include <cstdlib>
 #include <iostream>
 #include <string>
+#include <vector>
 
 #include <cuda_fp16.h>
 #include <cuda_runtime.h>
@@ -33,6 +38,19 @@ namespace sift_cuda {
 
 class Detector {
   public:
+    // Results of one frame of detectAndComputeBatch (host copies; only the first total_size entries are valid).
+    struct FrameResult {
+        std::vector<float3> kpts;
+        std::vector<float4> features;
+        std::vector<half> descriptors;          // total_size x 128 (empty when not requested)
+        std::vector<int> matches_from_previous; // matchBruteForce(previous frame -> this frame): previous_total entries
+        int total_size{0}, previous_total{0};
+    };
+
+    Detector(const CudaSiftConfig& config, const b200sift_options& options) : Detector(config) {
+        m_options = options;
+        m_have_options = true;
+    }
     Detector(const CudaSiftConfig& config) : m_config(config) {
         // Detector.hh:27-28 (the reference prints this line too)
         m_nOctaves = int(std::round(std::log(double(std::min(m_config.col_width * 2, m_config.row_width * 2))) / std::log(2.) - 2) + 1);
@@ -40,6 +58,7 @@ class Detector {
     }
     ~Detector() {
         if (m_handle) b200sift_destroy(m_handle);
+        if (m_stage) cudaFreeHost(m_stage);
     }
     Detector(const Detector&) = delete;
     Detector& operator=(const Detector&) = delete;
@@ -61,7 +80,7 @@ class Detector {
         c.edgeThreshould = m_config.edgeThreshould;
         c.sigma = m_config.sigma;
         c.upscale = m_config.upscale ? 1 : 0;
-        check(b200sift_create(&c, &m_handle), "b200sift_create");
+        check(b200sift_create_ex(&c, m_have_options ? &m_options : nullptr, &m_handle), "b200sift_create_ex");
         refresh_views();
         const size_t n = size_t(m_config.numFeatures);
         final_kpts.resize(n);        // Detector.cu:128-130
@@ -114,6 +133,70 @@ class Detector {
                                     reinterpret_cast<uint16_t*>(descriptors.data()), descriptor ? 1 : 0), "b200sift_copy_to_host");
     }
 
+    // The loop of tool/extract_and_match_example.cc:57-101 over a batch of frames in ONE pipelined native call
+    // (b200sift_detect_batch_host): the host->device copy of frame i+1 overlaps the graphs of frame i, sizes of the
+    // consecutive-frame matcher stay on the device, one synchronisation at the end. Results are staged through pinned
+    // buffers owned by this object (grown on demand, reused by later calls).
+    std::vector<FrameResult> detectAndComputeBatch(const std::vector<Imagef>& frames, bool descriptor = true, bool match = true) {
+        require_init();
+        const size_t n = frames.size(), nf = size_t(m_config.numFeatures);
+        std::vector<FrameResult> out(n);
+        if (n == 0) return out;
+        const size_t per = nf * (sizeof(float3) + sizeof(float4) + 128 * sizeof(half) + sizeof(int)) + 2 * sizeof(int);
+        if (m_stage_bytes < n * per) {
+            if (m_stage) cudaFreeHost(m_stage);
+            m_stage = nullptr;
+            m_stage_bytes = 0;
+            if (cudaMallocHost(&m_stage, n * per) != cudaSuccess) {
+                std::fprintf(stderr, "detectAndComputeBatch: cannot allocate %zu bytes of pinned memory\n", n * per);
+                std::exit(EXIT_FAILURE);
+            }
+            m_stage_bytes = n * per;
+        }
+        std::vector<const void*> img(n);
+        std::vector<float*> k(n), f(n);
+        std::vector<uint16_t*> d(n);
+        std::vector<int*> c(n), m(n);
+        for (size_t i = 0; i < n; i++) {
+            char* base = static_cast<char*>(m_stage) + i * per;
+            img[i] = frames[i].m_data->data();
+            k[i] = reinterpret_cast<float*>(base);
+            f[i] = reinterpret_cast<float*>(base + nf * sizeof(float3));
+            d[i] = descriptor ? reinterpret_cast<uint16_t*>(base + nf * (sizeof(float3) + sizeof(float4))) : nullptr;
+            m[i] = (match && i > 0) ? reinterpret_cast<int*>(base + nf * (sizeof(float3) + sizeof(float4) + 128 * sizeof(half))) : nullptr;
+            c[i] = reinterpret_cast<int*>(base + per - 2 * sizeof(int));
+        }
+        check(b200sift_detect_batch_host(m_handle, img.data(), int(n), int(frames[0].m_image_size.row), int(frames[0].m_image_size.col), 0,
+                                         k.data(), f.data(), d.data(), c.data(), m.data()), "b200sift_detect_batch_host");
+        for (size_t i = 0; i < n; i++) {
+            FrameResult& r = out[i];
+            r.total_size = c[i][0];
+            r.previous_total = i > 0 ? c[i][1] : 0;
+            const size_t t = size_t(r.total_size);
+            r.kpts.assign(reinterpret_cast<float3*>(k[i]), reinterpret_cast<float3*>(k[i]) + t);
+            r.features.assign(reinterpret_cast<float4*>(f[i]), reinterpret_cast<float4*>(f[i]) + t);
+            if (d[i]) r.descriptors.assign(reinterpret_cast<half*>(d[i]), reinterpret_cast<half*>(d[i]) + t * 128);
+            if (m[i]) r.matches_from_previous.assign(m[i], m[i] + r.previous_total);
+        }
+        total_size = out.back().total_size;
+        refresh_views();
+        return out;
+    }
+
+    // Stage methods of the reference (Detector.hh:36-43), public there but only called by detectAndCompute. Compatibility
+    // shims: each re-runs the pipeline on the LATEST frame's input up to and including its stage, eagerly, and blocks.
+    void createInitialImage() { rerun(1); }          // Detector.cu:235-259 (the initial blur is part of the pyramid launch chain here)
+    void getGaussianPyramid() { rerun(1); }          // Detector.cu:261-313
+    void getDogPyramid() { rerun(1); }               // Detector.cu:315-354: DoG is never stored here (one exact FADD where it is needed)
+    void getKeyPoints() { rerun(3); }                // Detector.cu:356-418
+    void adjustKpts() { rerun(4); }                  // Detector.cu:420-468
+    void adjustOrientationAndCleanup() { rerun(5); } // Detector.cu:470-553
+    void extractDescriptor() { rerun(7); }           // Detector.cu:555-582
+    void collectAcrossOctaves() {                    // Detector.cu:584-604: the gather is fused into the descriptor kernel
+        rerun(7);
+        synchronize();
+    }
+
     // Detector.hh:48: once set, every detectAndCompute dumps its intermediate stages into the (existing) directory
     // `path`: raw arrays + manifest.json (b200sift_dump_frame) instead of the reference's msgpack+zlib files.
     void setDataGen(const std::string& path) { m_debug_path = path; }
@@ -130,6 +213,11 @@ class Detector {
     int total_size{0};
 
   private:
+    void rerun(int last_stage) {
+        require_init();
+        check(b200sift_rerun_stages(m_handle, last_stage), "b200sift_rerun_stages");
+        refresh_views();
+    }
     void require_init() {
         if (!m_initialized) {
             std::fprintf(stderr, "sift_cuda::Detector used before gpuWarmUpAndAllocate()\n");
@@ -147,6 +235,10 @@ class Detector {
     int m_nOctaves{0};
     std::string m_debug_path;
     b200sift_detector* m_handle{nullptr};
+    b200sift_options m_options{};
+    bool m_have_options{false};
+    void* m_stage{nullptr};          // pinned staging for detectAndComputeBatch
+    size_t m_stage_bytes{0};
 };
 
 }  // namespace sift_cuda

@@ -27,7 +27,8 @@ def test_mirror_headers_compile_and_link():
 def test_mirror_keeps_reference_names():
     det = open(os.path.join(ROOT, "include", "sift_cuda", "interface", "Detector.hh")).read()
     for name in ("class Detector", "gpuWarmUpAndAllocate", "detectAndCompute(const Imagef&", "copyToHost(bool",
-                 "setDataGen", "device_kpts", "device_features", "device_descriptor", "prev_descriptor",
+                 "setDataGen", "createInitialImage", "getGaussianPyramid", "getDogPyramid", "getKeyPoints", "adjustKpts",
+                 "adjustOrientationAndCleanup", "extractDescriptor", "collectAcrossOctaves", "detectAndComputeBatch", "device_kpts", "device_features", "device_descriptor", "prev_descriptor",
                  "final_kpts", "final_features", "descriptors", "max_kpts", "total_size"):
         assert name in det, name
     cfg = open(os.path.join(ROOT, "include", "sift_cuda", "types", "CudaSiftConfig.hh")).read()
@@ -41,6 +42,9 @@ def test_cpp_example_runs_and_agrees_with_python_mirror():
     build_example()
     out = subprocess.run([EXE, "320", "240", "3"], capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stderr
-    frames = re.findall(r"frame (\d+): (\d+) keypoints, (\d+) matches", out.stdout)
+    frames = re.findall(r"^frame (\d+): (\d+) keypoints, (\d+) matches", out.stdout, re.M)
     assert len(frames) == 3 and all(int(k) > 20 for _, k, _ in frames)
     assert int(frames[1][2]) > 0  # consecutive (shifted) frames do match
+    # the pipelined C++ batch call and the stage-method shims agree with the blocking loop (the example exits non-zero otherwise)
+    batch = re.findall(r"^batch frame (\d+): (\d+) keypoints, (\d+) matches", out.stdout, re.M)
+    assert [b[1:] for b in batch] == [f[1:] for f in frames]
