@@ -85,6 +85,8 @@ SIGNATURES = {
     "b200sift_profile_frame": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float), C.POINTER(C.c_int)]),
     "b200sift_match_device": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
     "b200sift_match_host": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p]),
+    "b200sift_match_device_noalloc": (C.c_int, [C.c_void_p, C.c_int, C.c_void_p, C.c_int, C.c_void_p, C.c_void_p]),
+    "b200sift_match_noalloc_max_rows": (C.c_int, []),
     "b200sift_match_launches": (C.c_int, [C.c_int, C.c_int]),
     "b200sift_nccl_unique_id": (C.c_int, [C.c_void_p]),
     "b200sift_comm_create": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_void_p)]),

@@ -210,6 +210,22 @@ B200SIFT_API int b200sift_match_device(const uint16_t* d_query, int nq, const ui
                           int* d_out_idx, void* stream);
 /* Host-buffer convenience (copies in, matches, copies out, blocks). */
 B200SIFT_API int b200sift_match_host(const uint16_t* query, int nq, const uint16_t* train, int nt, int* out_idx);
+/* No counterpart in the reference. b200sift_match_device for callers that
+ * cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it): same matcher, same
+ * arguments, bit-identical result, but its scratch (survivor records + squared norms) lives in a file-scope
+ * `static __device__` array of the library (csrc/noalloc.cu, ~8.1 MiB, held by every GPU that loads the library until the
+ * process exits) instead of the cached cudaMalloc'd buffer. The call path allocates nothing: no cudaMalloc / cudaFree /
+ * allocating library routine. Limits and rules:
+ *   - nq <= B200SIFT_NOALLOC_MAX_ROWS and nt <= B200SIFT_NOALLOC_MAX_ROWS, else B200SIFT_EINVAL with a message naming the limit;
+ *   - every call on a device shares the one array, which keeps the previous call's contents (nothing in it has to start
+ *     at zero: a call writes every norm and survivor record before reading it); calls that OVERLAP on the GPU (different
+ *     streams without ordering) race on it and return garbage -- order them on one stream or with events;
+ *   - asynchronous on `stream` like b200sift_match_device; inputs and output are the caller's device buffers. */
+#define B200SIFT_NOALLOC_MAX_ROWS 8192
+B200SIFT_API int b200sift_match_device_noalloc(const uint16_t* d_query, int nq, const uint16_t* d_train, int nt,
+                                               int* d_out_idx, void* stream);
+/* B200SIFT_NOALLOC_MAX_ROWS as the loaded library was built with. */
+B200SIFT_API int b200sift_match_noalloc_max_rows(void);
 /* Kernel launches issued by one b200sift_match_device call for this problem size. */
 B200SIFT_API int b200sift_match_launches(int nq, int nt);
 
