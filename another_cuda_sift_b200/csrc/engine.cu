@@ -1219,7 +1219,8 @@ int b200sift_match_host(const uint16_t* query, int nq, const uint16_t* train, in
 int b200sift_match_launches(int nq, int nt) { return match_num_launches(nq, nt); }
 
 int b200sift_match_set_path(int path) {
-    if (path < 0 || path > 2) return fail(B200SIFT_EINVAL, "path must be 0 (tensor core), 1 (CUDA core) or 2 (tensor core, unpipelined large-set filter)");
+    if (path < 0 || path > 3)
+        return fail(B200SIFT_EINVAL, "path must be 0 (tensor core), 1 (CUDA core), 2 (tensor core, unpipelined large-set filter) or 3 (tensor core, two-pass streaming filter)");
     match_set_path(path);
     return 0;
 }

@@ -610,11 +610,18 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
 }
 
 // ---------------------------------------------------------------- streaming filter (per > 256: large train sets)
-// One CTA = 256 queries x ONE column chunk of the reference, streamed as 128-row train tiles, twice:
-//   pass 0  an upper bound of the chunk's second smallest distance per query (branch-free: the 2nd smallest of the
-//           minima of column quads is >= the true 2nd smallest, and equal to it unless both fall into one quad);
-//   pass 1  the same tiles again (MMA recomputed: cheaper than keeping 2 x 256 x per distances anywhere), every
-//           column with D <= thr(bound) is a survivor; a quad is only opened when its minimum passes.
+// One CTA = 256 queries x ONE column chunk of the reference, streamed ONCE as 128-row train tiles. Per step and thread
+// (64 distances of one query row):
+//   bound   the running (min, 2nd min) over the minima of column octets is updated first: the 2nd smallest octet minimum
+//           is an upper bound of the true 2nd smallest distance seen so far (equal unless both fall into one octet);
+//   record  the same octets are then tested against the threshold derived from the UPDATED running bound; an octet is
+//           only opened when its minimum passes, and a passing column is appended to the thread's candidate list with
+//           its distance. The running bound never increases, so its threshold is always >= the final one: every column
+//           under the FINAL threshold is recorded when it is scanned. Expected candidates per thread ~ 2 ln(steps) + 1;
+//           a full list (16) is first re-filtered with the current, tighter threshold, and only then overflows;
+//   finish  the two column halves of a row exchange their bounds, the lists are filtered by the final threshold: the
+//           survivors are exactly those of a two-pass filter (bound pass, then threshold pass) at half the MMA, TMA and
+//           scan work. (Round 1 ran the two passes: 4.2 of 5.0 ms at 100k x 100k.)
 // Measured on B200 (tools/probes/tmem_probe.cu, elimination runs and ncu source views of earlier versions of this
 // kernel): with both operands in shared memory a M128 N128 K16 MMA takes ~83 cycles instead of 64 (8 KB of operand
 // reads per instruction saturate the 128 B/cycle shared-memory port), and streaming the train tiles with cp.async
@@ -641,7 +648,9 @@ constexpr int kStreamScan = 512;                       // 16 scan warps: (lane q
 constexpr int kStreamThreads = kStreamScan + 64;       // + one warp that issues the MMAs and one that issues the TMA loads
 constexpr uint32_t kStreamAcol = 256;                  // first TMEM column of the query tiles
 constexpr uint32_t kStreamAcols = 72;                  // 32-bit columns per query tile (144 halves)
-constexpr size_t kStreamSmem = kStreamBufs * (size_t)kStreamTile + 128 + (kCand + 1) * kStreamScan * sizeof(int) + 2 * kStreamScan * sizeof(float);
+constexpr int kRunCap = 16;                            // candidate list per scan thread (column + distance)
+constexpr size_t kStreamSmem = kStreamBufs * (size_t)kStreamTile + 128 + (size_t)kRunCap * kStreamScan * (sizeof(int) + sizeof(float)) +
+                               kStreamScan * sizeof(int) + 2 * kStreamScan * sizeof(float);
 constexpr float kAugMaxNorm = 2.0e9f;                  // |b|^2 above this is not representable by the three-half split
 
 #define TMEM_ST32(addr, v)                                                                                     \
@@ -666,6 +675,7 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
     return d;
 }
 
+template <bool SINGLE>
 __global__ void __launch_bounds__(kStreamThreads, 1)
 match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_constant__ CUtensorMap train_map, int nt, int per,
                            CandRec* __restrict__ rec, const float* __restrict__ nrm_q, const float* __restrict__ nrm_t,
@@ -676,9 +686,10 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
     uint64_t* s_bar = reinterpret_cast<uint64_t*>(sB + kStreamBufs * kStreamTile);  // [0..1] MMA done (query half), [2..5] tile landed, [6..9] tile buffer free
     uint32_t* s_tmem = reinterpret_cast<uint32_t*>(s_bar + 12);
     int* s_nbmax = reinterpret_cast<int*>(s_tmem + 1);
-    int* s_cand = reinterpret_cast<int*>(s_bar + 16);       // [kCand][512] survivor columns (chunk-relative) of thread tid, then [512] counts
-    int* s_cn = s_cand + kCand * kStreamScan;
-    float* s_pair = reinterpret_cast<float*>(s_cn + kStreamScan);  // [2][512]: (min, 2nd min) of every thread's columns after pass 0
+    int* s_cand = reinterpret_cast<int*>(s_bar + 16);       // [kRunCap][512] candidate columns (chunk-relative) of thread tid; the first kCand rows end up holding the survivors
+    float* s_dist = reinterpret_cast<float*>(s_cand + kRunCap * kStreamScan);  // [kRunCap][512] their distances (|b|^2 - 2 a.b domain)
+    int* s_cn = reinterpret_cast<int*>(s_dist + kRunCap * kStreamScan);        // [512] survivor counts
+    float* s_pair = reinterpret_cast<float*>(s_cn + kStreamScan);  // [2][512]: (min, 2nd min) of every thread's columns
 
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
     const bool scanner = warp < kStreamScan / 32;
@@ -753,7 +764,7 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
     const float nbmax = __int_as_float(s_nbmax[0]);
     // |b|^2 beyond the three-half split (or not finite): every record of this CTA asks for the exact whole-chunk scan
     const bool bail = !(nbmax <= kAugMaxNorm);
-    const int S = bail ? 0 : 2 * T;
+    const int S = bail ? 0 : (SINGLE ? T : 2 * T);   // one pass over the chunk's tiles (two in the round-1 variant)
 
     const int nh = two_tiles ? 2 : 1;
     // step s works on tile s % T -> buffer s % 4; rows past the train set are zero-filled by the TMA unit, rows past
@@ -819,6 +830,95 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
         if (S > 0)
             for (int h = 0; h < nh; h++) asm volatile("barrier.cta.sync %0, %1;" ::"r"(1 + h), "r"(kStreamScan / 2 + 32) : "memory");
     } else if (scans) {
+      if constexpr (SINGLE) {
+        // ---- scan warps (single pass, see the kernel's header comment)
+        float m1[4] = {INFINITY, INFINITY, INFINITY, INFINITY}, m2[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
+        const uint32_t done = bar + 8u * half_id;
+        int rn = 0;          // candidates in this thread's list
+        bool ovf = false;    // more than kRunCap columns within the current threshold: the exact path scores the whole chunk
+        // {a1,a2} u {b1,b2}: min = min(a1,b1), 2nd = min(max(a1,b1), min(a2,b2))
+        auto merged = [&](float& a1, float& a2) {
+            const float x2 = fminf(fmaxf(m1[0], m1[1]), fminf(m2[0], m2[1])), x1 = fminf(m1[0], m1[1]);
+            const float y2 = fminf(fmaxf(m1[2], m1[3]), fminf(m2[2], m2[3])), y1 = fminf(m1[2], m1[3]);
+            a1 = fminf(x1, y1);
+            a2 = fminf(fmaxf(x1, y1), fminf(x2, y2));
+        };
+        // Survivors: D <= D2nd * (1+d)/(1-d) with d = 1.5e-3 (half roundings) + fp32 accumulation slack, compared in the
+        // |b|^2 - 2 a.b domain
+        auto threshold = [&](float a2) {
+            const float d2nd = fmaxf(__fadd_rn(a2, na), 0.f);
+            return __fsub_rn(__fmaf_rn(d2nd, 1.004f, slack), na);
+        };
+        auto refilter = [&](float thr) {   // keep the candidates still within `thr`, order preserved
+            int k = 0;
+            for (int i = 0; i < rn; i++) {
+                const float d = s_dist[i * kStreamScan + tid];
+                if (d <= thr) {
+                    s_dist[k * kStreamScan + tid] = d;
+                    s_cand[k * kStreamScan + tid] = s_cand[i * kStreamScan + tid];
+                    k++;
+                }
+            }
+            rn = k;
+        };
+        for (int s = 0; s < S; s++) {
+            uint32_t v[TN / 2];
+            mbar_wait(done, (uint32_t)s & 1u);
+            asm volatile("tcgen05.fence::after_thread_sync;");
+#pragma unroll
+            for (int cb = 0; cb < TN / 64; cb++) TMEM_LD32(v + cb * 32, taddr + cb * 32);
+            asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+            asm volatile("tcgen05.fence::before_thread_sync;");
+            asm volatile("barrier.cta.arrive %0, %1;" ::"r"(1 + half_id), "r"(kStreamScan / 2 + 32) : "memory");
+            float om[TN / 16];
+#pragma unroll
+            for (int i8 = 0; i8 < TN / 16; i8++) {
+                const float* f = reinterpret_cast<const float*>(v + i8 * 8);
+                om[i8] = fminf(fminf(fminf(f[0], f[1]), fminf(f[2], f[3])), fminf(fminf(f[4], f[5]), fminf(f[6], f[7])));  // +inf on padding columns
+                m2[i8 & 3] = fminf(m2[i8 & 3], fmaxf(m1[i8 & 3], om[i8]));
+                m1[i8 & 3] = fminf(m1[i8 & 3], om[i8]);
+            }
+            float a1, a2;
+            merged(a1, a2);
+            const float thr = threshold(a2);   // from this thread's columns so far: >= the final threshold
+            // 32 lanes = 32 independent query rows: in most octets SOME lane has a candidate, so this path is hot at warp
+            // level. It is kept small: ONE list clean-up site per step (a list more than half full is re-filtered with
+            // the current threshold, which has tightened since its entries were recorded), pushes are two predicated
+            // stores, and a push that finds the list full only raises the overflow flag (-> exact whole-chunk scan).
+            if (rn > kRunCap / 2) refilter(thr);
+            if (!(thr < INFINITY)) ovf = true;   // fewer than two finite octets so far: cannot bound anything (never happens for nt > 8192)
+            const int col0 = s * TN + col_half * (TN / 2);
+#pragma unroll
+            for (int i8 = 0; i8 < TN / 16; i8++) {
+                if (om[i8] <= thr) {
+                    const float* f = reinterpret_cast<const float*>(v + i8 * 8);
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        if (f[j] <= thr) {
+                            const int slot = min(rn, kRunCap - 1) * kStreamScan + tid;
+                            s_cand[slot] = col0 + i8 * 8 + j;
+                            s_dist[slot] = f[j];
+                            ovf |= rn >= kRunCap;
+                            rn = min(rn + 1, kRunCap);
+                        }
+                    }
+                }
+            }
+        }
+        if (S > 0) {
+            // the other column half of the row (thread tid ^ 256, same query half: named barrier 3 + half) -> final threshold
+            float a1, a2v;
+            merged(a1, a2v);
+            s_pair[tid] = a1;
+            s_pair[kStreamScan + tid] = a2v;
+            asm volatile("barrier.cta.sync %0, %1;" ::"r"(3 + half_id), "r"(kStreamScan / 2) : "memory");
+            const float b1 = s_pair[tid ^ 256], b2v = s_pair[kStreamScan + (tid ^ 256)];
+            const float a2 = fminf(fmaxf(a1, b1), fminf(a2v, b2v));
+            refilter(threshold(a2));
+            cn = ovf ? 2 * kCand + 2 : rn;   // an overflowed list makes the record ask for the whole-chunk scan
+        }
+      } else {
+        // ---- round-1 two-pass scan (kept for A/B measurements: b200sift_match_set_path(3))
         // ---- scan warps. Running (min, 2nd min) over the minima of column octets, four independent pairs: the 2nd
         // smallest octet minimum is >= the true 2nd smallest distance (equal unless both fall into one octet)
         float m1[4] = {INFINITY, INFINITY, INFINITY, INFINITY}, m2[4] = {INFINITY, INFINITY, INFINITY, INFINITY};
@@ -875,6 +975,7 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
                 }
             }
         }
+      }
     }
     if (scanner) s_cn[tid] = cn;
     asm volatile("tcgen05.fence::before_thread_sync;");
@@ -1178,7 +1279,8 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
         static bool attr_set[kMaxDevices] = {false};
         const int dev = current_device();
         if (!attr_set[dev]) {
-            cudaFuncSetAttribute(match_filter_stream_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStreamSmem);
+            cudaFuncSetAttribute(match_filter_stream_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStreamSmem);
+            cudaFuncSetAttribute(match_filter_stream_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kStreamSmem);
             attr_set[dev] = true;
         }
         // scratch: records | |b|^2 K chunks, tiled per chunk (4 KB per 128-row tile) | norms
@@ -1192,7 +1294,8 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
         match_aug_kernel<<<(32 * tiles * 128 + 255) / 256, 256, 0, s>>>(nrm_t, nt, per, tiles, aug);
         mark(0);
         dim3 grid((nq + kResQ - 1) / kResQ, 32);
-        match_filter_stream_kernel<<<grid, kStreamThreads, kStreamSmem, s>>>(q, nq, train_map, nt, per, rec, nrm_q, nrm_t, aug);
+        if (g_match_path == 3) match_filter_stream_kernel<false><<<grid, kStreamThreads, kStreamSmem, s>>>(q, nq, train_map, nt, per, rec, nrm_q, nrm_t, aug);
+        else match_filter_stream_kernel<true><<<grid, kStreamThreads, kStreamSmem, s>>>(q, nq, train_map, nt, per, rec, nrm_q, nrm_t, aug);
     }
     if (per <= 256 || dbg || g_match_path == 2) mark(0);  // those paths compute their norms inside / right before the filter
     mark(1);

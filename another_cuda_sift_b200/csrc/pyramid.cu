@@ -22,6 +22,8 @@
 // Roofline: HBM/L2-bound in the limit. Algorithmic bytes per layer = 8*w*h (read once, write once).
 #include <cuda.h>
 
+#include <algorithm>
+#include <cstdlib>
 #include <cstring>
 #include <type_traits>
 
@@ -324,6 +326,148 @@ blur_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__
     if constexpr (K >= 2) stage(std::integral_constant<int, (R2 < 0 ? 1 : R2)>{}, 2, p.taps[1], S1, K > 2 ? S0 : nullptr, p.out[1], E0 - R1 - R2);
     if constexpr (K >= 3) stage(std::integral_constant<int, (R3 < 0 ? 1 : R3)>{}, 3, p.taps[2], S0, nullptr, p.out[2], 0);
 }
+
+// ---------------------------------------------------------------- streaming single-stage blur (big layers)
+// A CTA owns a 128-column strip of a row segment and walks DOWN it. Thread t of the first 128 + 2R owns source column
+// reflect101(x0 - R + t): it keeps a sliding window of 2R + RS input rows in registers, loads every input pixel ONCE
+// (coalesced 4-byte loads, the next row group prefetched into registers while the current one is computed), and emits RS
+// row-filtered values per step as RS independent in-order chains into a double-buffered RS-row ring in shared memory;
+// the first 128 threads then run the horizontal pass of those RS rows (4 outputs per thread from LDS.128 windows, 4
+// independent chains, one STG.128). One barrier per RS rows, ~10 KB of shared memory, no phase in which the whole CTA
+// waits for a tile: the strip's loads, FMAs and stores overlap continuously, and the small footprint lets these CTAs
+// share an SM with the descriptor CTAs of the other frames in flight.
+constexpr int kStrTW = 128;       // output columns per strip
+constexpr int kStrThreads = 160;  // >= kStrTW + 2R for R <= 16
+constexpr int kStrRS = 8;         // rows per step
+
+template <int R>
+__global__ void __launch_bounds__(kStrThreads)
+blur_stream_kernel(const float* __restrict__ in, int in_pitch, float* __restrict__ out, int out_pitch, int w, int h,
+                   const __grid_constant__ Taps taps, int rows_per_cta) {
+    constexpr int NTAP = 2 * R + 1, RS = kStrRS;
+    constexpr int RP = round_up4(R);
+    constexpr int VW = kStrTW + 2 * RP;      // ring row length: column c <-> image column x0 - RP + c
+    constexpr int NV = (2 * RP + 4) / 4;     // float4 loads per output quad
+    __shared__ __align__(16) float ring[2][RS][VW];
+
+    const int tid = threadIdx.x;
+    const int x0 = blockIdx.x * kStrTW;
+    const int y0 = blockIdx.y * rows_per_cta;
+    const int y1 = min(h, y0 + rows_per_cta);
+    if (y0 >= y1) return;
+    const bool vthread = tid < kStrTW + 2 * R;
+    const int vc = RP - R + tid;                                        // this thread's ring column
+    const float* col = in + reflect101(x0 - R + min(tid, kStrTW + 2 * R - 1), w);  // the horizontal pass reads V at reflected columns
+    // Rows are consumed in strictly increasing order (y0 - R, y0 - R + 1, ...): a running pointer serves the interior
+    // segments (uniform branch: no reflection, one 64-bit add per row); border segments reflect each row index, without
+    // the modulo of reflect101 when one reflection suffices (h > 2R + RS, i.e. every layer this kernel is chosen for).
+    const bool interior = (y0 - R >= 0) && (y0 + ((y1 - y0 + RS - 1) / RS) * RS + R <= h);
+    const bool one_fold = h > 2 * R + RS;
+    const float* rowp = col + (ptrdiff_t)(y0 - R) * in_pitch;
+    int ynext = y0 - R;
+#define STREAM_LOAD(dst, count)                                                                                   \
+    do {                                                                                                          \
+        if (interior) {                                                                                           \
+            _Pragma("unroll") for (int i_ = 0; i_ < (count); i_++) {                                              \
+                (dst)[i_] = __ldg(rowp);                                                                          \
+                rowp += in_pitch;                                                                                 \
+            }                                                                                                     \
+        } else {                                                                                                  \
+            _Pragma("unroll") for (int i_ = 0; i_ < (count); i_++) {                                              \
+                const int y_ = ynext + i_;                                                                        \
+                const int yy_ = one_fold ? (y_ < 0 ? -y_ : (y_ >= h ? 2 * (h - 1) - y_ : y_)) : reflect101(y_, h); \
+                (dst)[i_] = __ldg(col + (ptrdiff_t)yy_ * in_pitch);                                               \
+            }                                                                                                     \
+        }                                                                                                         \
+        ynext += (count);                                                                                         \
+    } while (0)
+
+    float v[2 * R + RS], nxt[RS];
+    if (vthread) {
+        STREAM_LOAD(v, 2 * R);
+        STREAM_LOAD(nxt, RS);
+    }
+    int buf = 0;
+    for (int ys = y0; ys < y1; ys += RS, buf ^= 1) {
+        if (vthread) {
+#pragma unroll
+            for (int j = 0; j < RS; j++) v[2 * R + j] = nxt[j];
+            if (ys + RS < y1) {   // prefetch the next group's new rows
+                STREAM_LOAD(nxt, RS);
+            }
+            float acc[RS];
+#pragma unroll
+            for (int j = 0; j < RS; j++) acc[j] = 0.f;
+#pragma unroll
+            for (int k = 0; k < NTAP; k++) {   // RS independent chains, interleaved; each chain is in tap order
+#pragma unroll
+                for (int j = 0; j < RS; j++) acc[j] = __fmaf_rn(v[j + k], taps.v[k], acc[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < RS; j++) ring[buf][j][vc] = acc[j];
+#pragma unroll
+            for (int i = 0; i < 2 * R; i++) v[i] = v[i + RS];
+        }
+        __syncthreads();   // ring[buf] complete; ring[buf ^ 1] was read before the previous barrier... see below
+        // horizontal pass of the RS rows: 32 quads x RS rows = 256 items over the first 128 threads
+        if (tid < kStrTW) {
+#pragma unroll
+            for (int r2 = 0; r2 < RS * 32 / kStrTW; r2++) {
+                const int item = tid + r2 * kStrTW;
+                const int j = item >> 5, qd = item & 31;
+                const int x = x0 + 4 * qd, y = ys + j;
+                if (x < w && y < y1) {
+                    float q[NV * 4];
+                    const float4* src = reinterpret_cast<const float4*>(&ring[buf][j][4 * qd]);
+#pragma unroll
+                    for (int m = 0; m < NV; m++) {
+                        const float4 f = src[m];
+                        q[4 * m] = f.x; q[4 * m + 1] = f.y; q[4 * m + 2] = f.z; q[4 * m + 3] = f.w;
+                    }
+                    float o[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+                    for (int k = 0; k < NTAP; k++) {
+#pragma unroll
+                        for (int jj = 0; jj < 4; jj++) o[jj] = __fmaf_rn(q[RP - R + jj + k], taps.v[k], o[jj]);
+                    }
+                    float* dst = out + (size_t)y * out_pitch + x;
+                    if (x + 3 < w) {
+                        *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+                    } else {
+                        for (int jj = 0; jj < 4 && x + jj < w; jj++) dst[jj] = o[jj];
+                    }
+                }
+            }
+        }
+        // no second barrier: the next step writes the OTHER ring buffer; the step after that (which reuses this one) is
+        // separated from these reads by the next step's barrier
+    }
+#undef STREAM_LOAD
+}
+
+template <int R>
+void launch_stream_r(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
+    const int gx = (w + kStrTW - 1) / kStrTW;
+    // two CTAs per SM in one balanced wave where the image allows it; segments are whole row groups of at least 32 rows
+    int gy = std::max(1, (2 * 148) / gx);
+    int rows = (h + gy - 1) / gy;
+    rows = std::max(32, (rows + kStrRS - 1) / kStrRS * kStrRS);
+    gy = (h + rows - 1) / rows;
+    blur_stream_kernel<R><<<dim3(gx, gy), kStrThreads, 0, s>>>(in, in_pitch, out, out_pitch, w, h, taps, rows);
+}
+template <int R>
+struct StreamTable {
+    static void launch(int r, const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
+        if (r == R) launch_stream_r<R>(in, in_pitch, out, out_pitch, w, h, taps, s);
+        else StreamTable<R - 1>::launch(r, in, in_pitch, out, out_pitch, w, h, taps, s);
+    }
+};
+template <>
+struct StreamTable<0> {
+    static void launch(int, const float*, int, float*, int, int, int, const Taps&, cudaStream_t) {}
+};
+constexpr int kMaxStreamR = 16;
+constexpr int kStreamMinPixels = 512 * 1024;  // layers at least this big take the streaming kernel (1600x900, 1920x1200 octave 0)
 
 // ---------------------------------------------------------------- generic single-stage blur (any radius <= 42)
 constexpr int kGenTW = 64, kGenTH = 32, kGenThreads = 256;
@@ -646,7 +790,18 @@ void launch_blur_chain(const float* src, int src_pitch, int src_w, int src_h, bo
     else launch_chain_inst<false, kFuseThreads, kFuseTW, kFuseTH, kFuseRB, 8, 10, -1>(p, s);
 }
 
+int g_blur_mode = -1;  // -1: not read yet; 0 auto (streaming kernel for big layers), 1 tiles everywhere, 2 streaming everywhere
+
 void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
+    if (g_blur_mode < 0) {  // development switch for A/B measurements: B200SIFT_BLUR=auto|tile|stream
+        const char* e = std::getenv("B200SIFT_BLUR");
+        g_blur_mode = !e ? 0 : (!std::strcmp(e, "tile") ? 1 : (!std::strcmp(e, "stream") ? 2 : 0));
+    }
+    const int r = taps.n / 2;
+    if ((taps.n & 1) && r >= 1 && r <= kMaxStreamR && g_blur_mode != 1 && ((long)w * h >= kStreamMinPixels || g_blur_mode == 2)) {
+        StreamTable<kMaxStreamR>::launch(r, in, in_pitch, out, out_pitch, w, h, taps, s);
+        return;
+    }
     BlurStage st{out, &taps};
     if (blur_chain_supported(false, &st, 1) && in_pitch % 4 == 0) {
         launch_blur_chain(in, in_pitch, w, h, false, nullptr, &st, 1, out_pitch, w, h, s);

@@ -47,6 +47,28 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+# The contract is exactly ONE JSON line on stdout. Libraries print there too (NCCL's version banner, the reference's
+# constructor): file descriptor 1 is pointed at stderr for the whole run and the line is written to the saved descriptor.
+_REAL_STDOUT = None
+
+
+def protect_stdout():
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    sys.stdout.flush()
+    if _REAL_STDOUT is None:
+        os.write(1, data)
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def measured_peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -106,12 +128,13 @@ class ClockSampler(threading.Thread):
         return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons)}
 
 
-def make_frames(n: int, rank: int):
+def make_frames(n: int, rank: int, rows: int = None, cols: int = None):
     """A run of `n` consecutive synthetic frames: textured base frame, then each frame
     is the previous one shifted 2 px / rotated 0.5 deg + noise, so consecutive-frame matching is real."""
     from another_cuda_sift_b200.synth import next_frame, synth_frame
 
-    frames = [synth_frame(ROWS, COLS, 1000 * rank)]
+    rows, cols = rows or ROWS, cols or COLS
+    frames = [synth_frame(rows, cols, 1000 * rank)]
     for i in range(1, n):
         frames.append(next_frame(frames[-1], 1000 * rank + i))
     return frames
@@ -187,52 +210,46 @@ def sum_over_ranks(v: float, world: int) -> float:
     return float(t.item())
 
 
-def run_b200(args, world, rank, local):
-    """Our arm: device-resident `value`, host-buffer `e2e`, roofline of the dominant kernel class."""
+def measure_size(cols, rows, F, steps, warmup, world, rank, local, clocks=False, quick=False):
+    """One workload (frame size) on this rank's GPU: `steps` timed steps of F frames each, three ways --
+    resident (device frames, detectAndComputeAsync + matchConsecutiveAsync per frame, one sync per step),
+    e2e (detectAndComputeBatch on pinned HOST float frames, all results back to pinned host memory) and e2e_u8 (the
+    same call with 8-bit frames). Every step is bracketed by its own CUDA events (median / min / max are reported
+    next to the total the throughput is computed from); barrier + synchronize around the timed region, max over ranks."""
     import torch
 
-    from another_cuda_sift_b200 import CudaSiftConfig, Detector, matchBruteForce
+    from another_cuda_sift_b200 import CudaSiftConfig, Detector, HostResults
     from another_cuda_sift_b200 import _lib
 
     lib = _lib.load()
-    F = args.frames
-    frames = make_frames(F, rank)
-    det = Detector(CudaSiftConfig(col_width=COLS, row_width=ROWS, numFeatures=NUM_FEATURES))
+    frames = make_frames(F, rank, rows, cols)
+    det = Detector(CudaSiftConfig(col_width=cols, row_width=rows, numFeatures=NUM_FEATURES))
     assert det.gpuWarmUpAndAllocate()
     stream = torch.cuda.ExternalStream(det.stream)
-    d_frames = [torch.from_numpy(f).cuda() for f in frames]  # F x 9.2 MB resident in HBM (> L2 for F >= 14)
-    h_frames = [torch.from_numpy(f).pin_memory() for f in frames]
+    d_frames = [torch.from_numpy(f).cuda() for f in frames]
+    h_np = [torch.from_numpy(f).pin_memory().numpy() for f in frames]
+    h8_np = [torch.from_numpy(f.astype(np.uint8)).pin_memory().numpy() for f in frames]
     idx_dev = [torch.empty(NUM_FEATURES, dtype=torch.int32, device="cuda") for _ in range(det.frames_in_flight)]
-    idx_host = torch.empty(NUM_FEATURES, dtype=torch.int32).pin_memory()
-    launches_frame = det.launches_per_frame()
-    state = {"prev": 0, "kpts": 0, "launches": 0, "d2h": 0}
-
-    from another_cuda_sift_b200 import HostResults
-
     results = [HostResults(NUM_FEATURES) for _ in range(F)]
     match_host = [torch.empty(NUM_FEATURES, dtype=torch.int32).pin_memory() for _ in range(F)]
-    h_np = [h.numpy() for h in h_frames]
+    launches_frame = det.launches_per_frame()
     n_match_launches = lib.b200sift_match_launches(NUM_FEATURES, NUM_FEATURES)
+    state = {"launches": 0}
 
     def step_resident():
-        # inputs already in HBM; frame graph + consecutive-frame matcher per frame, sizes stay on the device,
-        # one host synchronisation per step
         for i in range(F):
             det.detectAndComputeAsync(d_frames[i])
             det.matchConsecutiveAsync(idx_dev[i % len(idx_dev)])
         det.synchronize()
         state["launches"] += F * (launches_frame + n_match_launches)
 
-    def step_e2e():
-        # the batched-frame public API with HOST buffers: pinned H2D of every frame (overlapping the previous
-        # frame's graph), keypoints + features + descriptors + match indices back to pinned host memory
-        det.detectAndComputeBatch(h_np, results, match_host)
-        state["d2h"] += F * (results[0].nbytes() + NUM_FEATURES * 4)
+    def step_resident_nomatch():
+        for i in range(F):
+            det.detectAndComputeAsync(d_frames[i])
+        det.synchronize()
 
-    # the same call fed with the 8-bit frames the reference's float images are cast from (cvUtils/ConversionImpl.hpp:25-27;
-    # the synthetic frames are integer valued, results are bit-identical: tests/test_gpu_parity.py): 4x fewer H2D bytes
-    h8_frames = [torch.from_numpy(f.astype(np.uint8)).pin_memory() for f in frames]
-    h8_np = [h.numpy() for h in h8_frames]
+    def step_e2e():
+        det.detectAndComputeBatch(h_np, results, match_host)
 
     def step_e2e_u8():
         det.detectAndComputeBatch(h8_np, results, match_host)
@@ -242,46 +259,54 @@ def run_b200(args, world, rank, local):
             for _ in range(warmup):
                 step_fn()
             barrier_sync(world)
-            state.update(kpts=0, launches=0, d2h=0)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            t0 = time.perf_counter()
-            e0.record(stream)
-            for _ in range(steps):
+            state["launches"] = 0
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(steps + 1)]
+            ev[0].record(stream)
+            for k in range(steps):
                 step_fn()
-            e1.record(stream)
+                ev[k + 1].record(stream)
             barrier_sync(world)
-            wall = (time.perf_counter() - t0) * 1e3
-            ms = e0.elapsed_time(e1)
-        return max_over_ranks(ms, world), wall
+            ms = ev[0].elapsed_time(ev[steps])
+            per = sorted(ev[k].elapsed_time(ev[k + 1]) for k in range(steps))
+        return max_over_ranks(ms, world), per
 
-    sampler = ClockSampler(local)
-    sampler.start()
-    ms_total, wall = timed(step_resident, args.steps, args.warmup)
-    clocks = sampler.stop()
-    kpts_per_frame = 0.0
+    sampler = ClockSampler(local) if clocks else None
+    if sampler:
+        sampler.start()
+    ms_res, per_res = timed(step_resident, steps, warmup)
+    clk = sampler.stop() if sampler else None
     launches = state["launches"]
-    ms_e2e, _ = (ms_total, 0) if args.quick else timed(step_e2e, args.steps, args.warmup)
-    d2h_per_step = state["d2h"] / args.steps if not args.quick else 0
-    ms_e2e_u8, _ = (ms_total, 0) if args.quick else timed(step_e2e_u8, args.steps, args.warmup)
-    if not args.quick:
-        kpts_per_frame = float(np.mean([r.total for r in results]))
+    out = dict(cols=cols, rows=rows, frames_per_step=F, steps=steps, det=det, frames=frames, clocks=clk, launches=launches,
+               ms_res=ms_res, per_res=per_res)
+    if quick:
+        out.update(ms_e2e=ms_res, ms_u8=ms_res, ms_nomatch=ms_res, kpts=0.0, d2h=0)
+        return out
+    ms_e2e, per_e2e = timed(step_e2e, steps, warmup)
+    kpts = float(np.mean([r.total for r in results]))
+    ms_u8, _ = timed(step_e2e_u8, steps, warmup)
+    ms_nomatch, _ = timed(step_resident_nomatch, steps, warmup)
+    out.update(ms_e2e=ms_e2e, per_e2e=per_e2e, ms_u8=ms_u8, ms_nomatch=ms_nomatch, kpts=kpts,
+               d2h=F * (results[0].nbytes() + NUM_FEATURES * 4))
+    return out
 
-    total_frames = sum_over_ranks(F * args.steps, world)
-    value = total_frames / (ms_total * 1e-3)
-    e2e_value = total_frames / (ms_e2e * 1e-3)
-    e2e_u8_value = total_frames / (ms_e2e_u8 * 1e-3)
 
-    # pure frame-graph time (no host sync per frame, no matcher) and per-class breakdown, rank 0 only
-    extra = {}
-    if rank == 0:
-        det.detectAndCompute(d_frames[0])
-        graph_ms = det.time_frames(5, 5 if args.quick else 100)
-        pipe_ms = det.time_frames_pipelined(6, 6 if args.quick else 120)
-        prof = det.profile_frame(1 if args.quick else 3, 1 if args.quick else 20)
-        extra = dict(graph_ms=graph_ms, pipe_ms=pipe_ms, prof=prof, kpts=det.total_size, stages=det.time_stages(5 if args.quick else 50))
-    return dict(value=value, ms_per_step=ms_total / args.steps, wall_ms=wall, e2e_value=e2e_value, e2e_u8_value=e2e_u8_value,
-                e2e_ms_per_step=ms_e2e / args.steps, clocks=clocks, kpts_per_frame=kpts_per_frame,
-                launches=launches, d2h_per_step=d2h_per_step, frames=frames, det=det, extra=extra)
+def size_summary(m, world):
+    """The per-configuration block of the JSON line (all ranks' frames over the max-over-ranks time)."""
+    F, steps = m["frames_per_step"], m["steps"]
+    total = sum_over_ranks(F * steps, world)
+    per_frame = lambda ms: ms / steps / F
+    med = lambda v: v[len(v) // 2]
+    d = {"frames_per_step_per_gpu": F, "steps": steps,
+         "value": total / (m["ms_res"] * 1e-3), "ms_per_frame": per_frame(m["ms_res"]),
+         "ms_per_step_median": med(m["per_res"]), "ms_per_step_min": m["per_res"][0], "ms_per_step_max": m["per_res"][-1],
+         "e2e": total / (m["ms_e2e"] * 1e-3), "e2e_ms_per_frame": per_frame(m["ms_e2e"]),
+         "e2e_u8": total / (m["ms_u8"] * 1e-3),
+         "keypoints_per_frame": round(m["kpts"], 1),
+         "h2d_bytes_per_step": F * m["cols"] * m["rows"] * 4, "d2h_bytes_per_step": int(m["d2h"]),
+         # where the time of a frame goes with every slot in flight (exposed cost of each part, this rank):
+         "breakdown_ms_per_frame": {"detect": per_frame(m["ms_nomatch"]), "match": per_frame(m["ms_res"] - m["ms_nomatch"]),
+                                    "host_copies_not_hidden": per_frame(m["ms_e2e"] - m["ms_res"])}}
+    return d
 
 
 def cpu_port_baseline(frames, budget_s: float = 12.0):
@@ -324,10 +349,54 @@ def opencv_baseline(frames, budget_s: float = 10.0):
                 sample=f"{n_done} frames, cv2.SIFT_create(5000,3,0.04,10,1.6) (2x upscale on) + BFMatcher knn2 + ratio 0.8")
 
 
+def opencv_config0(budget_s: float = 8.0):
+    """BASELINE.json configs[0]: 752x480 single-frame cv::SIFT detectAndCompute + a 2000 x 2000 128-D ratio-test match
+    via cv::BFMatcher (knn-2, 0.8), on this box's host cores (thirdparty/opencv/modules/features2d/src/sift.dispatch.cpp,
+    matchers.cpp:757 in the reference tree; here the cv2 wheel of the image). Reported, not optimised."""
+    try:
+        import cv2
+    except Exception as e:  # noqa: BLE001
+        return {"unavailable": f"cv2 import failed: {e}"}
+    from another_cuda_sift_b200.synth import synth_descriptors
+
+    frames = make_frames(4, 0, 480, 752)
+    sift = cv2.SIFT_create(5000, 3, 0.04, 10, 1.6)
+    ms, n_kp, t_start = [], 0, time.perf_counter()
+    for i in range(12):
+        t0 = time.perf_counter()
+        kp, _ = sift.detectAndCompute(frames[i % 4].astype(np.uint8), None)
+        ms.append((time.perf_counter() - t0) * 1e3)
+        n_kp = len(kp)
+        if time.perf_counter() - t_start > budget_s and i >= 3:
+            break
+    q, t = synth_descriptors(2000, 2000)
+    q32, t32 = q.astype(np.float32), t.astype(np.float32)
+    bf = cv2.BFMatcher(cv2.NORM_L2)
+    mm, good = [], 0
+    for _ in range(5):
+        t0 = time.perf_counter()
+        pairs = bf.knnMatch(q32, t32, k=2)
+        good = sum(1 for m in pairs if len(m) == 2 and m[0].distance < 0.8 * m[1].distance)
+        mm.append((time.perf_counter() - t0) * 1e3)
+    return {"workload": "752x480 cv2.SIFT_create(5000,3,0.04,10,1.6).detectAndCompute (2x upscale on) + BFMatcher(NORM_L2).knnMatch(k=2) "
+                        "2000 x 2000 x 128 + 0.8 ratio", "cores": cv2.getNumThreads(), "version": cv2.__version__,
+            "detect_ms_median": sorted(ms)[len(ms) // 2], "detect_frames_per_s": 1e3 / (sum(ms) / len(ms)), "keypoints": n_kp,
+            "match_2k2k_ms_median": sorted(mm)[len(mm) // 2], "match_accepted": good}
+
+
+def workload_config(cols, rows, frames, world):
+    """The `config` keys both arms print (identical for the same workload, so the driver can compare them)."""
+    return {"workload": f"{cols}x{rows} detectAndCompute + consecutive-frame matchBruteForce", "frames_per_step_per_gpu": frames,
+            "numFeatures": NUM_FEATURES, "numOctaveLayers": 3, "sigma": 1.6, "data": "synthetic frames, seed 1234 + 1000*rank + i"}
+
+
 def run_reference(args, world, rank, local):
     """The reference arm. The reference implements this path ONLY in CUDA (no CPU code), so its 'own
     implementation' is its CUDA build: oracle/_ref/libref_sift.so, compiled from the untouched sources for
-    sm_100a, driven through Detector::detectAndCompute / copyToHost / matchBruteForce. Rank 0 only."""
+    sm_100a. e2e = its stock public path (Detector::detectAndCompute(Imagef) -> copyToHost(true) -> matchBruteForce,
+    tool/extract_and_match_example.cc:57-101) over the SAME distinct frames as our arm; value = the same frames with the
+    host->device upload and copyToHost outside the timing (stage sequence of detectAndCompute on the resident image +
+    matchBruteForce). Rank 0 only."""
     from oracle.pyoracle import RefOracle, ref_available
     import ctypes as C
 
@@ -342,8 +411,7 @@ def run_reference(args, world, rank, local):
     lib = ref.lib
     lib.ref_add_frame.restype, lib.ref_add_frame.argtypes = C.c_int, [C.c_void_p, C.c_void_p]
     lib.ref_process_frame.restype, lib.ref_process_frame.argtypes = C.c_int, [C.c_void_p, C.c_int, C.c_int, C.c_int, C.POINTER(C.c_int)]
-    lib.ref_process_resident.restype, lib.ref_process_resident.argtypes = C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_int)]
-    lib.ref_upload_frame.restype, lib.ref_upload_frame.argtypes = None, [C.c_void_p, C.c_int]
+    lib.ref_process_timed.restype, lib.ref_process_timed.argtypes = C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_double)]
     for f in frames:
         lib.ref_add_frame(ref.h, np.ascontiguousarray(f).ctypes.data)
     nm = C.c_int(0)
@@ -356,23 +424,28 @@ def run_reference(args, world, rank, local):
     for _ in range(args.warmup):
         step_e2e()
     sampler.start()
-    t0 = time.perf_counter()
+    per = []
     for _ in range(args.steps):
+        t0 = time.perf_counter()
         step_e2e()
-    ms_e2e = (time.perf_counter() - t0) * 1e3  # every call ends in cudaDeviceSynchronize: wall == device
+        per.append((time.perf_counter() - t0) * 1e3)  # every call ends in cudaDeviceSynchronize: wall == device
+    ms_e2e = sum(per)
     clocks = sampler.stop()
-    # device-resident: the reference cannot take a device image, so one frame is uploaded outside the
-    # timing and the stage sequence of detectAndCompute is replayed on it (no H2D), + matcher.
-    lib.ref_upload_frame(ref.h, 0)
-    for _ in range(args.warmup * 4):
-        lib.ref_process_resident(ref.h, 1, C.byref(nm))
-    t0 = time.perf_counter()
-    for _ in range(args.steps * F):
-        lib.ref_process_resident(ref.h, 1, C.byref(nm))
-    ms_res = (time.perf_counter() - t0) * 1e3
+    # resident leg + breakdown: the same F distinct frames, every phase timed on its own
+    ms4 = (C.c_double * 4)()
+    acc = np.zeros(4)
+    for it in range(args.warmup + args.steps):
+        for i in range(F):
+            lib.ref_process_timed(ref.h, i, 1, ms4)
+            if it >= args.warmup:
+                acc += np.array(list(ms4))
     total = F * args.steps
+    h2d, detect, d2h, match = (acc / total).tolist()
+    ms_res = (detect + match) * total
+    per.sort()
     return dict(value=total / (ms_res * 1e-3), ms_per_step=ms_res / args.steps, e2e_value=total / (ms_e2e * 1e-3),
-                frames_per_step=F, clocks=clocks, kpts=int(lib.ref_total_size(ref.h)),
+                e2e_ms_per_step_median=per[len(per) // 2], frames_per_step=F, clocks=clocks, kpts=int(lib.ref_total_size(ref.h)),
+                breakdown={"h2d_upload": h2d, "detect": detect, "copy_to_host": d2h, "match": match},
                 cpu_baseline=dict(value=total / (ms_e2e * 1e-3), unit="frames/s", cores=1, kind="reference",
                                   sample=f"{total} frames; the reference has no CPU implementation of this path: this is its "
                                          "unmodified CUDA build (oracle/_ref, sm_100a) on the same B200, 1 host thread driving it"))
@@ -392,6 +465,13 @@ def class_bytes(kpts: int):
     }
 
 
+def other_sizes(world):
+    """BASELINE.json's other detector configurations: configs[1] 752x480, configs[3] 1600x900 (at 8 GPUs: the batch of
+    256 frames, 32 per GPU, frame-parallel)."""
+    out = [("752x480", 752, 480, 16), ("1600x900", 1600, 900, 32 if world == 8 else 16)]
+    return [o for o in out if (o[1], o[2]) != (COLS, ROWS)]
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -401,8 +481,10 @@ def main():
     ap.add_argument("--size", default="1920x1200", help="frame size WxH: 1920x1200 is BASELINE.json's metric; 752x480 and 1600x900 are its other configs")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--quick", action="store_true", help="profiler runs: skip e2e leg, per-class profile and CPU baselines")
+    ap.add_argument("--no-extras", action="store_true", help="headline configuration only (no other sizes, no 100k x 100k matcher)")
+    ap.add_argument("--quick", action="store_true", help="profiler runs: skip e2e leg, per-class profile, extras and CPU baselines")
     args = ap.parse_args()
+    protect_stdout()
     global COLS, ROWS, S_PIXELS, METRIC
     COLS, ROWS = (int(v) for v in args.size.lower().split("x"))
     if (COLS, ROWS) != (1920, 1200):
@@ -417,24 +499,65 @@ def main():
         if rank != 0:
             return 0
         r = run_reference(args, 1, 0, 0)
+        cfg = workload_config(COLS, ROWS, args.frames, 1)
+        cfg["reference"] = ("unmodified reference CUDA build (oracle/_ref) on 1 B200; the reference is single-GPU, so the same "
+                            "1-GPU figure is reported for every N")
         line = {
             "impl": "reference", "metric": METRIC, "value": r["value"], "unit": "frames/s", "n_gpus": 1,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": f"{COLS}x{ROWS} detectAndCompute + consecutive-frame matchBruteForce", "frames_per_step_per_gpu": args.frames,
-                       "numFeatures": NUM_FEATURES, "reference": "unmodified reference CUDA build (oracle/_ref) on 1 B200; "
-                       "the reference is single-GPU, so the same 1-GPU figure is reported for every N"},
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
             "e2e": {"value": r["e2e_value"], "unit": "frames/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "cpu_baseline": r["cpu_baseline"], "clocks": r.get("clocks"),
         }
-        if "note" in r:
-            line["note"] = r["note"]
-        print(json.dumps(line), flush=True)
+        for k in ("breakdown", "kpts", "e2e_ms_per_step_median", "note"):
+            if k in r:
+                line["breakdown_ms_per_frame" if k == "breakdown" else k] = r[k]
+        emit(line)
         return 0
 
     world, rank, local = dist_setup(args.gpus)
-    r = run_b200(args, world, rank, local)
-    launches_total = sum_over_ranks(r["launches"], world)
+    m = measure_size(COLS, ROWS, args.frames, args.steps, args.warmup, world, rank, local, clocks=True, quick=args.quick)
+    launches_total = sum_over_ranks(m["launches"], world)
+    head = size_summary(m, world)
+    clocks = m["clocks"]
+    det = m["det"]
+    # pure frame-graph time (no host sync per frame, no matcher) and per-class breakdown, rank 0 only
+    ex = {}
+    if rank == 0:
+        import torch
+
+        det.detectAndCompute(torch.from_numpy(m["frames"][0]).cuda())
+        ex = dict(graph_ms=det.time_frames(5, 5 if args.quick else 100), pipe_ms=det.time_frames_pipelined(6, 6 if args.quick else 120),
+                  prof=det.profile_frame(1 if args.quick else 3, 1 if args.quick else 20), kpts=det.total_size,
+                  stages=det.time_stages(5 if args.quick else 50))
+    fif = det.frames_in_flight
+    main_frames = m["frames"]
+    det.close()
+    del m, det
+
+    # the other BASELINE configurations and the sharded 100k x 100k matcher: every rank takes part (collective timing)
+    extras, match100k = {}, None
+    if not (args.quick or args.no_extras):
+        for name, c, r_, f in other_sizes(world):
+            mm = measure_size(c, r_, f, max(3, args.steps // 2), 3, world, rank, local)
+            lat = None
+            if rank == 0:
+                import torch
+
+                mm["det"].detectAndCompute(torch.from_numpy(mm["frames"][0]).cuda())
+                lat = mm["det"].time_frames(5, 50)
+            summ = size_summary(mm, world)
+            summ["frame_graph_ms"] = lat
+            if name == "1600x900" and world == 8:
+                summ["note"] = "BASELINE.json configs[3]: batch of 256 frames, 32 per GPU, frame-parallel over 8 GPUs"
+            extras[name] = summ
+            mm["det"].close()
+            del mm
+        sys.path.insert(0, os.path.join(ROOT, "tools"))
+        from bench_match import large_sharded
+
+        match100k = large_sharded(100000, world, rank, iters=5, check_rows=64)
+
     if rank != 0:
         if world > 1:
             import torch.distributed as dist
@@ -443,68 +566,72 @@ def main():
             dist.destroy_process_group()
         return 0
     hbm_peak, _, peak_kind = measured_peaks()
-    ex = r["extra"]
     prof = ex["prof"]
     cb = class_bytes(ex["kpts"])
-    # Dominant kernel FUNCTION of the frame by device time: blur_vh_kernel (the 6 octave-0 launches and the 21
-    # launches of the smaller octaves are two profiling classes of the same kernel). Bytes and time are the
-    # totals over its launches of one frame, i.e. bytes per launch / average launch duration.
-    groups = {"blur_vh_kernel": ["blur_oct0", "blur_small"], "detect_kernel": ["detect"], "descriptor_kernel": ["describe"]}
+    # Roofline of the dominant kernel FUNCTION of the frame, blur_chain_kernel (all Gaussian-pyramid launches of a frame:
+    # profiling classes blur_oct0 + blur_small). ONE method, the same in every round since r1's final commit: algorithmic
+    # bytes of those launches (8 B per pixel per layer) over the CUDA-event time of the frame GRAPH
+    # truncated after the pyramid (b200sift_time_stages: the launches exactly as the product runs them; the interval also
+    # holds the single-CTA tail kernel, so the rate is a lower bound). The eager per-launch sum is printed beside it.
+    groups = {"blur_chain_kernel": ["blur_oct0", "blur_small"], "detect_kernel": ["detect"], "descriptor_kernel": ["describe"]}
     gms = {g: sum(prof[k]["ms"] for k in ks) for g, ks in groups.items()}
-    dom = max(gms, key=gms.get)
-    dom_ms = gms[dom]
-    eager_ms = dom_ms
-    how = ("CUDA events around every launch of one frame run eagerly on a single stream (b200sift_profile_frame); "
-           "in the frame graph these launches overlap")
-    if dom == "blur_vh_kernel":
-        # The blur launches as the product runs them: the frame GRAPH truncated after the pyramid, replayed and timed with
-        # CUDA events on its stream (b200sift_time_stages). That interval also holds the 5 downsample launches and the tail
-        # kernel on the blur chain's critical path, so the blur rate derived from it is a lower bound; the eager per-launch
-        # figure (5-6 us of launch latency per dependent small kernel) is kept as eager_ms_per_frame.
-        dom_ms = ex["stages"]["pyramid"]
-        how = ("the frame graph truncated after the pyramid (27 blur launches + 5 downsample + tail kernel), replayed and timed "
-               "with CUDA events on its stream (b200sift_time_stages): a lower bound of the blur rate; eager_ms_per_frame is the "
-               "sum over the same launches run eagerly with an event after each")
+    dom = "blur_chain_kernel"
+    dom_ms = ex["stages"]["pyramid"]
     dom_bytes = sum(cb[k] for k in groups[dom])
     dom_launches = sum(prof[k]["launches"] for k in groups[dom])
     achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(dom)
+        tj = json.load(open(tpath))
+        traffic = tj.get(dom, tj.get("blur_vh_kernel"))
     frame_bytes = 4 * COLS * ROWS + 48 * S_PIXELS + 284 * ex["kpts"]
+    cfg = workload_config(COLS, ROWS, args.frames, world)
+    cfg.update({"global_frames_per_step": args.frames * world, "parallelism": f"frames x{world}", "cpu_affinity": AFFINITY,
+                "frames_in_flight_per_gpu": fif, "keypoints_per_frame": head["keypoints_per_frame"],
+                "l2": f"device-resident inputs are {args.frames} distinct frames = {args.frames * COLS * ROWS * 4 / 1e6:.0f} MB per step; with the {fif} pyramids in flight "
+                      f"({fif * 24 * S_PIXELS / 1e6:.0f} MB) the working set is {'larger' if (args.frames * COLS * ROWS * 4 + fif * 24 * S_PIXELS) > 126e6 else 'SMALLER'} than the 126 MB L2"})
     line = {
-        "metric": METRIC, "value": r["value"], "unit": "frames/s", "n_gpus": world, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"{COLS}x{ROWS} detectAndCompute + consecutive-frame matchBruteForce", "frames_per_step_per_gpu": args.frames,
-                   "global_frames_per_step": args.frames * world, "numFeatures": NUM_FEATURES, "parallelism": f"frames x{world}", "cpu_affinity": AFFINITY, "frames_in_flight_per_gpu": r["det"].frames_in_flight,
-                   "keypoints_per_frame": round(r["kpts_per_frame"], 1),
-                   "l2": f"device-resident inputs are {args.frames} distinct frames = {args.frames * COLS * ROWS * 4 / 1e6:.0f} MB per step; with the six pyramids in flight "
-                         f"({6 * 24 * S_PIXELS / 1e6:.0f} MB) the working set is {'larger' if (args.frames * COLS * ROWS * 4 + 6 * 24 * S_PIXELS) > 126e6 else 'SMALLER'} than the 126 MB L2"},
-        "ms_per_frame": r["ms_per_step"] / args.frames,
+        "metric": METRIC, "value": head["value"], "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": head["ms_per_frame"] * args.frames, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f32", "data": "synthetic", "config": cfg,
+        "ms_per_frame": head["ms_per_frame"],
+        "ms_per_step_median": head["ms_per_step_median"], "ms_per_step_min": head["ms_per_step_min"], "ms_per_step_max": head["ms_per_step_max"],
         "frame_graph_ms": ex["graph_ms"],             # latency of one frame's graphs, nothing else in flight
         "frame_pipelined_ms": ex["pipe_ms"],          # per frame with every frame slot in flight (graphs only)
-        "e2e": {"value": r["e2e_value"], "unit": "frames/s", "h2d_bytes_per_step": args.frames * COLS * ROWS * 4,
-                "d2h_bytes_per_step": int(r["d2h_per_step"]), "ms_per_frame": r["e2e_ms_per_step"] / args.frames},
-        "e2e_u8": {"value": r["e2e_u8_value"], "unit": "frames/s", "h2d_bytes_per_step": args.frames * COLS * ROWS,
+        "e2e": {"value": head["e2e"], "unit": "frames/s", "h2d_bytes_per_step": head["h2d_bytes_per_step"],
+                "d2h_bytes_per_step": head["d2h_bytes_per_step"], "ms_per_frame": head["e2e_ms_per_frame"]},
+        "e2e_u8": {"value": head["e2e_u8"], "unit": "frames/s", "h2d_bytes_per_step": args.frames * COLS * ROWS,
                    "note": "same public call with the 8-bit host frames the float images are cast from (b200sift_detect_host_u8_async): "
                            "identical results, a quarter of the H2D bytes; the float figure above is the headline"},
+        "breakdown_ms_per_frame": head["breakdown_ms_per_frame"],
         "gpu_launches": int(launches_total),
-        "clocks": r["clocks"],
+        "clocks": None,
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": achieved, "peak": hbm_peak, "unit": "GB/s",
                      "frac": achieved / hbm_peak, "traffic": traffic, "peak_kind": peak_kind,
                      "launches_per_frame": dom_launches, "ms_per_frame": dom_ms,
                      "bytes_per_launch": dom_bytes / max(dom_launches, 1), "us_per_launch": dom_ms * 1e3 / max(dom_launches, 1),
-                     "by_kernel": {g: {"ms_per_frame": round(gms[g], 5),
-                                       "GB/s": round(sum(cb[k] for k in groups[g]) / (gms[g] * 1e-3) / 1e9, 1)} for g in groups},
-                     "eager_ms_per_frame": eager_ms, "note": how},
+                     "by_kernel_eager": {g: {"ms_per_frame": round(gms[g], 5),
+                                             "GB/s": round(sum(cb[k] for k in groups[g]) / (gms[g] * 1e-3) / 1e9, 1)} for g in groups},
+                     "eager_ms_per_frame": gms[dom],
+                     "method": "algorithmic bytes of the pyramid launches / CUDA-event time of the frame graph truncated after the pyramid "
+                               "(in-graph, as the product runs them; lower bound: the interval also holds the tail kernel); by_kernel_eager = "
+                               "the same launches run eagerly on one stream with an event after each"},
         "roofline_frame": {"bytes": frame_bytes, "achieved": frame_bytes / (ex["pipe_ms"] * 1e-3) / 1e9,
                            "frac": frame_bytes / (ex["pipe_ms"] * 1e-3) / 1e9 / hbm_peak,
                            "note": "SURVEY 8(d) algorithmic bytes of one frame / pipelined frame time"},
         "kernel_ms_per_frame": {k: round(v["ms"], 5) for k, v in prof.items()},
         "graph_cumulative_ms": {k: round(v, 5) for k, v in ex["stages"].items()},
     }
+    return line, args, world, main_frames, extras, match100k, clocks
+
+
+def finish(line, args, world, main_frames, extras, match100k, clocks):
+    line["clocks"] = clocks
+    if extras:
+        line["configs"] = extras
+    if match100k is not None:
+        line["match_100k"] = match100k
     if not args.quick:
         # second half of BASELINE.json's metric: latency of the 2000 x 2000 x 128 ratio-test match (seeded synthetic
         # descriptor sets, device-resident, median of per-call CUDA-event times) + its tensor roofline
@@ -513,9 +640,10 @@ def main():
 
         line["match_2k2k"] = match_latency(2000, iters=200)
     if world == 1 and not args.no_cpu_baseline and not args.quick:
-        line["cpu_baseline"] = cpu_port_baseline(r["frames"])
-        line["opencv_cpu"] = opencv_baseline(r["frames"])
-    print(json.dumps(line), flush=True)
+        line["cpu_baseline"] = cpu_port_baseline(main_frames)
+        line["opencv_cpu"] = opencv_baseline(main_frames)
+        line["cpu_opencv_752x480"] = opencv_config0()
+    emit(line)
     if world > 1:
         import torch.distributed as dist
 
@@ -525,4 +653,5 @@ def main():
 
 
 if __name__ == "__main__":
-    sys.exit(main())
+    _r = main()
+    sys.exit(_r if isinstance(_r, int) else finish(*_r))

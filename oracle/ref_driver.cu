@@ -12,6 +12,7 @@
 // source is copied into this repository: the #include resolves into
 // /root/reference at build time only.
 #include <algorithm>
+#include <chrono>
 #include <cmath>
 #include <cstdint>
 #include <cstring>
@@ -271,6 +272,45 @@ int ref_process_resident(void* p, int do_match, int* n_matched) {
     }
     if (n_matched) *n_matched = acc;
     h->prev_size = cur;
+    return cur;
+}
+// One frame of the bench loop with a wall-clock split (every phase ends in cudaDeviceSynchronize, so wall == device):
+// ms4 = {H2D upload of frame idx (CudaImage::operator=, CudaImage.cu:88-105), the stage sequence of detectAndCompute on
+// the resident image, copyToHost(true), matchBruteForce(previous frame -> this frame)}. The stages are the reference's
+// own methods in the order of Detector.cu:133-233.
+int ref_process_timed(void* p, int idx, int do_match, double* ms4) {
+    auto* h = static_cast<RefHandle*>(p);
+    auto& d = *h->det;
+    using clk = std::chrono::steady_clock;
+    auto ms = [](clk::time_point a, clk::time_point b) { return std::chrono::duration<double, std::milli>(b - a).count(); };
+    cudaDeviceSynchronize();
+    const auto t0 = clk::now();
+    d.m_data.original_image = h->frames.at(idx);
+    cudaDeviceSynchronize();
+    const auto t1 = clk::now();
+    cudaMemcpyAsync(thrust::raw_pointer_cast(d.prev_descriptor.data()), thrust::raw_pointer_cast(d.device_descriptor.data()),
+                    d.prev_descriptor.size() * sizeof(half), cudaMemcpyDeviceToDevice);
+    d.createInitialImage();
+    d.getGaussianPyramid();
+    d.getDogPyramid();
+    d.getKeyPoints();
+    d.adjustKpts();
+    d.adjustOrientationAndCleanup();
+    d.extractDescriptor();
+    d.collectAcrossOctaves();
+    cudaDeviceSynchronize();
+    const auto t2 = clk::now();
+    d.copyToHost(true);
+    cudaDeviceSynchronize();
+    const auto t3 = clk::now();
+    const int cur = d.total_size;
+    if (do_match && h->prev_size > 0 && cur > 0) {
+        std::vector<int> m = sift_cuda::matchBruteForce(d.prev_descriptor, h->prev_size, d.device_descriptor, cur);
+        (void)m;
+    }
+    const auto t4 = clk::now();
+    h->prev_size = cur;
+    if (ms4) { ms4[0] = ms(t0, t1); ms4[1] = ms(t1, t2); ms4[2] = ms(t2, t3); ms4[3] = ms(t3, t4); }
     return cur;
 }
 void ref_upload_frame(void* p, int idx) {

@@ -202,6 +202,10 @@ def main():
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    if os.environ.get("B200SIFT_MATCH_PATH"):  # A/B measurements: 3 = round 1's two-pass streaming filter
+        from another_cuda_sift_b200 import _lib
+
+        _lib.load().b200sift_match_set_path(int(os.environ["B200SIFT_MATCH_PATH"]))
     line = {"metric": "matchBruteForce latency", "unit": "ms", "n_gpus": world, "data": "synthetic (seed 42/43)", "dtype": "f16 in, f32 accumulate, f64 ratio test"}
     if rank == 0 and args.small > 0:
         line["small"] = match_latency(args.small, args.iters)
