@@ -1220,7 +1220,7 @@ int b200sift_match_launches(int nq, int nt) { return match_num_launches(nq, nt);
 
 int b200sift_match_set_path(int path) {
     if (path < 0 || path > 3)
-        return fail(B200SIFT_EINVAL, "path must be 0 (tensor core), 1 (CUDA core), 2 (tensor core, unpipelined large-set filter) or 3 (tensor core, two-pass streaming filter)");
+        return fail(B200SIFT_EINVAL, "path must be 0 (tensor core), 1 (CUDA core), 2 (tensor core, unpipelined large-set filter) or 3 (tensor core, single-pass streaming filter)");
     match_set_path(path);
     return 0;
 }

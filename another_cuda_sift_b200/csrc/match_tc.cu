@@ -610,18 +610,18 @@ match_filter_resident_kernel(const __half* __restrict__ des, int nq, const __hal
 }
 
 // ---------------------------------------------------------------- streaming filter (per > 256: large train sets)
-// One CTA = 256 queries x ONE column chunk of the reference, streamed ONCE as 128-row train tiles. Per step and thread
-// (64 distances of one query row):
-//   bound   the running (min, 2nd min) over the minima of column octets is updated first: the 2nd smallest octet minimum
-//           is an upper bound of the true 2nd smallest distance seen so far (equal unless both fall into one octet);
-//   record  the same octets are then tested against the threshold derived from the UPDATED running bound; an octet is
-//           only opened when its minimum passes, and a passing column is appended to the thread's candidate list with
-//           its distance. The running bound never increases, so its threshold is always >= the final one: every column
-//           under the FINAL threshold is recorded when it is scanned. Expected candidates per thread ~ 2 ln(steps) + 1;
-//           a full list (16) is first re-filtered with the current, tighter threshold, and only then overflows;
-//   finish  the two column halves of a row exchange their bounds, the lists are filtered by the final threshold: the
-//           survivors are exactly those of a two-pass filter (bound pass, then threshold pass) at half the MMA, TMA and
-//           scan work. (Round 1 ran the two passes: 4.2 of 5.0 ms at 100k x 100k.)
+// One CTA = 256 queries x ONE column chunk of the reference, streamed as 128-row train tiles, twice:
+//   pass 0  an upper bound of the chunk's second smallest distance per query (branch-free: the 2nd smallest of the
+//           minima of column octets is >= the true 2nd smallest, and equal to it unless both fall into one octet);
+//   pass 1  the same tiles again (MMA recomputed: cheaper than keeping 2 x 256 x per distances anywhere), every
+//           column with D <= thr(bound) is a survivor; an octet is only opened when its minimum passes.
+// SINGLE = true is a one-pass variant (b200sift_match_set_path(3)): per step the running bound is updated first, then
+// the same octets are tested against the threshold of the UPDATED running bound (never below the final one, so every
+// final survivor is recorded when it is scanned) and passing columns go to a per-thread candidate list with their
+// distance, re-filtered when more than half full and by the final threshold at the end -- the same survivors at half
+// the MMA / TMA work. It is exact (same tests pass) but SLOWER: 5.69 vs 5.08 ms at 100k x 100k (profiles/r2_match_stream.md).
+// With 32 independent query rows per warp some lane has a candidate in most octets while the bound is still loose, so
+// the scan of a step costs ~2.3x, and the scan warps, not the tensor pipe, bound a step.
 // Measured on B200 (tools/probes/tmem_probe.cu, elimination runs and ncu source views of earlier versions of this
 // kernel): with both operands in shared memory a M128 N128 K16 MMA takes ~83 cycles instead of 64 (8 KB of operand
 // reads per instruction saturate the 128 B/cycle shared-memory port), and streaming the train tiles with cp.async
@@ -1294,8 +1294,10 @@ int match_launch(const __half* q, int nq, const __half* t, int nt, int* out, voi
         match_aug_kernel<<<(32 * tiles * 128 + 255) / 256, 256, 0, s>>>(nrm_t, nt, per, tiles, aug);
         mark(0);
         dim3 grid((nq + kResQ - 1) / kResQ, 32);
-        if (g_match_path == 3) match_filter_stream_kernel<false><<<grid, kStreamThreads, kStreamSmem, s>>>(q, nq, train_map, nt, per, rec, nrm_q, nrm_t, aug);
-        else match_filter_stream_kernel<true><<<grid, kStreamThreads, kStreamSmem, s>>>(q, nq, train_map, nt, per, rec, nrm_q, nrm_t, aug);
+        // single-pass variant (path 3): measured 5.69 ms against 5.08 ms for the two passes at 100k x 100k on one B200 (r2): a
+        // step is bounded by the scan warps, not by the tensor pipe, and one pass makes every step's scan more expensive
+        if (g_match_path == 3) match_filter_stream_kernel<true><<<grid, kStreamThreads, kStreamSmem, s>>>(q, nq, train_map, nt, per, rec, nrm_q, nrm_t, aug);
+        else match_filter_stream_kernel<false><<<grid, kStreamThreads, kStreamSmem, s>>>(q, nq, train_map, nt, per, rec, nrm_q, nrm_t, aug);
     }
     if (per <= 256 || dbg || g_match_path == 2) mark(0);  // those paths compute their norms inside / right before the filter
     mark(1);

@@ -14,8 +14,10 @@
 //                      layer of the Gaussian stack. Stage 0 is either a plain layer or the bilinear 2x resample
 //                      of the previous octave's layer n, computed on the fly (and stored as the base layer).
 //                      The frame graph runs one such launch per octave on the critical path
-//                      (resample + L1..Ln) and one on a side branch (L(n+1), L(n+2)); octave 0 uses single-stage
-//                      launches (its 2.3 Mpx are throughput-, not latency-bound).
+//                      (resample + L1..Ln) and one on a side branch (L(n+1), L(n+2)), in the largest of three tile
+//                      shapes that still fills the GPU (64x32, 32x16, 16x8): small octaves are latency-bound.
+//  blur_vh_kernel      one layer per launch (octave 0: its 2.3 Mpx are throughput-, not latency-bound; any unfused
+//                      radius <= 16): vertical pass from global memory in registers, horizontal pass from shared memory.
 //  blur_generic_kernel any radius <= 42 at run time (uncommon sigma / numOctaveLayers), one stage.
 //  pyramid_tail_kernel ONE CTA walks every octave of <= 4096 pixels.
 //
@@ -327,147 +329,129 @@ blur_chain_kernel(const __grid_constant__ ChainParams p, const __grid_constant__
     if constexpr (K >= 3) stage(std::integral_constant<int, (R3 < 0 ? 1 : R3)>{}, 3, p.taps[2], S0, nullptr, p.out[2], 0);
 }
 
-// ---------------------------------------------------------------- streaming single-stage blur (big layers)
-// A CTA owns a 128-column strip of a row segment and walks DOWN it. Thread t of the first 128 + 2R owns source column
-// reflect101(x0 - R + t): it keeps a sliding window of 2R + RS input rows in registers, loads every input pixel ONCE
-// (coalesced 4-byte loads, the next row group prefetched into registers while the current one is computed), and emits RS
-// row-filtered values per step as RS independent in-order chains into a double-buffered RS-row ring in shared memory;
-// the first 128 threads then run the horizontal pass of those RS rows (4 outputs per thread from LDS.128 windows, 4
-// independent chains, one STG.128). One barrier per RS rows, ~10 KB of shared memory, no phase in which the whole CTA
-// waits for a tile: the strip's loads, FMAs and stores overlap continuously, and the small footprint lets these CTAs
-// share an SM with the descriptor CTAs of the other frames in flight.
-constexpr int kStrTW = 128;       // output columns per strip
-constexpr int kStrThreads = 160;  // >= kStrTW + 2R for R <= 16
-constexpr int kStrRS = 8;         // rows per step
+// ---------------------------------------------------------------- single-stage blur (octave 0, unfused fallbacks)
+// One Gaussian layer per launch: vertical pass straight from global memory into registers (16 + 2R rows per thread, all
+// loads up front), the row-filtered tile in shared memory (<= 40 KB), horizontal pass from LDS.128 windows, STG.128.
+// Same-box A/B on a B200 at 1920x1200 (profiles/r2_pyramid_ab.md) against two replacements written in round 2 -- a
+// TMA-staged 128x64 tile kernel (~107 KB of shared memory per CTA) and a streaming column-strip kernel (register sliding
+// window, 10 KB of shared memory, 14% occupancy, long-scoreboard bound): octave 0 takes 65 us with this kernel, 67 us with
+// the tile kernel, 88 us with the streaming one, at the same 2.8-5.4 M warp instructions per launch; both were removed.
+constexpr int kVhTW = 128;      // output columns per CTA (one warp row = 32 lanes x 4 outputs)
+constexpr int kVhRB = 16;       // output rows per vertical register block
+constexpr int kVhThreads = 320;  // 10 warps: one vertical-pass sweep covers the 128 + 2R columns of two row blocks
 
+// One CTA: TH = nb*kVhRB output rows x kVhTW output columns.
+//  pass 1 (vertical):   each thread owns one column of one row block, keeps kVhRB+2R input pixels
+//                       in registers (all loads issued up front) and emits kVhRB row-filtered
+//                       values into shared memory. Columns cover the tile plus an R-wide halo,
+//                       taken at reflect-101 positions, because the horizontal pass of the
+//                       reference reads the row-filtered image at reflected columns.
+//  pass 2 (horizontal): each lane produces 4 consecutive outputs from 4+2R shared-memory values
+//                       fetched as conflict-free LDS.128, stores one STG.128.
 template <int R>
-__global__ void __launch_bounds__(kStrThreads)
-blur_stream_kernel(const float* __restrict__ in, int in_pitch, float* __restrict__ out, int out_pitch, int w, int h,
-                   const __grid_constant__ Taps taps, int rows_per_cta) {
-    constexpr int NTAP = 2 * R + 1, RS = kStrRS;
-    constexpr int RP = round_up4(R);
-    constexpr int VW = kStrTW + 2 * RP;      // ring row length: column c <-> image column x0 - RP + c
-    constexpr int NV = (2 * RP + 4) / 4;     // float4 loads per output quad
-    __shared__ __align__(16) float ring[2][RS][VW];
+__global__ void __launch_bounds__(kVhThreads)
+blur_vh_kernel(const float* __restrict__ in, int in_pitch, float* __restrict__ out, int out_pitch,
+               int w, int h, const __grid_constant__ Taps taps, int nb) {
+    constexpr int RP = (R + 3) & ~3;       // halo rounded up so that rows stay 16-byte aligned
+    constexpr int TWP = kVhTW + 2 * RP;      // shared row length
+    constexpr int NC = kVhTW + 2 * R;        // columns that are really needed
+    constexpr int NT = 2 * R + 1;
+    extern __shared__ __align__(16) float tmp[];  // [nb*kVhRB][TWP]
 
+    const int x0 = blockIdx.x * kVhTW;
+    const int y0 = blockIdx.y * nb * kVhRB;
     const int tid = threadIdx.x;
-    const int x0 = blockIdx.x * kStrTW;
-    const int y0 = blockIdx.y * rows_per_cta;
-    const int y1 = min(h, y0 + rows_per_cta);
-    if (y0 >= y1) return;
-    const bool vthread = tid < kStrTW + 2 * R;
-    const int vc = RP - R + tid;                                        // this thread's ring column
-    const float* col = in + reflect101(x0 - R + min(tid, kStrTW + 2 * R - 1), w);  // the horizontal pass reads V at reflected columns
-    // Rows are consumed in strictly increasing order (y0 - R, y0 - R + 1, ...): a running pointer serves the interior
-    // segments (uniform branch: no reflection, one 64-bit add per row); border segments reflect each row index, without
-    // the modulo of reflect101 when one reflection suffices (h > 2R + RS, i.e. every layer this kernel is chosen for).
-    const bool interior = (y0 - R >= 0) && (y0 + ((y1 - y0 + RS - 1) / RS) * RS + R <= h);
-    const bool one_fold = h > 2 * R + RS;
-    const float* rowp = col + (ptrdiff_t)(y0 - R) * in_pitch;
-    int ynext = y0 - R;
-#define STREAM_LOAD(dst, count)                                                                                   \
-    do {                                                                                                          \
-        if (interior) {                                                                                           \
-            _Pragma("unroll") for (int i_ = 0; i_ < (count); i_++) {                                              \
-                (dst)[i_] = __ldg(rowp);                                                                          \
-                rowp += in_pitch;                                                                                 \
-            }                                                                                                     \
-        } else {                                                                                                  \
-            _Pragma("unroll") for (int i_ = 0; i_ < (count); i_++) {                                              \
-                const int y_ = ynext + i_;                                                                        \
-                const int yy_ = one_fold ? (y_ < 0 ? -y_ : (y_ >= h ? 2 * (h - 1) - y_ : y_)) : reflect101(y_, h); \
-                (dst)[i_] = __ldg(col + (ptrdiff_t)yy_ * in_pitch);                                               \
-            }                                                                                                     \
-        }                                                                                                         \
-        ynext += (count);                                                                                         \
-    } while (0)
 
-    float v[2 * R + RS], nxt[RS];
-    if (vthread) {
-        STREAM_LOAD(v, 2 * R);
-        STREAM_LOAD(nxt, RS);
-    }
-    int buf = 0;
-    for (int ys = y0; ys < y1; ys += RS, buf ^= 1) {
-        if (vthread) {
+    for (int t = tid; t < NC * nb; t += kVhThreads) {
+        const int b = t / NC;
+        const int c = (RP - R) + (t - b * NC);
+        const int x = reflect101(x0 - RP + c, w);
+        const int ybase = y0 + b * kVhRB - R;
+        float v[kVhRB + 2 * R];
+        if (ybase >= 0 && ybase + kVhRB + 2 * R <= h) {
+            // one 64-bit pointer stepped by the row pitch: a single IMAD.WIDE per load instead of the four address
+            // instructions (IADD3 / IMAD.X / LEA / LEA.HI.X) an element-indexed p[i * pitch] compiles to
+            const float* p = in + (size_t)ybase * in_pitch + x;
 #pragma unroll
-            for (int j = 0; j < RS; j++) v[2 * R + j] = nxt[j];
-            if (ys + RS < y1) {   // prefetch the next group's new rows
-                STREAM_LOAD(nxt, RS);
+            for (int i = 0; i < kVhRB + 2 * R; i++) {
+                v[i] = __ldg(p);
+                asm volatile("mad.wide.s32 %0, %1, 4, %0;" : "+l"(p) : "r"(in_pitch));
             }
-            float acc[RS];
+        } else {
 #pragma unroll
-            for (int j = 0; j < RS; j++) acc[j] = 0.f;
-#pragma unroll
-            for (int k = 0; k < NTAP; k++) {   // RS independent chains, interleaved; each chain is in tap order
-#pragma unroll
-                for (int j = 0; j < RS; j++) acc[j] = __fmaf_rn(v[j + k], taps.v[k], acc[j]);
-            }
-#pragma unroll
-            for (int j = 0; j < RS; j++) ring[buf][j][vc] = acc[j];
-#pragma unroll
-            for (int i = 0; i < 2 * R; i++) v[i] = v[i + RS];
+            for (int i = 0; i < kVhRB + 2 * R; i++) v[i] = __ldg(in + (size_t)reflect101(ybase + i, h) * in_pitch + x);
         }
-        __syncthreads();   // ring[buf] complete; ring[buf ^ 1] was read before the previous barrier... see below
-        // horizontal pass of the RS rows: 32 quads x RS rows = 256 items over the first 128 threads
-        if (tid < kStrTW) {
+        float* dst = tmp + (size_t)(b * kVhRB) * TWP + c;
 #pragma unroll
-            for (int r2 = 0; r2 < RS * 32 / kStrTW; r2++) {
-                const int item = tid + r2 * kStrTW;
-                const int j = item >> 5, qd = item & 31;
-                const int x = x0 + 4 * qd, y = ys + j;
-                if (x < w && y < y1) {
-                    float q[NV * 4];
-                    const float4* src = reinterpret_cast<const float4*>(&ring[buf][j][4 * qd]);
+        for (int r = 0; r < kVhRB; r++) {
+            float acc = 0.f;
 #pragma unroll
-                    for (int m = 0; m < NV; m++) {
-                        const float4 f = src[m];
-                        q[4 * m] = f.x; q[4 * m + 1] = f.y; q[4 * m + 2] = f.z; q[4 * m + 3] = f.w;
-                    }
-                    float o[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-                    for (int k = 0; k < NTAP; k++) {
-#pragma unroll
-                        for (int jj = 0; jj < 4; jj++) o[jj] = __fmaf_rn(q[RP - R + jj + k], taps.v[k], o[jj]);
-                    }
-                    float* dst = out + (size_t)y * out_pitch + x;
-                    if (x + 3 < w) {
-                        *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
-                    } else {
-                        for (int jj = 0; jj < 4 && x + jj < w; jj++) dst[jj] = o[jj];
-                    }
-                }
-            }
+            for (int k = 0; k < NT; k++) acc = __fmaf_rn(v[r + k], taps.v[k], acc);
+            dst[r * TWP] = acc;
         }
-        // no second barrier: the next step writes the OTHER ring buffer; the step after that (which reuses this one) is
-        // separated from these reads by the next step's barrier
     }
-#undef STREAM_LOAD
+    __syncthreads();
+
+    const int warp = tid >> 5, lane = tid & 31;
+    const int TH = nb * kVhRB;
+    const int xo = 4 * lane;
+    const int x = x0 + xo;
+    if (x >= w) return;
+    for (int row = warp; row < TH; row += kVhThreads / 32) {
+        const int y = y0 + row;
+        if (y >= h) break;
+        constexpr int NV = (2 * RP + 4) / 4;
+        float q[NV * 4];
+        const float4* src = reinterpret_cast<const float4*>(tmp + (size_t)row * TWP + xo);
+#pragma unroll
+        for (int m = 0; m < NV; m++) {
+            float4 f = src[m];
+            q[4 * m] = f.x; q[4 * m + 1] = f.y; q[4 * m + 2] = f.z; q[4 * m + 3] = f.w;
+        }
+        float o[4];
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            float acc = 0.f;
+#pragma unroll
+            for (int k = 0; k < NT; k++) acc = __fmaf_rn(q[RP - R + j + k], taps.v[k], acc);
+            o[j] = acc;
+        }
+        float* dst = out + (size_t)y * out_pitch + x;
+        if (x + 3 < w) {
+            *reinterpret_cast<float4*>(dst) = make_float4(o[0], o[1], o[2], o[3]);
+        } else {
+            for (int j = 0; j < 4 && x + j < w; j++) dst[j] = o[j];
+        }
+    }
 }
 
 template <int R>
-void launch_stream_r(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
-    const int gx = (w + kStrTW - 1) / kStrTW;
-    // two CTAs per SM in one balanced wave where the image allows it; segments are whole row groups of at least 32 rows
-    int gy = std::max(1, (2 * 148) / gx);
-    int rows = (h + gy - 1) / gy;
-    rows = std::max(32, (rows + kStrRS - 1) / kStrRS * kStrRS);
-    gy = (h + rows - 1) / rows;
-    blur_stream_kernel<R><<<dim3(gx, gy), kStrThreads, 0, s>>>(in, in_pitch, out, out_pitch, w, h, taps, rows);
+void launch_vh_r(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
+    constexpr int RP = (R + 3) & ~3;
+    constexpr int TWP = kVhTW + 2 * RP;
+    // Taller tiles amortise the vertical halo on big images; short tiles spread small images
+    // over more SMs.
+    const int gx = (w + kVhTW - 1) / kVhTW;
+    int nb = 4;
+    while (nb > 1 && gx * ((h + nb * kVhRB - 1) / (nb * kVhRB)) < 2 * 148) nb >>= 1;
+    dim3 grid(gx, (h + nb * kVhRB - 1) / (nb * kVhRB));
+    size_t smem = (size_t)nb * kVhRB * TWP * sizeof(float);
+    blur_vh_kernel<R><<<grid, kVhThreads, smem, s>>>(in, in_pitch, out, out_pitch, w, h, taps, nb);
 }
+
+
 template <int R>
-struct StreamTable {
+struct VhTable {
     static void launch(int r, const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
-        if (r == R) launch_stream_r<R>(in, in_pitch, out, out_pitch, w, h, taps, s);
-        else StreamTable<R - 1>::launch(r, in, in_pitch, out, out_pitch, w, h, taps, s);
+        if (r == R) launch_vh_r<R>(in, in_pitch, out, out_pitch, w, h, taps, s);
+        else VhTable<R - 1>::launch(r, in, in_pitch, out, out_pitch, w, h, taps, s);
     }
 };
 template <>
-struct StreamTable<0> {
+struct VhTable<0> {
     static void launch(int, const float*, int, float*, int, int, int, const Taps&, cudaStream_t) {}
 };
-constexpr int kMaxStreamR = 16;
-constexpr int kStreamMinPixels = 512 * 1024;  // layers at least this big take the streaming kernel (1600x900, 1920x1200 octave 0)
+constexpr int kMaxVhR = 16;
 
 // ---------------------------------------------------------------- generic single-stage blur (any radius <= 42)
 constexpr int kGenTW = 64, kGenTH = 32, kGenThreads = 256;
@@ -661,10 +645,23 @@ u8_to_float_kernel(const uint8_t* __restrict__ in, size_t in_pitch, float* __res
 
 // ---- launch tables -------------------------------------------------------------------------------------------
 extern bool g_pyramid_error;
-// Single-stage tiles: 128 x 64 (two CTAs of 320 threads per SM) when that fills the GPU, else 128 x 32.
-constexpr int kOneThreads = 320, kOneTW = 128, kOneRB = 16;
-// Fused chains: 64 x 32 tiles, 256 threads, 8-row register blocks.
-constexpr int kFuseThreads = 256, kFuseTW = 64, kFuseTH = 32, kFuseRB = 8;
+// Fused chains: 256 threads, 8-row register blocks, three tile shapes. A CTA's latency grows with its tile (stage 0
+// covers the tile plus a 15 / 18 pixel halo on every side) and the octaves of one frame depend on each other, so every
+// octave takes the LARGEST shape that still gives the GPU one CTA per SM: 64 x 32 at 960 x 600 (285 CTAs), 32 x 16 at
+// 480 x 300, 16 x 8 from 240 x 150 down. The halo work this adds on the small octaves runs on SMs that had nothing to do.
+constexpr int kFuseThreads = 256, kFuseRB = 8;
+constexpr int kNumShapes = 3;
+template <int I> struct Shape;
+template <> struct Shape<0> { static constexpr int TW = 64, TH = 32; };
+template <> struct Shape<1> { static constexpr int TW = 32, TH = 16; };
+template <> struct Shape<2> { static constexpr int TW = 16, TH = 8; };
+
+int pick_shape(int w, int h) {
+    const int tw[kNumShapes] = {Shape<0>::TW, Shape<1>::TW, Shape<2>::TW}, th[kNumShapes] = {Shape<0>::TH, Shape<1>::TH, Shape<2>::TH};
+    for (int i = 0; i < kNumShapes; i++)
+        if (((w + tw[i] - 1) / tw[i]) * ((h + th[i] - 1) / th[i]) >= 148) return i;
+    return kNumShapes - 1;
+}
 
 // Tensor map of a w x h float layer with row pitch `pitch` floats; box = the CTA's stage-0 region. The encode function
 // comes from the driver through the runtime's entry-point query (no link-time dependency on libcuda).
@@ -690,11 +687,12 @@ bool encode_layer_map(CUtensorMap* map, const float* base, int w, int h, int pit
 template <bool DOWN, int NT, int TW, int TH, int RB, int R1, int R2, int R3>
 void launch_chain_inst(const ChainParams& p, cudaStream_t s) {
     using G = ChainGeom<TW, TH, RB, R1, R2, R3>;
+    static_assert(G::SW <= 256 && G::SH <= 256, "TMA box dimensions");
     dim3 grid((p.w + TW - 1) / TW, (p.h + TH - 1) / TH);
     CUtensorMap map;
     std::memset(&map, 0, sizeof(map));
     if (!DOWN && !encode_layer_map(&map, p.src, p.w, p.h, p.src_pitch, G::SW, G::SH)) {
-        g_pyramid_error = true;  // reported by pyramid_check() (engine.cu turns it into an error of the enqueueing call)
+        g_pyramid_error = true;  // reported by pyramid_failed() (engine.cu turns it into an error of the enqueueing call)
         return;
     }
     blur_chain_kernel<DOWN, NT, TW, TH, RB, R1, R2, R3><<<grid, NT, G::kSmem, s>>>(p, map);
@@ -706,39 +704,29 @@ cudaError_t setup_chain_inst() {
 }
 
 bool g_pyramid_error = false;
-constexpr int kMaxOneR = 16;  // single-stage instantiations exist for every radius 1..16
 
-template <int R>
-void launch_one_r(const ChainParams& p, cudaStream_t s) {
-    // taller tiles amortise the vertical halo; take them when they still give every SM its two CTAs' worth of work
-    const int gx = (p.w + kOneTW - 1) / kOneTW;
-    if (gx * ((p.h + 63) / 64) >= 148) launch_chain_inst<false, kOneThreads, kOneTW, 64, kOneRB, R, -1, -1>(p, s);
-    else launch_chain_inst<false, kOneThreads, kOneTW, 32, kOneRB, R, -1, -1>(p, s);
-}
-template <int R>
-cudaError_t setup_one_r() {
-    cudaError_t e = setup_chain_inst<false, kOneThreads, kOneTW, 64, kOneRB, R, -1, -1>();
-    if (e != cudaSuccess) return e;
-    return setup_chain_inst<false, kOneThreads, kOneTW, 32, kOneRB, R, -1, -1>();
-}
-template <int R>
-struct OneTable {
-    static void launch(int r, const ChainParams& p, cudaStream_t s) {
-        if (r == R) launch_one_r<R>(p, s);
-        else OneTable<R - 1>::launch(r, p, s);
+// the fused chains of the default configuration (sigma 1.6, numOctaveLayers 3): resample + 9/11/13 taps (layers 1..3 of
+// an octave, from layer 3 of the octave before) and 17/21 taps (layers 4, 5), each in every tile shape
+template <int I>
+struct ChainTable {
+    using S = Shape<I>;
+    static void launch(int shape, bool down, const ChainParams& p, cudaStream_t s) {
+        if (shape != I) return ChainTable<I + 1>::launch(shape, down, p, s);
+        if (down) launch_chain_inst<true, kFuseThreads, S::TW, S::TH, kFuseRB, 4, 5, 6>(p, s);
+        else launch_chain_inst<false, kFuseThreads, S::TW, S::TH, kFuseRB, 8, 10, -1>(p, s);
     }
     static cudaError_t setup() {
-        cudaError_t e = setup_one_r<R>();
-        return e != cudaSuccess ? e : OneTable<R - 1>::setup();
+        cudaError_t e = setup_chain_inst<true, kFuseThreads, S::TW, S::TH, kFuseRB, 4, 5, 6>();
+        if (e == cudaSuccess) e = setup_chain_inst<false, kFuseThreads, S::TW, S::TH, kFuseRB, 8, 10, -1>();
+        return e != cudaSuccess ? e : ChainTable<I + 1>::setup();
     }
 };
 template <>
-struct OneTable<0> {
-    static void launch(int, const ChainParams&, cudaStream_t) {}
+struct ChainTable<kNumShapes> {
+    static void launch(int, bool, const ChainParams&, cudaStream_t) {}
     static cudaError_t setup() { return cudaSuccess; }
 };
 
-// the fused chains of the default configuration (sigma 1.6, numOctaveLayers 3): resample + 9/11/13 taps, 17/21 taps
 bool is_radii(const BlurStage* st, int n, int a, int b, int c) {
     const int want[3] = {a, b, c};
     int k = 0;
@@ -758,20 +746,21 @@ bool pyramid_failed() {
 }
 
 cudaError_t pyramid_setup() {
-    cudaError_t e = OneTable<kMaxOneR>::setup();
-    if (e != cudaSuccess) return e;
-    e = setup_chain_inst<true, kFuseThreads, kFuseTW, kFuseTH, kFuseRB, 4, 5, 6>();
-    if (e != cudaSuccess) return e;
-    e = setup_chain_inst<false, kFuseThreads, kFuseTW, kFuseTH, kFuseRB, 8, 10, -1>();
+    cudaError_t e = ChainTable<0>::setup();
     if (e != cudaSuccess) return e;
     return cudaFuncSetAttribute(blur_generic_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 (int)((kGenTW + 2 * kGenMaxR) * kGenTH * sizeof(float)));
 }
 
+int g_fuse_mode = -1;  // 1 (default): fused resample + blur chains for octaves >= 1; 0: one launch per layer
+
 bool blur_chain_supported(bool from_prev_octave, const BlurStage* st, int n) {
-    if (from_prev_octave) return is_radii(st, n, 4, 5, 6);
-    if (n == 1) return (st[0].taps->n & 1) && st[0].taps->n / 2 >= 1 && st[0].taps->n / 2 <= kMaxOneR;
-    return is_radii(st, n, 8, 10, -1);
+    if (g_fuse_mode < 0) {  // development switch for same-box A/B runs: B200SIFT_FUSE=0 -> one launch per layer everywhere
+        const char* e = std::getenv("B200SIFT_FUSE");
+        g_fuse_mode = (e && e[0] == '0') ? 0 : 1;
+    }
+    if (!g_fuse_mode) return false;
+    return from_prev_octave ? is_radii(st, n, 4, 5, 6) : is_radii(st, n, 8, 10, -1);
 }
 
 void launch_blur_chain(const float* src, int src_pitch, int src_w, int src_h, bool from_prev_octave, float* base_out,
@@ -785,31 +774,17 @@ void launch_blur_chain(const float* src, int src_pitch, int src_w, int src_h, bo
         if (i < n) p.taps[i] = *st[i].taps;
         else p.taps[i].n = 0;
     }
-    if (from_prev_octave) launch_chain_inst<true, kFuseThreads, kFuseTW, kFuseTH, kFuseRB, 4, 5, 6>(p, s);
-    else if (n == 1) OneTable<kMaxOneR>::launch(st[0].taps->n / 2, p, s);
-    else launch_chain_inst<false, kFuseThreads, kFuseTW, kFuseTH, kFuseRB, 8, 10, -1>(p, s);
+    ChainTable<0>::launch(pick_shape(w, h), from_prev_octave, p, s);
 }
 
-int g_blur_mode = -1;  // -1: not read yet; 0 auto (streaming kernel for big layers), 1 tiles everywhere, 2 streaming everywhere
-
 void launch_blur(const float* in, int in_pitch, float* out, int out_pitch, int w, int h, const Taps& taps, cudaStream_t s) {
-    if (g_blur_mode < 0) {  // development switch for A/B measurements: B200SIFT_BLUR=auto|tile|stream
-        const char* e = std::getenv("B200SIFT_BLUR");
-        g_blur_mode = !e ? 0 : (!std::strcmp(e, "tile") ? 1 : (!std::strcmp(e, "stream") ? 2 : 0));
-    }
     const int r = taps.n / 2;
-    if ((taps.n & 1) && r >= 1 && r <= kMaxStreamR && g_blur_mode != 1 && ((long)w * h >= kStreamMinPixels || g_blur_mode == 2)) {
-        StreamTable<kMaxStreamR>::launch(r, in, in_pitch, out, out_pitch, w, h, taps, s);
+    if ((taps.n & 1) && r >= 1 && r <= kMaxVhR) {
+        VhTable<kMaxVhR>::launch(r, in, in_pitch, out, out_pitch, w, h, taps, s);
         return;
     }
-    BlurStage st{out, &taps};
-    if (blur_chain_supported(false, &st, 1) && in_pitch % 4 == 0) {
-        launch_blur_chain(in, in_pitch, w, h, false, nullptr, &st, 1, out_pitch, w, h, s);
-        return;
-    }
-    const int R = taps.n / 2;
     dim3 grid((w + kGenTW - 1) / kGenTW, (h + kGenTH - 1) / kGenTH);
-    blur_generic_kernel<<<grid, kGenThreads, (size_t)(kGenTW + 2 * R) * kGenTH * sizeof(float), s>>>(in, in_pitch, out, out_pitch, w, h, taps);
+    blur_generic_kernel<<<grid, kGenThreads, (size_t)(kGenTW + 2 * r) * kGenTH * sizeof(float), s>>>(in, in_pitch, out, out_pitch, w, h, taps);
 }
 
 void launch_downsample(const float* in, int in_pitch, int iw, int ih, float* out, int out_pitch, int ow, int oh, cudaStream_t s) {

@@ -260,7 +260,7 @@ B200SIFT_API int b200sift_match_sharded_profile(b200sift_comm* comm, const uint1
 /* Matcher implementation: 0 (default) = tcgen05 tensor-core filter + exact re-rank (csrc/match_tc.cu),
  * 1 = all-CUDA-core exact kernel (csrc/match.cu), kept as the on-device cross-check, 2 = as 0 but train sets
  * larger than 8192 rows go through the first, unpipelined tcgen05 filter (cross-check of the streaming one), 3 = as 0 with
- * round 1's two-pass streaming filter (A/B measurements).
+ * the single-pass variant of the streaming filter (exact, measured slower: A/B only).
  * All are bit-exact with the reference; process-wide setting. */
 B200SIFT_API int b200sift_match_set_path(int path);
 /* Test access to the tensor-core stage: d_dist[nq*nt] (device) receives the fp32 squared distances

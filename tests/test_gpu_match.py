@@ -23,7 +23,7 @@ def test_2000x2000_vs_golden(path):
     assert np.array_equal(matchBruteForce(q[:300], 300, q[:300], 300), g["self300"])
 
 
-@pytest.fixture(params=[0, 1, 2, 3], ids=["tensor-core", "cuda-core", "tensor-core-unpipelined", "tensor-core-two-pass-stream"])
+@pytest.fixture(params=[0, 1, 2, 3], ids=["tensor-core", "cuda-core", "tensor-core-unpipelined", "tensor-core-single-pass-stream"])
 def path(request):
     """Both matcher implementations (csrc/match_tc.cu: tcgen05 filter + exact re-rank; csrc/match.cu: exact
     CUDA-core kernel) must reproduce the reference bit for bit."""

@@ -202,7 +202,7 @@ def main():
         import torch.distributed as dist
 
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    if os.environ.get("B200SIFT_MATCH_PATH"):  # A/B measurements: 3 = round 1's two-pass streaming filter
+    if os.environ.get("B200SIFT_MATCH_PATH"):  # A/B measurements: 3 = single-pass streaming filter
         from another_cuda_sift_b200 import _lib
 
         _lib.load().b200sift_match_set_path(int(os.environ["B200SIFT_MATCH_PATH"]))
