@@ -12,6 +12,8 @@
 // order independent (deterministic) and lies inside the reference's own run-to-run envelope:
 // orientation bins as 2^-32 in 64 bits (peak selection is a discrete decision, keep it as exact as
 // possible), descriptor bins as 2^-15 in 32 bits (8 votes per sample: one ATOMS.ADD each).
+#include <cstdlib>
+
 #include "common.cuh"
 
 namespace b200sift {
@@ -40,7 +42,6 @@ __device__ __forceinline__ float fix_get(unsigned long long v) { return (float)(
 // must lie within +-65536, far above what 0..255-valued pixels blurred with sigma >= 1.6 can produce
 // (|gradient| < 170, weight <= 1, a few hundred samples per bin). Quantisation: <= 1.5e-5 per partial sum, i.e.
 // ~1e-6 relative on a bin -- below the fp32 rounding noise of the reference's own float accumulation.
-constexpr float kFix32 = 32768.f;
 constexpr float kUnfix32 = 1.f / 32768.f;
 
 // ---------------------------------------------------------------- orientation
@@ -306,12 +307,25 @@ constexpr int kDescWarps = kDescThreads / 32;
 constexpr int kHistSize = 6 * 6 * 10;
 constexpr int kPrivSlots = 32;  // 2 x 2 spatial neighbours x 8 orientation bins (bin 8 is folded onto 0 here, not in the epilogue)
 
-// The 4x4 sample cells (rbin_int, cbin_int) of the descriptor window, packed as R*4+C, largest first: row and
-// column 0 cover rbin in (-1,1) (truncating modff, quirk Q13), so cell (0,0) is four units of area, the other
-// row-0 / column-0 cells two, the rest one. Warps pull cells from this queue (longest-processing-time order).
-__constant__ signed char kCellOrder[16] = {0, 1, 2, 3, 4, 8, 12, 5, 6, 7, 9, 10, 11, 13, 14, 15};
-constexpr int kDescCtasPerSm = 7;  // persistent CTAs per SM (64 registers x 128 threads: register-limited at 8, shared memory at 7)
+// The 4x4 sample cells (rbin_int, cbin_int) of the descriptor window, packed as R*4+C. Row and column 0 cover rbin in
+// (-1,1) (truncating modff, quirk Q13), so cell (0,0) is four units of area, the other row-0 / column-0 cells two, the
+// rest one: 25 units, dealt to the four warps as 6 + 6 + 6 + 7. (A CTA-wide queue popped with a shared-memory atomic
+// balanced slightly better but cost ~25 instructions per pop: ptxas wraps the atomic into its warp-aggregation sequence.)
+__constant__ signed char kWarpCells[4][6] = {{0, 1, -1, -1, -1, -1}, {2, 3, 5, 6, -1, -1}, {4, 8, 7, 9, -1, -1}, {12, 10, 11, 13, 14, 15}};
+static_assert(kDescWarps == 4, "kWarpCells deals the cells to four warps");
+constexpr int kDescCtasPerSm = 8;  // persistent CTAs per SM (61 registers x 128 threads, 22 KB of shared memory each)
 constexpr int kRing = 64;  // per-warp ring of accepted samples (at most 31 pending + 32 appended)
+
+// Everything a warp needs to process one cell of the window, computed once per keypoint by one thread per cell
+// (three LDS.128 per cell instead of ~70 warp instructions of setup in each of the warps that own cells).
+struct __align__(16) CellInfo {
+    int i0, j0, wj, n;            // bounding box origin (patch offsets), its width, its number of points (0: empty)
+    int step_r, step_c, hbase;    // the (row, column) advance of 32 consecutive box points; histogram index of the cell's slot 0
+    float inv_wj;                 // 1 / wj (for the lanes' first points)
+    float r_gt, r_lt, c_gt, c_lt; // truncf(rbin) == R, truncf(cbin) == C written as open intervals
+    float fR, fC;
+    int pad0, pad1;
+};
 
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
@@ -364,7 +378,7 @@ __device__ __noinline__ float exact_obin(float dx, float dy, float abs_y, bool n
 // The set of samples and every per-sample coordinate (c_rot, r_rot, bins, fractions) are computed exactly
 // as in the reference; magnitude, angle and weight use the MUFU approximations (a few ulp; the result is
 // rounded to fp16).
-__global__ void __launch_bounds__(kDescThreads, 7)
+__global__ void __launch_bounds__(kDescThreads, kDescCtasPerSm)
 descriptor_kernel(const __grid_constant__ FrameParams fp) {
     // this launch covers octaves [o_begin, o_end); `first` keypoints of lower octaves precede it in the output
     int first = 0;
@@ -381,9 +395,7 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     __shared__ float s_norm;
     __shared__ __align__(128) float s_priv[kDescWarps][kPrivSlots][32];
     __shared__ int s_ring[kDescWarps][kRing];
-    __shared__ int s_next;
-    __shared__ int4 s_cbox[16];
-    __shared__ int2 s_cstep[16];
+    __shared__ __align__(16) CellInfo s_cell[16];
     float* priv = &s_priv[warp][0][lane];
 #pragma unroll
     for (int k = 0; k < kPrivSlots; k++) priv[k * 32] = 0.f;  // every flush leaves the columns zeroed again
@@ -395,7 +407,6 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     const OctParams& o = fp.oct[oi];
     const float3 kp = o.fin_kp[j];
     const float4 ft = o.fin_ft[j];
-    if (tid == 0) s_next = 0;
     for (int i = tid; i < kHistSize; i += kDescThreads) s_hist[i] = 0;  // the barrier after the cell boxes below covers these
 
     // unpackOctave (SiftOps.cu:389-401)
@@ -428,70 +439,84 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
     const float ch = cos_u * hist_width, sh = sin_u * hist_width;  // window -> patch coordinates
 
     if (tid < 16) {
-        // cell t of the queue: its extent in rotated coordinates (r_rot = rbin - 1.5), then its bounding box in patch
+        // cell tid = R*4 + C: its extent in rotated coordinates (r_rot = rbin - 1.5), then its bounding box in patch
         // offsets: i = (r cos - c sin) * hist_width, j = (r sin + c cos) * hist_width. floor/ceil leave up to a pixel of
         // slack, six orders of magnitude more than the rounding of these products. One thread per cell, once per
         // keypoint (the warps that own the cells used to recompute this, 83 warp instructions per cell).
-        const int cell = kCellOrder[tid];
-        const int R = cell >> 2, C = cell & 3;
+        const int R = tid >> 2, C = tid & 3;
         const float fR = (float)R, fC = (float)C;
         const float rlo = (R == 0 ? -1.f : fR) - 1.5f, rhi = fR - 0.5f;
         const float clo = (C == 0 ? -1.f : fC) - 1.5f, chi = fC - 0.5f;
         const float ia = rlo * ch, ib = rhi * ch, ic = -clo * sh, id = -chi * sh;
         const float ja = rlo * sh, jb = rhi * sh, jc = clo * ch, jd = chi * ch;
-        const int i0 = max(-radius, __float2int_rd(fminf(ia, ib) + fminf(ic, id)));
-        const int i1 = min(radius, __float2int_ru(fmaxf(ia, ib) + fmaxf(ic, id)));
-        const int j0 = max(-radius, __float2int_rd(fminf(ja, jb) + fminf(jc, jd)));
-        const int j1 = min(radius, __float2int_ru(fmaxf(ja, jb) + fmaxf(jc, jd)));
+        // ... clipped to the patch (|i|, |j| <= radius) and to the pixels the reference accepts (0 < x < w, 0 < y < h
+        // strictly, SiftOps.cu:541-547): the scan then needs no per-point image test
+        const int i0 = max(max(-radius, 1 - iy), __float2int_rd(fminf(ia, ib) + fminf(ic, id)));
+        const int i1 = min(min(radius, oh - 1 - iy), __float2int_ru(fmaxf(ia, ib) + fmaxf(ic, id)));
+        const int j0 = max(max(-radius, 1 - ix), __float2int_rd(fminf(ja, jb) + fminf(jc, jd)));
+        const int j1 = min(min(radius, ow - 1 - ix), __float2int_ru(fmaxf(ja, jb) + fmaxf(jc, jd)));
         const int wj = j1 - j0 + 1, wi = i1 - i0 + 1;
         const bool empty = wj <= 0 || wi <= 0;
+        const float inv_wj = __frcp_rn((float)max(wj, 1));
         // (k + 0.5) / wj is never within rounding distance of an integer, so this is an exact floor
-        const int step_r = empty ? 0 : __float2int_rd(32.5f * __frcp_rn((float)wj));
-        s_cbox[tid] = make_int4(i0, j0, wj, empty ? 0 : wi * wj);
-        s_cstep[tid] = make_int2(step_r, 32 - step_r * wj);
+        const int step_r = empty ? 0 : __float2int_rd(32.5f * inv_wj);
+        CellInfo ci;
+        ci.i0 = i0; ci.j0 = j0; ci.wj = wj; ci.n = empty ? 0 : wi * wj;
+        ci.step_r = step_r; ci.step_c = 32 - step_r * wj;
+        ci.hbase = ((R + 1) * 6 + (C + 1)) * 10;
+        ci.inv_wj = inv_wj;
+        // truncf(rbin) == R written as an interval: (-1, 1) for R == 0, [R, R+1) otherwise
+        ci.r_gt = R == 0 ? -1.f : __uint_as_float(__float_as_uint(fR) - 1u); ci.r_lt = fR + 1.f;
+        ci.c_gt = C == 0 ? -1.f : __uint_as_float(__float_as_uint(fC) - 1u); ci.c_lt = fC + 1.f;
+        ci.fR = fR; ci.fC = fC;
+        ci.pad0 = ci.pad1 = 0;
+        s_cell[tid] = ci;
     }
     __syncthreads();
 
     int* ring = s_ring[warp];
     const unsigned lt_mask = (1u << lane) - 1u;
-    const unsigned uw1 = (unsigned)(ow - 1), uh1 = (unsigned)(oh - 1);
-    for (;;) {
-        int t = 0;
-        if (lane == 0) t = atomicAdd(&s_next, 1);
-        t = __shfl_sync(0xffffffffu, t, 0);
-        if (t >= 16) break;
-        const int cell = kCellOrder[t];
-        const int R = cell >> 2, C = cell & 3;
-        const float fR = (float)R, fC = (float)C;
-        const int4 cbox = s_cbox[t];  // bounding box and scan steps, computed once per keypoint by 16 threads (below)
-        const int i0 = cbox.x, j0 = cbox.y, wj = cbox.z, n = cbox.w;
+    const int lane_hoff = ((lane >> 4) * 6 + ((lane >> 3) & 1)) * 10 + (lane & 7);  // slot `lane` = (dr*2 + dc)*8 + bin of a cell
+    // gradient reads: one 64-bit base per keypoint (the patch centre), 32-bit element offsets per sample
+    const int a_centre = iy * hdim + ix;
+    const float* centre = stack + a_centre;
+    const int off_lim = stack_left - hdim - a_centre;  // the row below exists in the stack iff off < off_lim
+    for (int qi = 0; qi < 6; qi++) {
+        // the broadcast tells the compiler that t (and with it the whole cell state) is warp-uniform: uniform datapath
+        const int t = __shfl_sync(0xffffffffu, (int)kWarpCells[warp][qi], 0);
+        if (t < 0) break;
+        const int4 c0 = reinterpret_cast<const int4*>(&s_cell[t])[0];
+        const int i0 = c0.x, j0 = c0.y, wj = c0.z, n = c0.w;
         if (n <= 0) continue;
-        const int2 cstep = s_cstep[t];
-        const int step_r = cstep.x, step_c = cstep.y;
+        const int4 c1 = reinterpret_cast<const int4*>(&s_cell[t])[1];
+        const float4 c2 = reinterpret_cast<const float4*>(&s_cell[t])[2];
+        const float2 c3 = reinterpret_cast<const float2*>(&s_cell[t])[6];
+        const int step_r = c1.x, step_c = c1.y, hbase = c1.z;
+        const float r_gt = c2.x, r_lt = c2.y, c_gt = c2.z, c_lt = c2.w;
+        const float fR = c3.x, fC = c3.y;
         // (k + 0.5) / wj is never within rounding distance of an integer, so this is an exact floor
-        int prow = __float2int_rd(((float)lane + 0.5f) * __frcp_rn((float)wj)), pcol = lane - prow * wj;
-        // truncf(rbin) == R written as an interval: (-1, 1) for R == 0, [R, R+1) otherwise
-        const float r_gt = R == 0 ? -1.f : __uint_as_float(__float_as_uint(fR) - 1u), r_lt = fR + 1.f;
-        const float c_gt = C == 0 ? -1.f : __uint_as_float(__float_as_uint(fC) - 1u), c_lt = fC + 1.f;
+        const int prow0 = __float2int_rd(((float)lane + 0.5f) * __int_as_float(c1.w));
+        int pi = i0 + prow0, pj = j0 + (lane - prow0 * wj);  // this lane's point of the current 32-point step
+        const int jend = j0 + wj;
+        int rem = n - lane;  // > 0 while this lane's point is inside the box
         int head = 0, tail = 0;  // accepted / consumed sample counts of this cell (warp-uniform)
         int scanned = 0;
         for (;;) {
             // ---- scan: until a full batch is pending or the box is exhausted
             while (scanned < n && head - tail < 32) {
-                const int idx_i = i0 + prow, idx_j = j0 + pcol;
-                const bool in_box = scanned + lane < n;
+                const int idx_i = pi, idx_j = pj;
+                const bool in_box = rem > 0;
                 scanned += 32;
-                prow += step_r;
-                pcol += step_c;
-                if (pcol >= wj) { pcol -= wj; prow++; }
+                rem -= 32;
+                pi += step_r;
+                pj += step_c;
+                if (pj >= jend) { pj -= wj; pi++; }
                 const float fi = (float)idx_i, fj = (float)idx_j;
                 const float c_rot = __fmaf_rn(fj, cos_t, -__fmul_rn(fi, sin_t));
                 const float r_rot = __fmaf_rn(fi, cos_t, __fmul_rn(fj, sin_t));
                 const float cbin = __fadd_rn(c_rot, 1.5f), rbin = __fadd_rn(r_rot, 1.5f);
-                // the reference's acceptance (rbin, cbin in (-1,4), pixel strictly inside (0,w) x (0,h)),
-                // restricted to this warp's cell
-                const bool ok = in_box && rbin > r_gt && rbin < r_lt && cbin > c_gt && cbin < c_lt &&
-                                (unsigned)(ix + idx_j - 1) < uw1 && (unsigned)(iy + idx_i - 1) < uh1;
+                // the reference's acceptance (rbin, cbin in (-1,4); the pixel test is in the box), restricted to this cell
+                const bool ok = in_box && rbin > r_gt && rbin < r_lt && cbin > c_gt && cbin < c_lt;
                 const unsigned b = __ballot_sync(0xffffffffu, ok);
                 if (ok) ring[(head + __popc(b & lt_mask)) & (kRing - 1)] = (idx_i & 0xffff) | (idx_j << 16);
                 head += __popc(b);
@@ -509,21 +534,21 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
                 const float cbin = __fadd_rn(c_rot, 1.5f), rbin = __fadd_rn(r_rot, 1.5f);
                 // quirk Q12: px == w-1 / py == h-1 are accepted, so these reads may land in the row
                 // padding, the next row or the next layer; clamp only at the end of the stack.
-                const int a = (iy + idx_i) * hdim + (ix + idx_j);
-                const float* pc = stack + a;
+                const int off = idx_i * hdim + idx_j;
+                const float *pc, *pu, *pd;  // one IMAD.WIDE each
+                asm("mad.wide.s32 %0, %1, 4, %2;" : "=l"(pc) : "r"(off), "l"(centre));
+                asm("mad.wide.s32 %0, %1, 4, %2;" : "=l"(pu) : "r"(off - hdim), "l"(centre));
+                asm("mad.wide.s32 %0, %1, 4, %2;" : "=l"(pd) : "r"(off + hdim), "l"(centre));
                 const float v_l = __ldg(pc - 1), v_r = __ldg(pc + 1);
-                // the rows above / below: one IMAD.WIDE each from pc instead of a fresh 64-bit address build
-                const float *pu = pc, *pd = pc;
-                asm("mad.wide.s32 %0, %1, -4, %0;" : "+l"(pu) : "r"(hdim));
-                asm("mad.wide.s32 %0, %1, 4, %0;" : "+l"(pd) : "r"(hdim));
                 const float v_up = __ldg(pu);
-                const float v_dn = a + hdim < stack_left ? __ldg(pd) : 0.f;
+                const float v_dn = off < off_lim ? __ldg(pd) : 0.f;
                 const float dx = __fsub_rn(v_r, v_l);
                 const float dy = __fsub_rn(v_up, v_dn);
                 // rbin_int = truncf(rbin) is R (as -0.0 for rbin in (-1,0): the fraction is then negative)
                 const float rbin_frac = __fsub_rn(rbin, fR), cbin_frac = __fsub_rn(cbin, fC);
                 const float d2 = __fmaf_rn(c_rot, c_rot, __fmul_rn(r_rot, r_rot));
-                const float weight = ex2_approx(d2 * (-0.125f * 1.4426950408889634f));
+                // Gaussian weight x 2^15 (the fixed-point scale of the integer sum, undone after it) in one MUFU.EX2
+                const float weight = ex2_approx(__fmaf_rn(d2, -0.125f * 1.4426950408889634f, 15.f));
                 const float g2 = __fmaf_rn(dx, dx, __fmul_rn(dy, dy));
                 const float grad_mag = g2 * rsqrt_approx(fmaxf(g2, 1e-30f));
                 // fast_atan2f (SiftOps.cu:403-419) with one approximate division
@@ -537,16 +562,20 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
                 float grad_ori = ang * 57.29577951308232f;
                 grad_ori = grad_ori < 0.f ? grad_ori + 360.f : grad_ori;
                 float obin = __fmul_rn(__fsub_rn(grad_ori, angle), bins_per_degree);
+                float obin_t = truncf(obin);
+                float obin_frac = __fsub_rn(obin, obin_t);
                 // The vote is a discontinuous function of the angle in two places: where fast_atan2f changes sign (the
                 // +360 wrap meets the truncating modff: obin and obin - 8 do not vote alike, quirk Q11) and where obin
                 // crosses a (negative) integer. The approximations above are good to ~2e-6 bins, so within 1e-4 bins /
                 // 1e-5 rad of either the reference's own instruction sequence decides (SASS of SiftOps.cu:403-419,565:
                 // IEEE division, FMUL + 2 FFMA, then double / pi * 180): identical bins, ~2 samples in 10,000.
-                if (fabsf(ang) < 1e-5f || fabsf(__fsub_rn(obin, rintf(obin))) < 1e-4f)
+                // |frac| < 1e-4 or > 1 - 1e-4  <=>  ||frac| - 0.5| > 0.4999
+                if (fabsf(ang) < 1e-5f || fabsf(fabsf(obin_frac) - 0.5f) > 0.4999f) {
                     obin = exact_obin(dx, dy, abs_y, neg, angle);
-                const float mag = grad_mag * weight * kFix32;  // x 2^15: exact scaling, undone after the integer sum
-                const float obin_t = truncf(obin);
-                const float obin_frac = __fsub_rn(obin, obin_t);
+                    obin_t = truncf(obin);
+                    obin_frac = __fsub_rn(obin, obin_t);
+                }
+                const float mag = grad_mag * weight;
                 const int ob = (int)obin_t & 7;  // -7..8 -> 0..7 (obin_int < 0: += 8, >= 8: -= 8)
                 const float v_r1 = mag * rbin_frac, v_r0 = mag * (1.f - rbin_frac);
                 const float omc = 1.f - cbin_frac, omo = 1.f - obin_frac;
@@ -579,7 +608,7 @@ descriptor_kernel(const __grid_constant__ FrameParams fp) {
             acc += v.x; acc += v.y; acc += v.z; acc += v.w;
         }
         const int tot = __float2int_rn(acc);
-        if (tot != 0) atomicAdd(s_hist + ((R + 1 + (lane >> 4)) * 6 + (C + 1 + ((lane >> 3) & 1))) * 10 + (lane & 7), tot);
+        if (tot != 0) atomicAdd(s_hist + hbase + lane_hoff, tot);
         __syncwarp();
     }
     __syncthreads();
@@ -651,7 +680,13 @@ cudaError_t launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cud
     long cap = 0;
     for (int i = o_begin; i < o_end; i++) cap += fp.oct[i].cap;
     long grid = cap < (long)fp.numFeatures ? cap : (long)fp.numFeatures;
-    if (grid > 148L * kDescCtasPerSm) grid = 148L * kDescCtasPerSm;
+    static int per_sm = 0;
+    if (!per_sm) {  // development switch for same-box A/B runs: B200SIFT_DESC_CTAS=<persistent CTAs per SM>
+        const char* e = std::getenv("B200SIFT_DESC_CTAS");
+        per_sm = e ? std::atoi(e) : kDescCtasPerSm;
+        if (per_sm < 1 || per_sm > kDescCtasPerSm) per_sm = kDescCtasPerSm;
+    }
+    if (grid > 148L * per_sm) grid = 148L * per_sm;
     // Lowest stream priority: the descriptor grids would otherwise fill every CTA slot and starve the short
     // latency-bound kernels of the other graph branches (the priority is recorded in the captured node).
     cudaLaunchConfig_t cfg = {};

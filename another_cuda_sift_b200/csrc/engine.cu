@@ -85,9 +85,12 @@ inline int pitch_floats(int w) { return ((w * 4 + 511) / 512) * 512 / 4; }
 constexpr int kSideStreams = 6;   // side branches of the frame graph
 constexpr int kBranchPixels = 65536;  // an octave with at least this many pixels gets a branch of its own
 
-// Frames in flight: a create-time option (b200sift_options::frames_in_flight, 3..8). Measured at 1920x1200: 3 -> 3290,
-// 4 -> 3680, 6 -> 3850 frames/s; ~85 MB of device memory per slot there.
-constexpr int kDefaultSlots = 6, kMinSlots = 3, kMaxSlots = 8;
+// Frames in flight: a create-time option (b200sift_options::frames_in_flight, 3..32), ~85 MB of device memory per slot
+// at 1920x1200. Every slot has its own stream, so frame n + nslots queues behind frame n: with few slots the pyramid of a
+// new frame cannot start before the descriptors of the frame that held its slot are done. Measured on one B200 (same box,
+// frames/s with device-resident input, 32 frames per synchronisation): 6 -> 4051, 16 -> 4433, 32 -> 4552 at 1920x1200;
+// 16 frames per synchronisation: 6 -> 3772, 8 -> 3948, 12 -> 3975, 16 -> 4147; 752x480: 6 -> 8920, 16 -> 10979.
+constexpr int kDefaultSlots = 16, kMinSlots = 3, kMaxSlots = 32;
 
 // Everything one frame touches. Frame n runs in slot n % nslots on the slot's own streams, so the frame graph
 // of frame n+1 (pyramid, extrema: latency-bound chains of small launches) overlaps the descriptor kernels of

@@ -14,8 +14,7 @@
 //                      layer of the Gaussian stack. Stage 0 is either a plain layer or the bilinear 2x resample
 //                      of the previous octave's layer n, computed on the fly (and stored as the base layer).
 //                      The frame graph runs one such launch per octave on the critical path
-//                      (resample + L1..Ln) and one on a side branch (L(n+1), L(n+2)), in the largest of three tile
-//                      shapes that still fills the GPU (64x32, 32x16, 16x8): small octaves are latency-bound.
+//                      (resample + L1..Ln) and one on a side branch (L(n+1), L(n+2)), 64 x 32 tiles.
 //  blur_vh_kernel      one layer per launch (octave 0: its 2.3 Mpx are throughput-, not latency-bound; any unfused
 //                      radius <= 16): vertical pass from global memory in registers, horizontal pass from shared memory.
 //  blur_generic_kernel any radius <= 42 at run time (uncommon sigma / numOctaveLayers), one stage.
@@ -645,23 +644,18 @@ u8_to_float_kernel(const uint8_t* __restrict__ in, size_t in_pitch, float* __res
 
 // ---- launch tables -------------------------------------------------------------------------------------------
 extern bool g_pyramid_error;
-// Fused chains: 256 threads, 8-row register blocks, three tile shapes. A CTA's latency grows with its tile (stage 0
-// covers the tile plus a 15 / 18 pixel halo on every side) and the octaves of one frame depend on each other, so every
-// octave takes the LARGEST shape that still gives the GPU one CTA per SM: 64 x 32 at 960 x 600 (285 CTAs), 32 x 16 at
-// 480 x 300, 16 x 8 from 240 x 150 down. The halo work this adds on the small octaves runs on SMs that had nothing to do.
+// Fused chains: 256 threads, 8-row register blocks, 64 x 32 tiles. Smaller tiles for the small octaves (32 x 16 at
+// 480 x 300, 16 x 8 below: a CTA's latency grows with its tile plus the 15 / 18 pixel halo, and a 64 x 32 grid leaves most
+// SMs idle there) were measured on a B200 at 1920x1200: the three launches got 4-5.5 us shorter each under ncu, the
+// pyramid 4 us shorter inside the frame graph (0.151 -> 0.147 ms), and the pipelined throughput fell from 3700 to 3456
+// frames/s (three times as many CTAs queue behind the other frames' descriptor CTAs, twice the halo work). Kept as a
+// table of one so that the trade can be re-measured (profiles/r2_pyramid_ab.md).
 constexpr int kFuseThreads = 256, kFuseRB = 8;
-constexpr int kNumShapes = 3;
+constexpr int kNumShapes = 1;
 template <int I> struct Shape;
 template <> struct Shape<0> { static constexpr int TW = 64, TH = 32; };
-template <> struct Shape<1> { static constexpr int TW = 32, TH = 16; };
-template <> struct Shape<2> { static constexpr int TW = 16, TH = 8; };
 
-int pick_shape(int w, int h) {
-    const int tw[kNumShapes] = {Shape<0>::TW, Shape<1>::TW, Shape<2>::TW}, th[kNumShapes] = {Shape<0>::TH, Shape<1>::TH, Shape<2>::TH};
-    for (int i = 0; i < kNumShapes; i++)
-        if (((w + tw[i] - 1) / tw[i]) * ((h + th[i] - 1) / th[i]) >= 148) return i;
-    return kNumShapes - 1;
-}
+int pick_shape(int, int) { return 0; }
 
 // Tensor map of a w x h float layer with row pitch `pitch` floats; box = the CTA's stage-0 region. The encode function
 // comes from the driver through the runtime's entry-point query (no link-time dependency on libcuda).

@@ -223,7 +223,8 @@ def measure_size(cols, rows, F, steps, warmup, world, rank, local, clocks=False,
 
     lib = _lib.load()
     frames = make_frames(F, rank, rows, cols)
-    det = Detector(CudaSiftConfig(col_width=cols, row_width=rows, numFeatures=NUM_FEATURES))
+    slots = int(os.environ.get("B200SIFT_BENCH_SLOTS", "0"))  # development switch: frames in flight (0: the engine's default)
+    det = Detector(CudaSiftConfig(col_width=cols, row_width=rows, numFeatures=NUM_FEATURES), **({"frames_in_flight": slots} if slots else {}))
     assert det.gpuWarmUpAndAllocate()
     stream = torch.cuda.ExternalStream(det.stream)
     d_frames = [torch.from_numpy(f).cuda() for f in frames]
@@ -468,7 +469,7 @@ def class_bytes(kpts: int):
 def other_sizes(world):
     """BASELINE.json's other detector configurations: configs[1] 752x480, configs[3] 1600x900 (at 8 GPUs: the batch of
     256 frames, 32 per GPU, frame-parallel)."""
-    out = [("752x480", 752, 480, 16), ("1600x900", 1600, 900, 32 if world == 8 else 16)]
+    out = [("752x480", 752, 480, 64), ("1600x900", 1600, 900, 32 if world == 8 else 64)]
     return [o for o in out if (o[1], o[2]) != (COLS, ROWS)]
 
 
@@ -477,7 +478,7 @@ def main():
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
-    ap.add_argument("--frames", type=int, default=16, help="frames per step per GPU")
+    ap.add_argument("--frames", type=int, default=64, help="frames per step per GPU")
     ap.add_argument("--size", default="1920x1200", help="frame size WxH: 1920x1200 is BASELINE.json's metric; 752x480 and 1600x900 are its other configs")
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--no-cpu-baseline", action="store_true")

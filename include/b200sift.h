@@ -54,7 +54,7 @@ typedef struct b200sift_detector b200sift_detector; /* opaque handle */
  * to its default) = the reference's behaviour, bit for bit. The three fixes are the TODOs the reference itself lists;
  * they change results and are therefore opt-in. */
 typedef struct b200sift_options {
-    int frames_in_flight;        /* internal frame slots, 3..8 (0 = default 6): throughput vs ~85 MB of HBM per slot at 1920x1200 */
+    int frames_in_flight;        /* internal frame slots, 3..32 (0 = default 16): throughput vs ~85 MB of HBM per slot at 1920x1200 */
     int remove_duplicates;       /* interface/Detector.cu:220 "TODO: remove duplicate": drop keypoints whose (x, y, size, angle)
                                     equal an earlier keypoint of the same octave before description (first one kept) */
     int interpolate_orientation; /* sift_func/SiftOps.cu:359 "TODO: interpolate the peak": parabolic peak interpolation of the
