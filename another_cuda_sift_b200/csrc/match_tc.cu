@@ -1004,22 +1004,10 @@ match_filter_stream_kernel(const __half* __restrict__ des, int nq, const __grid_
     }
 }
 
-// The reference's per-pair score (Match.cu:93-111), warp-cooperative: lane i owns half2 i and i+32 of both
-// rows. The xor butterfly adds the same operand pairs in the same order as the reference's shfl_down tree
-// does for lane 0, and fp32 addition is commutative, so EVERY lane ends up with lane 0's exact value.
-__device__ __forceinline__ float exact_score(__half2 a0, __half2 a1, __half2 b0, __half2 b1) {
-    const __half2 inv = __floats2half2_rn(0.25f, 0.25f);
-    __half2 d0 = __hmul2(__hsub2(a0, b0), inv);
-    __half2 d1 = __hmul2(__hsub2(a1, b1), inv);
-    d0 = __hmul2(d0, d0);
-    d1 = __hmul2(d1, d1);
-    const float2 f0 = __half22float2(d0), f1 = __half22float2(d1);
-    float s = __fadd_rn(__fadd_rn(f0.x, f0.y), __fadd_rn(f1.x, f1.y));
-#pragma unroll
-    for (int off = 16; off > 0; off >>= 1) s = __fadd_rn(s, __shfl_xor_sync(0xffffffffu, s, off));
-    return s;
-}
-
+// The reference's per-pair score (Match.cu:93-111) is warp-cooperative: lane i owns half2 i and i+32 of both rows and a
+// shfl_down tree (offsets 16, 8, 4, 2, 1) sums the 32 partial sums. The re-rank kernel below plays it with 8 lanes per
+// pair (four pairs per warp step): the same operand pairs are added in the same tree, fp32 addition is commutative, so
+// every score is bit-identical to the reference's lane-0 value.
 constexpr int kRerankWarps = 4;
 constexpr int kListCap = 32 * kCand;
 
@@ -1042,7 +1030,6 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
         return;
     }
     const __half2* arow = reinterpret_cast<const __half2*>(des + (size_t)q * 128);
-    const __half2 a0 = arow[lane], a1 = arow[lane + 32];
     // lane c <- survivors of chunk c
     const int4* rp = reinterpret_cast<const int4*>(rec + (size_t)q * 32 + lane);
     const int4 r0 = __ldg(rp), r1 = __ldg(rp + 1);
@@ -1114,18 +1101,56 @@ match_rerank_kernel(const __half* __restrict__ des, int nq, const __half* __rest
             else if (v < mn2) { mn2 = v; id2 = col; }
         }
     }
-    // overflowed chunks: every column of the chunk, exactly as the reference scans them
+    // overflowed chunks: every column of the chunk, exactly as the reference scans them. Sixteen columns per step:
+    // lane group g (8 lanes) scores column t + 4s + g with the same 8-lane arithmetic as above (bit-identical to the
+    // reference's tree), all 32 loads of a step are issued before the first score, and lane `ch` applies the 16 results
+    // in ascending column order. (One column per step, as this loop first was, made a single overflowed chunk of a
+    // 100k-row train set a 0.5 ms serial chain: the floor of the whole kernel, whatever the number of query rows.)
     unsigned ovf = __ballot_sync(0xffffffffu, overflow);
-    while (ovf) {
-        const int ch = __ffs(ovf) - 1;
-        ovf &= ovf - 1;
-        const int t_end = min(nt, (ch + 1) * per);
-        for (int t = ch * per; t < t_end; t++) {
-            const __half2* brow = reinterpret_cast<const __half2*>(src + (size_t)t * 128);
-            const float val = exact_score(a0, a1, __ldg(brow + lane), __ldg(brow + lane + 32));
-            if (lane == ch) {
-                if (val < mn) { mn2 = mn; id2 = id; mn = val; id = t; }
-                else if (val < mn2) { mn2 = val; id2 = t; }
+    if (ovf) {
+        const int g = lane >> 3, l = lane & 7;
+        __half2 a8[8];
+#pragma unroll
+        for (int k = 0; k < 8; k++) a8[k] = arow[l + 8 * k];
+        const __half2 inv = __floats2half2_rn(0.25f, 0.25f);
+        while (ovf) {
+            const int ch = __ffs(ovf) - 1;
+            ovf &= ovf - 1;
+            const int t_end = min(nt, (ch + 1) * per);
+            for (int t = ch * per; t < t_end; t += 16) {
+                __half2 bb[4][8];
+#pragma unroll
+                for (int st = 0; st < 4; st++) {
+                    const int col = min(t + 4 * st + g, t_end - 1);
+                    const __half2* brow = reinterpret_cast<const __half2*>(src + (size_t)col * 128);
+#pragma unroll
+                    for (int k = 0; k < 8; k++) bb[st][k] = __ldg(brow + l + 8 * k);
+                }
+#pragma unroll
+                for (int st = 0; st < 4; st++) {
+                    float sv[4];
+#pragma unroll
+                    for (int v = 0; v < 4; v++) {
+                        __half2 d0 = __hmul2(__hsub2(a8[v], bb[st][v]), inv);
+                        __half2 d1 = __hmul2(__hsub2(a8[v + 4], bb[st][v + 4]), inv);
+                        d0 = __hmul2(d0, d0);
+                        d1 = __hmul2(d1, d1);
+                        const float2 f0 = __half22float2(d0), f1 = __half22float2(d1);
+                        sv[v] = __fadd_rn(__fadd_rn(f0.x, f0.y), __fadd_rn(f1.x, f1.y));
+                    }
+                    float val = __fadd_rn(__fadd_rn(sv[0], sv[2]), __fadd_rn(sv[1], sv[3]));
+#pragma unroll
+                    for (int off = 4; off > 0; off >>= 1) val = __fadd_rn(val, __shfl_xor_sync(0xffffffffu, val, off));
+#pragma unroll
+                    for (int gg = 0; gg < 4; gg++) {
+                        const float vv = __shfl_sync(0xffffffffu, val, 8 * gg);
+                        const int col = t + 4 * st + gg;
+                        if (lane == ch && col < t_end) {
+                            if (vv < mn) { mn2 = mn; id2 = id; mn = vv; id = col; }
+                            else if (vv < mn2) { mn2 = vv; id2 = col; }
+                        }
+                    }
+                }
             }
         }
     }
