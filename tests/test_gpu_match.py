@@ -105,6 +105,46 @@ def test_streaming_filter_adversarial_vs_cpu_oracle(path):
     assert np.array_equal(matchBruteForce(qb, len(qb), big, len(big)), cpu.match(qb, big))
 
 
+def test_overflowed_survivor_lists_rescore_whole_chunks(path):
+    """More than 7 survivors in one (query, chunk) record: the re-rank kernel re-scores the whole chunk, 16 columns per
+    step. A query's best match (an exact or almost exact copy) sits among 11 noisy copies that all pass the filter's
+    slack; chunk lengths that are not multiples of 16, the best column at the very end of a chunk / of the train set /
+    inside the last partial step, two overflowed chunks for one query; resident filter (nt <= 8192) and streaming
+    filter (nt > 8192)."""
+    from another_cuda_sift_b200 import matchBruteForce
+    from oracle.pyoracle import CpuOracle
+
+    cpu = CpuOracle(64, 64, 100)
+    rng = np.random.default_rng(23)
+
+    def noisy(row, n, dims=128):
+        out = np.repeat(row[None].astype(np.float32), n, axis=0)
+        out[:, :dims] += rng.integers(-1, 2, (n, dims))
+        return out.clip(0, 512).astype(np.float16)
+
+    for nt in (32 * 37 + 5, 8192 + 32 * 11 + 3):
+        per = -(-nt // 32)
+        t = (rng.random((nt, 128)) * 150).astype(np.float16)
+        q = (20 + rng.random((24, 128)) * 110).astype(np.float16)
+        for k in range(12):            # 11 noisy copies + the best one in the LAST column of chunk k (k even) / first of the 12 (k odd)
+            hi = min(nt, (k + 1) * per)
+            t[hi - 12:hi] = noisy(q[k], 12)
+            t[hi - 1 if k % 2 == 0 else hi - 12] = q[k] if k % 4 < 2 else noisy(q[k], 1, dims=6)[0]
+        for k in range(12, 18):        # spread over a whole chunk, best one anywhere
+            rows = (k + 1) * per + rng.permutation(per)[:10]
+            t[rows] = noisy(q[k], 10)
+            t[rows[k % 10]] = noisy(q[k], 1, dims=4)[0]
+        t[nt - 9:] = noisy(q[18], 9)   # the last (short) chunk ends with 9 copies, the exact one last
+        t[nt - 1] = q[18]
+        t[5 * per + 3:5 * per + 14] = noisy(q[19], 11)   # query 19: two overflowed chunks, the best in the second
+        t[9 * per:9 * per + 11] = noisy(q[19], 11)
+        t[9 * per + 10] = q[19]
+        want = cpu.match(q, t)
+        assert (want[:20] >= 0).sum() >= 15, want   # the construction really produces matches, not a column of -1
+        got = matchBruteForce(q, len(q), t, nt)
+        assert np.array_equal(got, want), nt
+
+
 def test_empty_inputs():
     from another_cuda_sift_b200 import matchBruteForce
 
