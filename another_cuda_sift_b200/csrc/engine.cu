@@ -88,8 +88,8 @@ constexpr int kBranchPixels = 65536;  // an octave with at least this many pixel
 // Frames in flight: a create-time option (b200sift_options::frames_in_flight, 3..32), ~85 MB of device memory per slot
 // at 1920x1200. Every slot has its own stream, so frame n + nslots queues behind frame n: with few slots the pyramid of a
 // new frame cannot start before the descriptors of the frame that held its slot are done. Measured on one B200 (same box,
-// frames/s with device-resident input, 32 frames per synchronisation): 6 -> 4051, 16 -> 4433, 32 -> 4552 at 1920x1200;
-// 16 frames per synchronisation: 6 -> 3772, 8 -> 3948, 12 -> 3975, 16 -> 4147; 752x480: 6 -> 8920, 16 -> 10979.
+// frames/s with device-resident input, ~3800 keypoints per frame): 6 -> 3772, 8 -> 3948, 12 -> 3975, 16 -> 4147, 32 -> 4209
+// at 1920x1200; 752x480: 6 -> 8920, 16 -> 10979 (profiles/r2_pyramid_ab.md section 4).
 constexpr int kDefaultSlots = 16, kMinSlots = 3, kMaxSlots = 32;
 
 // Everything one frame touches. Frame n runs in slot n % nslots on the slot's own streams, so the frame graph

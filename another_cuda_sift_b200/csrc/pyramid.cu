@@ -648,14 +648,28 @@ extern bool g_pyramid_error;
 // 480 x 300, 16 x 8 below: a CTA's latency grows with its tile plus the 15 / 18 pixel halo, and a 64 x 32 grid leaves most
 // SMs idle there) were measured on a B200 at 1920x1200: the three launches got 4-5.5 us shorter each under ncu, the
 // pyramid 4 us shorter inside the frame graph (0.151 -> 0.147 ms), and the pipelined throughput fell from 3700 to 3456
-// frames/s (three times as many CTAs queue behind the other frames' descriptor CTAs, twice the halo work). Kept as a
-// table of one so that the trade can be re-measured (profiles/r2_pyramid_ab.md).
+// frames/s (three times as many CTAs queue behind the other frames' descriptor CTAs, twice the halo work). The smaller
+// shapes stay compiled behind B200SIFT_CHAIN_SHAPES=1 so that the trade can be re-measured (profiles/r2_pyramid_ab.md).
 constexpr int kFuseThreads = 256, kFuseRB = 8;
-constexpr int kNumShapes = 1;
+constexpr int kNumShapes = 3;
 template <int I> struct Shape;
 template <> struct Shape<0> { static constexpr int TW = 64, TH = 32; };
+template <> struct Shape<1> { static constexpr int TW = 32, TH = 16; };
+template <> struct Shape<2> { static constexpr int TW = 16, TH = 8; };
 
-int pick_shape(int, int) { return 0; }
+int g_small_shapes = -1;  // development switch B200SIFT_CHAIN_SHAPES=1: the largest shape that still gives 148 CTAs
+
+int pick_shape(int w, int h) {
+    if (g_small_shapes < 0) {
+        const char* e = std::getenv("B200SIFT_CHAIN_SHAPES");
+        g_small_shapes = (e && e[0] == '1') ? 1 : 0;
+    }
+    if (!g_small_shapes) return 0;
+    const int tw[kNumShapes] = {Shape<0>::TW, Shape<1>::TW, Shape<2>::TW}, th[kNumShapes] = {Shape<0>::TH, Shape<1>::TH, Shape<2>::TH};
+    for (int i = 0; i < kNumShapes; i++)
+        if (((w + tw[i] - 1) / tw[i]) * ((h + th[i] - 1) / th[i]) >= 148) return i;
+    return kNumShapes - 1;
+}
 
 // Tensor map of a w x h float layer with row pitch `pitch` floats; box = the CTA's stage-0 region. The encode function
 // comes from the driver through the runtime's entry-point query (no link-time dependency on libcuda).
