@@ -77,6 +77,7 @@ SIGNATURES = {
     "b200sift_launches_per_frame": (C.c_int, [C.c_void_p]),
     "b200sift_time_frames": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]),
     "b200sift_time_frames_pipelined": (C.c_int, [C.c_void_p, C.c_int, C.c_int, C.POINTER(C.c_float)]),
+    "b200sift_debug_timeline": (C.c_int, [C.c_void_p, C.c_int, C.POINTER(C.c_float)]),
     "b200sift_match_consecutive_async": (C.c_int, [C.c_void_p, C.c_void_p]),
     "b200sift_copy_results_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "b200sift_detect_batch_host": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_void_p,

@@ -686,7 +686,13 @@ cudaError_t launch_descriptor(const FrameParams& fp, int o_begin, int o_end, cud
         per_sm = e ? std::atoi(e) : kDescCtasPerSm;
         if (per_sm < 1 || per_sm > kDescCtasPerSm) per_sm = kDescCtasPerSm;
     }
-    if (grid > 148L * per_sm) grid = 148L * per_sm;
+    static int waves = 0;
+    if (!waves) {  // development switch: B200SIFT_DESC_WAVES=k -> up to k waves of shorter-lived CTAs instead of one persistent wave
+        const char* e = std::getenv("B200SIFT_DESC_WAVES");
+        waves = e ? std::atoi(e) : 1;
+        if (waves < 1 || waves > 64) waves = 1;
+    }
+    if (grid > 148L * per_sm * waves) grid = 148L * per_sm * waves;
     // Lowest stream priority: the descriptor grids would otherwise fill every CTA slot and starve the short
     // latency-bound kernels of the other graph branches (the priority is recorded in the captured node).
     cudaLaunchConfig_t cfg = {};

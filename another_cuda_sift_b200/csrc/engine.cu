@@ -107,6 +107,8 @@ struct Slot {
     int* d_match_idx = nullptr;      // match indices of b200sift_detect_batch_host (numFeatures ints)
     cudaStream_t stream = nullptr;   // main stream of the slot's frame graph
     cudaStream_t side[kSideStreams] = {nullptr};
+    cudaStream_t stream_a = nullptr;  // capture-time streams of part A (their priority ends up in its kernel nodes)
+    cudaStream_t side_a[kSideStreams] = {nullptr};
     cudaEvent_t ev_fork[kMaxOctaves] = {nullptr}, ev_join[kMaxOctaves] = {nullptr}, ev_counts[kMaxOctaves] = {nullptr};
     cudaEvent_t ev_copied = nullptr, ev_consumed = nullptr;  // input buffer hand-over with the copy stream
     cudaEvent_t ev_done = nullptr;      // the slot's frame is complete
@@ -396,6 +398,10 @@ int build(b200sift_detector* d) {
     // everything but the descriptor launches (launch_descriptor) runs at the highest stream priority
     int prio_least = 0, prio_greatest = 0;
     CU(cudaDeviceGetStreamPriorityRange(&prio_least, &prio_greatest));
+    int prio_a = prio_greatest;
+    if (const char* e = std::getenv("B200SIFT_PRIO_A")) {  // development switch: priority of part A relative to the greatest (0, 1, 2 ..: lower)
+        prio_a = std::min(prio_least, prio_greatest + std::atoi(e));
+    }
     CU(cudaStreamCreateWithFlags(&d->copy_stream, cudaStreamNonBlocking));
     CU(cudaEventCreateWithFlags(&d->ev_user, cudaEventDisableTiming));
 
@@ -487,6 +493,10 @@ int build(b200sift_detector* d) {
         *sl.h_total = 0;
         CU(cudaStreamCreateWithPriority(&sl.stream, cudaStreamNonBlocking, prio_greatest));
         for (int i = 0; i < kSideStreams; i++) CU(cudaStreamCreateWithPriority(&sl.side[i], cudaStreamNonBlocking, prio_greatest));
+        // part A (pyramid + extrema) is captured on streams of their own so that its kernel nodes can carry a lower priority
+        // than part B's (the ordered candidate stages, whose latency under load bounds the frame rate)
+        CU(cudaStreamCreateWithPriority(&sl.stream_a, cudaStreamNonBlocking, prio_a));
+        for (int i = 0; i < kSideStreams; i++) CU(cudaStreamCreateWithPriority(&sl.side_a[i], cudaStreamNonBlocking, prio_a));
         for (int o = 0; o < kMaxOctaves; o++) {
             CU(cudaEventCreateWithFlags(&sl.ev_fork[o], cudaEventDisableTiming));
             CU(cudaEventCreateWithFlags(&sl.ev_join[o], cudaEventDisableTiming));
@@ -522,9 +532,21 @@ int build(b200sift_detector* d) {
         int total = 0;
         for (int g = 0; g < 3; g++) {
             int n = 0;
-            CU(cudaStreamBeginCapture(sl.stream, cudaStreamCaptureModeThreadLocal));
-            int rc = enqueue_frame(d, sl, 7, &n, nullptr, parts[g]);
-            cudaError_t e = cudaStreamEndCapture(sl.stream, &sl.graph[g]);
+            const bool on_a = parts[g] == kPartA;   // part A is captured on its own (possibly lower-priority) streams
+            if (on_a) {
+                std::swap(sl.stream, sl.stream_a);
+                for (int i = 0; i < kSideStreams; i++) std::swap(sl.side[i], sl.side_a[i]);
+            }
+            cudaError_t e = cudaStreamBeginCapture(sl.stream, cudaStreamCaptureModeThreadLocal);
+            int rc = 0;
+            if (e == cudaSuccess) {
+                rc = enqueue_frame(d, sl, 7, &n, nullptr, parts[g]);
+                e = cudaStreamEndCapture(sl.stream, &sl.graph[g]);
+            }
+            if (on_a) {
+                std::swap(sl.stream, sl.stream_a);
+                for (int i = 0; i < kSideStreams; i++) std::swap(sl.side[i], sl.side_a[i]);
+            }
             if (rc) return rc;
             CU(e);
             CU(cudaGraphInstantiate(&sl.exec[g], sl.graph[g], 0));
@@ -624,6 +646,9 @@ int b200sift_destroy(b200sift_detector* d) {
         if (sl.ev_matched) cudaEventDestroy(sl.ev_matched);
         if (sl.h_total) cudaFreeHost(sl.h_total);
         if (sl.stream) cudaStreamDestroy(sl.stream);
+        if (sl.stream_a) cudaStreamDestroy(sl.stream_a);
+        for (int i = 0; i < kSideStreams; i++)
+            if (sl.side_a[i]) cudaStreamDestroy(sl.side_a[i]);
         for (int i = 0; i < kSideStreams; i++)
             if (sl.side[i]) cudaStreamDestroy(sl.side[i]);
         for (int o = 0; o < kMaxOctaves; o++) {
@@ -1042,6 +1067,54 @@ int b200sift_time_frames_pipelined(b200sift_detector* d, int warmup, int iters, 
     cudaEventDestroy(e0);
     for (int i = 0; i < nslots; i++) cudaEventDestroy(e1[i]);
     *ms_per_frame = ms / (float)total;
+    return 0;
+}
+
+// Development aid: the frame graphs with every slot in flight as b200sift_time_frames_pipelined runs them, with a timing
+// event before part A and after parts A, B and C of every frame. ms_out[4 * i + {0, 1, 2, 3}] = the time (ms since the
+// common start) at which frame i's stream reached part A / finished A / finished B / finished C.
+int b200sift_debug_timeline(b200sift_detector* d, int n_frames, float* ms_out) {
+    if (!d || !ms_out || n_frames <= 0 || n_frames > 1024) return fail(B200SIFT_EINVAL, "bad argument");
+    if (int rc = sync_all(d)) return rc;
+    const int nslots = d->nslots;
+    Slot& src = d->cur();
+    const size_t in_bytes = (size_t)d->in_pitch * d->cfg.row_width * sizeof(float);
+    for (int i = 0; i < nslots; i++)
+        if (&d->slot[i] != &src) CU(cudaMemcpy(d->slot[i].d_input, src.d_input, in_bytes, cudaMemcpyDeviceToDevice));
+    std::vector<cudaEvent_t> ev((size_t)4 * n_frames);
+    for (auto& e : ev) CU(cudaEventCreate(&e));
+    cudaEvent_t e0;
+    CU(cudaEventCreate(&e0));
+    const int first = (int)(d->frame_no % nslots);
+    Slot* last = &src;
+    for (int i = 0; i < 2 * nslots; i++) {  // warm-up: two rotations
+        Slot& sl = d->slot[(first + i) % nslots];
+        if (int rc = launch_graphs(sl, last)) return rc;
+        last = &sl;
+    }
+    if (int rc = sync_all(d)) return rc;
+    CU(cudaEventRecord(e0, d->slot[0].stream));
+    for (int i = 1; i < nslots; i++) CU(cudaStreamWaitEvent(d->slot[i].stream, e0, 0));
+    for (int i = 0; i < n_frames; i++) {
+        Slot& sl = d->slot[(first + i) % nslots];
+        CU(cudaEventRecord(ev[4 * i], sl.stream));
+        CU(cudaGraphLaunch(sl.exec[0], sl.stream));
+        CU(cudaEventRecord(sl.ev_consumed, sl.stream));
+        CU(cudaEventRecord(ev[4 * i + 1], sl.stream));
+        CU(cudaStreamWaitEvent(sl.stream, last->ev_chain, 0));
+        CU(cudaGraphLaunch(sl.exec[1], sl.stream));
+        CU(cudaEventRecord(sl.ev_chain, sl.stream));
+        CU(cudaEventRecord(ev[4 * i + 2], sl.stream));
+        CU(cudaGraphLaunch(sl.exec[2], sl.stream));
+        CU(cudaEventRecord(sl.ev_done, sl.stream));
+        CU(cudaEventRecord(ev[4 * i + 3], sl.stream));
+        last = &sl;
+    }
+    if (int rc = sync_all(d)) return rc;
+    for (int i = 0; i < 4 * n_frames; i++) CU(cudaEventElapsedTime(&ms_out[i], e0, ev[i]));
+    for (auto& e : ev) cudaEventDestroy(e);
+    cudaEventDestroy(e0);
+    d->have_frame = true;
     return 0;
 }
 

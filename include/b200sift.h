@@ -153,6 +153,9 @@ B200SIFT_API int b200sift_time_frames(b200sift_detector* det, int warmup, int it
 /* Same with all frame slots in flight (one frame per internal slot, each on its own stream): ms per frame of the
  * pipelined engine, i.e. 1 / throughput. */
 B200SIFT_API int b200sift_time_frames_pipelined(b200sift_detector* det, int warmup, int iters, float* ms_per_frame);
+/* Development aid (no reference counterpart): the same pipelined replay with a timing event before part A and after parts A, B, C of each
+ * of n_frames frames; ms_out[4*i + k] = milliseconds since the common start (tools/dev_timeline.py prints the steady-state schedule). */
+B200SIFT_API int b200sift_debug_timeline(b200sift_detector* det, int n_frames, float* ms_out);
 
 /* Pipelined (batched-frame) use, no host synchronisation per frame. After b200sift_detect_*_async:
  *  - b200sift_match_consecutive_async: matchBruteForce(prev_descriptor, previous total, device_descriptor, this
