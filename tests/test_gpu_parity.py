@@ -307,6 +307,35 @@ def test_live_reference_bin_edges_and_1600x900(cols, rows, kind):
         print("live", kind, fr, info)
 
 
+@pytest.mark.parametrize("nf", [1500, 5000], ids=["nf1500-octave0-past-cap", "nf5000-orientation-slots-dropped"])
+def test_slot_capacity_at_full_size_vs_live_reference(nf):
+    """The busiest case the slot semantics see: 1920x1200 frames of 5-pixel binary block noise put ~23,400 raw extrema
+    into octave 0. With numFeatures = 1500 that is PAST the octave's slot capacity (cap = 10 * numFeatures = 15,000:
+    candidates beyond it are dropped, quirk Q6, and refine_kernel's guard on stale slots is live); with the default 5000
+    the 15,800 refined keypoints leave room for only (cap - M) / 36 of them in the orientation expansion (Q6) and the
+    output is truncated (Q7). Three consecutive frames, so the stale last slot of every compaction (Q5) comes from a
+    frame of the same size. Engine vs the unmodified reference build: counts, keypoint sets and descriptors."""
+    from oracle.pyoracle import RefOracle, ref_available
+
+    if not ref_available():
+        pytest.skip("oracle/_ref not built (needs /root/reference at build time)")
+    cols, rows = 1920, 1200
+    det, ref = _det(cols, rows, nf), RefOracle(cols, rows, nf)
+    rng = np.random.default_rng(3)
+    for fr in range(3):
+        g = rng.random((rows // 5 + 1, cols // 5 + 1)) < 0.5
+        img = (np.kron(g, np.ones((5, 5)))[:rows, :cols] * 255).astype(np.float32)
+        ref.detect(img)
+        det.detectAndCompute(img)
+        c0 = det.debug_counts(0)
+        assert c0["P"] > 20000 and (c0["P"] > det.octaves[0]["cap"] if nf == 1500 else c0["M"] > 15000), c0
+        octs = [(o["w"], o["h"], o["pitch"], o["cap"]) for o in det.octaves]
+        want = ref.results()
+        info = check_results(_res(det), want, min_agree=0.995, desc_tol=DESC_TOL, desc_frac=DESC_FRAC, octaves=octs,
+                             tag=f"live/blocknoise_{cols}x{rows}_nf{nf}/f{fr}")
+        assert info["n_got"] == info["n_want"] and info["n_got"] > 1000, info
+
+
 @pytest.mark.parametrize("nf", [3000, 150], ids=["nf3000", "nf150-slot-cap-overflow"])
 def test_slot_wraparound_pipelines_equal_blocking(nf):
     """More frames than twice the engine's frame slots, so every slot is reused while work is in flight: the

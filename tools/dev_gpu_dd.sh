@@ -1,0 +1,4 @@
+set +e
+mkdir -p gpurun_out; rm -f gpurun_out/parity_metrics.jsonl
+python -m pytest tests -m gpu -q > gpurun_out/r2_pytest_gpu_final.log 2>&1; tail -3 gpurun_out/r2_pytest_gpu_final.log
+python -c "import __graft_entry__ as g; g.smoke(); print('smoke ok')" 2>&1 | tail -2
