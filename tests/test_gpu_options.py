@@ -154,3 +154,32 @@ def test_frames_in_flight_option(slots):
     for bad in (1, 2, 33):
         with pytest.raises(B200SiftError):
             Detector(CudaSiftConfig(col_width=64, row_width=48), frames_in_flight=bad).gpuWarmUpAndAllocate()
+
+
+def test_debug_timeline_is_ordered():
+    """b200sift_debug_timeline (development aid behind tools/dev_timeline.py): for every frame the four time stamps
+    (stream reaches part A, end of A, end of B, end of C) are ordered, part B ends in frame order (the shared candidate
+    lists), and the replay leaves the detector usable with unchanged results."""
+    import ctypes as C
+
+    from another_cuda_sift_b200 import _lib
+    from another_cuda_sift_b200.synth import synth_frame
+
+    cols, rows = 320, 240
+    det = _det(cols, rows, 2000, frames_in_flight=4)
+    img = synth_frame(rows, cols, 9)
+    for _ in range(3):   # the same frame repeatedly: the stale-slot history (quirk Q5) has settled after the second
+        det.detectAndCompute(img)
+    det.copyToHost(True)
+    n0, d0 = det.total_size, det.descriptors[:det.total_size].copy()
+    assert n0 > 50
+    n = 23
+    out = (C.c_float * (4 * n))()
+    _lib.check(det.lib.b200sift_debug_timeline(det._h, n, out))
+    t = np.array(list(out)).reshape(n, 4)
+    assert (np.diff(t, axis=1) >= 0).all(), t
+    assert (np.diff(t[:, 2]) > 0).all(), t[:, 2]
+    assert t.max() < 1e3
+    det.detectAndCompute(img)
+    det.copyToHost(True)
+    assert det.total_size == n0 and np.array_equal(det.descriptors[:n0].view(np.uint16), d0.view(np.uint16))
