@@ -177,9 +177,43 @@ class CpuOracle(_Oracle):
         return int(self.lib.oracle_get_threads())
 
 
+def _zero_free_device_memory():
+    """The reference never zeroes its candidate / collected-keypoint buffers (plain cudaMalloc) and CONSUMES their stale
+    last slots. In a fresh process cudaMalloc hands out zeroed memory; inside a long-lived process
+    (a test suite) it hands out whatever earlier allocations left behind, and the reference then reads gradients at
+    garbage coordinates: at best other results, at worst an illegal address that poisons the CUDA context for everything
+    that follows. So before the reference allocates, grab (nearly) all free device memory, zero it and give it back: the
+    reference starts from the state it has in a process of its own -- and from the state the engine, which zeroes its
+    buffers, always starts from. Test infrastructure only."""
+    try:
+        rt = C.CDLL("libcudart.so")
+    except OSError:
+        try:
+            rt = C.CDLL("libcudart.so.12")
+        except OSError:
+            return
+    free, total = C.c_size_t(0), C.c_size_t(0)
+    if rt.cudaMemGetInfo(C.byref(free), C.byref(total)) != 0:
+        return
+    want = int(free.value) - (1 << 30)
+    while want > (1 << 28):
+        p = C.c_void_p(0)
+        if rt.cudaMalloc(C.byref(p), C.c_size_t(want)) == 0:
+            rt.cudaMemset(p, 0, C.c_size_t(want))
+            rt.cudaDeviceSynchronize()
+            rt.cudaFree(p)
+            return
+        rt.cudaGetLastError()
+        want //= 2
+
+
 class RefOracle(_Oracle):
     prefix = "ref_"
     lib_path = REF_LIB
+
+    def __init__(self, *args, **kwargs):
+        _zero_free_device_memory()
+        super().__init__(*args, **kwargs)
 
     def counts_raw(self, o: int):
         """(prefix_sum[last], prefix_sum[cap-1]); meaning depends on the stage just run."""
