@@ -7,6 +7,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <string>
@@ -559,6 +560,13 @@ int build(b200sift_detector* d) {
 }
 
 }  // namespace
+
+// The engine keeps up to 32 frames in flight, each on its own stream with up to five graph branches. With the CUDA
+// default of 8 hardware work queues per device those streams alias onto the same queues and only ~4 frames really overlap
+// (profiles/r2_timeline.md); 32 queues are worth +7.5% end to end at 1920x1200 and +9-11% at 752x480. The variable is read
+// when the CUDA context is created, so it is set when the library is loaded (a C++ program that links the library: before
+// main), and never over a value the user chose.
+__attribute__((constructor)) static void b200sift_on_load() { setenv("CUDA_DEVICE_MAX_CONNECTIONS", "32", /*overwrite=*/0); }
 
 // ------------------------------------------------------------------------------------ C ABI
 extern "C" {

@@ -36,6 +36,11 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
+# The engine's own default (another_cuda_sift_b200/__init__.py, csrc/engine.cu: b200sift_on_load), stated here because it
+# must be in the environment before the first CUDA call of the process, and so that BOTH arms run under the same setting:
+# 32 hardware work queues instead of CUDA's default 8 (profiles/r2_timeline.md). A value from the caller's environment wins.
+os.environ.setdefault("CUDA_DEVICE_MAX_CONNECTIONS", "32")
+
 METRIC = "detectAndCompute frames/s @1920x1200"
 AFFINITY = "off"
 COLS, ROWS = 1920, 1200
@@ -410,7 +415,8 @@ def workload_config(cols, rows, frames, world):
     return {"workload": f"{cols}x{rows} detectAndCompute + consecutive-frame matchBruteForce", "frames_per_step_per_gpu": frames,
             "distinct_frames": min(frames, DISTINCT_FRAMES),
             "frame_order": "the distinct frames walked forwards and backwards (every consecutive pair is a real consecutive pair; a longer step is the same workload)",
-            "numFeatures": NUM_FEATURES, "numOctaveLayers": 3, "sigma": 1.6, "data": "synthetic frames, seed 1234 + 1000*rank + i"}
+            "numFeatures": NUM_FEATURES, "numOctaveLayers": 3, "sigma": 1.6, "data": "synthetic frames, seed 1234 + 1000*rank + i",
+            "cuda_device_max_connections": os.environ.get("CUDA_DEVICE_MAX_CONNECTIONS")}
 
 
 def run_reference(args, world, rank, local):
