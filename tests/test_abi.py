@@ -103,3 +103,24 @@ def test_product_never_imports_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".hh", ".cpp")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in text.replace("on-device oracle", ""), f
+
+
+def test_library_load_sets_hardware_queue_default_without_overriding():
+    """Loading libb200sift.so puts CUDA_DEVICE_MAX_CONNECTIONS=32 into the process environment (the engine's frames in
+    flight need more than CUDA's 8 default work queues) and never replaces a value the user chose. Checked in fresh
+    processes, through the C library itself (getenv from libc, not os.environ, which is a snapshot)."""
+    import subprocess
+    import sys
+
+    from another_cuda_sift_b200 import _lib
+
+    code = ("import ctypes, os, sys\n"
+            "libc = ctypes.CDLL(None); libc.getenv.restype = ctypes.c_char_p\n"
+            "ctypes.CDLL(sys.argv[1])\n"
+            "print((libc.getenv(b'CUDA_DEVICE_MAX_CONNECTIONS') or b'').decode())\n")
+    env = {k: v for k, v in os.environ.items() if k != "CUDA_DEVICE_MAX_CONNECTIONS"}
+    out = subprocess.run([sys.executable, "-c", code, _lib.LIB_PATH], env=env, capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and out.stdout.strip() == "32", (out.stdout, out.stderr[-300:])
+    env["CUDA_DEVICE_MAX_CONNECTIONS"] = "12"
+    out = subprocess.run([sys.executable, "-c", code, _lib.LIB_PATH], env=env, capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0 and out.stdout.strip() == "12", (out.stdout, out.stderr[-300:])
